@@ -1,0 +1,158 @@
+/*
+ * hg_b200.h -- C ABI of the B200-native hypergraph-construction hot path.
+ *
+ * Drop-in boundary for zz9tf/multimodal-fusion `build_hypergraph/` (reference
+ * paths below are relative to the reference root).  The reference is pure
+ * Python; its "FFI" for this path is the set of torch / scikit-learn calls the
+ * functions below replace.  Every entry point takes plain device pointers and
+ * sizes plus a `cudaStream_t` passed as `void*` -- no torch types.
+ *
+ * Conventions:
+ *  - every function returns int: 0 = HG_OK, negative = HG_ERR_*;
+ *    hg_last_error() returns a thread-local message for the last failure;
+ *  - the CALLER allocates every buffer (with torch, cudaMalloc, ...); the
+ *    library never allocates or frees user-visible memory; scratch comes from
+ *    a caller workspace whose size is asked first (`*_workspace_bytes`);
+ *  - calls are asynchronous on `stream` unless documented (the count half of a
+ *    count -> fill pair synchronises the stream to return the count);
+ *  - all matrices are row-major, float32, densely packed unless a leading
+ *    dimension is given; indices out are int32 (kNN lists) or int64 (COO/CSR,
+ *    the reference's `edge_index` dtype, preprocess_hypergraph.py:410).
+ */
+#ifndef HG_B200_H
+#define HG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HG_OK               0
+#define HG_ERR_BAD_ARG     (-1)
+#define HG_ERR_UNSUPPORTED (-2)
+#define HG_ERR_CUDA        (-3)
+#define HG_ERR_WORKSPACE   (-4)
+
+/* ranking metric of the fused similarity + top-k kernel */
+#define HG_METRIC_EUCLIDEAN 0 /* value out = squared distance (clamped >= 0)            */
+#define HG_METRIC_GAUSSIAN  1 /* value out = exp(-lambda_h d2_h - lambda_g d2_g)         */
+#define HG_METRIC_COSINE    2 /* value out = cos(f_i, f_j), norms clamped at 1e-8        */
+
+/* form of the squared distance in hg_similarity_dense */
+#define HG_FORM_EXPANSION 0   /* |a|^2 + |b|^2 - 2 a.b   similarity_kernel.py:43-49     */
+#define HG_FORM_DIRECT    1   /* sum (a-b)^2             preprocess_hypergraph.py:254-255 */
+
+int hg_version(void);
+const char* hg_last_error(void);
+
+/* ---- operand preparation -------------------------------------------------
+ * Splits FP32 rows into BF16 hi/lo planes (x ~= hi + lo, 16 significant bits)
+ * laid out [2][n_pad][d_pad] for TMA, zero padded to n_pad = ceil256(n),
+ * d_pad = ceil64(d), and writes per-row squared norms (FP32, from the original
+ * data).  Replaces `torch.sum(features**2)` (similarity_kernel.py:43) and is the
+ * input of the tensor-core Gram product that replaces `torch.mm` (:46). */
+size_t hg_operand_bytes(int64_t n, int64_t d);
+int hg_split_operands(const float* feats, int64_t n, int64_t d,
+                      void* ops, float* sq_norms, void* stream);
+
+/* ---- A1/A2/A4: fused similarity + running top-k (N x N never materialised) --
+ * For rows [row_begin, row_end) of `feats` [n, d]: the k best columns among all
+ * n (self excluded by index when exclude_self != 0), ordered best first with
+ * ties broken by ascending column index.
+ *   EUCLIDEAN: sklearn NearestNeighbors(k+1,'euclidean') minus self,
+ *              preprocess_hypergraph.py:379-388;
+ *   GAUSSIAN : per-row top-k of K = K_h * K_g, similarity_kernel.py:52,84,122
+ *              (pos may be NULL -> K_h only);
+ *   COSINE   : sklearn metric='cosine' (preprocess_hypergraph.py:311) /
+ *              F.cosine_similarity (:419).
+ * out_idx [rows, k] int32 (-1 when fewer than k candidates exist),
+ * out_val [rows, k] float32.  `precision`: 0 = 3xBF16 tensor-core candidates +
+ * exact FP32 re-rank (default), 1 = plain FP32 SIMT kernel (any shape). */
+int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k,
+                                   int64_t row_begin, int64_t row_end, size_t* bytes);
+int hg_knn_feature(const float* feats, int64_t n, int64_t d,
+                   const float* pos, int pos_dim,
+                   int metric, float lambda_h, float lambda_g,
+                   int k, int64_t row_begin, int64_t row_end, int exclude_self,
+                   int precision,
+                   int32_t* out_idx, float* out_val,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A1/A2/A7: dense (small-N / rectangular) Gaussian kernel -----------------
+ * out[i, j] = exp(-lambda_h d2(a_i, b_j) - lambda_g d2(pa_i, pb_j)), un-clamped.
+ * b == NULL means b = a (square).  pos_* may be NULL.
+ * similarity_kernel.py:17-124, preprocess_hypergraph.py:248-257. */
+int hg_similarity_dense(const float* a, int64_t m, const float* b, int64_t n, int64_t d,
+                        const float* pos_a, const float* pos_b, int pos_dim,
+                        float lambda_h, float lambda_g, int form,
+                        float* out, int64_t ld_out, void* stream);
+
+/* ---- A9: mean / unbiased std / min / max / lower median of `count` floats -----
+ * preprocess_hypergraph.py:190-196, 259-265.  stats_out: 5 doubles on the
+ * DEVICE.  If exclude_diag_n > 0 the buffer is an n x n matrix whose diagonal is
+ * skipped (similarity_kernel.py:183-186). */
+int hg_stats_workspace_bytes(int64_t count, size_t* bytes);
+int hg_similarity_stats(const float* values, int64_t count, int64_t exclude_diag_n,
+                        double* stats_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A3: spatial-coordinate kNN ------------------------------------------------
+ * k smallest |g_i - g_j|^2 (direct-difference FP32), self excluded, ties by
+ * (d2, index).  Semantics pinned by similarity_kernel.py:57-86 (top-k of a K_g
+ * row).  pos [n, pos_dim], pos_dim in {2, 3}. */
+int hg_knn_spatial_workspace_bytes(int64_t n, int k, int64_t row_begin, int64_t row_end, size_t* bytes);
+int hg_knn_spatial(const float* pos, int64_t n, int pos_dim, int k,
+                   int64_t row_begin, int64_t row_end,
+                   int32_t* out_idx, float* out_d2,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A5: edge assembly ------------------------------------------------------------
+ * Directed kNN pairs (i, knn_idx[i, :]) of up to 4 neighbour lists (feature
+ * kNN, spatial kNN, ...; knn_lists is a HOST array of device pointers, entries
+ * < 0 are skipped) plus all pairs inside every cluster
+ * label in [0, num_hyperedges) (labels may be NULL), canonicalised to (min, max),
+ * radix-sorted and de-duplicated.  preprocess_hypergraph.py:385-410.
+ * hg_edges_count runs the pipeline into the workspace, synchronises `stream`
+ * and returns E; hg_edges_fill then copies edge_index [2, E] int64 (row 0 < row
+ * 1, lexicographic order) out of the same workspace. */
+int hg_edges_workspace_bytes(int64_t n, int64_t knn_slots /* sum over lists of n*k */,
+                             int num_hyperedges, int64_t clique_pairs, size_t* bytes);
+/* number of intra-cluster pairs sum s_c (s_c - 1) / 2 (synchronises `stream`) */
+int hg_clique_pairs(const int32_t* labels, int64_t n, int num_hyperedges,
+                    int64_t* pairs_out_host, void* stream);
+int hg_edges_count(const int32_t* const* knn_lists, const int* ks, int num_lists, int64_t n,
+                   const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                   int64_t* num_edges_out_host,
+                   void* workspace, size_t workspace_bytes, void* stream);
+int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
+                  const void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A6: w_e = max(0, cos(f_i, f_j)), eps = 1e-8 -- preprocess_hypergraph.py:413-422 */
+int hg_edge_weights_cosine(const float* feats, int64_t n, int64_t d,
+                           const int64_t* edge_index, int64_t num_edges,
+                           float* weights, void* stream);
+
+/* ---- CSR incidence of the undirected pair list ---------------------------------------
+ * rowptr [n+1], col [2E] (neighbour), eid [2E] (edge id), rows sorted by neighbour.
+ * Requires edge_index sorted as produced by hg_edges_fill. */
+int hg_csr_workspace_bytes(int64_t n, int64_t num_edges, size_t* bytes);
+int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int64_t n,
+                    int64_t* rowptr, int64_t* col, int64_t* eid,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A8: dense-threshold builder -------------------------------------------------------
+ * Keep every ordered (i, j), diagonal included, with K[i, j] >= threshold, row
+ * major.  similarity_kernel.py:193-210.  K is a dense n x n matrix (small N). */
+int hg_threshold_edges_count(const float* K, int64_t n, float threshold,
+                             int64_t* num_edges_out_host,
+                             void* workspace, size_t workspace_bytes, void* stream);
+int hg_threshold_edges_fill(const float* K, int64_t n, float threshold, int64_t num_edges,
+                            int64_t* edge_index, float* edge_weights,
+                            const void* workspace, size_t workspace_bytes, void* stream);
+int hg_threshold_workspace_bytes(int64_t n, size_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HG_B200_H */

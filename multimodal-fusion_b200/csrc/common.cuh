@@ -1,0 +1,71 @@
+// Shared helpers for the hg_b200 CUDA sources (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <math.h>
+
+#include "../../include/hg_b200.h"
+
+namespace hg {
+
+// ---- error plumbing: no exceptions cross the C ABI -------------------------
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define HG_CHECK_CUDA(expr)                                                          \
+    do {                                                                             \
+        cudaError_t _e = (expr);                                                     \
+        if (_e != cudaSuccess) {                                                     \
+            hg::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,              \
+                          cudaGetErrorString(_e));                                   \
+            return HG_ERR_CUDA;                                                      \
+        }                                                                            \
+    } while (0)
+
+#define HG_CHECK_LAUNCH() HG_CHECK_CUDA(cudaGetLastError())
+
+#define HG_REQUIRE(cond, code, ...)                                                  \
+    do {                                                                             \
+        if (!(cond)) {                                                               \
+            hg::set_error(__VA_ARGS__);                                              \
+            return (code);                                                           \
+        }                                                                            \
+    } while (0)
+
+constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs
+
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+__host__ __device__ inline int64_t min64(int64_t a, int64_t b) { return a < b ? a : b; }
+__host__ __device__ inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
+
+// workspace carving: every sub-buffer 256-byte aligned
+struct Carver {
+    char* base;
+    size_t off;
+    explicit Carver(void* p) : base(static_cast<char*>(p)), off(0) {}
+    template <typename T>
+    T* take(size_t count) {
+        T* p = reinterpret_cast<T*>(base + off);
+        off += (count * sizeof(T) + 255) & ~size_t(255);
+        return p;
+    }
+};
+
+// ---- geometry of the tensor-core operand buffer ------------------------------
+constexpr int kRowPad = 256;   // operand rows padded to a multiple of the widest TMA box
+constexpr int kColPad = 64;    // feature dim padded to one 128-byte swizzle atom of BF16
+
+inline int64_t ops_rows(int64_t n) { return round_up(n, kRowPad); }
+inline int64_t ops_cols(int64_t d) { return round_up(d, kColPad); }
+
+// ---- internal launchers shared across translation units ----------------------
+// per-column epilogue parameters of the fused kernel: score = a_j + b_j * dot
+struct ColParam { float a, b; };
+
+int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
+                 cudaStream_t st);
+
+}  // namespace hg

@@ -1,0 +1,116 @@
+// C ABI of the feature-space kNN: operand split -> fused tcgen05 similarity/top-k ->
+// merge + exact re-rank.  See include/hg_b200.h for the contract.
+#include "knn_tc.cuh"
+#include "sim_simt.cuh"
+
+namespace hg {
+
+struct KnnWs {
+    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, bytes;
+    TcPlan plan;
+    int64_t n_pad, d_pad;
+};
+
+static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
+    KnnWs w{};
+    w.plan = tc_make_plan(n, r1 - r0, k);
+    w.n_pad = ops_rows(n);
+    w.d_pad = ops_cols(d);
+    size_t off = 0;
+    auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
+    w.off_ops = take(size_t(2) * w.n_pad * w.d_pad * 2);
+    w.off_norms = take(size_t(w.n_pad) * 4);
+    w.off_colp = take(size_t(w.n_pad) * 8);
+    w.off_pos4 = take(has_pos ? size_t(w.n_pad) * 16 : 0);
+    const size_t part = size_t(w.plan.splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
+    w.off_pval = take(part * 4);
+    w.off_pidx = take(part * 4);
+    w.bytes = off;
+    return w;
+}
+
+}  // namespace hg
+
+using namespace hg;
+
+static int check_knn_args(int64_t n, int64_t d, int k, int64_t r0, int64_t r1) {
+    HG_REQUIRE(n > 1, HG_ERR_BAD_ARG, "number of nodes must be greater than 1, got N=%lld", (long long)n);
+    HG_REQUIRE(d > 0 && k >= 1, HG_ERR_BAD_ARG, "hg_knn_feature: bad d / k");
+    HG_REQUIRE(r0 >= 0 && r0 < r1 && r1 <= n, HG_ERR_BAD_ARG, "hg_knn_feature: bad row range [%lld, %lld)",
+               (long long)r0, (long long)r1);
+    HG_REQUIRE(n < (int64_t(1) << 31) - 512, HG_ERR_UNSUPPORTED, "hg_knn_feature: n too large");
+    return HG_OK;
+}
+
+extern "C" int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
+                                              size_t* bytes) {
+    HG_REQUIRE(bytes, HG_ERR_BAD_ARG, "hg_knn_feature_workspace_bytes: null");
+    int rc = check_knn_args(n, d, k, row_begin, row_end);
+    if (rc != HG_OK) return rc;
+    *bytes = plan_ws(n, d, k, row_begin, row_end, true).bytes;
+    return HG_OK;
+}
+
+extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
+                              const float* pos, int pos_dim,
+                              int metric, float lambda_h, float lambda_g,
+                              int k, int64_t row_begin, int64_t row_end, int exclude_self,
+                              int precision,
+                              int32_t* out_idx, float* out_val,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(feats && out_idx && out_val, HG_ERR_BAD_ARG, "hg_knn_feature: null buffer");
+    int rc = check_knn_args(n, d, k, row_begin, row_end);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(metric == HG_METRIC_EUCLIDEAN || metric == HG_METRIC_GAUSSIAN || metric == HG_METRIC_COSINE,
+               HG_ERR_BAD_ARG, "hg_knn_feature: unknown metric %d", metric);
+    if (metric != HG_METRIC_GAUSSIAN || lambda_g == 0.f) pos = nullptr;
+    HG_REQUIRE(pos == nullptr || (pos_dim >= 1 && pos_dim <= 3), HG_ERR_UNSUPPORTED, "hg_knn_feature: pos_dim must be 1..3");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    if (precision == 1) {                                   // plain FP32 SIMT path
+        SimArgs a{};
+        a.a = feats; a.b = feats; a.m = n; a.n = n; a.d = d; a.pa = pos; a.pb = pos; a.pos_dim = pos_dim;
+        a.lambda_h = lambda_h; a.lambda_g = lambda_g; a.metric = metric; a.k = k;
+        a.row_begin = row_begin; a.row_end = row_end; a.exclude_self = exclude_self;
+        a.out_idx = out_idx; a.out_val = out_val;
+        return launch_topk_fp32(a, st);
+    }
+    HG_REQUIRE(precision == 0, HG_ERR_BAD_ARG, "hg_knn_feature: unknown precision %d", precision);
+    HG_REQUIRE(k <= 32, HG_ERR_UNSUPPORTED, "hg_knn_feature: the tensor-core path supports k <= 32 (got %d)", k);
+    HG_REQUIRE(metric != HG_METRIC_GAUSSIAN || lambda_h > 0.f || pos == nullptr, HG_ERR_UNSUPPORTED,
+               "hg_knn_feature: lambda_h must be > 0 when positions are given");
+
+    const KnnWs w = plan_ws(n, d, k, row_begin, row_end, pos != nullptr);
+    HG_REQUIRE(workspace && workspace_bytes >= w.bytes, HG_ERR_WORKSPACE,
+               "hg_knn_feature: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
+    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG,
+               "hg_knn_feature: workspace must be 1024-byte aligned");
+    char* ws = static_cast<char*>(workspace);
+    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    float* norms = reinterpret_cast<float*>(ws + w.off_norms);
+    float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
+    float4* pos4 = pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
+
+    rc = launch_split(feats, n, d, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st);
+    if (rc != HG_OK) return rc;
+
+    TcParams tp{};
+    tp.n = n; tp.row_begin = row_begin; tp.row_end = row_end; tp.d_pad = int(w.d_pad);
+    tp.plan = w.plan; tp.colp = colp; tp.pos4 = pos4;
+    tp.gscale = (pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
+    tp.exclude_self = exclude_self;
+    tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
+    tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
+    rc = tc_launch(ops, w.n_pad, tp, st);
+    if (rc != HG_OK) return rc;
+
+    RerankParams rp{};
+    rp.feats = feats; rp.n = n; rp.d = d; rp.pos = pos; rp.pos_dim = pos_dim;
+    rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = pos ? lambda_g : 0.f;
+    rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
+    rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
+    rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val;
+    return rerank_launch(rp, st);
+}

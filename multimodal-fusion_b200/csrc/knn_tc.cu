@@ -1,0 +1,314 @@
+// Fused pairwise-similarity + running top-k on the sm_100a tensor cores.
+//
+// Replaces, without ever writing the N x N matrix to HBM:
+//   reference similarity_kernel.py:46   torch.mm(features, features.t())
+//             similarity_kernel.py:49-52 n_i + n_j - 2 dot -> exp(-lambda .)
+//             similarity_kernel.py:79-84,122  the spatial factor K_g
+//             preprocess_hypergraph.py:379-382  sklearn brute-force kNN
+//
+// Arithmetic: FP32 rows are pre-split into BF16 hi/lo planes (split.cu).  The dot
+// product is accumulated in FP32 in TMEM from three tcgen05 MMAs per k-step:
+//   hi*lo^T + lo*hi^T + hi*hi^T   ("3xBF16", ~2^-17 relative per product).
+// The epilogue turns the accumulator into a ranking score  a_j + b_j * dot
+// (+ g * |pos_i - pos_j|^2)  and keeps a per-row sorted list of the KL best
+// (score, column) pairs in registers.  The candidates are re-ranked exactly in
+// FP32 by rerank.cu, so the tensor-core pass only has to find the right set.
+//
+// Structure (one CTA per SM, persistent over work units):
+//   warp 0      TMA producer: A tile [2 planes][128 rows][64] + B tile [2][256][64] per stage
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
+//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns, score, register top-k
+// Two 256-column FP32 accumulators (all 512 TMEM columns) let the epilogue of tile
+// t overlap the MMAs of tile t+1.
+//
+// Work unit = (row block of 128 queries, one of S column ranges).  Units are
+// numbered split-major so the CTAs running concurrently sweep the SAME column
+// range in the same order: a B tile is fetched from HBM once and then served to
+// all 148 SMs out of L2, while each CTA's A block (128 rows) stays L2-resident.
+#include "knn_tc.cuh"
+#include "ptx.cuh"
+#include "topk_list.cuh"
+#include <cudaTypedefs.h>
+
+namespace hg {
+
+constexpr int TC_STAGES = 2;
+constexpr int TC_A_PLANE = TC_BM * TC_BK * 2;                 // 16 KB
+constexpr int TC_B_PLANE = TC_BN * TC_BK * 2;                 // 32 KB
+constexpr int TC_STAGE_BYTES = 2 * TC_A_PLANE + 2 * TC_B_PLANE;   // 96 KB
+constexpr int TC_THREADS = 192;
+constexpr int TC_EPI_THREADS = 128;
+constexpr int TC_TMEM_COLS = 512;
+
+struct TcSmem {                       // lives after the (1024-byte aligned) stage buffers
+    float2 colp[2][TC_BN];
+    float4 cpos[2][TC_BN];
+    uint64_t full[TC_STAGES], empty[TC_STAGES], tmem_full[2], tmem_empty[2];
+    uint32_t tmem_base;
+};
+constexpr size_t TC_SMEM_BYTES = 1024 + size_t(TC_STAGES) * TC_STAGE_BYTES + sizeof(TcSmem);
+
+template <int KL, bool HAS_POS>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+              const TcParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+    TcSmem* sm = reinterpret_cast<TcSmem*>(smem_al + size_t(TC_STAGES) * TC_STAGE_BYTES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_kb = p.d_pad / TC_BK;
+    const int units = p.plan.num_rb * p.plan.splits;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) {
+            ptx::mbar_init(ptx::smem_u32(&sm->full[s]), 1);
+            ptx::mbar_init(ptx::smem_u32(&sm->empty[s]), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(ptx::smem_u32(&sm->tmem_full[b]), 1);
+            ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), TC_EPI_THREADS);
+        }
+        ptx::fence_barrier_init();
+        ptx::fence_proxy_async();
+    }
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tmap_a);
+        ptx::prefetch_tensormap(&tmap_b);
+    }
+    if (warp == 1) {
+        ptx::tmem_alloc<1>(ptx::smem_u32(&sm->tmem_base), TC_TMEM_COLS);
+        ptx::tmem_relinquish<1>();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = sm->tmem_base;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int split = u / p.plan.num_rb, rb = u % p.plan.num_rb;
+                const int row0 = int(p.row_begin) + rb * TC_BM;
+                const int ct0 = split * p.plan.ct_per_split;
+                const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+                for (int ct = ct0; ct < ct1; ++ct) {
+                    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                        const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
+                        ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
+                        const uint32_t full = ptx::smem_u32(&sm->full[stage]);
+                        const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
+                        ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                        ptx::tma_load_3d(dst, &tmap_a, full, kb * TC_BK, row0, 0, ptx::kEvictLast);
+                        ptx::tma_load_3d(dst + 2 * TC_A_PLANE, &tmap_b, full, kb * TC_BK, ct * TC_BN, 0,
+                                         ptx::kEvictNormal);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ==============================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM, TC_BN);
+            uint32_t it = 0, tile = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int split = u / p.plan.num_rb;
+                const int ct0 = split * p.plan.ct_per_split;
+                const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+                for (int ct = ct0; ct < ct1; ++ct, ++tile) {
+                    const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
+                    ptx::mbar_wait(ptx::smem_u32(&sm->tmem_empty[buf]), tph ^ 1u);
+                    ptx::tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + buf * TC_BN;
+                    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                        const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
+                        ptx::mbar_wait(ptx::smem_u32(&sm->full[stage]), ph);
+                        ptx::tc_fence_after();
+                        const uint32_t a_addr = smem_base + stage * TC_STAGE_BYTES;
+                        const uint32_t b_addr = a_addr + 2 * TC_A_PLANE;
+                        const uint64_t a_hi = ptx::make_smem_desc_sw128(a_addr);
+                        const uint64_t a_lo = ptx::make_smem_desc_sw128(a_addr + TC_A_PLANE);
+                        const uint64_t b_hi = ptx::make_smem_desc_sw128(b_addr);
+                        const uint64_t b_lo = ptx::make_smem_desc_sw128(b_addr + TC_B_PLANE);
+#pragma unroll
+                        for (int ks = 0; ks < TC_BK / 16; ++ks) {
+                            const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
+                            ptx::mma_bf16<1>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
+                            ptx::mma_bf16<1>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
+                            ptx::mma_bf16<1>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                        }
+                        ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));   // frees the stage when the MMAs retire
+                    }
+                    ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
+                }
+            }
+        }
+    } else {
+        // ============================ epilogue ================================
+        const int et = threadIdx.x - 64;                 // 0..127
+        const int quarter = warp & 3;                    // TMEM lane quarter this warp may read
+        const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+        uint32_t tile = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int split = u / p.plan.num_rb, rb = u % p.plan.num_rb;
+            const int64_t row0 = p.row_begin + int64_t(rb) * TC_BM;
+            const int64_t row = row0 + quarter * 32 + lane;
+            const int ct0 = split * p.plan.ct_per_split;
+            const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+            float lv[KL];
+            int li[KL];
+#pragma unroll
+            for (int q = 0; q < KL; ++q) { lv[q] = INFINITY; li[q] = -1; }
+            float4 mypos = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (HAS_POS && row < p.n) mypos = __ldg(p.pos4 + row);
+            for (int ct = ct0; ct < ct1; ++ct, ++tile) {
+                const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
+                const int col0 = ct * TC_BN;
+                sm->colp[buf][et] = __ldg(p.colp + col0 + et);
+                sm->colp[buf][et + 128] = __ldg(p.colp + col0 + et + 128);
+                if (HAS_POS) {
+                    sm->cpos[buf][et] = __ldg(p.pos4 + col0 + et);
+                    sm->cpos[buf][et + 128] = __ldg(p.pos4 + col0 + et + 128);
+                }
+                ptx::named_bar_sync(1, TC_EPI_THREADS);
+                ptx::mbar_wait(ptx::smem_u32(&sm->tmem_full[buf]), tph);
+                ptx::tc_fence_after();
+                const bool diag = p.exclude_self && (col0 < row0 + TC_BM) && (row0 < col0 + TC_BN);
+                const int self_col = diag ? int(row - col0) : -1;     // column inside this tile, if any
+#pragma unroll 1
+                for (int ch = 0; ch < TC_BN / 32; ++ch) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(tmem_base + lane_base + buf * TC_BN + ch * 32, r);
+                    ptx::tmem_ld_wait();
+                    // pass 1 (straight-line): scores in place, bitmask of columns beating the current k-th
+                    uint32_t hits = 0;
+                    const float thr = lv[KL - 1];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int c = ch * 32 + j;
+                        const float2 cp = sm->colp[buf][c];
+                        float s = fmaf(cp.y, __uint_as_float(r[j]), cp.x);
+                        if (HAS_POS) {
+                            const float4 q = sm->cpos[buf][c];
+                            const float dx = mypos.x - q.x, dy = mypos.y - q.y, dz = mypos.z - q.z;
+                            s = fmaf(p.gscale, fmaf(dx, dx, fmaf(dy, dy, dz * dz)), s);
+                        }
+                        if (c == self_col) s = INFINITY;
+                        r[j] = __float_as_uint(s);
+                        hits |= (s < thr) ? (1u << j) : 0u;
+                    }
+                    // pass 2 (rare): ascending column order keeps the lowest index among equal scores
+                    while (hits) {
+                        const int j = __ffs(hits) - 1;
+                        hits &= hits - 1;
+                        uint32_t bits = r[0];
+#pragma unroll
+                        for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
+                        const float s = __uint_as_float(bits);
+                        if (s < lv[KL - 1]) list_insert<KL>(lv, li, s, col0 + ch * 32 + j);
+                    }
+                }
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
+            }
+            if (row < p.row_end) {
+                const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+#pragma unroll
+                for (int q = 0; q < KL; ++q) { p.part_val[o + q] = lv[q]; p.part_idx[o + q] = li[q]; }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<1>(tmem_base, TC_TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k) {
+    TcPlan pl{};
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_ct = int(ceil_div(n, TC_BN));
+    // list length: k plus slack for the exact re-rank, in the register-array sizes compiled
+    pl.kl = (k + 4 <= 8) ? 8 : (k + 4 <= 16) ? 16 : (k + 8 <= 24) ? 24 : 32;
+    // column splits: fewest that fill the machine and waste < 6% of the last round
+    int best = 1;
+    double best_eff = 0.0;
+    for (int s = 1; s <= TC_MAX_SPLITS && s <= pl.num_ct; ++s) {
+        const int64_t units = int64_t(pl.num_rb) * s;
+        const double eff = double(units) / double(ceil_div(units, kNumSMs) * kNumSMs);
+        if (eff > best_eff + 0.02) { best_eff = eff; best = s; }
+        if (eff >= 0.94) break;
+    }
+    pl.splits = best;
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
+    pl.splits = int(ceil_div(pl.num_ct, pl.ct_per_split));
+    pl.grid = int(min64(kNumSMs, int64_t(pl.num_rb) * pl.splits));
+    return pl;
+}
+
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    return fn;
+}
+
+static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows) {
+    auto enc = get_encode_fn();
+    HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+    cuuint64_t dims[3] = {cuuint64_t(d_pad), cuuint64_t(n_pad), 2};
+    cuuint64_t strides[2] = {cuuint64_t(d_pad) * 2, cuuint64_t(n_pad) * cuuint64_t(d_pad) * 2};
+    cuuint32_t box[3] = {cuuint32_t(TC_BK), cuuint32_t(box_rows), 2};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    HG_REQUIRE(r == CUDA_SUCCESS, HG_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", int(r));
+    return HG_OK;
+}
+
+template <int KL>
+static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+    if (p.pos4 != nullptr) {
+        HG_CHECK_CUDA(cudaFuncSetAttribute(knn_tc_kernel<KL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           int(TC_SMEM_BYTES)));
+        knn_tc_kernel<KL, true><<<p.plan.grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
+    } else {
+        HG_CHECK_CUDA(cudaFuncSetAttribute(knn_tc_kernel<KL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           int(TC_SMEM_BYTES)));
+        knn_tc_kernel<KL, false><<<p.plan.grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
+    }
+    HG_CHECK_LAUNCH();
+    return HG_OK;
+}
+
+int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
+    CUtensorMap ta, tb;
+    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM);
+    if (rc != HG_OK) return rc;
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN);
+    if (rc != HG_OK) return rc;
+    switch (p.plan.kl) {
+        case 8:  return launch_kl<8>(ta, tb, p, st);
+        case 16: return launch_kl<16>(ta, tb, p, st);
+        case 24: return launch_kl<24>(ta, tb, p, st);
+        case 32: return launch_kl<32>(ta, tb, p, st);
+        default: break;
+    }
+    set_error("tc_launch: unsupported list length %d", p.plan.kl);
+    return HG_ERR_UNSUPPORTED;
+}
+
+}  // namespace hg

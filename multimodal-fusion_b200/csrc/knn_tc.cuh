@@ -1,0 +1,51 @@
+// Interface between the fused tensor-core kNN kernel (knn_tc.cu) and its host driver (knn_api.cu).
+#pragma once
+#include "common.cuh"
+
+namespace hg {
+
+constexpr int TC_BM = 128;      // query rows per CTA tile  (UMMA M)
+constexpr int TC_BN = 256;      // candidate columns per tile (UMMA N)
+constexpr int TC_BK = 64;       // K per pipeline stage = one 128-byte swizzle atom of BF16
+constexpr int TC_MAX_SPLITS = 8;
+
+struct TcPlan {
+    int64_t n_rows;             // row_end - row_begin
+    int num_rb;                 // ceil(n_rows / 128)
+    int num_ct;                 // ceil(n / 256)
+    int splits;                 // column splits S (partial lists per row)
+    int ct_per_split;
+    int kl;                     // list length kept per (row, split): 8 / 16 / 24 / 32
+    int grid;                   // CTAs launched
+};
+
+struct TcParams {
+    int64_t n, row_begin, row_end;
+    int d_pad;
+    TcPlan plan;
+    const float2* colp;         // [n_pad]  score_j = colp.x + colp.y * dot   (+inf, 0 beyond n)
+    const float4* pos4;         // [n_pad]  (x, y, z, 0) or null
+    float gscale;               // weight of the squared spatial distance in the ranking score
+    int exclude_self;
+    float* part_val;            // [S][n_rows][kl]
+    int32_t* part_idx;
+};
+
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k);
+int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
+
+struct RerankParams {
+    const float* feats; int64_t n, d;
+    const float* pos; int pos_dim;
+    int metric; float lambda_h, lambda_g;
+    const float* part_val; const int32_t* part_idx;
+    int splits, kl; int64_t n_rows, row_begin;
+    int k;
+    int32_t* out_idx; float* out_val;
+};
+int rerank_launch(const RerankParams& p, cudaStream_t st);
+
+int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
+                     float2* colp, float4* pos4, cudaStream_t st);
+
+}  // namespace hg

@@ -1,0 +1,176 @@
+// Merge of the per-split candidate lists + exact FP32 re-rank, and the per-column
+// epilogue parameters of the fused kernel.
+//
+// The tensor-core pass (knn_tc.cu) ranks with 3xBF16 dot products; this pass
+// recomputes the distance of every surviving candidate in direct-difference
+// FP32 -- sum (x_i - x_j)^2, the more accurate of the two forms the reference
+// uses (preprocess_hypergraph.py:254-255 vs similarity_kernel.py:49) -- and
+// orders the final k by (exact value, index).  One warp per query row, 128-bit
+// loads; the query row stays in L1 while its ~KL candidates stream from L2.
+// Algorithmic bytes per row: KL * 4 D (candidate rows) + 4 D (query) + 8 k out.
+#include "knn_tc.cuh"
+
+namespace hg {
+
+__global__ void colparams_kernel(const float* __restrict__ sq_norms, const float* __restrict__ pos, int pos_dim,
+                                 int64_t n, int64_t n_pad, int metric, float2* __restrict__ colp,
+                                 float4* __restrict__ pos4) {
+    const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (j >= n_pad) return;
+    float2 cp = make_float2(INFINITY, 0.f);          // padded columns can never be selected
+    if (j < n) {
+        const float nj = sq_norms[j];
+        if (metric == HG_METRIC_COSINE) cp = make_float2(0.f, -1.f / fmaxf(sqrtf(nj), 1e-8f));
+        else cp = make_float2(nj, -2.f);             // n_j - 2 dot (+ the row constant n_i, irrelevant to ranking)
+    }
+    colp[j] = cp;
+    if (pos4 != nullptr) {
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j < n) {
+            q.x = pos[j * pos_dim];
+            if (pos_dim > 1) q.y = pos[j * pos_dim + 1];
+            if (pos_dim > 2) q.z = pos[j * pos_dim + 2];
+        }
+        pos4[j] = q;
+    }
+}
+
+int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
+                     float2* colp, float4* pos4, cudaStream_t st) {
+    colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, pos, pos_dim, n, n_pad, metric, colp, pos4);
+    HG_CHECK_LAUNCH();
+    return HG_OK;
+}
+
+__device__ __forceinline__ bool pair_less(float va, int ia, float vb, int ib) {
+    return va < vb || (va == vb && ia < ib);
+}
+
+constexpr int RR_WARPS = 8;
+constexpr int RR_MAX_CAND = TC_MAX_SPLITS * 32;      // 256 candidates per row at most
+
+__global__ void __launch_bounds__(RR_WARPS * 32)
+rerank_kernel(const RerankParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t r = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
+    if (r >= p.n_rows) return;
+    const int64_t row = p.row_begin + r;
+    const int total = p.splits * p.kl;
+
+    // ---- 1. merge: the kl best approximate candidates, lane t ends up holding the t-th -------------
+    float cv[RR_MAX_CAND / 32];
+    int ci[RR_MAX_CAND / 32];
+#pragma unroll
+    for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+        const int t = lane + 32 * q;
+        cv[q] = INFINITY; ci[q] = 0x7fffffff;
+        if (t < total) {
+            const int s = t / p.kl, w = t - s * p.kl;
+            const int64_t o = (int64_t(s) * p.n_rows + r) * p.kl + w;
+            const int idx = p.part_idx[o];
+            if (idx >= 0) { cv[q] = p.part_val[o]; ci[q] = idx; }
+        }
+    }
+    int sel = -1;                                    // candidate column held by this lane (lane < kl)
+    for (int t = 0; t < p.kl; ++t) {
+        float bv = INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+        for (int q = 0; q < RR_MAX_CAND / 32; ++q)
+            if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) break;                 // fewer than kl real candidates
+#pragma unroll
+        for (int q = 0; q < RR_MAX_CAND / 32; ++q)
+            if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }   // column ids are unique per row
+        if (lane == t) sel = bi;
+    }
+
+    // ---- 2. exact values ---------------------------------------------------------------------------
+    const float* xi = p.feats + row * p.d;
+    const bool vec = (p.d & 3) == 0 && (reinterpret_cast<uintptr_t>(p.feats) & 15) == 0;
+    float ni = 0.f;
+    if (p.metric == HG_METRIC_COSINE) {
+        for (int64_t c = lane; c < p.d; c += 32) { const float x = __ldg(xi + c); ni = fmaf(x, x, ni); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ni += __shfl_xor_sync(0xffffffffu, ni, o);
+    }
+    float my_val = INFINITY;                         // ranking key (ascending) of this lane's candidate
+    float my_out = NAN;
+    for (int t = 0; t < p.kl; ++t) {
+        const int j = __shfl_sync(0xffffffffu, sel, t);
+        if (j < 0) continue;                         // warp-uniform
+        const float* xj = p.feats + int64_t(j) * p.d;
+        float acc = 0.f, nj = 0.f;
+        if (p.metric == HG_METRIC_COSINE) {
+            for (int64_t c = lane; c < p.d; c += 32) {
+                const float x = __ldg(xi + c), y = __ldg(xj + c);
+                acc = fmaf(x, y, acc); nj = fmaf(y, y, nj);
+            }
+        } else if (vec) {
+            for (int64_t c = lane; c < (p.d >> 2); c += 32) {
+                const float4 x = __ldg(reinterpret_cast<const float4*>(xi) + c);
+                const float4 y = __ldg(reinterpret_cast<const float4*>(xj) + c);
+                const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+                acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+            }
+        } else {
+            for (int64_t c = lane; c < p.d; c += 32) {
+                const float df = __ldg(xi + c) - __ldg(xj + c);
+                acc = fmaf(df, df, acc);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            nj += __shfl_xor_sync(0xffffffffu, nj, o);
+        }
+        if (lane == t) {
+            if (p.metric == HG_METRIC_COSINE) {
+                const float cs = acc / (fmaxf(sqrtf(ni), 1e-8f) * fmaxf(sqrtf(nj), 1e-8f));
+                my_val = -cs; my_out = cs;
+            } else if (p.metric == HG_METRIC_EUCLIDEAN) {
+                my_val = acc; my_out = acc;
+            } else {
+                float d2g = 0.f;
+                if (p.pos != nullptr) {
+                    for (int q = 0; q < p.pos_dim; ++q) {
+                        const float df = __ldg(p.pos + row * p.pos_dim + q) - __ldg(p.pos + int64_t(j) * p.pos_dim + q);
+                        d2g = fmaf(df, df, d2g);
+                    }
+                }
+                my_val = p.lambda_h * acc + p.lambda_g * d2g;
+                my_out = expf(-my_val);
+            }
+        }
+    }
+
+    // ---- 3. final order by (exact value, index); best k written out ----------------------------------
+    const int my_idx = (sel >= 0) ? sel : 0x7fffffff;
+    int rank = 0;
+    for (int t = 0; t < p.kl; ++t) {
+        const float ov = __shfl_sync(0xffffffffu, my_val, t);
+        const int oi = __shfl_sync(0xffffffffu, my_idx, t);
+        rank += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
+    }
+    if (lane < p.kl && sel >= 0 && rank < p.k) {
+        p.out_idx[r * p.k + rank] = sel;
+        p.out_val[r * p.k + rank] = my_out;
+    }
+    // rows with fewer than k candidates: pad with (-1, NaN)
+    int have = __popc(__ballot_sync(0xffffffffu, lane < p.kl && sel >= 0));
+    for (int t = have + lane; t < p.k; t += 32) { p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN; }
+}
+
+int rerank_launch(const RerankParams& p, cudaStream_t st) {
+    HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_CAND, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
+    rerank_kernel<<<(unsigned)ceil_div(p.n_rows, RR_WARPS), RR_WARPS * 32, 0, st>>>(p);
+    HG_CHECK_LAUNCH();
+    return HG_OK;
+}
+
+}  // namespace hg

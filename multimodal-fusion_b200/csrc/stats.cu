@@ -1,0 +1,147 @@
+// A9: mean / unbiased std / min / max / lower median of a float buffer.
+//
+// Reference: preprocess_hypergraph.py:190-196 (`K_wsi.mean/std/min/max/median`),
+// :259-265 (WSI x TMA matrix) and similarity_kernel.py:183-186 (lower median of
+// the off-diagonal).  torch.median returns the LOWER middle element for an even
+// count; std is the unbiased estimator.
+//
+// One streaming pass for the moments (double accumulators), then a 4-pass MSB
+// radix select on the order-preserving uint32 image of the floats for the median:
+// 5 reads of the buffer in total, no sort, no copy.
+#include "common.cuh"
+
+namespace hg {
+
+struct StatsState {
+    double sum, sumsq;
+    unsigned int min_key, max_key;
+    unsigned int prefix;             // selected high bytes so far
+    unsigned int pad;
+    unsigned long long rank;         // rank still to descend inside the selected bucket
+    unsigned long long count;
+    unsigned int hist[256];
+};
+
+__device__ __forceinline__ unsigned int ordered_key(float f) {
+    const unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_to_float(unsigned int k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+__device__ __forceinline__ bool stats_live(int64_t i, int64_t diag_n) {
+    return diag_n <= 0 || (i % (diag_n + 1)) != 0;
+}
+
+__global__ void stats_init_kernel(StatsState* s, unsigned long long count) {
+    if (threadIdx.x == 0) {
+        s->sum = 0.0; s->sumsq = 0.0; s->min_key = 0xffffffffu; s->max_key = 0u;
+        s->prefix = 0u; s->rank = (count - 1) / 2; s->count = count;
+    }
+    s->hist[threadIdx.x] = 0u;
+}
+
+__global__ void __launch_bounds__(256)
+stats_moments_kernel(const float* __restrict__ v, int64_t len, int64_t diag_n, StatsState* s) {
+    double sum = 0.0, sq = 0.0;
+    unsigned int mn = 0xffffffffu, mx = 0u;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < len; i += int64_t(gridDim.x) * blockDim.x) {
+        if (!stats_live(i, diag_n)) continue;
+        const float x = v[i];
+        sum += double(x); sq += double(x) * double(x);
+        const unsigned int k = ordered_key(x);
+        mn = min(mn, k); mx = max(mx, k);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s->sum, sum); atomicAdd(&s->sumsq, sq);
+        atomicMin(&s->min_key, mn); atomicMax(&s->max_key, mx);
+    }
+}
+
+// histogram of byte `byte_idx` (3 = most significant) over keys matching the prefix above it
+__global__ void __launch_bounds__(256)
+stats_hist_kernel(const float* __restrict__ v, int64_t len, int64_t diag_n, int byte_idx, StatsState* s) {
+    __shared__ unsigned int h[256];
+    h[threadIdx.x] = 0u;
+    __syncthreads();
+    const unsigned int prefix = s->prefix;
+    const int hi_shift = (byte_idx + 1) * 8;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < len; i += int64_t(gridDim.x) * blockDim.x) {
+        if (!stats_live(i, diag_n)) continue;
+        const unsigned int k = ordered_key(v[i]);
+        if (byte_idx == 3 || (k >> hi_shift) == (prefix >> hi_shift)) atomicAdd(&h[(k >> (byte_idx * 8)) & 255u], 1u);
+    }
+    __syncthreads();
+    if (h[threadIdx.x]) atomicAdd(&s->hist[threadIdx.x], h[threadIdx.x]);
+}
+
+__global__ void stats_select_kernel(int byte_idx, StatsState* s) {
+    __shared__ unsigned int h[256];
+    h[threadIdx.x] = s->hist[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long r = s->rank;
+        int b = 0;
+        for (; b < 255; ++b) {
+            if (r < h[b]) break;
+            r -= h[b];
+        }
+        s->rank = r;
+        s->prefix |= (unsigned int)b << (byte_idx * 8);
+    }
+    __syncthreads();
+    s->hist[threadIdx.x] = 0u;
+}
+
+__global__ void stats_final_kernel(const StatsState* s, double* out) {
+    if (threadIdx.x != 0) return;
+    const double n = double(s->count);
+    const double mean = s->sum / n;
+    double var = (s->sumsq - s->sum * s->sum / n) / (n - 1.0);
+    if (var < 0.0) var = 0.0;
+    out[0] = mean;
+    out[1] = (s->count > 1) ? sqrt(var) : nan("");
+    out[2] = double(key_to_float(s->min_key));
+    out[3] = double(key_to_float(s->max_key));
+    out[4] = double(key_to_float(s->prefix));
+}
+
+}  // namespace hg
+
+using namespace hg;
+
+extern "C" int hg_stats_workspace_bytes(int64_t count, size_t* bytes) {
+    HG_REQUIRE(bytes && count > 0, HG_ERR_BAD_ARG, "hg_stats_workspace_bytes: bad argument");
+    *bytes = (sizeof(StatsState) + 255) & ~size_t(255);
+    return HG_OK;
+}
+
+extern "C" int hg_similarity_stats(const float* values, int64_t count, int64_t exclude_diag_n,
+                                   double* stats_out, void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(values && count > 0 && stats_out, HG_ERR_BAD_ARG, "hg_similarity_stats: bad argument");
+    HG_REQUIRE(exclude_diag_n <= 0 || exclude_diag_n * exclude_diag_n == count, HG_ERR_BAD_ARG,
+               "hg_similarity_stats: exclude_diag_n^2 must equal count");
+    HG_REQUIRE(workspace && workspace_bytes >= sizeof(StatsState), HG_ERR_WORKSPACE, "hg_similarity_stats: workspace too small");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    StatsState* s = static_cast<StatsState*>(workspace);
+    const unsigned long long live = exclude_diag_n > 0 ? (unsigned long long)(count - exclude_diag_n) : (unsigned long long)count;
+    HG_REQUIRE(live > 0, HG_ERR_BAD_ARG, "hg_similarity_stats: nothing left after excluding the diagonal");
+    const int blocks = int(min64(ceil_div(count, 256 * 8), 148 * 8));
+    stats_init_kernel<<<1, 256, 0, st>>>(s, live);
+    stats_moments_kernel<<<blocks, 256, 0, st>>>(values, count, exclude_diag_n, s);
+    for (int b = 3; b >= 0; --b) {
+        stats_hist_kernel<<<blocks, 256, 0, st>>>(values, count, exclude_diag_n, b, s);
+        stats_select_kernel<<<1, 256, 0, st>>>(b, s);
+    }
+    stats_final_kernel<<<1, 32, 0, st>>>(s, stats_out);
+    HG_CHECK_LAUNCH();
+    return HG_OK;
+}

@@ -1,0 +1,190 @@
+"""Torch-tensor front end of the C ABI: allocates outputs / workspaces with torch and
+passes raw pointers to libhg_b200.so.  One function per kernel family."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+def _size(fn, *args) -> int:
+    out = C.c_size_t(0)
+    L.check(fn(*args, C.byref(out)))
+    return int(out.value)
+
+
+# --------------------------------------------------------------------------- kNN
+def knn_feature(features: torch.Tensor, k: int, metric: str = "euclidean",
+                positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0, lambda_g: float = 0.0,
+                rows: Optional[Tuple[int, int]] = None, exclude_self: bool = True,
+                precision: str = "tc", device=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Fused similarity + top-k (A1/A2/A4).  Returns (idx int32 [R,k], val float32 [R,k]);
+    val = squared distance / Gaussian K / cosine depending on `metric`."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    n, d = x.shape
+    pos = L.f32c(positions, dev) if positions is not None else None
+    r0, r1 = (0, n) if rows is None else rows
+    if n <= 1:
+        raise ValueError(f"Number of nodes must be greater than 1, got N={n}.")
+    out_idx = torch.empty((max(r1 - r0, 0), k), dtype=torch.int32, device=dev)
+    out_val = torch.empty((max(r1 - r0, 0), k), dtype=torch.float32, device=dev)
+    prec = {"tc": 0, "fp32": 1}[precision]
+    with torch.cuda.device(dev):
+        ws = None
+        nbytes = 0
+        if prec == 0:
+            nbytes = _size(lib.hg_knn_feature_workspace_bytes, n, d, k, r0, r1)
+            ws = L.Workspace.get(dev, nbytes)
+        L.check(lib.hg_knn_feature(
+            L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1], L.METRIC[metric],
+            float(lambda_h), float(lambda_g), k, r0, r1, int(exclude_self), prec,
+            L.ptr(out_idx), L.ptr(out_val), L.ptr(ws), nbytes, L.stream_ptr(dev)))
+    return out_idx, out_val
+
+
+def knn_spatial(positions: torch.Tensor, k: int, rows: Optional[Tuple[int, int]] = None,
+                device=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """A3: k smallest squared spatial distances, ties by (d2, index).  (idx int32, d2 float32)."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (positions.device if positions.is_cuda else None))
+    p = L.f32c(positions, dev)
+    n, pd = p.shape
+    r0, r1 = (0, n) if rows is None else rows
+    out_idx = torch.empty((r1 - r0, k), dtype=torch.int32, device=dev)
+    out_d2 = torch.empty((r1 - r0, k), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = _size(lib.hg_knn_spatial_workspace_bytes, n, k, r0, r1)
+        ws = L.Workspace.get(dev, nbytes)
+        L.check(lib.hg_knn_spatial(L.ptr(p), n, pd, k, r0, r1, L.ptr(out_idx), L.ptr(out_d2),
+                                   L.ptr(ws), nbytes, L.stream_ptr(dev)))
+    return out_idx, out_d2
+
+
+# ------------------------------------------------------------------- dense kernels
+def similarity_dense(a: torch.Tensor, b: Optional[torch.Tensor] = None,
+                     pos_a: Optional[torch.Tensor] = None, pos_b: Optional[torch.Tensor] = None,
+                     lambda_h: float = 1.0, lambda_g: float = 0.0, form: int = L.FORM_EXPANSION,
+                     device=None) -> torch.Tensor:
+    """A1/A2/A7: dense exp(-lambda_h d2_h - lambda_g d2_g), [M,N] float32."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (a.device if a.is_cuda else None))
+    xa = L.f32c(a, dev)
+    xb = L.f32c(b, dev) if b is not None else None
+    pa = L.f32c(pos_a, dev) if pos_a is not None else None
+    pb = L.f32c(pos_b, dev) if pos_b is not None else None
+    m, d = xa.shape
+    n = m if xb is None else xb.shape[0]
+    out = torch.empty((m, n), dtype=torch.float32, device=dev)
+    if m == 0 or n == 0:
+        return out
+    with torch.cuda.device(dev):
+        L.check(lib.hg_similarity_dense(L.ptr(xa), m, L.ptr(xb), n, d, L.ptr(pa), L.ptr(pb),
+                                        0 if pa is None else pa.shape[1], float(lambda_h), float(lambda_g),
+                                        form, L.ptr(out), n, L.stream_ptr(dev)))
+    return out
+
+
+def similarity_stats(mat: torch.Tensor, exclude_diagonal: bool = False) -> dict:
+    """A9: mean / std / min / max / lower-median of a CUDA float32 matrix (one D2H of 5 doubles)."""
+    lib = L.load_library()
+    dev = L.require_cuda(mat.device if mat.is_cuda else None)
+    m = L.f32c(mat, dev)
+    count = m.numel()
+    out = torch.empty(5, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = _size(lib.hg_stats_workspace_bytes, count)
+        ws = L.Workspace.get(dev, nbytes, "stats")
+        L.check(lib.hg_similarity_stats(L.ptr(m), count, m.shape[0] if exclude_diagonal else 0, L.ptr(out),
+                                        L.ptr(ws), nbytes, L.stream_ptr(dev)))
+    v = out.cpu().tolist()
+    return {"mean": v[0], "std": v[1], "min": v[2], "max": v[3], "median": v[4]}
+
+
+# ------------------------------------------------------------------ edge assembly
+def build_edges(knn_lists: Sequence[torch.Tensor], n: int, labels: Optional[torch.Tensor] = None,
+                num_hyperedges: int = 0, device=None) -> torch.Tensor:
+    """A5: kNN pairs (+ intra-cluster cliques) -> unique (min,max) edge_index int64 [2,E], sorted."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (knn_lists[0].device if knn_lists else None))
+    lists = [t.to(device=dev, dtype=torch.int32).contiguous() for t in knn_lists]
+    for t in lists:
+        if t.shape[0] != n:
+            raise ValueError("every neighbour list must have n rows")
+    ks = [int(t.shape[1]) for t in lists]
+    lab = None
+    pairs = C.c_int64(0)
+    with torch.cuda.device(dev):
+        st = L.stream_ptr(dev)
+        if labels is not None and num_hyperedges > 0:
+            lab = torch.as_tensor(labels).to(device=dev, dtype=torch.int32).contiguous()
+            if lab.numel() != n:
+                raise ValueError("labels must have n entries")
+            L.check(lib.hg_clique_pairs(L.ptr(lab), n, num_hyperedges, C.byref(pairs), st))
+        else:
+            num_hyperedges = 0
+        slots = sum(n * k for k in ks)
+        nbytes = _size(lib.hg_edges_workspace_bytes, n, slots, num_hyperedges, pairs.value)
+        ws = L.Workspace.get(dev, nbytes, "edges")
+        arr_p = (C.c_void_p * max(len(lists), 1))(*[t.data_ptr() for t in lists])
+        arr_k = (C.c_int * max(len(lists), 1))(*ks)
+        e = C.c_int64(0)
+        L.check(lib.hg_edges_count(arr_p, arr_k, len(lists), n, L.ptr(lab), num_hyperedges, pairs.value,
+                                   C.byref(e), L.ptr(ws), nbytes, st))
+        edge_index = torch.empty((2, e.value), dtype=torch.int64, device=dev)
+        L.check(lib.hg_edges_fill(e.value, L.ptr(edge_index), L.ptr(ws), nbytes, st))
+    return edge_index
+
+
+def edge_weights_cosine(features: torch.Tensor, edge_index: torch.Tensor) -> torch.Tensor:
+    """A6: max(0, cos(f_i, f_j)) per edge, float32 [E]."""
+    lib = L.load_library()
+    dev = L.require_cuda(edge_index.device if edge_index.is_cuda else None)
+    x = L.f32c(features, dev)
+    ei = edge_index.to(device=dev, dtype=torch.int64).contiguous()
+    e = ei.shape[1]
+    w = torch.empty(e, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(lib.hg_edge_weights_cosine(L.ptr(x), x.shape[0], x.shape[1], L.ptr(ei), e, L.ptr(w), L.stream_ptr(dev)))
+    return w
+
+
+def csr_from_coo(edge_index: torch.Tensor, n: int):
+    """CSR incidence: (rowptr [n+1], col [2E], eid [2E]) int64."""
+    lib = L.load_library()
+    dev = L.require_cuda(edge_index.device if edge_index.is_cuda else None)
+    ei = edge_index.to(device=dev, dtype=torch.int64).contiguous()
+    e = ei.shape[1]
+    rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    col = torch.empty(2 * e, dtype=torch.int64, device=dev)
+    eid = torch.empty(2 * e, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = _size(lib.hg_csr_workspace_bytes, n, e)
+        ws = L.Workspace.get(dev, nbytes, "csr")
+        L.check(lib.hg_csr_from_coo(L.ptr(ei), e, n, L.ptr(rowptr), L.ptr(col), L.ptr(eid), L.ptr(ws), nbytes,
+                                    L.stream_ptr(dev)))
+    return rowptr, col, eid
+
+
+def threshold_edges(K: torch.Tensor, threshold: float):
+    """A8: every ordered (i, j) with not (K[i,j] < threshold), row-major; (edge_index, weights)."""
+    lib = L.load_library()
+    dev = L.require_cuda(K.device if K.is_cuda else None)
+    Kc = L.f32c(K, dev)
+    n = Kc.shape[0]
+    with torch.cuda.device(dev):
+        st = L.stream_ptr(dev)
+        nbytes = _size(lib.hg_threshold_workspace_bytes, n)
+        ws = L.Workspace.get(dev, nbytes, "thr")
+        e = C.c_int64(0)
+        L.check(lib.hg_threshold_edges_count(L.ptr(Kc), n, float(threshold), C.byref(e), L.ptr(ws), nbytes, st))
+        ei = torch.empty((2, e.value), dtype=torch.int64, device=dev)
+        w = torch.empty(e.value, dtype=torch.float32, device=dev)
+        L.check(lib.hg_threshold_edges_fill(L.ptr(Kc), n, float(threshold), e.value, L.ptr(ei), L.ptr(w),
+                                            L.ptr(ws), nbytes, st))
+    return ei, w

@@ -1,0 +1,73 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol
+that include/hg_b200.h declares, and the Python surface mirrors the reference's names.
+No compute calls (there is no GPU here)."""
+import ctypes
+import inspect
+import os
+import re
+
+import pytest
+import torch
+
+import hg_b200
+from hg_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REFERENCE_EXPORTS = [       # reference build_hypergraph/__init__.py:28-46
+    "compute_morphological_similarity", "compute_spatial_similarity", "compute_combined_similarity",
+    "build_weighted_hypergraph", "mean_pool_with_similarity", "process_single_file", "process_dataset",
+    "load_wsi_data", "load_tma_data", "aggregate_wsi_super_patches", "compute_wsi_tma_similarity",
+    "group_by_similarity", "build_hypergraph_knn_kmeans", "save_hypergraph_to_h5",
+    "load_similarity_matrices", "rebuild_hypergraph_from_similarity", "batch_rebuild_hypergraph",
+]
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "hg_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(hg_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load_library()
+    syms = _header_symbols()
+    assert len(syms) >= 20
+    for name in syms:
+        assert hasattr(lib, name), f"{name} declared in hg_b200.h but not exported"
+        assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
+    assert sorted(_lib.SIGNATURES) == syms
+    assert lib.hg_version() >= 100
+
+
+def test_error_convention_without_gpu():
+    lib = _lib.load_library()
+    out = ctypes.c_size_t(0)
+    assert lib.hg_knn_feature_workspace_bytes(1, 16, 4, 0, 1, ctypes.byref(out)) == _lib.HG_ERR_BAD_ARG
+    assert b"greater than 1" in lib.hg_last_error()
+    with pytest.raises(ValueError):
+        _lib.check(_lib.HG_ERR_BAD_ARG)
+    assert lib.hg_knn_feature_workspace_bytes(50_000, 1024, 16, 0, 50_000, ctypes.byref(out)) == 0
+    assert out.value > 2 * 50_000 * 1024 * 2        # operand planes + lists
+    assert lib.hg_operand_bytes(4096, 1024) == 2 * 4096 * 1024 * 2
+
+
+def test_python_surface_mirrors_reference():
+    for name in REFERENCE_EXPORTS:
+        assert name in hg_b200.__all__ and callable(getattr(hg_b200, name))
+    import build_hypergraph                      # alias package with the reference's name
+    assert build_hypergraph.build_hypergraph_knn_kmeans is hg_b200.build_hypergraph_knn_kmeans
+    sig = inspect.signature(hg_b200.build_hypergraph_knn_kmeans)
+    assert list(sig.parameters)[:6] == ["wsi_features", "tma_features", "group_labels", "k", "num_hyperedges", "device"]
+    assert sig.parameters["k"].default == 5 and sig.parameters["num_hyperedges"].default == 10
+    sig = inspect.signature(hg_b200.build_weighted_hypergraph)
+    assert list(sig.parameters) == ["features", "positions", "lambda_h", "lambda_g", "threshold_median_ratio", "device"]
+    sig = inspect.signature(hg_b200.process_single_file)
+    assert [p.default for p in list(sig.parameters.values())[1:]] == [100, 10, 5, 10, 1.0, 1.0, None]
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        hg_b200.compute_morphological_similarity(torch.randn(4, 8))
+    with pytest.raises(RuntimeError):
+        hg_b200.build_hypergraph_knn_kmeans(torch.randn(8, 4), torch.randn(8, 4), None)

@@ -1,0 +1,308 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the golden
+fixtures generated from the reference.  Bit-exact for indices / edges / CSR; 1e-5 relative
+for similarity values (north_star tolerance); neighbour sets exact except reported near-ties
+(oracle gap between the swapped candidates below 1e-5 relative)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle_np as oracle
+from hg_b200 import _lib, ops, synth
+import hg_b200 as hg
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5          # north_star: similarity values within 1e-5 relative
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _oracle_score(feats, pos, metric, lambda_h, lambda_g, i, js):
+    """float64 ranking score (ascending = better) of row i against columns js."""
+    x = feats.astype(np.float64)
+    if metric == "cosine":
+        xn = x / np.maximum(np.linalg.norm(x, axis=1, keepdims=True), 1e-8)
+        return -(xn[js] @ xn[i])
+    d2 = ((x[js] - x[i]) ** 2).sum(1)
+    if metric == "gaussian":
+        d2 = lambda_h * d2
+        if pos is not None and lambda_g:
+            p = pos.astype(np.float64)
+            d2 = d2 + lambda_g * ((p[js] - p[i]) ** 2).sum(1)
+    return d2
+
+
+def check_knn(idx_gpu, feats, k, metric, rows=None, pos=None, lambda_h=1.0, lambda_g=0.0, max_near_ties=None):
+    """Sets equal per row, except rows whose differing members are near-ties of the oracle's
+    k-th score (|gap| <= RTOL * scale).  Returns the number of near-tie rows (reported)."""
+    rows = np.arange(feats.shape[0]) if rows is None else np.asarray(rows)
+    idx_or, _ = oracle.knn_feature(feats, k, metric, positions=pos, lambda_h=lambda_h, lambda_g=lambda_g, rows=rows)
+    idx_gpu = np.asarray(idx_gpu, dtype=np.int64)
+    assert idx_gpu.shape == idx_or.shape
+    assert (idx_gpu >= 0).all() and (idx_gpu != rows[:, None]).all()
+    bad = np.nonzero((np.sort(idx_gpu, 1) != np.sort(idx_or, 1)).any(1))[0]
+    for r in bad:
+        i = rows[r]
+        only_g = np.setdiff1d(idx_gpu[r], idx_or[r])
+        only_o = np.setdiff1d(idx_or[r], idx_gpu[r])
+        sg = _oracle_score(feats, pos, metric, lambda_h, lambda_g, i, only_g)
+        so = _oracle_score(feats, pos, metric, lambda_h, lambda_g, i, only_o)
+        scale = max(1.0, float(np.abs(so).max()))
+        assert np.abs(sg.max() - so.min()) <= RTOL * scale, \
+            f"row {i}: GPU picked {only_g} (scores {sg}) instead of {only_o} (scores {so})"
+    limit = max(2, len(rows) // 500) if max_near_ties is None else max_near_ties
+    assert len(bad) <= limit, f"{len(bad)} near-tie rows out of {len(rows)}"
+    return len(bad)
+
+
+# ------------------------------------------------------------------------------- operands
+def test_split_operands():
+    lib = _lib.load_library()
+    n, d = 300, 100
+    x = synth.make_features(n, d, 3, "gaussian")
+    xc = _cuda(x)
+    nbytes = lib.hg_operand_bytes(n, d)
+    n_pad, d_pad = 512, 128
+    assert nbytes == 2 * n_pad * d_pad * 2
+    ops_buf = torch.empty(nbytes // 2, dtype=torch.bfloat16, device="cuda")
+    norms = torch.empty(n, dtype=torch.float32, device="cuda")
+    _lib.check(lib.hg_split_operands(xc.data_ptr(), n, d, ops_buf.data_ptr(), norms.data_ptr(), 0))
+    torch.cuda.synchronize()
+    planes = ops_buf.view(2, n_pad, d_pad).float().cpu().numpy()
+    rec = planes[0] + planes[1]
+    assert np.abs(rec[:n, :d] - x).max() <= 2.0 ** -16 * np.abs(x).max()
+    assert (rec[n:] == 0).all() and (rec[:, d:] == 0).all()
+    np.testing.assert_allclose(norms.cpu().numpy(), (x.astype(np.float64) ** 2).sum(1), rtol=1e-6)
+
+
+# ------------------------------------------------------------------------ dense kernels (A1/A2/A7)
+def test_dense_kernels_vs_reference_golden(golden):
+    g = golden("dense_n192_d64")
+    feats, pos = synth.make_slide(int(g["n"]), int(g["d"]), int(g["seed"]), "gaussian")
+    lh, lg = float(g["lambda_h"]), float(g["lambda_g"])
+    f, p = _cuda(feats), _cuda(pos)
+    K_h = hg.compute_morphological_similarity(f, lh).cpu().numpy()
+    K_g = hg.compute_spatial_similarity(p, lg).cpu().numpy()
+    K = hg.compute_combined_similarity(f, p, lh, lg).cpu().numpy()
+    np.testing.assert_allclose(K_h, g["K_h"], rtol=RTOL)
+    np.testing.assert_allclose(K_g, g["K_g"], rtol=RTOL)
+    np.testing.assert_allclose(K, g["K"], rtol=RTOL)
+    np.testing.assert_allclose(K, oracle.combined_similarity(feats, pos, lh, lg), rtol=RTOL)
+    tma = synth.make_features(int(g["n_tma"]), int(g["d"]), int(g["seed"]) + 1, "gaussian")
+    sim, st = hg.compute_wsi_tma_similarity(f[:100], p[:100], _cuda(tma), lh, lg)
+    np.testing.assert_allclose(sim.cpu().numpy(), g["wsi_tma"], rtol=RTOL)
+    got = np.array([st[s] for s in ("mean", "std", "min", "max", "median")])
+    np.testing.assert_allclose(got, g["wsi_tma_stats"], rtol=RTOL)
+    pooled = hg.mean_pool_with_similarity(f).cpu().numpy()
+    np.testing.assert_allclose(pooled, g["pooled"], rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("m,n,d", [(1, 1, 1), (65, 130, 33), (257, 64, 1024), (100, 80, 7)])
+def test_dense_ragged_shapes(m, n, d):
+    rng = np.random.default_rng(m * 1000 + n)
+    a = (rng.standard_normal((m, d)) * 0.3).astype(np.float32)
+    b = (rng.standard_normal((n, d)) * 0.3).astype(np.float32)
+    for form in (_lib.FORM_EXPANSION, _lib.FORM_DIRECT):
+        out = ops.similarity_dense(_cuda(a), _cuda(b), lambda_h=0.7, form=form).cpu().numpy()
+        ref = np.exp(-0.7 * oracle.sq_dists_f64(a, b))
+        np.testing.assert_allclose(out, ref, rtol=RTOL, atol=1e-30)
+
+
+def test_stats_and_offdiag_median():
+    rng = np.random.default_rng(5)
+    for n in (2, 37, 300):
+        K = rng.random((n, n)).astype(np.float32) - 0.3
+        st = ops.similarity_stats(_cuda(K))
+        ref = oracle.similarity_stats(K)
+        for key in ref:
+            assert np.isclose(st[key], ref[key], rtol=1e-6, atol=1e-7), (n, key, st[key], ref[key])
+        med = ops.similarity_stats(_cuda(K), exclude_diagonal=True)["median"]
+        assert med == oracle.lower_median(K[~np.eye(n, dtype=bool)])
+
+
+@pytest.mark.parametrize("tag,ratio", [("thr", 1.0), ("thr2", 0.5)])
+def test_threshold_builder_vs_reference_golden(golden, tag, ratio):
+    g = golden("dense_n192_d64")
+    feats, pos = synth.make_slide(int(g["n"]), int(g["d"]), int(g["seed"]), "gaussian")
+    nt = int(g["n_thr"])
+    ei, w = hg.build_weighted_hypergraph(_cuda(feats[:nt]), _cuda(pos[:nt]), float(g["lambda_h"]),
+                                         float(g["lambda_g"]), threshold_median_ratio=ratio)
+    ei, w = ei.cpu().numpy(), w.cpu().numpy()
+    ref_ei, ref_w = g[tag + "_edge_index"], g[tag + "_edge_weights"]
+    a, b = set(map(tuple, ei.T.tolist())), set(map(tuple, ref_ei.T.tolist()))
+    assert len(a ^ b) <= 2            # entries sitting on the threshold may flip with FP32 summation order
+    if len(a ^ b) == 0:
+        assert (ei == ref_ei).all()   # row-major order, diagonal and both directions kept
+        np.testing.assert_allclose(w, ref_w, rtol=RTOL)
+    # ratio None keeps everything (documented intent of the reference)
+    ei_all, _ = hg.build_weighted_hypergraph(_cuda(feats[:nt]), _cuda(pos[:nt]), 1.0, 1.0)
+    assert ei_all.shape[1] == nt * nt
+    with pytest.raises(ValueError):
+        hg.build_weighted_hypergraph(_cuda(feats[:1]), _cuda(pos[:1]), 1.0, 1.0, 1.0)
+
+
+# --------------------------------------------------------------------------------- kNN (A1/A2/A4)
+KNN_SHAPES = [
+    # n, d, k, metric, seed
+    (512, 128, 8, "cosine", 21),
+    (1000, 100, 5, "euclidean", 31),
+    (300, 70, 16, "gaussian", 32),
+    (2500, 256, 16, "gaussian", 33),
+    (4096, 1024, 8, "cosine", 1235),      # BASELINE config C1
+    (129, 64, 32, "euclidean", 34),
+    (257, 192, 1, "cosine", 35),
+]
+
+
+@pytest.mark.parametrize("precision", ["tc", "fp32"])
+@pytest.mark.parametrize("n,d,k,metric,seed", KNN_SHAPES)
+def test_knn_feature_vs_oracle(n, d, k, metric, seed, precision):
+    mode = "cosine" if metric == "cosine" else "gaussian"
+    feats = synth.make_features(n, d, seed, mode)
+    idx, val = ops.knn_feature(_cuda(feats), k, metric, precision=precision)
+    idx, val = idx.cpu().numpy(), val.cpu().numpy()
+    check_knn(idx, feats, k, metric)
+    # values: 1e-5 relative against float64 for the returned neighbours, best first
+    rows = np.arange(n)
+    x = feats.astype(np.float64)
+    for r in rows[:: max(1, n // 64)]:
+        s = _oracle_score(feats, None, metric, 1.0, 0.0, r, idx[r].astype(np.int64))
+        ref = {"euclidean": s, "gaussian": np.exp(-s), "cosine": -s}[metric]
+        np.testing.assert_allclose(val[r], ref, rtol=RTOL, atol=1e-6)
+        assert (np.diff(s) >= -RTOL * max(1.0, np.abs(s).max())).all()
+
+
+def test_knn_gaussian_with_positions():
+    n, d, k = 3000, 128, 16
+    feats, pos = synth.make_slide(n, d, 41, "gaussian")
+    lam_g = 1.0 / 128.0
+    idx, val = ops.knn_feature(_cuda(feats), k, "gaussian", positions=_cuda(pos), lambda_h=1.0, lambda_g=lam_g)
+    idx = idx.cpu().numpy()
+    check_knn(idx, feats, k, "gaussian", pos=pos, lambda_h=1.0, lambda_g=lam_g)
+    K = oracle.combined_similarity(feats[:256], pos[:256], 1.0, lam_g)      # value spot check on a sub-block
+    r = 17
+    inside = idx[r] < 256
+    np.testing.assert_allclose(val[r].cpu().numpy()[inside], K[r, idx[r][inside]], rtol=RTOL)
+
+
+def test_knn_row_range_matches_full():
+    n, d, k = 2000, 128, 8
+    feats = synth.make_features(n, d, 51, "gaussian")
+    f = _cuda(feats)
+    full_i, full_v = ops.knn_feature(f, k, "euclidean")
+    for r0, r1 in [(0, 700), (700, 1301), (1301, 2000), (5, 6)]:
+        pi, pv = ops.knn_feature(f, k, "euclidean", rows=(r0, r1))
+        assert torch.equal(pi, full_i[r0:r1])
+        assert torch.equal(pv, full_v[r0:r1])
+
+
+def test_knn_errors():
+    f = torch.randn(1, 16, device="cuda")
+    with pytest.raises(ValueError):
+        ops.knn_feature(f, 1)                                    # N <= 1, reference similarity_kernel.py:176
+    f = torch.randn(64, 16, device="cuda")
+    with pytest.raises(ValueError):
+        ops.knn_feature(f, 40)                                   # k > 32 on the tensor-core path
+    with pytest.raises(ValueError):
+        ops.knn_feature(f, 4, rows=(10, 5))
+    idx, _ = ops.knn_feature(f[:5], 8, precision="fp32")         # fewer candidates than k -> padded with -1
+    assert (idx[:, 4:] == -1).all() and (idx[:, :4] >= 0).all()
+    idx, _ = ops.knn_feature(f[:5], 8)
+    assert (idx[:, 4:] == -1).all() and (idx[:, :4] >= 0).all()
+
+
+# ------------------------------------------------------------------------------- spatial kNN (A3)
+@pytest.mark.parametrize("n,k,pd", [(500, 8, 2), (5000, 8, 2), (3000, 16, 3), (40, 32, 2)])
+def test_knn_spatial_exact(n, k, pd):
+    pos = synth.make_positions(n, n + k)
+    if pd == 3:
+        pos = np.concatenate([pos, (np.arange(n) % 3)[:, None].astype(np.float32)], 1)
+    idx, d2 = ops.knn_spatial(_cuda(pos), k)
+    ref_idx, ref_d2 = oracle.knn_spatial(pos, k)
+    assert (idx.cpu().numpy() == ref_idx).all()          # grid ties resolved by (d2, index): bit-exact
+    assert (d2.cpu().numpy() == ref_d2.astype(np.float32)).all()
+    pi, pd2 = ops.knn_spatial(_cuda(pos), k, rows=(n // 3, n // 2))
+    assert torch.equal(pi, idx[n // 3: n // 2]) and torch.equal(pd2, d2[n // 3: n // 2])
+
+
+# ------------------------------------------------------------------- edges / weights / CSR (A5/A6)
+KNN_GOLDEN = ["knn_n512_d128_k8", "knn_n768_d256_k5_cliques", "knn_n1024_d1024_k8"]
+
+
+@pytest.mark.parametrize("name", KNN_GOLDEN)
+def test_build_hypergraph_knn_kmeans_vs_reference_golden(golden, name):
+    g = golden(name)
+    n_wsi, n = int(g["n_wsi"]), int(g["n_wsi"]) + int(g["n_tma"])
+    feats = synth.make_features(n, int(g["d"]), int(g["seed"]), str(g["mode"]))
+    ei, w, stats = hg.build_hypergraph_knn_kmeans(
+        _cuda(feats[:n_wsi]), _cuda(feats[n_wsi:]), np.zeros(n_wsi, dtype=np.int64), k=int(g["k"]),
+        num_hyperedges=int(g["num_hyperedges"]), hyperedge_labels=g["labels"], return_csr=True)
+    assert ei.dtype == torch.int64 and w.dtype == torch.float32
+    assert stats["num_edges"] == int(g["num_edges"]) and stats["num_nodes"] == n
+    assert (ei.cpu().numpy() == g["edge_index"]).all()                  # bit-exact incidence
+    np.testing.assert_allclose(w.cpu().numpy(), g["edge_weights"], rtol=RTOL, atol=1e-6)
+    rowptr, col, eid = (t.cpu().numpy() for t in stats["csr"])
+    r_ref, c_ref, e_ref = oracle.csr_from_coo(g["edge_index"], n)
+    assert (rowptr == r_ref).all() and (col == c_ref).all() and (eid == e_ref).all()
+
+
+def test_edges_ragged_inputs():
+    rng = np.random.default_rng(9)
+    n = 777
+    a = rng.integers(-1, n, size=(n, 7)).astype(np.int32)       # -1 = missing neighbour, self loops possible
+    b = rng.integers(0, n, size=(n, 3)).astype(np.int32)
+    labels = rng.integers(-2, 9, size=n).astype(np.int32)
+    ei = ops.build_edges([_cuda(a), _cuda(b)], n, _cuda(labels), 5).cpu().numpy()
+    ref = oracle.edges_from_knn(np.concatenate([a, b], 1), labels, 5)
+    ref = ref[:, ref[0] != ref[1]]
+    assert ei.shape == ref.shape and (ei == ref).all()
+    empty = ops.build_edges([_cuda(np.full((n, 2), -1, np.int32))], n)
+    assert empty.shape == (2, 0)
+    rowptr, col, eid = ops.csr_from_coo(empty, n)
+    assert (rowptr == 0).all() and col.numel() == 0
+    w = ops.edge_weights_cosine(torch.randn(n, 8, device="cuda"), empty)
+    assert w.numel() == 0
+
+
+def test_radix_sort_large_keys():
+    """2^20 random pairs over a 200k-node id space: 36-bit keys, 5 radix passes."""
+    rng = np.random.default_rng(11)
+    n = 200_000
+    a = rng.integers(0, n, size=(n, 5)).astype(np.int32)
+    ei = ops.build_edges([_cuda(a)], n).cpu().numpy()
+    ref = oracle.edges_from_knn(a)
+    ref = ref[:, ref[0] != ref[1]]
+    assert ei.shape == ref.shape and (ei == ref).all()
+    rowptr, col, eid = (t.cpu().numpy() for t in ops.csr_from_coo(_cuda(ei), n))
+    r_ref, c_ref, e_ref = oracle.csr_from_coo(ei, n)
+    assert (rowptr == r_ref).all() and (col == c_ref).all() and (eid == e_ref).all()
+
+
+# ------------------------------------------------------------------------------ full-size properties
+def test_c2_full_size_sampled_rows():
+    """BASELINE config C2 (N=50k x 1024, Gaussian k=16): 512 sampled rows against the float64
+    oracle, plus size-independent properties of the whole result."""
+    n, d, k = 50_000, 1024, 16
+    feats = synth.make_features(n, d, 1236, "gaussian")
+    out = hg.knn_hyperedges(_cuda(feats), k=k, kernel="gaussian", lambda_h=1.0, return_csr=True)
+    idx = out["knn_idx"].cpu().numpy()
+    rows = np.random.default_rng(0).choice(n, 512, replace=False)
+    check_knn(idx[rows], feats, k, "gaussian", rows=rows)
+    val = out["knn_val"].cpu().numpy()
+    assert (np.diff(val, axis=1) <= 0).all()                     # best first
+    assert (idx != np.arange(n)[:, None]).all() and (idx >= 0).all() and (idx < n).all()
+    assert all(len(set(r)) == k for r in idx[:: 97])
+    ei = out["edge_index"].cpu().numpy()
+    assert (ei[0] < ei[1]).all()
+    key = ei[0] * n + ei[1]
+    assert (np.diff(key) > 0).all()                              # sorted and unique
+    ref = oracle.edges_from_knn(idx)
+    assert ei.shape == ref.shape and (ei == ref).all()           # assembly bit-exact given the lists
+    rowptr = out["csr_rowptr"].cpu().numpy()
+    assert rowptr[0] == 0 and rowptr[-1] == 2 * ei.shape[1] and (np.diff(rowptr) >= 0).all()
+    deg = np.bincount(np.concatenate([ei[0], ei[1]]), minlength=n)
+    assert (np.diff(rowptr) == deg).all()
+    w = out["edge_weights"].cpu().numpy()
+    sel = np.random.default_rng(1).choice(ei.shape[1], 2000, replace=False)
+    np.testing.assert_allclose(w[sel], oracle.edge_weights_cosine(feats, ei[:, sel]), rtol=RTOL, atol=1e-6)
