@@ -46,6 +46,12 @@ extern "C" {
 
 int hg_version(void);
 const char* hg_last_error(void);
+/* kernels launched by this library since load (monotonic; bench.py's gpu_launches) */
+int64_t hg_launch_count(void);
+/* in-stream CUDA-event timer around the fused similarity+top-k kernel: enable, run,
+ * then collect the summed duration (ms) and the number of launches it covers */
+int hg_profile_enable(int on);
+int hg_profile_collect(float* ms_total, int* launches);
 
 /* ---- operand preparation -------------------------------------------------
  * Splits FP32 rows into BF16 hi/lo planes (x ~= hi + lo, 16 significant bits)

@@ -14,6 +14,9 @@ namespace hg {
 // ---- error plumbing: no exceptions cross the C ABI -------------------------
 void set_error(const char* fmt, ...);
 const char* get_error();
+void count_launches(int n);              // kernels launched by this library (bench.py gpu_launches)
+void prof_begin(cudaStream_t st);         // optional CUDA-event bracket around the fused kernel
+void prof_end(cudaStream_t st);
 
 #define HG_CHECK_CUDA(expr)                                                          \
     do {                                                                             \

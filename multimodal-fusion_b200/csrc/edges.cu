@@ -219,6 +219,7 @@ extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, in
         const int blocks = int(min64(ceil_div(p.knn_slots, 256), 148 * 16));
         emit_knn_keys_kernel<<<blocks, 256, 0, st>>>(L, n, sentinel, keys);
         HG_CHECK_LAUNCH();
+        count_launches(1);
     }
     if (num_hyperedges > 0 && clique_pairs > 0) {
         uint64_t* lkeys = reinterpret_cast<uint64_t*>(ws + p.off_lkeys);
@@ -240,6 +241,7 @@ extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, in
         expand_cliques_kernel<<<blocks, 256, 0, st>>>(sv, counts, moff, poff, num_hyperedges, n, clique_pairs,
                                                       sentinel, keys + p.knn_slots);
         HG_CHECK_LAUNCH();
+        count_launches(3);
     }
     unsigned long long* d_count = reinterpret_cast<unsigned long long*>(ws + p.off_count);
     uint64_t* sorted = keys;
@@ -253,6 +255,7 @@ extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, in
     write_header_kernel<<<1, 32, 0, st>>>(reinterpret_cast<EdgesHeader*>(ws + p.off_header), d_count,
                                           (unsigned long long)(reinterpret_cast<char*>(uniq) - ws), (unsigned long long)n);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     unsigned long long h_count = 0;
     HG_CHECK_CUDA(cudaMemcpyAsync(&h_count, d_count, 8, cudaMemcpyDeviceToHost, st));
     HG_CHECK_CUDA(cudaStreamSynchronize(st));
@@ -270,5 +273,6 @@ extern "C" int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
     decode_edges_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const EdgesHeader*>(workspace), static_cast<const char*>(workspace), num_edges, edge_index);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }

@@ -124,6 +124,7 @@ extern "C" int hg_edge_weights_cosine(const float* feats, int64_t n, int64_t d,
     const int blocks = int(min64(ceil_div(num_edges, 8), 148 * 8));
     edge_cosine_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(feats, d, edge_index, num_edges, weights);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -160,12 +161,14 @@ extern "C" int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int
     const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 16));
     csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, num_edges, uint64_t(n), keys, vals);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     uint64_t* sk; uint32_t* sv;
     int rc = radix_sort_u64(keys, tmp, vals, vtmp, nnz, bits_for(uint64_t(n) * uint64_t(n)), table, &sk, &sv, st);
     if (rc != HG_OK) return rc;
     csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, nnz, uint64_t(n),
                                                                                          rowptr, col, eid);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -188,6 +191,7 @@ extern "C" int hg_threshold_edges_count(const float* K, int64_t n, float thresho
     const int nt = int(unique_tiles(n * n));
     thr_count_kernel<<<nt, SC_THREADS, 0, st>>>(K, n * n, threshold, tiles);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     int rc = scan_tile_sums(tiles, nt, d_count, st);
     if (rc != HG_OK) return rc;
     unsigned long long h = 0;
@@ -210,5 +214,6 @@ extern "C" int hg_threshold_edges_fill(const float* K, int64_t n, float threshol
     thr_scatter_kernel<<<nt, SC_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(K, n, n * n, threshold, tiles, num_edges,
                                                                                edge_index, edge_weights);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }

@@ -103,7 +103,9 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
     tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
+    prof_begin(st);
     rc = tc_launch(ops, w.n_pad, tp, st);
+    prof_end(st);
     if (rc != HG_OK) return rc;
 
     RerankParams rp{};

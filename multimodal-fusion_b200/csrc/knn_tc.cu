@@ -291,6 +291,7 @@ static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
         knn_tc_kernel<KL, false><<<p.plan.grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
     }
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 

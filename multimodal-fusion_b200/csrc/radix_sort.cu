@@ -151,6 +151,7 @@ int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t*
         else
             rs_scatter_kernel<false><<<num_tiles, RS_THREADS, 0, st>>>(src, nullptr, count, shift, table, num_tiles, dst, nullptr);
         HG_CHECK_LAUNCH();
+        count_launches(3);
         uint64_t* t = src; src = dst; dst = t;
         uint32_t* tv = vsrc; vsrc = vdst; vdst = tv;
     }
@@ -246,6 +247,7 @@ size_t unique_tiles(int64_t count) { return size_t(ceil_div(count, SC_TILE)); }
 int scan_tile_sums(uint32_t* sums, int64_t len, unsigned long long* total_out, cudaStream_t st) {
     scan_sums_kernel<<<1, 1024, 0, st>>>(sums, len, total_out);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -260,6 +262,7 @@ int unique_sorted_u64(const uint64_t* keys, int64_t count, uint64_t sentinel, ui
     scan_sums_kernel<<<1, 1024, 0, st>>>(tile_sums, tiles, count_out);
     unique_scatter_kernel<<<tiles, SC_THREADS, 0, st>>>(keys, count, sentinel, tile_sums, out);
     HG_CHECK_LAUNCH();
+    count_launches(3);
     return HG_OK;
 }
 

@@ -39,6 +39,7 @@ int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64
                      float2* colp, float4* pos4, cudaStream_t st) {
     colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, pos, pos_dim, n, n_pad, metric, colp, pos4);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -170,6 +171,7 @@ int rerank_launch(const RerankParams& p, cudaStream_t st) {
     HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_CAND, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
     rerank_kernel<<<(unsigned)ceil_div(p.n_rows, RR_WARPS), RR_WARPS * 32, 0, st>>>(p);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 

@@ -164,6 +164,7 @@ int launch_dense(const SimArgs& p, int form, cudaStream_t st) {
         else   sim_tile_kernel<MODE_DENSE, HG_FORM_EXPANSION, false, 1><<<grid, 256, 0, st>>>(p);
     }
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -179,6 +180,7 @@ int launch_topk_fp32(const SimArgs& p, cudaStream_t st) {
         else   sim_tile_kernel<MODE_TOPK, HG_FORM_EXPANSION, false, 64><<<grid, 256, 0, st>>>(p);
     }
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 

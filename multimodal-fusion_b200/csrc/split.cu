@@ -83,6 +83,7 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
     else
         split_rows_kernel<false><<<(unsigned)n_pad, 128, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
     HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 

@@ -27,6 +27,9 @@ _pi64 = C.POINTER(C.c_int64)
 SIGNATURES = {
     "hg_version": (_i32, []),
     "hg_last_error": (C.c_char_p, []),
+    "hg_launch_count": (_i64, []),
+    "hg_profile_enable": (_i32, [_i32]),
+    "hg_profile_collect": (_i32, [C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "hg_operand_bytes": (_sz, [_i64, _i64]),
     "hg_split_operands": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "hg_knn_feature_workspace_bytes": (_i32, [_i64, _i64, _i32, _i64, _i64, _psz]),
