@@ -34,17 +34,20 @@ rs_hist_kernel(const uint64_t* __restrict__ keys, int64_t count, int shift, uint
     table[size_t(threadIdx.x) * num_tiles + blockIdx.x] = hist[threadIdx.x];
 }
 
-// Single-CTA exclusive scan of a uint32 table (<= a few 100k entries).
-__global__ void __launch_bounds__(1024)
-rs_scan_table_kernel(uint32_t* __restrict__ table, int64_t len) {
-    __shared__ uint32_t warp_tot[32];
+// Exclusive scan of the digit-major table in two levels: CTA `d` scans row d (one entry per
+// tile) in place and publishes the row total; the scatter kernel turns the 256 row totals into
+// digit bases itself.  256 CTAs instead of one long single-CTA sweep.
+__global__ void __launch_bounds__(256)
+rs_scan_rows_kernel(uint32_t* __restrict__ table, int num_tiles, uint32_t* __restrict__ digit_totals) {
+    __shared__ uint32_t warp_tot[8];
     __shared__ uint32_t carry_s;
+    uint32_t* row = table + size_t(blockIdx.x) * num_tiles;
     if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = 0; base < len; base += 1024) {
-        const int64_t i = base + threadIdx.x;
-        const uint32_t v = (i < len) ? table[i] : 0u;
+    for (int base = 0; base < num_tiles; base += 256) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = (i < num_tiles) ? row[i] : 0u;
         uint32_t x = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -53,29 +56,20 @@ rs_scan_table_kernel(uint32_t* __restrict__ table, int64_t len) {
         }
         if (lane == 31) warp_tot[warp] = x;
         __syncthreads();
-        if (warp == 0) {
-            uint32_t w = warp_tot[lane];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += y;
-            }
-            warp_tot[lane] = w;                       // inclusive over warps
-        }
+        uint32_t pre = carry_s;
+        for (int w = 0; w < warp; ++w) pre += warp_tot[w];
+        if (i < num_tiles) row[i] = pre + x - v;
         __syncthreads();
-        const uint32_t carry = carry_s;
-        const uint32_t pre = (warp ? warp_tot[warp - 1] : 0u) + carry;
-        if (i < len) table[i] = pre + x - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry_s = carry + warp_tot[31];
+        if (threadIdx.x == 255) carry_s = pre + x;
         __syncthreads();
     }
+    if (threadIdx.x == 0) digit_totals[blockIdx.x] = carry_s;
 }
 
 template <bool HAS_VALS>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t count, int shift,
-                  const uint32_t* __restrict__ table, int num_tiles,
+                  const uint32_t* __restrict__ table, const uint32_t* __restrict__ digit_totals, int num_tiles,
                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
     __shared__ uint32_t cnt[RS_WARPS][256];
     __shared__ uint32_t gbase[256];
@@ -115,7 +109,20 @@ rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict_
             cnt[w][dgt] = run;
             run += c;
         }
-        gbase[dgt] = table[size_t(dgt) * num_tiles + blockIdx.x];
+        // digit base = exclusive prefix of the 256 digit totals (8 warp scans + 8 partials)
+        const uint32_t tot = digit_totals[dgt];
+        uint32_t inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += y;
+        }
+        if (lane == 31) gbase[warp] = inc;            // gbase doubles as scratch for the warp totals
+        __syncthreads();
+        uint32_t pre = 0;
+        for (int w = 0; w < warp; ++w) pre += gbase[w];
+        __syncthreads();
+        gbase[dgt] = pre + inc - tot + table[size_t(dgt) * num_tiles + blockIdx.x];
     }
     __syncthreads();
 #pragma unroll
@@ -130,7 +137,7 @@ rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict_
     }
 }
 
-size_t sort_table_entries(int64_t count) { return size_t(256) * size_t(ceil_div(count, RS_TILE)); }
+size_t sort_table_entries(int64_t count) { return size_t(256) * size_t(ceil_div(count, RS_TILE)) + 256; }
 
 // Sorts ascending on bits [0, bits).  Returns (through *sorted_keys / *sorted_vals)
 // which of the two ping-pong buffers holds the result.
@@ -143,13 +150,14 @@ int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t*
     const int num_tiles = int(ceil_div(count, RS_TILE));
     uint64_t* src = keys; uint64_t* dst = keys_tmp;
     uint32_t* vsrc = vals; uint32_t* vdst = vals_tmp;
+    uint32_t* digit_totals = table + size_t(256) * num_tiles;
     for (int shift = 0; shift < bits; shift += 8) {
         rs_hist_kernel<<<num_tiles, RS_THREADS, 0, st>>>(src, count, shift, table, num_tiles);
-        rs_scan_table_kernel<<<1, 1024, 0, st>>>(table, int64_t(256) * num_tiles);
+        rs_scan_rows_kernel<<<256, 256, 0, st>>>(table, num_tiles, digit_totals);
         if (vals)
-            rs_scatter_kernel<true><<<num_tiles, RS_THREADS, 0, st>>>(src, vsrc, count, shift, table, num_tiles, dst, vdst);
+            rs_scatter_kernel<true><<<num_tiles, RS_THREADS, 0, st>>>(src, vsrc, count, shift, table, digit_totals, num_tiles, dst, vdst);
         else
-            rs_scatter_kernel<false><<<num_tiles, RS_THREADS, 0, st>>>(src, nullptr, count, shift, table, num_tiles, dst, nullptr);
+            rs_scatter_kernel<false><<<num_tiles, RS_THREADS, 0, st>>>(src, nullptr, count, shift, table, digit_totals, num_tiles, dst, nullptr);
         HG_CHECK_LAUNCH();
         count_launches(3);
         uint64_t* t = src; src = dst; dst = t;

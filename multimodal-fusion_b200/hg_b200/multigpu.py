@@ -43,13 +43,17 @@ def all_gather_rows(local: torch.Tensor, n: int, group=None) -> torch.Tensor:
     world = dist.get_world_size(group)
     shape = tuple(local.shape[1:])
     sizes = [row_range(n, r, world)[1] - row_range(n, r, world)[0] for r in range(world)]
-    out = torch.empty((n,) + shape, dtype=local.dtype, device=local.device)
-    chunks = list(out.split(sizes, 0))
     if len(set(sizes)) == 1:
+        out = torch.empty((n,) + shape, dtype=local.dtype, device=local.device)
         dist.all_gather_into_tensor(out, local.contiguous(), group=group)
-    else:
-        dist.all_gather(chunks, local.contiguous(), group=group)
-    return out
+        return out
+    # ragged blocks: pad to the largest block (at most one extra row), gather, drop the padding
+    m = max(sizes)
+    padded = torch.zeros((m,) + shape, dtype=local.dtype, device=local.device)
+    padded[: local.shape[0]] = local
+    gathered = torch.empty((world * m,) + shape, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    return torch.cat([gathered[r * m: r * m + sizes[r]] for r in range(world)], 0)
 
 
 def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: int = 16, kernel: str = "gaussian",

@@ -306,3 +306,24 @@ def test_c2_full_size_sampled_rows():
     w = out["edge_weights"].cpu().numpy()
     sel = np.random.default_rng(1).choice(ei.shape[1], 2000, replace=False)
     np.testing.assert_allclose(w[sel], oracle.edge_weights_cosine(feats, ei[:, sel]), rtol=RTOL, atol=1e-6)
+
+
+def test_c3_combined_feature_and_spatial_sampled_rows():
+    """BASELINE config C3 (N=100k x 1536, feature k=16 + spatial-grid k=8): sampled rows vs the oracle."""
+    n, d, k, ks = 100_000, 1536, 16, 8
+    feats, pos = synth.make_slide(n, d, 1237, "gaussian")
+    lam_g = 1.0 / 128.0
+    out = hg.knn_hyperedges(_cuda(feats), _cuda(pos), k=k, kernel="gaussian", lambda_h=1.0, lambda_g=lam_g,
+                            spatial_k=ks, return_csr=True)
+    idx = out["knn_idx"].cpu().numpy()
+    rows = np.random.default_rng(3).choice(n, 384, replace=False)
+    check_knn(idx[rows], feats, k, "gaussian", rows=rows, pos=pos, lambda_h=1.0, lambda_g=lam_g)
+    sidx = out["spatial_idx"].cpu().numpy()
+    ref_sidx, ref_sd2 = oracle.knn_spatial(pos, ks, rows=rows)
+    assert (sidx[rows] == ref_sidx).all()
+    assert (out["spatial_d2"].cpu().numpy()[rows] == ref_sd2.astype(np.float32)).all()
+    ei = out["edge_index"].cpu().numpy()
+    ref = oracle.edges_from_knn(np.concatenate([idx, sidx], 1))
+    assert ei.shape == ref.shape and (ei == ref).all()
+    rowptr = out["csr_rowptr"].cpu().numpy()
+    assert rowptr[-1] == 2 * ei.shape[1]

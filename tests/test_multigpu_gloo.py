@@ -1,0 +1,82 @@
+"""Host-side multi-GPU logic on CPU: world_size-2 gloo processes (no GPU needed).
+The CUDA stages are injected with the oracle so only the sharding / gather plumbing is under test."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle_np as oracle
+from hg_b200 import multigpu, synth
+
+
+def test_shard_slides_lpt_balance():
+    sizes = synth.slide_sizes(512)
+    assert sizes.min() >= 2048 and sizes.max() <= 8192
+    for world in (1, 2, 4, 8):
+        plan = multigpu.shard_slides(sizes, world)
+        flat = sorted(i for p in plan for i in p)
+        assert flat == list(range(512))                       # every slide exactly once
+        load = [sum(int(sizes[i]) ** 2 for i in p) for p in plan]
+        assert max(load) / (sum(load) / world) < 1.01         # LPT: < 1 % imbalance on 512 slides
+
+
+def test_row_range_partition():
+    for n, world in [(250_000, 8), (10, 3), (7, 8), (1, 2)]:
+        edges = [multigpu.row_range(n, r, world) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+        lens = [b - a for a, b in edges]
+        assert max(lens) - min(lens) <= 1
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n, d, k, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        feats = synth.make_features(n, d, 77, "gaussian")
+        r0, r1 = multigpu.row_range(n, rank, world)
+
+        def knn_fn(x, rows):                                   # stands in for ops.knn_feature on this rank's rows
+            idx, val = oracle.knn_feature(x.numpy(), k, "gaussian", rows=np.arange(rows[0], rows[1]))
+            return torch.from_numpy(idx.astype(np.int32)), torch.from_numpy(val.astype(np.float32))
+
+        def assemble_fn(lists, x):
+            ei = oracle.edges_from_knn(lists[0].numpy())
+            return {"edge_index": torch.from_numpy(ei)}
+
+        out = multigpu.knn_hyperedges_row_partitioned(torch.from_numpy(feats[r0:r1]), n, k=k, knn_fn=knn_fn,
+                                                      assemble_fn=assemble_fn)
+        q.put((rank, out["knn_idx"].numpy(), out["edge_index"].numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_row_partitioned_equals_single_process():
+    n, d, k, world = 301, 32, 4, 2                             # odd n: uneven row blocks -> all_gather of ragged chunks
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, d, k, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=100) for _ in range(world)]
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    feats = synth.make_features(n, d, 77, "gaussian")
+    ref_idx, _ = oracle.knn_feature(feats, k, "gaussian")
+    ref_ei = oracle.edges_from_knn(ref_idx)
+    for _, idx, ei in results:
+        assert (idx == ref_idx).all()
+        assert (ei == ref_ei).all()
