@@ -158,6 +158,23 @@ int hg_threshold_edges_fill(const float* K, int64_t n, float threshold, int64_t 
                             const void* workspace, size_t workspace_bytes, void* stream);
 int hg_threshold_workspace_bytes(int64_t n, size_t* bytes);
 
+/* ---- one call per slide: A4 (+A3) -> A5 -> A6 -> CSR ---------------------------------------
+ * The body of build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433) on one stream with
+ * a single synchronisation (the edge count).  Variable-size outputs are caller buffers sized for
+ * `max_edges` >= n*(k+spatial_k)+clique_pairs; they are filled compactly: edge_index as [2, E]
+ * (row 1 starts at offset E), edge_weights [E], csr_col/csr_eid [2E].  csr_* may be NULL (no
+ * CSR), spatial_* may be NULL when spatial_k == 0, labels may be NULL (no cliques). */
+int hg_build_workspace_bytes(int64_t n, int64_t d, int k, int spatial_k, int num_hyperedges,
+                             int64_t clique_pairs, int64_t max_edges, int want_csr, size_t* bytes);
+int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                            int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                            const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                            int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                            int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                            int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                            int64_t* num_edges_out_host,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,106 @@
+// One-call per-slide build: feature kNN (+ spatial kNN) -> edge assembly -> cosine weights ->
+// CSR.  It only composes the stage entry points of this library on one stream, so a slide costs
+// one host call and one stream synchronisation (the edge count) instead of a dozen round trips
+// through the host language -- what matters for batches of small slides (BASELINE config C4).
+// Mirrors the body of the reference's build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433).
+#include "common.cuh"
+
+namespace hg {
+static size_t al1k(size_t b) { return (b + 1023) & ~size_t(1023); }
+
+struct BuildWs { size_t off_knn, off_spatial, off_edges, off_csr, bytes; size_t knn, spatial, edges, csr; };
+
+static int plan_build(int64_t n, int64_t d, int k, int spatial_k, int num_hyperedges, int64_t clique_pairs,
+                      int64_t max_edges, bool want_csr, BuildWs* w) {
+    int rc = hg_knn_feature_workspace_bytes(n, d, k, 0, n, &w->knn);
+    if (rc != HG_OK) return rc;
+    w->spatial = 0;
+    if (spatial_k > 0) {
+        rc = hg_knn_spatial_workspace_bytes(n, spatial_k, 0, n, &w->spatial);
+        if (rc != HG_OK) return rc;
+    }
+    rc = hg_edges_workspace_bytes(n, n * int64_t(k) + n * int64_t(spatial_k), num_hyperedges, clique_pairs, &w->edges);
+    if (rc != HG_OK) return rc;
+    w->csr = 0;
+    if (want_csr) {
+        rc = hg_csr_workspace_bytes(n, max_edges, &w->csr);
+        if (rc != HG_OK) return rc;
+    }
+    // the kNN scratch (operand planes, candidate lists) is dead once the lists exist: the edge
+    // and CSR stages reuse the same bytes
+    w->off_knn = 0;
+    w->off_spatial = al1k(w->knn);
+    const size_t stage1 = w->off_spatial + al1k(w->spatial);
+    w->off_edges = 0;
+    w->off_csr = al1k(w->edges);
+    const size_t stage2 = w->off_csr + al1k(w->csr);
+    w->bytes = stage1 > stage2 ? stage1 : stage2;
+    return HG_OK;
+}
+}  // namespace hg
+
+using namespace hg;
+
+extern "C" int hg_build_workspace_bytes(int64_t n, int64_t d, int k, int spatial_k, int num_hyperedges,
+                                        int64_t clique_pairs, int64_t max_edges, int want_csr, size_t* bytes) {
+    HG_REQUIRE(bytes && max_edges >= 0, HG_ERR_BAD_ARG, "hg_build_workspace_bytes: bad argument");
+    BuildWs w{};
+    int rc = plan_build(n, d, k, spatial_k, num_hyperedges, clique_pairs, max_edges, want_csr != 0, &w);
+    if (rc != HG_OK) return rc;
+    *bytes = w.bytes;
+    return HG_OK;
+}
+
+extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                       int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                       const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                                       int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                                       int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                                       int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                                       int64_t* num_edges_out_host,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(feats && knn_idx && knn_val && edge_index && edge_weights && num_edges_out_host, HG_ERR_BAD_ARG,
+               "hg_build_knn_hypergraph: null buffer");
+    HG_REQUIRE(spatial_k == 0 || (pos && spatial_idx && spatial_d2), HG_ERR_BAD_ARG,
+               "hg_build_knn_hypergraph: spatial_k > 0 needs positions and spatial output buffers");
+    const bool want_csr = csr_rowptr != nullptr;
+    HG_REQUIRE(!want_csr || (csr_col && csr_eid), HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: incomplete CSR buffers");
+    if (labels == nullptr) { num_hyperedges = 0; clique_pairs = 0; }
+    const int64_t bound = n * int64_t(k) + n * int64_t(spatial_k) + clique_pairs;
+    HG_REQUIRE(max_edges >= bound, HG_ERR_BAD_ARG,
+               "hg_build_knn_hypergraph: max_edges %lld below the bound n*(k+spatial_k)+clique_pairs = %lld",
+               (long long)max_edges, (long long)bound);
+    BuildWs w{};
+    int rc = plan_build(n, d, k, spatial_k, num_hyperedges, clique_pairs, max_edges, want_csr, &w);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(workspace && workspace_bytes >= w.bytes, HG_ERR_WORKSPACE,
+               "hg_build_knn_hypergraph: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
+    char* ws = static_cast<char*>(workspace);
+
+    rc = hg_knn_feature(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, 0, n, 1, 0, knn_idx, knn_val,
+                        ws + w.off_knn, w.knn, stream);
+    if (rc != HG_OK) return rc;
+    const int32_t* lists[2] = {knn_idx, nullptr};
+    int ks[2] = {k, 0};
+    int num_lists = 1;
+    if (spatial_k > 0) {
+        rc = hg_knn_spatial(pos, n, pos_dim, spatial_k, 0, n, spatial_idx, spatial_d2, ws + w.off_spatial, w.spatial,
+                            stream);
+        if (rc != HG_OK) return rc;
+        lists[1] = spatial_idx; ks[1] = spatial_k; num_lists = 2;
+    }
+    rc = hg_edges_count(lists, ks, num_lists, n, labels, num_hyperedges, clique_pairs, num_edges_out_host,
+                        ws + w.off_edges, w.edges, stream);
+    if (rc != HG_OK) return rc;
+    const int64_t e = *num_edges_out_host;
+    HG_REQUIRE(e <= max_edges, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: %lld edges exceed max_edges", (long long)e);
+    rc = hg_edges_fill(e, edge_index, ws + w.off_edges, w.edges, stream);
+    if (rc != HG_OK) return rc;
+    rc = hg_edge_weights_cosine(feats, n, d, edge_index, e, edge_weights, stream);
+    if (rc != HG_OK) return rc;
+    if (want_csr) {
+        rc = hg_csr_from_coo(edge_index, e, n, csr_rowptr, csr_col, csr_eid, ws + w.off_csr, w.csr, stream);
+        if (rc != HG_OK) return rc;
+    }
+    return HG_OK;
+}

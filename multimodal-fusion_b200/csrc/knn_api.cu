@@ -13,9 +13,9 @@ struct KnnWs {
 
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
     KnnWs w{};
-    w.plan = tc_make_plan(n, r1 - r0, k);
     w.n_pad = ops_rows(n);
     w.d_pad = ops_cols(d);
+    w.plan = tc_make_plan(n, r1 - r0, k, w.d_pad);
     size_t off = 0;
     auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
     w.off_ops = take(size_t(2) * w.n_pad * w.d_pad * 2);

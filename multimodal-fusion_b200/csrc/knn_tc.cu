@@ -48,6 +48,21 @@ struct TcSmem {                       // lives after the (1024-byte aligned) sta
 };
 constexpr size_t TC_SMEM_BYTES = 1024 + size_t(TC_STAGES) * TC_STAGE_BYTES + sizeof(TcSmem);
 
+// Unit order (see the header comment): row blocks are taken in chunks of rc; inside a chunk the
+// units run split-group-major, then split, then row block, so any 148 consecutive units cover
+// about rc row blocks x cc column splits.
+__device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, int& split) {
+    const int per_chunk = pl.rc * pl.splits;
+    const int g = u / per_chunk;
+    const int rows_here = min(pl.rc, pl.num_rb - g * pl.rc);
+    int rem = u - g * per_chunk;
+    const int h = rem / (rows_here * pl.cc);
+    rem -= h * rows_here * pl.cc;
+    const int c = rem / rows_here;
+    rb = g * pl.rc + (rem - c * rows_here);
+    split = h * pl.cc + c;
+}
+
 template <int KL, bool HAS_POS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -91,7 +106,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         if (lane == 0) {
             uint32_t it = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x) {
-                const int split = u / p.plan.num_rb, rb = u % p.plan.num_rb;
+                int split, rb;
+                decode_unit(p.plan, u, rb, split);
                 const int row0 = int(p.row_begin) + rb * TC_BM;
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
@@ -115,7 +131,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM, TC_BN);
             uint32_t it = 0, tile = 0;
             for (int u = blockIdx.x; u < units; u += gridDim.x) {
-                const int split = u / p.plan.num_rb;
+                int split, rb;
+                decode_unit(p.plan, u, rb, split);
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct, ++tile) {
@@ -153,7 +170,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         const uint32_t lane_base = uint32_t(quarter * 32) << 16;
         uint32_t tile = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
-            const int split = u / p.plan.num_rb, rb = u % p.plan.num_rb;
+            int split, rb;
+            decode_unit(p.plan, u, rb, split);
             const int64_t row0 = p.row_begin + int64_t(rb) * TC_BM;
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = split * p.plan.ct_per_split;
@@ -230,25 +248,35 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 }
 
 // ---------------------------------------------------------------------------------------------
-TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k) {
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     TcPlan pl{};
     pl.n_rows = n_rows;
     pl.num_rb = int(ceil_div(n_rows, TC_BM));
     pl.num_ct = int(ceil_div(n, TC_BN));
     // list length: k plus slack for the exact re-rank, in the register-array sizes compiled
     pl.kl = (k + 4 <= 8) ? 8 : (k + 4 <= 16) ? 16 : (k + 8 <= 24) ? 24 : 32;
-    // column splits: fewest that fill the machine and waste < 6% of the last round
-    int best = 1;
-    double best_eff = 0.0;
-    for (int s = 1; s <= TC_MAX_SPLITS && s <= pl.num_ct; ++s) {
-        const int64_t units = int64_t(pl.num_rb) * s;
-        const double eff = double(units) / double(ceil_div(units, kNumSMs) * kNumSMs);
-        if (eff > best_eff + 0.02) { best_eff = eff; best = s; }
-        if (eff >= 0.94) break;
+    // Concurrency shape rc x cc = 148: the A row blocks of the CTAs running together must stay
+    // L2-resident while B streams through (A block = 128 rows x d_pad x (hi + lo)); keep them
+    // under ~40 MB of the 126 MB L2.  Then the fewest column splits (a multiple of cc) whose
+    // last round wastes the least.
+    const int64_t a_block = int64_t(TC_BM) * d_pad * 4;
+    const int64_t rc_cap = (int64_t(40) << 20) / a_block;
+    int best_cc = 4, best_s = 4;
+    double best_eff = -1.0;
+    for (int cc = 1; cc <= 4; cc *= 2) {
+        const int rc = kNumSMs / cc;
+        if (rc > rc_cap && cc < 4) continue;
+        for (int s = cc; s <= TC_MAX_SPLITS; s += cc) {
+            if (s > pl.num_ct && s > cc) break;
+            const int64_t units = int64_t(pl.num_rb) * s;
+            const double eff = double(units) / double(ceil_div(units, kNumSMs) * kNumSMs);
+            if (eff > best_eff + 0.015) { best_eff = eff; best_cc = cc; best_s = s; }
+        }
     }
-    pl.splits = best;
-    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
-    pl.splits = int(ceil_div(pl.num_ct, pl.ct_per_split));
+    pl.cc = best_cc;
+    pl.rc = kNumSMs / best_cc;
+    pl.splits = best_s;
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));     // trailing splits may be empty
     pl.grid = int(min64(kNumSMs, int64_t(pl.num_rb) * pl.splits));
     return pl;
 }

@@ -13,7 +13,9 @@ struct TcPlan {
     int64_t n_rows;             // row_end - row_begin
     int num_rb;                 // ceil(n_rows / 128)
     int num_ct;                 // ceil(n / 256)
-    int splits;                 // column splits S (partial lists per row)
+    int splits;                 // column splits S (partial lists per row), a multiple of cc
+    int rc;                     // row blocks per chunk: CTAs running together cover rc row blocks ...
+    int cc;                     // ... x cc column splits (rc * cc = 148): bounds the L2 working set of A
     int ct_per_split;
     int kl;                     // list length kept per (row, split): 8 / 16 / 24 / 32
     int grid;                   // CTAs launched
@@ -31,7 +33,7 @@ struct TcParams {
     int32_t* part_idx;
 };
 
-TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k);
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad);
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
 
 struct RerankParams {

@@ -188,3 +188,60 @@ def threshold_edges(K: torch.Tensor, threshold: float):
         L.check(lib.hg_threshold_edges_fill(L.ptr(Kc), n, float(threshold), e.value, L.ptr(ei), L.ptr(w),
                                             L.ptr(ws), nbytes, st))
     return ei, w
+
+
+# ------------------------------------------------------------------ one call per slide
+def build_knn_hypergraph(features: torch.Tensor, k: int, metric: str = "euclidean",
+                         positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0, lambda_g: float = 0.0,
+                         spatial_k: int = 0, labels: Optional[torch.Tensor] = None, num_hyperedges: int = 0,
+                         return_csr: bool = False, device=None) -> dict:
+    """hg_build_knn_hypergraph: kNN lists, edge_index, weights (and CSR) of one slide with a single
+    host call and a single stream synchronisation."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    n, d = x.shape
+    if n <= 1:
+        raise ValueError(f"Number of nodes must be greater than 1, got N={n}.")
+    pos = L.f32c(positions, dev) if positions is not None else None
+    if pos is None:
+        spatial_k = 0
+    out = {}
+    with torch.cuda.device(dev):
+        st = L.stream_ptr(dev)
+        lab, pairs = None, C.c_int64(0)
+        if labels is not None and num_hyperedges > 0:
+            lab = torch.as_tensor(labels).to(device=dev, dtype=torch.int32).contiguous()
+            if lab.numel() != n:
+                raise ValueError("labels must have n entries")
+            L.check(lib.hg_clique_pairs(L.ptr(lab), n, num_hyperedges, C.byref(pairs), st))
+        else:
+            num_hyperedges = 0
+        max_e = n * (k + spatial_k) + pairs.value
+        knn_idx = torch.empty((n, k), dtype=torch.int32, device=dev)
+        knn_val = torch.empty((n, k), dtype=torch.float32, device=dev)
+        sidx = torch.empty((n, spatial_k), dtype=torch.int32, device=dev) if spatial_k else None
+        sd2 = torch.empty((n, spatial_k), dtype=torch.float32, device=dev) if spatial_k else None
+        ei_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev)
+        w_buf = torch.empty(max_e, dtype=torch.float32, device=dev)
+        rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev) if return_csr else None
+        col_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None
+        eid_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None
+        nbytes = _size(lib.hg_build_workspace_bytes, n, d, k, spatial_k, num_hyperedges, pairs.value, max_e,
+                       int(return_csr))
+        ws = L.Workspace.get(dev, nbytes)
+        e = C.c_int64(0)
+        L.check(lib.hg_build_knn_hypergraph(
+            L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1], L.METRIC[metric], float(lambda_h),
+            float(lambda_g), k, spatial_k, L.ptr(lab), num_hyperedges, pairs.value,
+            L.ptr(knn_idx), L.ptr(knn_val), L.ptr(sidx), L.ptr(sd2), max_e, L.ptr(ei_buf), L.ptr(w_buf),
+            L.ptr(rowptr), L.ptr(col_buf), L.ptr(eid_buf), C.byref(e), L.ptr(ws), nbytes, st))
+    ne = e.value
+    out["knn_idx"], out["knn_val"] = knn_idx, knn_val
+    if spatial_k:
+        out["spatial_idx"], out["spatial_d2"] = sidx, sd2
+    out["edge_index"] = ei_buf[: 2 * ne].view(2, ne)
+    out["edge_weights"] = w_buf[:ne]
+    if return_csr:
+        out["csr_rowptr"], out["csr_col"], out["csr_eid"] = rowptr, col_buf[: 2 * ne], eid_buf[: 2 * ne]
+    return out

@@ -218,11 +218,19 @@ def build_hypergraph_knn_kmeans(wsi_features: torch.Tensor, tma_features: torch.
     dev = _device(device, wsi_features)
     allf = torch.cat([L.f32c(wsi_features, dev), L.f32c(tma_features, dev)], 0)
     n = allf.shape[0]
-    idx, _ = ops.knn_feature(allf, k, "euclidean", device=dev)                  # reference :379-388
     if hyperedge_labels is None:
         hyperedge_labels = _kmeans(num_hyperedges).fit_predict(allf.cpu().numpy())   # reference :391-392
-    edge_index = ops.build_edges([idx], n, torch.as_tensor(np.asarray(hyperedge_labels)), num_hyperedges, device=dev)
-    edge_weights = ops.edge_weights_cosine(allf, edge_index)                    # reference :413-422
+    if k <= 32:
+        # kNN (reference :379-388) + cliques + de-dup (:394-410) + weights (:413-422): one C call
+        built = ops.build_knn_hypergraph(allf, k, "euclidean", labels=torch.as_tensor(np.asarray(hyperedge_labels)),
+                                         num_hyperedges=num_hyperedges, return_csr=return_csr, device=dev)
+        edge_index, edge_weights = built["edge_index"], built["edge_weights"]
+        csr = (built["csr_rowptr"], built["csr_col"], built["csr_eid"]) if return_csr else None
+    else:
+        idx, _ = ops.knn_feature(allf, k, "euclidean", precision="fp32", device=dev)
+        edge_index = ops.build_edges([idx], n, torch.as_tensor(np.asarray(hyperedge_labels)), num_hyperedges, device=dev)
+        edge_weights = ops.edge_weights_cosine(allf, edge_index)
+        csr = ops.csr_from_coo(edge_index, n) if return_csr else None
     stats = {
         "num_nodes": n,
         "num_wsi_super_patches": int(wsi_features.shape[0]),
@@ -232,7 +240,7 @@ def build_hypergraph_knn_kmeans(wsi_features: torch.Tensor, tma_features: torch.
         "k": k,
     }
     if return_csr:
-        stats["csr"] = ops.csr_from_coo(edge_index, n)
+        stats["csr"] = csr
     return edge_index, edge_weights, stats
 
 
