@@ -247,17 +247,17 @@ def run_ours(args):
 
     # the same through the dataset-loop API (hg_b200.pipeline): slide i+1's H2D and slide i-1's D2H
     # overlap slide i's build on separate streams; every step still copies its inputs and outputs
-    from hg_b200.pipeline import build_many
+    from hg_b200.pipeline import SlidePipeline, build_many
+    pipe = SlidePipeline(dev, keys=keys, k=k, kernel=w["kernel"], lambda_h=w["lambda_h"], return_csr=True)
 
     def e2e_pipelined(steps):
         got = 0
-        for res in build_many((x_host for _ in range(steps)), device=dev, keys=keys, k=k, kernel=w["kernel"],
-                              lambda_h=w["lambda_h"], return_csr=True):
+        for res in build_many((x_host for _ in range(steps)), pipeline=pipe):
             got += int(res["edge_index"].shape[1] == num_edges)
         torch.cuda.synchronize()
         assert got == steps, "pipelined build returned a different edge count"
 
-    e2e_pipelined(3)
+    e2e_pipelined(4)
     barrier()
     t0 = time.perf_counter()
     e2e_pipelined(args.steps)

@@ -110,10 +110,12 @@ class SlidePipeline:
             yield host
 
 
-def build_many(slides: Iterable, device=None, **build_kwargs) -> Iterator[dict]:
+def build_many(slides: Iterable, device=None, pipeline: Optional[SlidePipeline] = None, **build_kwargs) -> Iterator[dict]:
     """slides: iterable of `features` or `(features, positions)` host tensors (pinned memory makes
-    the H2D asynchronous).  Yields one result dict (pinned host tensors) per slide, in order."""
-    pipe = SlidePipeline(device, **build_kwargs)
+    the H2D asynchronous).  Yields one result dict (pinned host tensors) per slide, in order.
+    Pass a long-lived `pipeline` to keep its streams, device staging and pinned buffers warm
+    across calls (a fresh pipeline pays cudaMalloc / cudaHostAlloc on its first slides)."""
+    pipe = pipeline if pipeline is not None else SlidePipeline(device, **build_kwargs)
     for item in slides:
         feats, pos = item if isinstance(item, (tuple, list)) else (item, None)
         pipe.submit(feats, pos)

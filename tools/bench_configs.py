@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "multimodal-fusion_b200"))
 import hg_b200                                             # noqa: E402
 from hg_b200 import _lib, multigpu, synth                  # noqa: E402
-from hg_b200.pipeline import build_many                    # noqa: E402
+from hg_b200.pipeline import SlidePipeline, build_many     # noqa: E402
 
 
 def main():
@@ -106,10 +106,14 @@ def main():
                 for i in mine:
                     hg_b200.knn_hyperedges(dpools[i % 4][: int(sizes[i])], **kw)
 
+            pipe = SlidePipeline(dev, **kw)
+
             def from_host():
-                for _ in build_many((pools[i % 4][: int(sizes[i])] for i in mine), device=dev, **kw):
+                for _ in build_many((pools[i % 4][: int(sizes[i])] for i in mine), pipeline=pipe):
                     pass
                 torch.cuda.synchronize()
+
+            from_host()                                    # warm the pipeline's buffers
 
             ms, kms = timed(resident, 1, warmup=1)
             sync()
