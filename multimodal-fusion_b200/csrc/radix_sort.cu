@@ -2,88 +2,78 @@
 // scan, and adjacent-unique compaction -- the building blocks of edge assembly
 // (reference preprocess_hypergraph.py:403 `set(tuple(sorted(edge)))`).
 //
-// Per 8-bit pass: (1) per-tile digit histogram -> table[digit][tile],
-// (2) exclusive scan of the table, (3) stable scatter.  Stability inside a tile
-// comes from warp-synchronous ranking: each warp owns a contiguous run of the
-// tile, ranks its keys digit by digit with __match_any_sync + popc, and the
-// per-warp digit totals are prefix-summed across warps.
-// HBM-bound: each pass reads the keys twice and writes them once.
+// "Onesweep" organisation: one kernel histograms every digit position up front
+// (digit totals do not depend on the order of the keys), then ONE kernel per 8-bit
+// pass ranks and scatters.  A tile learns how many keys of each digit precede it
+// from its predecessors through a chained look-back on per-(tile, digit) status
+// words (aggregate -> inclusive prefix), so there is no separate scan kernel and
+// the keys are read once per pass.  Stability inside a tile comes from
+// warp-synchronous ranking: each warp owns a contiguous run of the tile, ranks its
+// keys with __match_any_sync + popc, and per-warp digit totals are prefix-summed.
+// HBM-bound: (1 + passes) reads and `passes` writes of the key array.
 #include "common.cuh"
 #include "sort_scan.cuh"
 
 namespace hg {
 
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;   // 4096 keys per CTA
 constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_MAX_PASSES = 8;
+constexpr int RS_SMALL_ITEMS = 4;      // 1024-key tiles: more CTAs when a slide has few edges
+constexpr int RS_LARGE_ITEMS = 16;     // 4096-key tiles
+constexpr int64_t RS_SMALL_COUNT = int64_t(1) << 19;
+constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_PREFIX = 2u << 30, RS_VALUE_MASK = (1u << 30) - 1u;
 
+static int rs_items_for(int64_t count) { return count <= RS_SMALL_COUNT ? RS_SMALL_ITEMS : RS_LARGE_ITEMS; }
+static int rs_tiles_for(int64_t count) { return int(ceil_div(count, int64_t(RS_THREADS) * rs_items_for(count))); }
+
+// hist[pass][digit] += occurrences, for every pass at once
 __global__ void __launch_bounds__(RS_THREADS)
-rs_hist_kernel(const uint64_t* __restrict__ keys, int64_t count, int shift, uint32_t* __restrict__ table,
-               int num_tiles) {
-    __shared__ uint32_t hist[256];
-    hist[threadIdx.x] = 0;
+rs_global_hist_kernel(const uint64_t* __restrict__ keys, int64_t count, int passes, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t h[RS_MAX_PASSES][256];
+    for (int p = 0; p < passes; ++p) h[p][threadIdx.x] = 0;
     __syncthreads();
-    const int64_t base = int64_t(blockIdx.x) * RS_TILE;
-#pragma unroll 4
-    for (int it = 0; it < RS_ITEMS; ++it) {
-        const int64_t i = base + it * RS_THREADS + threadIdx.x;
-        if (i < count) atomicAdd(&hist[(keys[i] >> shift) & 255u], 1u);
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += int64_t(gridDim.x) * blockDim.x) {
+        const uint64_t key = keys[i];
+        for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(key >> (8 * p)) & 255u], 1u);
     }
     __syncthreads();
-    table[size_t(threadIdx.x) * num_tiles + blockIdx.x] = hist[threadIdx.x];
+    for (int p = 0; p < passes; ++p)
+        if (h[p][threadIdx.x]) atomicAdd(&hist[p * 256 + threadIdx.x], h[p][threadIdx.x]);
 }
 
-// Exclusive scan of the digit-major table in two levels: CTA `d` scans row d (one entry per
-// tile) in place and publishes the row total; the scatter kernel turns the 256 row totals into
-// digit bases itself.  256 CTAs instead of one long single-CTA sweep.
-__global__ void __launch_bounds__(256)
-rs_scan_rows_kernel(uint32_t* __restrict__ table, int num_tiles, uint32_t* __restrict__ digit_totals) {
-    __shared__ uint32_t warp_tot[8];
-    __shared__ uint32_t carry_s;
-    uint32_t* row = table + size_t(blockIdx.x) * num_tiles;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < num_tiles; base += 256) {
-        const int i = base + threadIdx.x;
-        const uint32_t v = (i < num_tiles) ? row[i] : 0u;
-        uint32_t x = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
-        }
-        if (lane == 31) warp_tot[warp] = x;
-        __syncthreads();
-        uint32_t pre = carry_s;
-        for (int w = 0; w < warp; ++w) pre += warp_tot[w];
-        if (i < num_tiles) row[i] = pre + x - v;
-        __syncthreads();
-        if (threadIdx.x == 255) carry_s = pre + x;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) digit_totals[blockIdx.x] = carry_s;
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <bool HAS_VALS>
+template <bool HAS_VALS, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t count, int shift,
-                  const uint32_t* __restrict__ table, const uint32_t* __restrict__ digit_totals, int num_tiles,
-                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
+rs_onesweep_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t count, int shift,
+                   const uint32_t* __restrict__ digit_hist,   // [256] totals of this pass
+                   uint32_t* __restrict__ status,             // [tiles][256], zeroed; status[tiles*256] = tile ticket
+                   int num_tiles, uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
     __shared__ uint32_t cnt[RS_WARPS][256];
     __shared__ uint32_t gbase[256];
+    __shared__ uint32_t tile_s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // tickets are handed out in launch order, so every predecessor tile is already running
+    if (threadIdx.x == 0) tile_s = atomicAdd(status + size_t(num_tiles) * 256, 1u);
     for (int w = 0; w < RS_WARPS; ++w) cnt[w][threadIdx.x] = 0;
     __syncthreads();
+    const uint32_t tile = tile_s;
 
-    // warp `warp` owns keys [base + warp*512, +512) in (it, lane) order
-    const int64_t wbase = int64_t(blockIdx.x) * RS_TILE + int64_t(warp) * (32 * RS_ITEMS);
-    uint64_t key[RS_ITEMS];
-    uint32_t rank[RS_ITEMS];
+    // warp `warp` owns keys [tile*TILE + warp*32*ITEMS, +32*ITEMS) in (it, lane) order
+    const int64_t wbase = int64_t(tile) * (RS_THREADS * ITEMS) + int64_t(warp) * (32 * ITEMS);
+    uint64_t key[ITEMS];
+    uint32_t rank[ITEMS];
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int it = 0; it < RS_ITEMS; ++it) {
+    for (int it = 0; it < ITEMS; ++it) {
         const int64_t i = wbase + it * 32 + lane;
         const bool ok = i < count;
         key[it] = ok ? keys[i] : ~0ull;
@@ -100,17 +90,32 @@ rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict_
         __syncwarp();
     }
     __syncthreads();
-    {   // thread t = digit t: exclusive prefix over warps + global base of (digit, tile)
+    {   // thread t = digit t
         const int dgt = threadIdx.x;
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; ++w) {
             const uint32_t c = cnt[w][dgt];
-            cnt[w][dgt] = run;
+            cnt[w][dgt] = run;                        // exclusive prefix over the warps of this tile
             run += c;
         }
+        uint32_t* my = status + size_t(tile) * 256 + dgt;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            st_volatile_u32(my, RS_FLAG_PREFIX | run);
+        } else {
+            st_volatile_u32(my, RS_FLAG_AGG | run);
+            for (int t = int(tile) - 1; t >= 0; --t) {            // chained look-back
+                const uint32_t* q = status + size_t(t) * 256 + dgt;
+                uint32_t s = ld_volatile_u32(q);
+                while ((s & ~RS_VALUE_MASK) == 0u) { __nanosleep(20); s = ld_volatile_u32(q); }
+                excl += s & RS_VALUE_MASK;
+                if (s & RS_FLAG_PREFIX) break;
+            }
+            st_volatile_u32(my, RS_FLAG_PREFIX | (excl + run));
+        }
         // digit base = exclusive prefix of the 256 digit totals (8 warp scans + 8 partials)
-        const uint32_t tot = digit_totals[dgt];
+        const uint32_t tot = digit_hist[dgt];
         uint32_t inc = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -122,11 +127,11 @@ rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict_
         uint32_t pre = 0;
         for (int w = 0; w < warp; ++w) pre += gbase[w];
         __syncthreads();
-        gbase[dgt] = pre + inc - tot + table[size_t(dgt) * num_tiles + blockIdx.x];
+        gbase[dgt] = pre + inc - tot + excl;
     }
     __syncthreads();
 #pragma unroll
-    for (int it = 0; it < RS_ITEMS; ++it) {
+    for (int it = 0; it < ITEMS; ++it) {
         const int64_t i = wbase + it * 32 + lane;
         if (i < count) {
             const uint32_t dgt = uint32_t((key[it] >> shift) & 255u);
@@ -137,7 +142,21 @@ rs_scatter_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict_
     }
 }
 
-size_t sort_table_entries(int64_t count) { return size_t(256) * size_t(ceil_div(count, RS_TILE)) + 256; }
+// uint32 scratch entries: per-pass digit totals + one status array (tiles x 256) + the ticket
+size_t sort_table_entries(int64_t count) {
+    return size_t(RS_MAX_PASSES) * 256 + size_t(rs_tiles_for(count)) * 256 + 64;
+}
+
+template <bool HAS_VALS>
+static void launch_onesweep(int items, int tiles, const uint64_t* src, const uint32_t* vsrc, int64_t count, int shift,
+                            const uint32_t* hist, uint32_t* status, uint64_t* dst, uint32_t* vdst, cudaStream_t st) {
+    if (items == RS_SMALL_ITEMS)
+        rs_onesweep_kernel<HAS_VALS, RS_SMALL_ITEMS><<<tiles, RS_THREADS, 0, st>>>(src, vsrc, count, shift, hist, status,
+                                                                                   tiles, dst, vdst);
+    else
+        rs_onesweep_kernel<HAS_VALS, RS_LARGE_ITEMS><<<tiles, RS_THREADS, 0, st>>>(src, vsrc, count, shift, hist, status,
+                                                                                   tiles, dst, vdst);
+}
 
 // Sorts ascending on bits [0, bits).  Returns (through *sorted_keys / *sorted_vals)
 // which of the two ping-pong buffers holds the result.
@@ -146,20 +165,25 @@ int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t*
     *sorted_keys = keys;
     if (sorted_vals) *sorted_vals = vals;
     if (count <= 1) return HG_OK;
-    HG_REQUIRE(count < (int64_t(1) << 32), HG_ERR_UNSUPPORTED, "radix sort: more than 2^32 keys");
-    const int num_tiles = int(ceil_div(count, RS_TILE));
+    HG_REQUIRE(count < (int64_t(1) << 30), HG_ERR_UNSUPPORTED, "radix sort: more than 2^30 keys");
+    const int passes = (bits + 7) / 8;
+    HG_REQUIRE(passes <= RS_MAX_PASSES, HG_ERR_BAD_ARG, "radix sort: bad bit count %d", bits);
+    const int items = rs_items_for(count), tiles = rs_tiles_for(count);
+    uint32_t* hist = table;
+    uint32_t* status = table + size_t(RS_MAX_PASSES) * 256;
+    const size_t status_bytes = (size_t(tiles) * 256 + 1) * sizeof(uint32_t);
+    HG_CHECK_CUDA(cudaMemsetAsync(hist, 0, size_t(RS_MAX_PASSES) * 256 * sizeof(uint32_t), st));
+    const int hist_blocks = int(min64(ceil_div(count, 256 * 8), 148 * 4));
+    rs_global_hist_kernel<<<hist_blocks, RS_THREADS, 0, st>>>(keys, count, passes, hist);
+    count_launches(1);
     uint64_t* src = keys; uint64_t* dst = keys_tmp;
     uint32_t* vsrc = vals; uint32_t* vdst = vals_tmp;
-    uint32_t* digit_totals = table + size_t(256) * num_tiles;
-    for (int shift = 0; shift < bits; shift += 8) {
-        rs_hist_kernel<<<num_tiles, RS_THREADS, 0, st>>>(src, count, shift, table, num_tiles);
-        rs_scan_rows_kernel<<<256, 256, 0, st>>>(table, num_tiles, digit_totals);
-        if (vals)
-            rs_scatter_kernel<true><<<num_tiles, RS_THREADS, 0, st>>>(src, vsrc, count, shift, table, digit_totals, num_tiles, dst, vdst);
-        else
-            rs_scatter_kernel<false><<<num_tiles, RS_THREADS, 0, st>>>(src, nullptr, count, shift, table, digit_totals, num_tiles, dst, nullptr);
+    for (int p = 0; p < passes; ++p) {
+        HG_CHECK_CUDA(cudaMemsetAsync(status, 0, status_bytes, st));
+        if (vals) launch_onesweep<true>(items, tiles, src, vsrc, count, 8 * p, hist + p * 256, status, dst, vdst, st);
+        else      launch_onesweep<false>(items, tiles, src, nullptr, count, 8 * p, hist + p * 256, status, dst, nullptr, st);
         HG_CHECK_LAUNCH();
-        count_launches(3);
+        count_launches(1);
         uint64_t* t = src; src = dst; dst = t;
         uint32_t* tv = vsrc; vsrc = vdst; vdst = tv;
     }
@@ -167,6 +191,7 @@ int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t*
     if (sorted_vals) *sorted_vals = vsrc;
     return HG_OK;
 }
+
 
 // ---- device-wide exclusive scan of uint32 -> uint64 totals --------------------------
 // flags[i] = 1 where keys[i] starts a new run; per-tile totals -> tile_sums

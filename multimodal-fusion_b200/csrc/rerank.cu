@@ -102,49 +102,77 @@ rerank_kernel(const RerankParams p) {
     }
     float my_val = INFINITY;                         // ranking key (ascending) of this lane's candidate
     float my_out = NAN;
-    for (int t = 0; t < p.kl; ++t) {
-        const int j = __shfl_sync(0xffffffffu, sel, t);
-        if (j < 0) continue;                         // warp-uniform
-        const float* xj = p.feats + int64_t(j) * p.d;
-        float acc = 0.f, nj = 0.f;
-        if (p.metric == HG_METRIC_COSINE) {
-            for (int64_t c = lane; c < p.d; c += 32) {
-                const float x = __ldg(xi + c), y = __ldg(xj + c);
-                acc = fmaf(x, y, acc); nj = fmaf(y, y, nj);
-            }
-        } else if (vec) {
+    const bool is_cos = p.metric == HG_METRIC_COSINE;
+    // four candidates per pass: one read of the query row serves four distance sums and the four
+    // warp reductions overlap (the loop is latency-bound otherwise); kl is a multiple of 8
+    for (int t0 = 0; t0 < p.kl; t0 += 4) {
+        int j[4];
+        const float* xj[4];
+        bool any = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            j[q] = __shfl_sync(0xffffffffu, sel, t0 + q);
+            any |= j[q] >= 0;
+            xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
+        }
+        if (!any) continue;                          // warp-uniform
+        float acc[4] = {0.f, 0.f, 0.f, 0.f}, nj[4] = {0.f, 0.f, 0.f, 0.f};
+        if (vec) {
             for (int64_t c = lane; c < (p.d >> 2); c += 32) {
                 const float4 x = __ldg(reinterpret_cast<const float4*>(xi) + c);
-                const float4 y = __ldg(reinterpret_cast<const float4*>(xj) + c);
-                const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
-                acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+                float4 y[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) y[q] = __ldg(reinterpret_cast<const float4*>(xj[q]) + c);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (is_cos) {
+                        acc[q] = fmaf(x.x, y[q].x, acc[q]); acc[q] = fmaf(x.y, y[q].y, acc[q]);
+                        acc[q] = fmaf(x.z, y[q].z, acc[q]); acc[q] = fmaf(x.w, y[q].w, acc[q]);
+                        nj[q] = fmaf(y[q].x, y[q].x, nj[q]); nj[q] = fmaf(y[q].y, y[q].y, nj[q]);
+                        nj[q] = fmaf(y[q].z, y[q].z, nj[q]); nj[q] = fmaf(y[q].w, y[q].w, nj[q]);
+                    } else {
+                        const float d0 = x.x - y[q].x, d1 = x.y - y[q].y, d2 = x.z - y[q].z, d3 = x.w - y[q].w;
+                        acc[q] = fmaf(d0, d0, acc[q]); acc[q] = fmaf(d1, d1, acc[q]);
+                        acc[q] = fmaf(d2, d2, acc[q]); acc[q] = fmaf(d3, d3, acc[q]);
+                    }
+                }
             }
         } else {
             for (int64_t c = lane; c < p.d; c += 32) {
-                const float df = __ldg(xi + c) - __ldg(xj + c);
-                acc = fmaf(df, df, acc);
+                const float x = __ldg(xi + c);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float y = __ldg(xj[q] + c);
+                    if (is_cos) { acc[q] = fmaf(x, y, acc[q]); nj[q] = fmaf(y, y, nj[q]); }
+                    else { const float df = x - y; acc[q] = fmaf(df, df, acc[q]); }
+                }
             }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-            acc += __shfl_xor_sync(0xffffffffu, acc, o);
-            nj += __shfl_xor_sync(0xffffffffu, nj, o);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+                if (is_cos) nj[q] += __shfl_xor_sync(0xffffffffu, nj[q], o);
+            }
         }
-        if (lane == t) {
-            if (p.metric == HG_METRIC_COSINE) {
-                const float cs = acc / (fmaxf(sqrtf(ni), 1e-8f) * fmaxf(sqrtf(nj), 1e-8f));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (lane != t0 + q || j[q] < 0) continue;
+            if (is_cos) {
+                const float cs = acc[q] / (fmaxf(sqrtf(ni), 1e-8f) * fmaxf(sqrtf(nj[q]), 1e-8f));
                 my_val = -cs; my_out = cs;
             } else if (p.metric == HG_METRIC_EUCLIDEAN) {
-                my_val = acc; my_out = acc;
+                my_val = acc[q]; my_out = acc[q];
             } else {
                 float d2g = 0.f;
                 if (p.pos != nullptr) {
-                    for (int q = 0; q < p.pos_dim; ++q) {
-                        const float df = __ldg(p.pos + row * p.pos_dim + q) - __ldg(p.pos + int64_t(j) * p.pos_dim + q);
+                    for (int c = 0; c < p.pos_dim; ++c) {
+                        const float df = __ldg(p.pos + row * p.pos_dim + c) - __ldg(p.pos + int64_t(j[q]) * p.pos_dim + c);
                         d2g = fmaf(df, df, d2g);
                     }
                 }
-                my_val = p.lambda_h * acc + p.lambda_g * d2g;
+                my_val = p.lambda_h * acc[q] + p.lambda_g * d2g;
                 my_out = expf(-my_val);
             }
         }
