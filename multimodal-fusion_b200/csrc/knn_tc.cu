@@ -29,6 +29,7 @@
 #include "ptx.cuh"
 #include "topk_list.cuh"
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 namespace hg {
 
@@ -272,6 +273,11 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
             const double eff = double(units) / double(ceil_div(units, kNumSMs) * kNumSMs);
             if (eff > best_eff + 0.015) { best_eff = eff; best_cc = cc; best_s = s; }
         }
+    }
+    if (const char* ov = getenv("HG_B200_TC_PLAN")) {          // tuning override: "cc,splits"
+        int cc = 0, sp = 0;
+        if (sscanf(ov, "%d,%d", &cc, &sp) == 2 && (cc == 1 || cc == 2 || cc == 4) && sp >= cc && sp <= TC_MAX_SPLITS &&
+            sp % cc == 0) { best_cc = cc; best_s = sp; }
     }
     pl.cc = best_cc;
     pl.rc = kNumSMs / best_cc;
