@@ -103,6 +103,14 @@ int hg_stats_workspace_bytes(int64_t count, size_t* bytes);
 int hg_similarity_stats(const float* values, int64_t count, int64_t exclude_diag_n,
                         double* stats_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* A9 when N x N does not fit: the same five statistics of K = K_h * K_g over all N^2 entries,
+ * streamed chunk by chunk through the tensor-core kernel (K from 3xBF16 dot products, relative
+ * error ~1e-6) -- the matrix is never stored in full.  preprocess_hypergraph.py:137,190-196. */
+int hg_similarity_stats_streaming_workspace_bytes(int64_t n, int64_t d, size_t* bytes);
+int hg_similarity_stats_streaming(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                  float lambda_h, float lambda_g, double* stats_out,
+                                  void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- A3: spatial-coordinate kNN ------------------------------------------------
  * k smallest |g_i - g_j|^2 (direct-difference FP32), self excluded, ties by
  * (d2, index).  Semantics pinned by similarity_kernel.py:57-86 (top-k of a K_g

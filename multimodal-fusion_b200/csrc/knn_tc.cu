@@ -177,10 +177,12 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = split * p.plan.ct_per_split;
             const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
-            float lv[KL];
-            int li[KL];
+            constexpr int KLA = KL > 0 ? KL : 1;           // KL == 0: dense-output mode, no lists
+            float lv[KLA];
+            int li[KLA];
 #pragma unroll
-            for (int q = 0; q < KL; ++q) { lv[q] = INFINITY; li[q] = -1; }
+            for (int q = 0; q < KLA; ++q) { lv[q] = INFINITY; li[q] = -1; }
+            const float row_norm = (KL == 0 && row < p.n) ? __ldg(p.colp + row).x : 0.f;
             float4 mypos = make_float4(0.f, 0.f, 0.f, 0.f);
             if (HAS_POS && row < p.n) mypos = __ldg(p.pos4 + row);
             for (int ct = ct0; ct < ct1; ++ct, ++tile) {
@@ -202,9 +204,39 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     uint32_t r[32];
                     ptx::tmem_ld_32x32(tmem_base + lane_base + buf * TC_BN + ch * 32, r);
                     ptx::tmem_ld_wait();
+                    if constexpr (KL == 0) {
+                        // dense mode: K = exp(-lambda_h (n_i + n_j - 2 dot + g d2_g)), 128 contiguous bytes per thread
+                        float* dst = p.dense_out + (row - p.row_begin) * p.dense_ld + col0 + ch * 32;
+                        const bool row_ok = row < p.row_end;
+                        const bool full = row_ok && (col0 + ch * 32 + 32 <= p.n) && ((p.dense_ld & 3) == 0);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float v[4];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const int c = ch * 32 + j + q;
+                                const float2 cp = sm->colp[buf][c];
+                                float s = fmaf(cp.y, __uint_as_float(r[j + q]), cp.x);
+                                if (HAS_POS) {
+                                    const float4 g4 = sm->cpos[buf][c];
+                                    const float dx = mypos.x - g4.x, dy = mypos.y - g4.y, dz = mypos.z - g4.z;
+                                    s = fmaf(p.gscale, fmaf(dx, dx, fmaf(dy, dy, dz * dz)), s);
+                                }
+                                v[q] = expf(-p.lambda_h * (row_norm + s));
+                            }
+                            if (full) {
+                                *reinterpret_cast<float4*>(dst + j) = make_float4(v[0], v[1], v[2], v[3]);
+                            } else if (row_ok) {
+#pragma unroll
+                                for (int q = 0; q < 4; ++q)
+                                    if (col0 + ch * 32 + j + q < p.n) dst[j + q] = v[q];
+                            }
+                        }
+                        continue;
+                    }
                     // pass 1 (straight-line): scores in place, bitmask of columns beating the current k-th
                     uint32_t hits = 0;
-                    const float thr = lv[KL - 1];
+                    const float thr = lv[KLA - 1];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int c = ch * 32 + j;
@@ -227,13 +259,13 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 #pragma unroll
                         for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
                         const float s = __uint_as_float(bits);
-                        if (s < lv[KL - 1]) list_insert<KL>(lv, li, s, col0 + ch * 32 + j);
+                        if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, col0 + ch * 32 + j);
                     }
                 }
                 ptx::tc_fence_before();
                 ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
             }
-            if (row < p.row_end) {
+            if (KL > 0 && row < p.row_end) {
                 const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
 #pragma unroll
                 for (int q = 0; q < KL; ++q) { p.part_val[o + q] = lv[q]; p.part_idx[o + q] = li[q]; }
@@ -336,6 +368,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaSt
     rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN);
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
+        case 0:  return launch_kl<0>(ta, tb, p, st);
         case 8:  return launch_kl<8>(ta, tb, p, st);
         case 16: return launch_kl<16>(ta, tb, p, st);
         case 24: return launch_kl<24>(ta, tb, p, st);

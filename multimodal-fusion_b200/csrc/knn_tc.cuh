@@ -31,6 +31,11 @@ struct TcParams {
     int exclude_self;
     float* part_val;            // [S][n_rows][kl]
     int32_t* part_idx;
+    // dense mode (plan.kl == 0): K[i, j] = exp(-lambda_h * (colp[i].x + score_ij)) written to
+    // dense_out[(i - row_begin) * dense_ld + j] instead of keeping lists (streaming statistics, A9)
+    float* dense_out;
+    int64_t dense_ld;
+    float lambda_h;
 };
 
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad);

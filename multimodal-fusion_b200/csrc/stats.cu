@@ -9,6 +9,8 @@
 // radix select on the order-preserving uint32 image of the floats for the median:
 // 5 reads of the buffer in total, no sort, no copy.
 #include "common.cuh"
+#include "knn_tc.cuh"
+#include <stdlib.h>
 
 namespace hg {
 
@@ -144,5 +146,98 @@ extern "C" int hg_similarity_stats(const float* values, int64_t count, int64_t e
     stats_final_kernel<<<1, 32, 0, st>>>(s, stats_out);
     HG_CHECK_LAUNCH();
     count_launches(11);
+    return HG_OK;
+}
+
+
+// ---- A9 for slides whose N x N kernel does not fit: streaming statistics -----------------------------
+// K = K_h * K_g is produced chunk by chunk (row ranges) by the tensor-core kernel in dense-output
+// mode into a bounded scratch buffer and folded into the same moment / radix-select state, one
+// sweep over the whole matrix per select pass (4 sweeps; the first also takes the moments).  The
+// N x N matrix never exists in full; HBM traffic per sweep is one write + one read of the chunk.
+namespace hg {
+struct StreamWs { size_t off_ops, off_norms, off_colp, off_pos4, off_state, off_chunk, bytes; int64_t chunk_rows; };
+
+static StreamWs plan_stream(int64_t n, int64_t d, bool has_pos) {
+    StreamWs w{};
+    const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
+    size_t off = 0;
+    auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
+    w.off_ops = take(size_t(2) * n_pad * d_pad * 2);
+    w.off_norms = take(size_t(n_pad) * 4);
+    w.off_colp = take(size_t(n_pad) * 8);
+    w.off_pos4 = take(has_pos ? size_t(n_pad) * 16 : 0);
+    w.off_state = take(sizeof(StatsState));
+    int64_t budget = int64_t(2) << 30;                                   // <= 2 GiB of K at a time
+    if (const char* mb = getenv("HG_B200_STATS_CHUNK_MB")) budget = (int64_t(atoi(mb)) > 0 ? int64_t(atoi(mb)) : 1) << 20;
+    int64_t rows = (budget / (n * 4)) / TC_BM * TC_BM;
+    if (rows < TC_BM) rows = TC_BM;
+    if (rows > round_up(n, TC_BM)) rows = round_up(n, TC_BM);
+    w.chunk_rows = rows;
+    w.off_chunk = take(size_t(rows) * size_t(n) * 4);
+    w.bytes = off;
+    return w;
+}
+}  // namespace hg
+
+extern "C" int hg_similarity_stats_streaming_workspace_bytes(int64_t n, int64_t d, size_t* bytes) {
+    HG_REQUIRE(bytes && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_similarity_stats_streaming_workspace_bytes: bad argument");
+    *bytes = plan_stream(n, d, true).bytes;
+    return HG_OK;
+}
+
+extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                             float lambda_h, float lambda_g, double* stats_out,
+                                             void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(feats && stats_out && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_similarity_stats_streaming: bad argument");
+    HG_REQUIRE(lambda_h > 0.f, HG_ERR_UNSUPPORTED, "hg_similarity_stats_streaming: lambda_h must be > 0");
+    if (lambda_g == 0.f) pos = nullptr;
+    HG_REQUIRE(pos == nullptr || (pos_dim >= 1 && pos_dim <= 3), HG_ERR_UNSUPPORTED, "pos_dim must be 1..3");
+    const StreamWs w = plan_stream(n, d, pos != nullptr);
+    HG_REQUIRE(workspace && workspace_bytes >= w.bytes, HG_ERR_WORKSPACE,
+               "hg_similarity_stats_streaming: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
+    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "workspace must be 1024-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    char* ws = static_cast<char*>(workspace);
+    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    float* norms = reinterpret_cast<float*>(ws + w.off_norms);
+    float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
+    float4* pos4 = pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
+    StatsState* state = reinterpret_cast<StatsState*>(ws + w.off_state);
+    float* chunk = reinterpret_cast<float*>(ws + w.off_chunk);
+    const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
+
+    int rc = launch_split(feats, n, d, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    rc = launch_colparams(norms, pos, pos_dim, n, n_pad, HG_METRIC_GAUSSIAN, colp, pos4, st);
+    if (rc != HG_OK) return rc;
+    stats_init_kernel<<<1, 256, 0, st>>>(state, (unsigned long long)n * (unsigned long long)n);
+    count_launches(1);
+    for (int pass = 0; pass < 4; ++pass) {
+        const int byte_idx = 3 - pass;
+        for (int64_t r0 = 0; r0 < n; r0 += w.chunk_rows) {
+            const int64_t r1 = min64(n, r0 + w.chunk_rows);
+            TcParams tp{};
+            tp.n = n; tp.row_begin = r0; tp.row_end = r1; tp.d_pad = int(d_pad);
+            tp.plan = tc_make_plan(n, r1 - r0, 1, d_pad);
+            tp.plan.kl = 0;                                        // dense-output mode
+            tp.colp = colp; tp.pos4 = pos4;
+            tp.gscale = pos ? lambda_g / lambda_h : 0.f;
+            tp.exclude_self = 0;
+            tp.dense_out = chunk; tp.dense_ld = n; tp.lambda_h = lambda_h;
+            rc = tc_launch(ops, n_pad, tp, st);
+            if (rc != HG_OK) return rc;
+            const int64_t cnt = (r1 - r0) * n;
+            const int blocks = int(min64(ceil_div(cnt, 256 * 8), 148 * 8));
+            if (pass == 0) stats_moments_kernel<<<blocks, 256, 0, st>>>(chunk, cnt, 0, state);
+            stats_hist_kernel<<<blocks, 256, 0, st>>>(chunk, cnt, 0, byte_idx, state);
+            count_launches(pass == 0 ? 2 : 1);
+        }
+        stats_select_kernel<<<1, 256, 0, st>>>(byte_idx, state);
+        count_launches(1);
+    }
+    stats_final_kernel<<<1, 32, 0, st>>>(state, stats_out);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }

@@ -106,6 +106,25 @@ def similarity_stats(mat: torch.Tensor, exclude_diagonal: bool = False) -> dict:
     return {"mean": v[0], "std": v[1], "min": v[2], "max": v[3], "median": v[4]}
 
 
+def similarity_stats_streaming(features: torch.Tensor, positions: Optional[torch.Tensor] = None,
+                               lambda_h: float = 1.0, lambda_g: float = 0.0, device=None) -> dict:
+    """A9 for large N: statistics of K = K_h * K_g over all N^2 entries without storing the matrix."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    pos = L.f32c(positions, dev) if positions is not None else None
+    n, d = x.shape
+    out = torch.empty(5, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = _size(lib.hg_similarity_stats_streaming_workspace_bytes, n, d)
+        ws = L.Workspace.get(dev, nbytes)
+        L.check(lib.hg_similarity_stats_streaming(L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1],
+                                                  float(lambda_h), float(lambda_g), L.ptr(out), L.ptr(ws), nbytes,
+                                                  L.stream_ptr(dev)))
+    v = out.cpu().tolist()
+    return {"mean": v[0], "std": v[1], "min": v[2], "max": v[3], "median": v[4]}
+
+
 # ------------------------------------------------------------------ edge assembly
 def build_edges(knn_lists: Sequence[torch.Tensor], n: int, labels: Optional[torch.Tensor] = None,
                 num_hyperedges: int = 0, device=None) -> torch.Tensor:

@@ -130,7 +130,7 @@ def aggregate_wsi_super_patches(wsi_features: torch.Tensor, wsi_positions: torch
 
     Returns (super_features [S, D], super_positions [S, 2|3], stats, K_wsi).  K_wsi is the
     dense N x N kernel when N <= HG_B200_MAX_DENSE_N, else None (the reference cannot run
-    there at all); its statistics come from the streaming CUDA reduction (A9)."""
+    there at all) and its statistics are streamed through the tensor-core kernel (A9)."""
     dev = _device(device, wsi_features)
     feats = L.f32c(wsi_features, dev)
     pos = L.f32c(wsi_positions, dev)
@@ -151,22 +151,28 @@ def aggregate_wsi_super_patches(wsi_features: torch.Tensor, wsi_positions: torch
     super_f = torch.zeros(num_super_patches, feats.shape[1], device=dev).index_add_(0, labels, feats) * inv
     super_p = torch.zeros(num_super_patches, pos.shape[1], device=dev).index_add_(0, labels, pos) * inv
     intra = []
+    order = torch.argsort(labels, stable=True)
+    bounds = torch.cumsum(counts, 0).tolist()
+    start = 0
+    for c in range(num_super_patches):                                          # reference :175-184
+        idx = order[start:bounds[c]]
+        start = bounds[c]
+        m = idx.numel()
+        if m > 1:
+            # large slides: the cluster's own m x m kernel block is recomputed instead of gathered
+            blk = K_wsi[idx][:, idx] if K_wsi is not None else \
+                ops.similarity_dense(feats[idx], pos_a=pos[idx], pos_b=pos[idx], lambda_h=lambda_h,
+                                     lambda_g=lambda_g, device=dev)
+            intra.append(float((blk.sum() - blk.diagonal().sum()) / (m * (m - 1))))
     if K_wsi is not None:
-        order = torch.argsort(labels, stable=True)
-        bounds = torch.cumsum(counts, 0).tolist()
-        start = 0
-        for c in range(num_super_patches):                                      # reference :175-184
-            idx = order[start:bounds[c]]
-            start = bounds[c]
-            m = idx.numel()
-            if m > 1:
-                blk = K_wsi[idx][:, idx]
-                intra.append(float((blk.sum() - blk.diagonal().sum()) / (m * (m - 1))))
+        k_stats = ops.similarity_stats(K_wsi)
+    else:
+        k_stats = ops.similarity_stats_streaming(feats, pos, lambda_h, lambda_g, device=dev)
     stats = {
         "num_original_patches": n,
         "num_super_patches": num_super_patches,
         "avg_intra_cluster_similarity": float(np.mean(intra)) if intra else 0.0,
-        "wsi_similarity_matrix_stats": ops.similarity_stats(K_wsi) if K_wsi is not None else None,
+        "wsi_similarity_matrix_stats": k_stats,
     }
     return super_f, super_p, stats, K_wsi
 

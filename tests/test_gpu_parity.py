@@ -327,3 +327,37 @@ def test_c3_combined_feature_and_spatial_sampled_rows():
     assert ei.shape == ref.shape and (ei == ref).all()
     rowptr = out["csr_rowptr"].cpu().numpy()
     assert rowptr[-1] == 2 * ei.shape[1]
+
+
+def test_streaming_stats_match_dense(monkeypatch):
+    """A9 without the N x N matrix: chunked tensor-core sweep == statistics of the dense kernel."""
+    n, d = 3000, 128
+    feats, pos = synth.make_slide(n, d, 61, "gaussian")
+    lam_g = 1.0 / 256
+    ref = oracle.similarity_stats(oracle.combined_similarity(feats, pos, 1.0, lam_g))
+    for chunk_mb in ("1", "4096"):                       # 24 chunks of 128 rows, then a single chunk
+        monkeypatch.setenv("HG_B200_STATS_CHUNK_MB", chunk_mb)
+        got = ops.similarity_stats_streaming(_cuda(feats), _cuda(pos), 1.0, lam_g)
+        for key in ref:
+            assert np.isclose(got[key], ref[key], rtol=RTOL, atol=1e-12), (chunk_mb, key, got[key], ref[key])
+    got = ops.similarity_stats_streaming(_cuda(feats), None, 0.7, 0.0)
+    ref = oracle.similarity_stats(oracle.morphological_similarity(feats, 0.7))
+    for key in ref:
+        assert np.isclose(got[key], ref[key], rtol=RTOL, atol=1e-12), (key, got[key], ref[key])
+
+
+def test_aggregate_large_slide_streams_stats(monkeypatch):
+    from hg_b200 import preprocess_hypergraph as pp
+    monkeypatch.setattr(pp, "MAX_DENSE_N", 256)          # force the no-N x N branch on a small slide
+    n, d = 700, 64
+    feats, pos = synth.make_slide(n, d, 62, "gaussian")
+    sf, sp, stats, K = pp.aggregate_wsi_super_patches(_cuda(feats), _cuda(pos), 6, 1.0, 1.0 / 128)
+    assert K is None and sf.shape == (6, d) and sp.shape == (6, 2)
+    Kref = oracle.combined_similarity(feats, pos, 1.0, 1.0 / 128)
+    ref = oracle.similarity_stats(Kref)
+    for key in ref:
+        assert np.isclose(stats["wsi_similarity_matrix_stats"][key], ref[key], rtol=RTOL), key
+    monkeypatch.setattr(pp, "MAX_DENSE_N", 32768)
+    _, _, stats_dense, K2 = pp.aggregate_wsi_super_patches(_cuda(feats), _cuda(pos), 6, 1.0, 1.0 / 128)
+    assert K2 is not None
+    assert np.isclose(stats["avg_intra_cluster_similarity"], stats_dense["avg_intra_cluster_similarity"], rtol=1e-5)
