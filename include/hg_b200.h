@@ -166,6 +166,20 @@ int hg_threshold_edges_fill(const float* K, int64_t n, float threshold, int64_t 
                             const void* workspace, size_t workspace_bytes, void* stream);
 int hg_threshold_workspace_bytes(int64_t n, size_t* bytes);
 
+/* ---- row (f)1, "next": KMeans building blocks (Lloyd assign / update, kmeans++ distances) -------
+ * Replace sklearn.cluster.KMeans at preprocess_hypergraph.py:150-151, 299-300, 391-392; the
+ * driver loop (n_init restarts, kmeans++ seeding, tolerance) is hg_b200/kmeans.py.  Parity with
+ * scikit-learn is statistical (inertia), not label-exact. */
+int hg_kmeans_assign(const float* x, int64_t n, int64_t d, const float* centroids, int c,
+                     int32_t* labels, float* d2, void* stream);
+int hg_kmeans_workspace_bytes(int64_t d, int c, size_t* bytes);
+int hg_kmeans_update(const float* x, int64_t n, int64_t d, const int32_t* labels, int c,
+                     float* centroids, double* shift2, uint32_t* counts_out,
+                     void* workspace, size_t workspace_bytes, void* stream);
+int hg_kmeans_inertia(const float* d2, int64_t n, double* inertia, void* stream);
+int hg_kmeans_candidate_d2(const float* x, int64_t n, int64_t d, const int64_t* cand, int t,
+                           float* out, void* stream);
+
 /* ---- one call per slide: A4 (+A3) -> A5 -> A6 -> CSR ---------------------------------------
  * The body of build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433) on one stream with
  * a single synchronisation (the edge count).  Variable-size outputs are caller buffers sized for

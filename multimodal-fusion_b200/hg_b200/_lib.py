@@ -51,6 +51,11 @@ SIGNATURES = {
     "hg_csr_from_coo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_threshold_workspace_bytes": (_i32, [_i64, _psz]),
     "hg_threshold_edges_count": (_i32, [_vp, _i64, _f32, _pi64, _vp, _sz, _vp]),
+    "hg_kmeans_assign": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp, _vp]),
+    "hg_kmeans_workspace_bytes": (_i32, [_i64, _i32, _psz]),
+    "hg_kmeans_update": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_kmeans_inertia": (_i32, [_vp, _i64, _vp, _vp]),
+    "hg_kmeans_candidate_d2": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
     "hg_build_workspace_bytes": (_i32, [_i64, _i64, _i32, _i32, _i32, _i64, _i64, _i32, _psz]),
     "hg_build_knn_hypergraph": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i32, _vp, _i32, _i64,
                                        _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _pi64, _vp, _sz, _vp]),

@@ -1,0 +1,95 @@
+"""KMeans on the GPU (scope row (f)1, "next"): the driver loop around the C-ABI building blocks
+hg_kmeans_assign / hg_kmeans_update / hg_kmeans_candidate_d2.
+
+Mirrors the estimator the reference constructs at preprocess_hypergraph.py:150, :299, :391 --
+``KMeans(n_clusters, random_state=42, n_init=10)`` with scikit-learn's defaults: greedy
+k-means++ seeding (2 + log(k) local trials), Lloyd iterations until the summed squared centre
+shift falls below ``tol * mean(var(X))`` or ``max_iter`` = 300, best of ``n_init`` runs by
+inertia.  The random stream differs from scikit-learn's, so labels are not comparable one to one;
+the parity bar is the inertia (tests/test_gpu_kmeans.py).  torch is used for the O(n) vector
+plumbing (cumsum / searchsorted for the D^2 sampling); every O(n*d) step is a CUDA kernel of ours.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Tuple
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+
+def _kmeanspp(lib, x, n_clusters: int, gen: torch.Generator, st) -> torch.Tensor:
+    n, d = x.shape
+    dev = x.device
+    trials = min(16, 2 + int(math.log(n_clusters)))
+    centers = torch.empty(n_clusters, dtype=torch.int64, device=dev)
+    first = torch.randint(n, (1,), generator=gen, device=dev)
+    centers[0:1] = first
+    cand_d2 = torch.empty((16, n), dtype=torch.float32, device=dev)
+    L.check(lib.hg_kmeans_candidate_d2(L.ptr(x), n, d, L.ptr(first), 1, L.ptr(cand_d2), st))
+    closest = cand_d2[0].clone()
+    for c in range(1, n_clusters):
+        cum = torch.cumsum(closest.double(), 0)
+        r = torch.rand(trials, generator=gen, device=dev, dtype=torch.float64) * cum[-1]
+        cand = torch.searchsorted(cum, r).clamp_(max=n - 1)
+        L.check(lib.hg_kmeans_candidate_d2(L.ptr(x), n, d, L.ptr(cand), trials, L.ptr(cand_d2), st))
+        pot = torch.minimum(cand_d2[:trials], closest.unsqueeze(0))
+        best = torch.argmin(pot.double().sum(1))
+        closest = pot[best].clone()
+        centers[c] = cand[best]
+    return x.index_select(0, centers).contiguous()
+
+
+def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: int = 300, tol: float = 1e-4,
+           seed: int = 42, device=None) -> Tuple[np.ndarray, torch.Tensor, float]:
+    """Returns (labels int64 numpy [n], centers float32 CUDA [k, d], inertia)."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    n, d = x.shape
+    if n < n_clusters:
+        raise ValueError(f"n_samples={n} should be >= n_clusters={n_clusters}.")     # scikit-learn's message
+    with torch.cuda.device(dev):
+        st = L.stream_ptr(dev)
+        tol_abs = float(x.var(dim=0, unbiased=False).mean()) * tol
+        nbytes = C.c_size_t(0)
+        L.check(lib.hg_kmeans_workspace_bytes(d, n_clusters, C.byref(nbytes)))
+        ws = L.Workspace.get(dev, nbytes.value, "kmeans")
+        labels = torch.empty(n, dtype=torch.int32, device=dev)
+        d2 = torch.empty(n, dtype=torch.float32, device=dev)
+        scal = torch.zeros(2, dtype=torch.float64, device=dev)          # [shift^2, inertia]
+        best = None
+        for run in range(n_init):
+            gen = torch.Generator(device=dev)
+            gen.manual_seed(seed + 1000003 * run)
+            centers = _kmeanspp(lib, x, n_clusters, gen, st)
+            for _ in range(max_iter):
+                L.check(lib.hg_kmeans_assign(L.ptr(x), n, d, L.ptr(centers), n_clusters, L.ptr(labels), L.ptr(d2), st))
+                L.check(lib.hg_kmeans_update(L.ptr(x), n, d, L.ptr(labels), n_clusters, L.ptr(centers),
+                                             scal.data_ptr(), None, L.ptr(ws), nbytes.value, st))
+                if float(scal[0]) <= tol_abs:
+                    break
+            L.check(lib.hg_kmeans_assign(L.ptr(x), n, d, L.ptr(centers), n_clusters, L.ptr(labels), L.ptr(d2), st))
+            L.check(lib.hg_kmeans_inertia(L.ptr(d2), n, scal.data_ptr() + 8, st))
+            inertia = float(scal[1])
+            if best is None or inertia < best[2]:
+                best = (labels.clone(), centers.clone(), inertia)
+    return best[0].cpu().numpy().astype(np.int64), best[1], best[2]
+
+
+class KMeans:
+    """The slice of scikit-learn's estimator API the reference uses: KMeans(...).fit_predict(X)."""
+
+    def __init__(self, n_clusters: int = 8, random_state: int = 42, n_init: int = 10, max_iter: int = 300,
+                 tol: float = 1e-4):
+        self.n_clusters, self.random_state, self.n_init, self.max_iter, self.tol = \
+            n_clusters, random_state, n_init, max_iter, tol
+
+    def fit_predict(self, X) -> np.ndarray:
+        t = X if isinstance(X, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
+        self.labels_, self.cluster_centers_, self.inertia_ = kmeans(
+            t, self.n_clusters, self.n_init, self.max_iter, self.tol, seed=int(self.random_state or 0))
+        return self.labels_

@@ -38,9 +38,23 @@ def _h5py():
     return h5py
 
 
+KMEANS_BACKEND = os.environ.get("HG_B200_KMEANS", "sklearn")        # "sklearn" (reference behaviour) | "cuda"
+
+
 def _kmeans(n_clusters: int):
-    from sklearn.cluster import KMeans     # reference :20, :150, :299, :391
+    """KMeans(n_clusters, random_state=42, n_init=10) as at reference :150, :299, :391.  The default
+    is scikit-learn on the host, label-for-label what the reference computes; HG_B200_KMEANS=cuda
+    (or KMEANS_BACKEND = "cuda") switches to the GPU Lloyd of hg_b200.kmeans (statistical parity)."""
+    if KMEANS_BACKEND == "cuda":
+        from .kmeans import KMeans
+    else:
+        from sklearn.cluster import KMeans     # reference :20
     return KMeans(n_clusters=n_clusters, random_state=42, n_init=10)
+
+
+def _cluster(x: torch.Tensor, n_clusters: int) -> np.ndarray:
+    est = _kmeans(n_clusters)
+    return est.fit_predict(x if KMEANS_BACKEND == "cuda" else x.detach().cpu().numpy())
 
 
 def _device(device, *tensors) -> torch.device:
@@ -141,7 +155,7 @@ def aggregate_wsi_super_patches(wsi_features: torch.Tensor, wsi_positions: torch
         K_wsi = compute_combined_similarity(feats, pos, lambda_h, lambda_g)
     else:
         K_wsi = None
-    labels_np = _kmeans(num_super_patches).fit_predict(feats.cpu().numpy())     # reference :147-151
+    labels_np = _cluster(feats, num_super_patches)                              # reference :147-151
     labels = torch.from_numpy(labels_np.astype(np.int64)).to(dev)
     counts = torch.bincount(labels, minlength=num_super_patches)
     empty = torch.nonzero(counts == 0)
@@ -193,7 +207,7 @@ def group_by_similarity(similarity_matrix: torch.Tensor, num_groups: int, method
     """Group WSI super-patches by their similarity rows (reference :270-332)."""
     sim_np = similarity_matrix.detach().cpu().numpy()
     if method == "kmeans":
-        labels = _kmeans(num_groups).fit_predict(sim_np)
+        labels = _cluster(similarity_matrix, num_groups)
         stats = {"method": "kmeans", "num_groups": num_groups}
     elif method == "knn":
         # unused by the pipeline (process_single_file passes 'kmeans'); kept on scikit-learn
@@ -225,7 +239,7 @@ def build_hypergraph_knn_kmeans(wsi_features: torch.Tensor, tma_features: torch.
     allf = torch.cat([L.f32c(wsi_features, dev), L.f32c(tma_features, dev)], 0)
     n = allf.shape[0]
     if hyperedge_labels is None:
-        hyperedge_labels = _kmeans(num_hyperedges).fit_predict(allf.cpu().numpy())   # reference :391-392
+        hyperedge_labels = _cluster(allf, num_hyperedges)                            # reference :391-392
     if k <= 32:
         # kNN (reference :379-388) + cliques + de-dup (:394-410) + weights (:413-422): one C call
         built = ops.build_knn_hypergraph(allf, k, "euclidean", labels=torch.as_tensor(np.asarray(hyperedge_labels)),

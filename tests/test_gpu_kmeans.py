@@ -1,0 +1,73 @@
+"""KMeans on the GPU (scope row (f)1): one Lloyd step against numpy, and the full estimator's
+inertia against scikit-learn's on the same data (labels are not comparable: different RNG)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from hg_b200 import _lib, synth
+from hg_b200.kmeans import KMeans, kmeans
+
+pytestmark = pytest.mark.gpu
+
+
+def test_lloyd_step_matches_numpy():
+    lib = _lib.load_library()
+    n, d, c = 5000, 96, 37
+    x = synth.make_features(n, d, 71, "gaussian")
+    rng = np.random.default_rng(0)
+    cen = x[rng.choice(n, c, replace=False)].copy()
+    xd, cd = torch.from_numpy(x).cuda(), torch.from_numpy(cen).cuda()
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    d2 = torch.empty(n, dtype=torch.float32, device="cuda")
+    _lib.check(lib.hg_kmeans_assign(xd.data_ptr(), n, d, cd.data_ptr(), c, labels.data_ptr(), d2.data_ptr(), 0))
+    full = ((x[:, None, :].astype(np.float64) - cen[None].astype(np.float64)) ** 2).sum(-1)
+    ref_lab = full.argmin(1)
+    got = labels.cpu().numpy()
+    diff = np.nonzero(got != ref_lab)[0]
+    for i in diff:                                    # only FP32 near-ties may differ
+        assert abs(full[i, got[i]] - full[i, ref_lab[i]]) <= 1e-5 * max(1.0, full[i].min())
+    assert len(diff) <= 3
+    np.testing.assert_allclose(d2.cpu().numpy(), full[np.arange(n), got], rtol=1e-4, atol=1e-5)
+    nb = C.c_size_t(0)
+    _lib.check(lib.hg_kmeans_workspace_bytes(d, c, C.byref(nb)))
+    ws = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    shift = torch.zeros(1, dtype=torch.float64, device="cuda")
+    counts = torch.zeros(c, dtype=torch.int32, device="cuda")
+    _lib.check(lib.hg_kmeans_update(xd.data_ptr(), n, d, labels.data_ptr(), c, cd.data_ptr(), shift.data_ptr(),
+                                    counts.data_ptr(), ws.data_ptr(), nb.value, 0))
+    new = np.stack([x[got == k].astype(np.float64).mean(0) if (got == k).any() else cen[k] for k in range(c)])
+    np.testing.assert_allclose(cd.cpu().numpy(), new, rtol=1e-5, atol=1e-6)
+    assert (counts.cpu().numpy() == np.bincount(got, minlength=c)).all()
+    assert np.isclose(float(shift), ((new - cen) ** 2).sum(), rtol=1e-4)
+
+
+@pytest.mark.parametrize("n,d,c", [(4096, 1024, 10), (6000, 128, 100)])
+def test_inertia_on_par_with_sklearn(n, d, c):
+    from sklearn.cluster import KMeans as SkKMeans
+    x = synth.make_features(n, d, 72, "gaussian")
+    sk = SkKMeans(n_clusters=c, random_state=42, n_init=10).fit(x)
+    labels, centers, inertia = kmeans(torch.from_numpy(x).cuda(), c, n_init=10, seed=42)
+    assert labels.shape == (n,) and labels.min() >= 0 and labels.max() < c
+    assert len(np.unique(labels)) == c                                 # no empty cluster
+    assert inertia <= sk.inertia_ * 1.01, (inertia, sk.inertia_)       # statistical parity: within 1 %
+    # reported inertia is consistent with the returned labels / centres
+    cen = centers.cpu().numpy().astype(np.float64)
+    ref = ((x.astype(np.float64) - cen[labels]) ** 2).sum()
+    assert np.isclose(inertia, ref, rtol=1e-4)
+    est = KMeans(n_clusters=c, random_state=42, n_init=2)
+    assert est.fit_predict(x).shape == (n,) and est.inertia_ > 0
+
+
+def test_pipeline_with_cuda_kmeans(monkeypatch):
+    from hg_b200 import preprocess_hypergraph as pp
+    monkeypatch.setattr(pp, "KMEANS_BACKEND", "cuda")
+    n, d = 1500, 64
+    feats, pos = synth.make_slide(n, d, 73, "gaussian")
+    sf, sp, stats, K = pp.aggregate_wsi_super_patches(torch.from_numpy(feats).cuda(), torch.from_numpy(pos).cuda(),
+                                                      12, 1.0, 1.0 / 128)
+    assert sf.shape == (12, d) and stats["num_super_patches"] == 12
+    tma = torch.from_numpy(synth.make_features(80, d, 74, "gaussian")).cuda()
+    ei, w, st = pp.build_hypergraph_knn_kmeans(sf, tma, np.zeros(12), k=3, num_hyperedges=4)
+    assert ei.shape[0] == 2 and w.shape[0] == ei.shape[1] == st["num_edges"]
