@@ -125,7 +125,8 @@ class Workspace:
 
     @classmethod
     def get(cls, dev, nbytes: int, slot: str = "main") -> torch.Tensor:
-        key = (dev.index, slot)
+        # one buffer per (device, stream, purpose): builds running on different streams never share scratch
+        key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, slot)
         buf = cls._cache.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = None
