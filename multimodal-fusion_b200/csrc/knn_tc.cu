@@ -33,10 +33,19 @@
 
 namespace hg {
 
-constexpr int TC_STAGES = 2;
-constexpr int TC_A_PLANE = TC_BM * TC_BK * 2;                 // 16 KB
-constexpr int TC_B_PLANE = TC_BN * TC_BK * 2;                 // 32 KB
-constexpr int TC_STAGE_BYTES = 2 * TC_A_PLANE + 2 * TC_B_PLANE;   // 96 KB
+// CG = 1: one CTA per tile (M = 128).  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) shares
+// one 256 x 256 tile: each CTA stages its own 128 A rows and HALF of the B tile, the leader issues
+// M = 256 MMAs that read both halves, so operand traffic per CTA drops from 96 to 64 KB per stage
+// and a third pipeline stage fits.
+template <int CG>
+struct TcCfg {
+    static constexpr int STAGES = CG == 1 ? 2 : 3;
+    static constexpr int B_ROWS = TC_BN / CG;                       // B rows staged by this CTA
+    static constexpr int A_PLANE = TC_BM * TC_BK * 2;               // 16 KB
+    static constexpr int B_PLANE = B_ROWS * TC_BK * 2;              // 32 / 16 KB
+    static constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * B_PLANE;   // 96 / 64 KB
+};
+constexpr int TC_MAX_STAGES = 3;
 constexpr int TC_THREADS = 192;
 constexpr int TC_EPI_THREADS = 128;
 constexpr int TC_TMEM_COLS = 512;
@@ -44,10 +53,11 @@ constexpr int TC_TMEM_COLS = 512;
 struct TcSmem {                       // lives after the (1024-byte aligned) stage buffers
     float2 colp[2][TC_BN];
     float4 cpos[2][TC_BN];
-    uint64_t full[TC_STAGES], empty[TC_STAGES], tmem_full[2], tmem_empty[2];
+    uint64_t full[TC_MAX_STAGES], empty[TC_MAX_STAGES], tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
 };
-constexpr size_t TC_SMEM_BYTES = 1024 + size_t(TC_STAGES) * TC_STAGE_BYTES + sizeof(TcSmem);
+template <int CG>
+constexpr size_t tc_smem_bytes() { return 1024 + size_t(TcCfg<CG>::STAGES) * TcCfg<CG>::STAGE_BYTES + sizeof(TcSmem); }
 
 // Unit order (see the header comment): row blocks are taken in chunks of rc; inside a chunk the
 // units run split-group-major, then split, then row block, so any 148 consecutive units cover
@@ -64,10 +74,13 @@ __device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, in
     split = h * pl.cc + c;
 }
 
-template <int KL, bool HAS_POS>
+template <int KL, bool HAS_POS, int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
               const TcParams p) {
+    using Cfg = TcCfg<CG>;
+    constexpr int TC_STAGES = Cfg::STAGES;
+    constexpr int TC_A_PLANE = Cfg::A_PLANE, TC_B_PLANE = Cfg::B_PLANE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -76,6 +89,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = p.d_pad / TC_BK;
     const int units = p.plan.num_rb * p.plan.splits;
+    const uint32_t crank = (CG == 2) ? ptx::cluster_ctarank() : 0u;     // 0 = leader of the CTA pair
+    const int wid = blockIdx.x / CG, nworkers = gridDim.x / CG;          // a worker = one CTA or one pair
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_STAGES; ++s) {
@@ -84,7 +99,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(ptx::smem_u32(&sm->tmem_full[b]), 1);
-            ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), TC_EPI_THREADS);
+            ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), TC_EPI_THREADS * CG);
         }
         ptx::fence_barrier_init();
         ptx::fence_proxy_async();
@@ -93,9 +108,10 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         ptx::prefetch_tensormap(&tmap_a);
         ptx::prefetch_tensormap(&tmap_b);
     }
+    if (CG == 2) ptx::cluster_sync();                  // the peer's barriers exist before anything signals them
     if (warp == 1) {
-        ptx::tmem_alloc<1>(ptx::smem_u32(&sm->tmem_base), TC_TMEM_COLS);
-        ptx::tmem_relinquish<1>();
+        ptx::tmem_alloc<CG>(ptx::smem_u32(&sm->tmem_base), TC_TMEM_COLS);
+        ptx::tmem_relinquish<CG>();
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -106,10 +122,10 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         // ============================ TMA producer ============================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            for (int u = wid; u < units; u += nworkers) {
                 int split, rb;
                 decode_unit(p.plan, u, rb, split);
-                const int row0 = int(p.row_begin) + rb * TC_BM;
+                const int row0 = int(p.row_begin) + rb * (TC_BM * CG) + int(crank) * TC_BM;
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
@@ -118,20 +134,29 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
                         const uint32_t full = ptx::smem_u32(&sm->full[stage]);
                         const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
-                        ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
-                        ptx::tma_load_3d(dst, &tmap_a, full, kb * TC_BK, row0, 0, ptx::kEvictLast);
-                        ptx::tma_load_3d(dst + 2 * TC_A_PLANE, &tmap_b, full, kb * TC_BK, ct * TC_BN, 0,
-                                         ptx::kEvictNormal);
+                        if (CG == 1) {
+                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            ptx::tma_load_3d(dst, &tmap_a, full, kb * TC_BK, row0, 0, ptx::kEvictLast);
+                            ptx::tma_load_3d(dst + 2 * TC_A_PLANE, &tmap_b, full, kb * TC_BK, ct * TC_BN, 0,
+                                             ptx::kEvictNormal);
+                        } else {
+                            // both CTAs' bytes are counted on the LEADER's barrier (peer bit cleared)
+                            const uint32_t lead_full = full & 0xFEFFFFFFu;
+                            if (crank == 0) ptx::mbar_expect_tx(full, 2 * TC_STAGE_BYTES);
+                            ptx::tma_load_3d_2sm(dst, &tmap_a, lead_full, kb * TC_BK, row0, 0, ptx::kEvictLast);
+                            ptx::tma_load_3d_2sm(dst + 2 * TC_A_PLANE, &tmap_b, lead_full, kb * TC_BK,
+                                                 ct * TC_BN + int(crank) * Cfg::B_ROWS, 0, ptx::kEvictNormal);
+                        }
                     }
                 }
             }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ==============================
-        if (lane == 0) {
-            constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM, TC_BN);
+        if (lane == 0 && crank == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM * CG, TC_BN);
             uint32_t it = 0, tile = 0;
-            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            for (int u = wid; u < units; u += nworkers) {
                 int split, rb;
                 decode_unit(p.plan, u, rb, split);
                 const int ct0 = split * p.plan.ct_per_split;
@@ -154,13 +179,16 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 #pragma unroll
                         for (int ks = 0; ks < TC_BK / 16; ++ks) {
                             const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
-                            ptx::mma_bf16<1>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
-                            ptx::mma_bf16<1>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
-                            ptx::mma_bf16<1>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                            ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
+                            ptx::mma_bf16<CG>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
+                            ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
                         }
-                        ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));   // frees the stage when the MMAs retire
+                        // frees the stage (in both CTAs of a pair) when the MMAs retire
+                        if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));
+                        else ptx::mma_commit_2sm(ptx::smem_u32(&sm->empty[stage]), 3);
                     }
-                    ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
+                    if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
+                    else ptx::mma_commit_2sm(ptx::smem_u32(&sm->tmem_full[buf]), 3);
                 }
             }
         }
@@ -170,10 +198,10 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         const int quarter = warp & 3;                    // TMEM lane quarter this warp may read
         const uint32_t lane_base = uint32_t(quarter * 32) << 16;
         uint32_t tile = 0;
-        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        for (int u = wid; u < units; u += nworkers) {
             int split, rb;
             decode_unit(p.plan, u, rb, split);
-            const int64_t row0 = p.row_begin + int64_t(rb) * TC_BM;
+            const int64_t row0 = p.row_begin + int64_t(rb) * (TC_BM * CG) + int64_t(crank) * TC_BM;
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = split * p.plan.ct_per_split;
             const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
@@ -263,7 +291,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     }
                 }
                 ptx::tc_fence_before();
-                ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
+                if (CG == 1) ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
+                else ptx::mbar_arrive_cluster(ptx::smem_u32(&sm->tmem_empty[buf]), 0);     // the leader's barrier
             }
             if (KL > 0 && row < p.row_end) {
                 const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
@@ -274,48 +303,58 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     }
     ptx::tc_fence_before();
     __syncthreads();
+    if (CG == 2) ptx::cluster_sync();                  // neither CTA may leave while its peer still reads its smem
     if (warp == 1) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc<1>(tmem_base, TC_TMEM_COLS);
+        ptx::tmem_dealloc<CG>(tmem_base, TC_TMEM_COLS);
     }
 }
 
 // ---------------------------------------------------------------------------------------------
+int tc_cta_group() {                       // 1 (default) or 2 = CTA pairs, HG_B200_TC_CG=2
+    const char* e = getenv("HG_B200_TC_CG");
+    return (e && atoi(e) == 2) ? 2 : 1;
+}
+
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     TcPlan pl{};
+    pl.cg = tc_cta_group();
+    const int workers = kNumSMs / pl.cg;               // CTAs or CTA pairs
+    const int rb_rows = TC_BM * pl.cg;                 // query rows per work unit
     pl.n_rows = n_rows;
-    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_rb = int(ceil_div(n_rows, rb_rows));
     pl.num_ct = int(ceil_div(n, TC_BN));
     // list length: k plus slack for the exact re-rank, in the register-array sizes compiled
     pl.kl = (k + 4 <= 8) ? 8 : (k + 4 <= 16) ? 16 : (k + 8 <= 24) ? 24 : 32;
-    // Concurrency shape rc x cc = 148: the A row blocks of the CTAs running together must stay
-    // L2-resident while B streams through (A block = 128 rows x d_pad x (hi + lo)); keep them
+    // Concurrency shape rc x cc = workers: the A row blocks of the workers running together must
+    // stay L2-resident while B streams through (A block = rows x d_pad x (hi + lo)); keep them
     // under ~40 MB of the 126 MB L2.  Then the fewest column splits (a multiple of cc) whose
     // last round wastes the least.
-    const int64_t a_block = int64_t(TC_BM) * d_pad * 4;
+    const int64_t a_block = int64_t(rb_rows) * d_pad * 4;
     const int64_t rc_cap = (int64_t(40) << 20) / a_block;
-    int best_cc = 4, best_s = 4;
+    const int cc_max = 4 / pl.cg;                      // 148 = 4 * 37, 74 = 2 * 37
+    int best_cc = cc_max, best_s = cc_max;
     double best_eff = -1.0;
-    for (int cc = 1; cc <= 4; cc *= 2) {
-        const int rc = kNumSMs / cc;
-        if (rc > rc_cap && cc < 4) continue;
+    for (int cc = 1; cc <= cc_max; cc *= 2) {
+        const int rc = workers / cc;
+        if (rc > rc_cap && cc < cc_max) continue;
         for (int s = cc; s <= TC_MAX_SPLITS; s += cc) {
             if (s > pl.num_ct && s > cc) break;
             const int64_t units = int64_t(pl.num_rb) * s;
-            const double eff = double(units) / double(ceil_div(units, kNumSMs) * kNumSMs);
+            const double eff = double(units) / double(ceil_div(units, workers) * workers);
             if (eff > best_eff + 0.015) { best_eff = eff; best_cc = cc; best_s = s; }
         }
     }
     if (const char* ov = getenv("HG_B200_TC_PLAN")) {          // tuning override: "cc,splits"
         int cc = 0, sp = 0;
-        if (sscanf(ov, "%d,%d", &cc, &sp) == 2 && (cc == 1 || cc == 2 || cc == 4) && sp >= cc && sp <= TC_MAX_SPLITS &&
-            sp % cc == 0) { best_cc = cc; best_s = sp; }
+        if (sscanf(ov, "%d,%d", &cc, &sp) == 2 && (cc == 1 || cc == 2 || cc == 4) && cc <= cc_max && sp >= cc &&
+            sp <= TC_MAX_SPLITS && sp % cc == 0) { best_cc = cc; best_s = sp; }
     }
     pl.cc = best_cc;
-    pl.rc = kNumSMs / best_cc;
+    pl.rc = workers / best_cc;
     pl.splits = best_s;
     pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));     // trailing splits may be empty
-    pl.grid = int(min64(kNumSMs, int64_t(pl.num_rb) * pl.splits));
+    pl.grid = int(min64(workers, int64_t(pl.num_rb) * pl.splits)) * pl.cg;
     return pl;
 }
 
@@ -345,27 +384,38 @@ static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, i
     return HG_OK;
 }
 
-template <int KL>
-static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
-    if (p.pos4 != nullptr) {
-        HG_CHECK_CUDA(cudaFuncSetAttribute(knn_tc_kernel<KL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           int(TC_SMEM_BYTES)));
-        knn_tc_kernel<KL, true><<<p.plan.grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
-    } else {
-        HG_CHECK_CUDA(cudaFuncSetAttribute(knn_tc_kernel<KL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           int(TC_SMEM_BYTES)));
-        knn_tc_kernel<KL, false><<<p.plan.grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
-    }
-    HG_CHECK_LAUNCH();
+template <int KL, bool HAS_POS, int CG>
+static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+    auto kern = knn_tc_kernel<KL, HAS_POS, CG>;
+    constexpr size_t smem = tc_smem_bytes<CG>();
+    HG_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(unsigned(p.plan.grid));
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (CG > 1) ? 1 : 0;
+    HG_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     count_launches(1);
     return HG_OK;
+}
+
+template <int KL>
+static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+    if (p.plan.cg == 2)
+        return p.pos4 ? launch_one<KL, true, 2>(ta, tb, p, st) : launch_one<KL, false, 2>(ta, tb, p, st);
+    return p.pos4 ? launch_one<KL, true, 1>(ta, tb, p, st) : launch_one<KL, false, 1>(ta, tb, p, st);
 }
 
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
     CUtensorMap ta, tb;
     int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN);
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg);     // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

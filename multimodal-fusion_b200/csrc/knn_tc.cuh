@@ -19,6 +19,7 @@ struct TcPlan {
     int ct_per_split;
     int kl;                     // list length kept per (row, split): 8 / 16 / 24 / 32
     int grid;                   // CTAs launched
+    int cg;                     // 1 = one CTA per 128-row tile, 2 = CTA pairs (cta_group::2) on 256-row tiles
 };
 
 struct TcParams {
