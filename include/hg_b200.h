@@ -75,9 +75,18 @@ int hg_split_operands(const float* feats, int64_t n, int64_t d,
  *              F.cosine_similarity (:419).
  * out_idx [rows, k] int32 (-1 when fewer than k candidates exist),
  * out_val [rows, k] float32.  `precision`: 0 = 3xBF16 tensor-core candidates +
- * exact FP32 re-rank (default), 1 = plain FP32 SIMT kernel (any shape). */
+ * exact FP32 re-rank (default), 1 = plain FP32 SIMT kernel (any shape).
+ * Over the full row range of a large slide (n >= 8192) the tensor-core pass exploits the symmetry
+ * of K: about half of the tiles are computed and each serves both (i, j) and (j, i); results are
+ * identical to the full pass (HG_B200_TC_SYM=0 in the environment forces the full pass). */
 int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k,
                                    int64_t row_begin, int64_t row_end, size_t* bytes);
+/* What hg_knn_feature will run for this shape: symmetric_stride > 0 means the symmetric
+ * (half-of-the-tiles) pass with a threshold pre-pass over every stride-th column; mma_flop is the
+ * BF16 tensor-core work actually issued (3 MMAs per product, padded tiles), which is about
+ * 0.56 x 3 x 2 N^2 D in symmetric mode. */
+int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
+                        int* symmetric_stride, double* mma_flop);
 int hg_knn_feature(const float* feats, int64_t n, int64_t d,
                    const float* pos, int pos_dim,
                    int metric, float lambda_h, float lambda_g,

@@ -2,14 +2,27 @@
 // merge + exact re-rank.  See include/hg_b200.h for the contract.
 #include "knn_tc.cuh"
 #include "sim_simt.cuh"
+#include <stdlib.h>
+#include <vector>
 
 namespace hg {
 
 struct KnnWs {
-    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, bytes;
-    TcPlan plan;
+    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_thr, off_cnt, off_ovf, off_bkt, bytes;
+    TcPlan plan;                 // classic plan (the only one, or the overflow fallback of symmetric mode)
+    TcPlan sym_plan, pre_plan;   // symmetric mode: main pass and threshold pre-pass
+    int sym_stride;              // 0 = classic
     int64_t n_pad, d_pad;
 };
+
+// entries per row bucket; HG_B200_TC_BKT_CAP lowers it (tests force the overflow fallback with it)
+static int bucket_cap() {
+    if (const char* e = getenv("HG_B200_TC_BKT_CAP")) {
+        const int v = atoi(e);
+        if (v >= 1 && v <= TC_BKT_CAP) return v;
+    }
+    return TC_BKT_CAP;
+}
 
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
     KnnWs w{};
@@ -22,9 +35,22 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     w.off_norms = take(size_t(w.n_pad) * 4);
     w.off_colp = take(size_t(w.n_pad) * 8);
     w.off_pos4 = take(has_pos ? size_t(w.n_pad) * 16 : 0);
-    const size_t part = size_t(w.plan.splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
+    int max_splits = w.plan.splits;
+    w.sym_stride = tc_sym_stride(n, r1 - r0, k);
+    if (w.sym_stride > 0) {
+        w.sym_plan = tc_make_plan_sym(n, k, w.d_pad);
+        w.pre_plan = tc_make_plan_prepass(n, k, w.d_pad, w.sym_stride);
+        if (w.sym_plan.splits > max_splits) max_splits = w.sym_plan.splits;
+    }
+    const size_t part = size_t(max_splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
+    if (w.sym_stride > 0) {
+        w.off_thr = take(size_t(w.n_pad) * 4);
+        w.off_cnt = take(size_t(w.n_pad) * 4);
+        w.off_ovf = take(8);                    // overflow flag, largest squared norm
+        w.off_bkt = take(size_t(w.n_pad) * TC_BKT_CAP * 8);
+    }
     w.bytes = off;
     return w;
 }
@@ -48,6 +74,28 @@ extern "C" int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k, int64
     int rc = check_knn_args(n, d, k, row_begin, row_end);
     if (rc != HG_OK) return rc;
     *bytes = plan_ws(n, d, k, row_begin, row_end, true).bytes;
+    return HG_OK;
+}
+
+extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
+                                   int* symmetric_stride, double* mma_flop) {
+    int rc = check_knn_args(n, d, k, row_begin, row_end);
+    if (rc != HG_OK) return rc;
+    const KnnWs w = plan_ws(n, d, k, row_begin, row_end, false);
+    auto tiles_of = [](const TcPlan& pl) {
+        if (!pl.sym) return double(pl.num_rb) * double(pl.num_ct);
+        double t = 0;
+        for (int rb = 0; rb < pl.num_rb; ++rb)
+            for (int ct = 0; ct < pl.num_ct; ++ct) {
+                const int a = rb >> 1;
+                t += (ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0))) ? 1.0 : 0.0;
+            }
+        return t;
+    };
+    const double per_tile = 3.0 * 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);     // 3 BF16 MMAs per product
+    double tiles = w.sym_stride > 0 ? tiles_of(w.sym_plan) + tiles_of(w.pre_plan) : tiles_of(w.plan) * w.plan.cg;
+    if (symmetric_stride) *symmetric_stride = w.sym_stride;
+    if (mma_flop) *mma_flop = tiles * per_tile;
     return HG_OK;
 }
 
@@ -91,9 +139,17 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
     float4* pos4 = pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
 
+    const bool sym = w.sym_stride > 0;
+    float* thr = sym ? reinterpret_cast<float*>(ws + w.off_thr) : nullptr;
+    int32_t* bkt_cnt = sym ? reinterpret_cast<int32_t*>(ws + w.off_cnt) : nullptr;
+    int* ovf = sym ? reinterpret_cast<int*>(ws + w.off_ovf) : nullptr;
+    uint2* bkt = sym ? reinterpret_cast<uint2*>(ws + w.off_bkt) : nullptr;
+
     rc = launch_split(feats, n, d, ops, norms, st);
     if (rc != HG_OK) return rc;
-    rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st);
+    float* norm_max = sym ? reinterpret_cast<float*>(ws + w.off_ovf) + 1 : nullptr;
+    if (sym) HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 8, st));
+    rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st, thr, bkt_cnt, norm_max);
     if (rc != HG_OK) return rc;
 
     TcParams tp{};
@@ -104,6 +160,22 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
     tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
     prof_begin(st);
+    if (sym) {
+        // (1) pre-pass over every stride-th column: thr[row] = an upper bound of the row's k-th best
+        //     (the (k+1)-th best of the sample, self not excluded, plus error slack), (2) the half pass,
+        //     (3) the classic full pass, which exits at once unless a bucket overflowed
+        TcParams pre = tp;
+        pre.plan = w.pre_plan; pre.col_stride = w.sym_stride; pre.exclude_self = 0;
+        pre.thr_out = thr; pre.thr_rank = k;
+        pre.thr_margin_cos = (metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
+        rc = tc_launch(ops, w.n_pad, pre, st);
+        if (rc != HG_OK) return rc;
+        TcParams sp = tp;
+        sp.plan = w.sym_plan; sp.thr = thr; sp.bkt_cnt = bkt_cnt; sp.bkt = bkt; sp.bkt_cap = bucket_cap(); sp.ovf = ovf;
+        rc = tc_launch(ops, w.n_pad, sp, st);
+        if (rc != HG_OK) return rc;
+        tp.guard = ovf;
+    }
     rc = tc_launch(ops, w.n_pad, tp, st);
     prof_end(st);
     if (rc != HG_OK) return rc;
@@ -114,5 +186,19 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val;
-    return rerank_launch(rp, st);
+    if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
+    rc = rerank_launch(rp, st);
+    if (rc == HG_OK && sym && getenv("HG_B200_TC_DEBUG")) {      // tuning aid: bucket occupancy (synchronises)
+        std::vector<int32_t> cnt(static_cast<size_t>(n), 0);
+        int h_ovf = 0;
+        HG_CHECK_CUDA(cudaStreamSynchronize(st));
+        HG_CHECK_CUDA(cudaMemcpy(cnt.data(), bkt_cnt, size_t(n) * 4, cudaMemcpyDeviceToHost));
+        HG_CHECK_CUDA(cudaMemcpy(&h_ovf, ovf, 4, cudaMemcpyDeviceToHost));
+        int64_t sum = 0; int mx = 0;
+        for (int32_t c : cnt) { sum += c; mx = c > mx ? c : mx; }
+        fprintf(stderr, "hg_b200 sym: n=%lld stride=%d splits=%d cps=%d pre_ct=%d bucket mean=%.1f max=%d ovf=%d\n",
+                (long long)n, w.sym_stride, w.sym_plan.splits, w.sym_plan.ct_per_split, w.pre_plan.num_ct,
+                double(sum) / double(n), mx, h_ovf);
+    }
+    return rc;
 }

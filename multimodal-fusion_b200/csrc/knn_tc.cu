@@ -25,6 +25,19 @@
 // numbered split-major so the CTAs running concurrently sweep the SAME column
 // range in the same order: a B tile is fetched from HBM once and then served to
 // all 148 SMs out of L2, while each CTA's A block (128 rows) stays L2-resident.
+//
+// Symmetric mode (SYM, full row range): K is symmetric, so only about half of the tiles are
+// computed -- half the MMAs.  With A = the 256-row super-block a row block belongs to and C = a
+// column tile, tile (A, C) is computed iff C == A, or C > A with A + C even, or C < A with A + C
+// odd (a checkerboard: of the two tiles (A, C) and (C, A) exactly one is computed, and every row
+// block sweeps about half of the column tiles).  A computed off-diagonal tile serves two directions:
+//   * row direction, as above: column j is a candidate of row i;
+//   * transposed direction: row i is a candidate OF column j.  Its score a_i + b_i * dot is
+//     compared with thr[j], an upper bound of j's final k-th best that a strided pre-pass (same
+//     kernel, 1/stride of the columns) computed, and the rare survivors go through a per-warp
+//     shared-memory queue into bucket j in global memory.
+// Every ordered pair (i, j), i != j, is covered exactly once; every row receives about half of
+// its candidates through each direction, so bucket occupancy is uniform.
 #include "knn_tc.cuh"
 #include "ptx.cuh"
 #include "topk_list.cuh"
@@ -50,9 +63,14 @@ constexpr int TC_THREADS = 192;
 constexpr int TC_EPI_THREADS = 128;
 constexpr int TC_TMEM_COLS = 512;
 
+constexpr int TC_WQ_CAP = 256;        // transposed-candidate queue entries per epilogue warp
+
 struct TcSmem {                       // lives after the (1024-byte aligned) stage buffers
     float2 colp[2][TC_BN];
     float4 cpos[2][TC_BN];
+    float thr[2][TC_BN];              // SYM: admission threshold of each column of the tile
+    uint2 wq[4][TC_WQ_CAP];           // SYM: (score bits, column-in-tile << 8 | row-in-block)
+    int wq_cnt[4];
     uint64_t full[TC_MAX_STAGES], empty[TC_MAX_STAGES], tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
 };
@@ -65,7 +83,7 @@ constexpr size_t tc_smem_bytes() { return 1024 + size_t(TcCfg<CG>::STAGES) * TcC
 __device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, int& split) {
     const int per_chunk = pl.rc * pl.splits;
     const int g = u / per_chunk;
-    const int rows_here = min(pl.rc, pl.num_rb - g * pl.rc);
+    const int rows_here = min(pl.rc, pl.num_u - g * pl.rc);
     int rem = u - g * per_chunk;
     const int h = rem / (rows_here * pl.cc);
     rem -= h * rows_here * pl.cc;
@@ -74,13 +92,29 @@ __device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, in
     split = h * pl.cc + c;
 }
 
-template <int KL, bool HAS_POS, int CG>
+// Does the unit of row block rb (classic: every tile; symmetric: the checkerboard) own column tile ct?
+template <bool SYM, int CG>
+__device__ __forceinline__ bool owns_tile(int rb, int ct) {
+    if (!SYM) return true;
+    const int a = rb >> 1;                              // 256-row super-block of a 128-row block
+    return ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0));
+}
+
+__device__ __forceinline__ void bucket_push(const TcParams& p, int col, int row, uint32_t score_bits) {
+    const int slot = atomicAdd(p.bkt_cnt + col, 1);
+    if (slot < p.bkt_cap) p.bkt[int64_t(col) * p.bkt_cap + slot] = make_uint2(score_bits, uint32_t(row));
+    else *p.ovf = 1;
+}
+
+template <int KL, bool HAS_POS, int CG, bool SYM>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
               const TcParams p) {
     using Cfg = TcCfg<CG>;
     constexpr int TC_STAGES = Cfg::STAGES;
     constexpr int TC_A_PLANE = Cfg::A_PLANE, TC_B_PLANE = Cfg::B_PLANE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
+    static_assert(!SYM || (CG == 1 && KL > 0), "symmetric mode: single-CTA tiles with candidate lists");
+    if (p.guard != nullptr && *p.guard == 0) return;   // fallback launch that is not needed (grid-uniform)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -88,7 +122,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = p.d_pad / TC_BK;
-    const int units = p.plan.num_rb * p.plan.splits;
+    const int units = p.plan.num_u * p.plan.splits;
     const uint32_t crank = (CG == 2) ? ptx::cluster_ctarank() : 0u;     // 0 = leader of the CTA pair
     const int wid = blockIdx.x / CG, nworkers = gridDim.x / CG;          // a worker = one CTA or one pair
 
@@ -101,6 +135,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             ptx::mbar_init(ptx::smem_u32(&sm->tmem_full[b]), 1);
             ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), TC_EPI_THREADS * CG);
         }
+        for (int q = 0; q < 4; ++q) sm->wq_cnt[q] = 0;
         ptx::fence_barrier_init();
         ptx::fence_proxy_async();
     }
@@ -129,6 +164,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
+                    if (!owns_tile<SYM, CG>(rb, ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
                         ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
@@ -161,7 +197,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 decode_unit(p.plan, u, rb, split);
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
-                for (int ct = ct0; ct < ct1; ++ct, ++tile) {
+                for (int ct = ct0; ct < ct1; ++ct) {
+                    if (!owns_tile<SYM, CG>(rb, ct)) continue;
                     const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
                     ptx::mbar_wait(ptx::smem_u32(&sm->tmem_empty[buf]), tph ^ 1u);
                     ptx::tc_fence_after();
@@ -189,6 +226,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     }
                     if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
                     else ptx::mma_commit_2sm(ptx::smem_u32(&sm->tmem_full[buf]), 3);
+                    ++tile;
                 }
             }
         }
@@ -197,6 +235,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         const int et = threadIdx.x - 64;                 // 0..127
         const int quarter = warp & 3;                    // TMEM lane quarter this warp may read
         const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+        constexpr int KLA = KL > 0 ? KL : 1;             // KL == 0: dense-output mode, no lists
+        const int cstride = p.col_stride;
         uint32_t tile = 0;
         for (int u = wid; u < units; u += nworkers) {
             int split, rb;
@@ -205,28 +245,50 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = split * p.plan.ct_per_split;
             const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
-            constexpr int KLA = KL > 0 ? KL : 1;           // KL == 0: dense-output mode, no lists
             float lv[KLA];
             int li[KLA];
 #pragma unroll
             for (int q = 0; q < KLA; ++q) { lv[q] = INFINITY; li[q] = -1; }
-            const float row_norm = (KL == 0 && row < p.n) ? __ldg(p.colp + row).x : 0.f;
+            // this row's own score parameters; padded rows: (+inf, 0)
+            const float2 me = (row < p.n_pad) ? __ldg(p.colp + row) : make_float2(INFINITY, 0.f);
+            const float row_norm = me.x, ta = me.x, tb = me.y;
             float4 mypos = make_float4(0.f, 0.f, 0.f, 0.f);
             if (HAS_POS && row < p.n) mypos = __ldg(p.pos4 + row);
-            for (int ct = ct0; ct < ct1; ++ct, ++tile) {
+            // SYM: the pre-pass bound of this row also gates its own list (nothing above it can be in
+            // the final top-k), which removes the warm-up insertions of every unit; NaN on padded rows
+            const float row_bound = SYM ? __ldg(p.thr + row) : INFINITY;
+            for (int ct = ct0; ct < ct1; ++ct) {
+                if (!owns_tile<SYM, CG>(rb, ct)) continue;
                 const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
                 const int col0 = ct * TC_BN;
-                sm->colp[buf][et] = __ldg(p.colp + col0 + et);
-                sm->colp[buf][et + 128] = __ldg(p.colp + col0 + et + 128);
-                if (HAS_POS) {
-                    sm->cpos[buf][et] = __ldg(p.pos4 + col0 + et);
-                    sm->cpos[buf][et + 128] = __ldg(p.pos4 + col0 + et + 128);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c = et + 128 * h;
+                    const int64_t src = int64_t(col0 + c) * cstride;      // operand row behind column c
+                    const bool ok = src < p.n_pad;
+                    sm->colp[buf][c] = ok ? __ldg(p.colp + src) : make_float2(INFINITY, 0.f);
+                    if (HAS_POS) sm->cpos[buf][c] = ok ? __ldg(p.pos4 + src) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (SYM) sm->thr[buf][c] = __ldg(p.thr + col0 + c);    // NaN beyond n: never admitted
                 }
                 ptx::named_bar_sync(1, TC_EPI_THREADS);
                 ptx::mbar_wait(ptx::smem_u32(&sm->tmem_full[buf]), tph);
                 ptx::tc_fence_after();
-                const bool diag = p.exclude_self && (col0 < row0 + TC_BM) && (row0 < col0 + TC_BN);
+                const bool diag = p.exclude_self && (col0 < row0 + TC_BM) && (row0 < col0 + TC_BN) && cstride == 1;
                 const int self_col = diag ? int(row - col0) : -1;     // column inside this tile, if any
+                const bool transposed = SYM && ct != (rb >> 1);        // the diagonal tile serves rows only
+                // ranking score of (this row, column c) and, SYM, of (column c, this row)
+                auto scores = [&](int c, float dot, float& s_row, float& s_tr) {
+                    const float2 cp = sm->colp[buf][c];
+                    s_row = fmaf(cp.y, dot, cp.x);
+                    if (SYM) s_tr = fmaf(tb, dot, ta);
+                    if (HAS_POS) {
+                        const float4 q = sm->cpos[buf][c];
+                        const float dx = mypos.x - q.x, dy = mypos.y - q.y, dz = mypos.z - q.z;
+                        const float g = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                        s_row = fmaf(p.gscale, g, s_row);
+                        if (SYM) s_tr = fmaf(p.gscale, g, s_tr);
+                    }
+                };
 #pragma unroll 1
                 for (int ch = 0; ch < TC_BN / 32; ++ch) {
                     uint32_t r[32];
@@ -242,14 +304,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                             float v[4];
 #pragma unroll
                             for (int q = 0; q < 4; ++q) {
-                                const int c = ch * 32 + j + q;
-                                const float2 cp = sm->colp[buf][c];
-                                float s = fmaf(cp.y, __uint_as_float(r[j + q]), cp.x);
-                                if (HAS_POS) {
-                                    const float4 g4 = sm->cpos[buf][c];
-                                    const float dx = mypos.x - g4.x, dy = mypos.y - g4.y, dz = mypos.z - g4.z;
-                                    s = fmaf(p.gscale, fmaf(dx, dx, fmaf(dy, dy, dz * dz)), s);
-                                }
+                                float s, unused;
+                                scores(ch * 32 + j + q, __uint_as_float(r[j + q]), s, unused);
                                 v[q] = expf(-p.lambda_h * (row_norm + s));
                             }
                             if (full) {
@@ -262,22 +318,18 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         }
                         continue;
                     }
-                    // pass 1 (straight-line): scores in place, bitmask of columns beating the current k-th
-                    uint32_t hits = 0;
-                    const float thr = lv[KLA - 1];
+                    // pass 1 (straight-line): bitmask of the columns that beat the row's current k-th
+                    // best and, SYM, of the columns whose admission threshold this row beats
+                    uint32_t hits = 0, hits_t = 0;
+                    const float thr = SYM ? fminf(lv[KLA - 1], row_bound) : lv[KLA - 1];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int c = ch * 32 + j;
-                        const float2 cp = sm->colp[buf][c];
-                        float s = fmaf(cp.y, __uint_as_float(r[j]), cp.x);
-                        if (HAS_POS) {
-                            const float4 q = sm->cpos[buf][c];
-                            const float dx = mypos.x - q.x, dy = mypos.y - q.y, dz = mypos.z - q.z;
-                            s = fmaf(p.gscale, fmaf(dx, dx, fmaf(dy, dy, dz * dz)), s);
-                        }
+                        float s, st;
+                        scores(c, __uint_as_float(r[j]), s, st);
                         if (c == self_col) s = INFINITY;
-                        r[j] = __float_as_uint(s);
                         hits |= (s < thr) ? (1u << j) : 0u;
+                        if (SYM) hits_t |= (st < sm->thr[buf][c]) ? (1u << j) : 0u;
                     }
                     // pass 2 (rare): ascending column order keeps the lowest index among equal scores
                     while (hits) {
@@ -286,18 +338,63 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         uint32_t bits = r[0];
 #pragma unroll
                         for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
-                        const float s = __uint_as_float(bits);
-                        if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, col0 + ch * 32 + j);
+                        float s, st;
+                        scores(ch * 32 + j, __uint_as_float(bits), s, st);
+                        if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, (col0 + ch * 32 + j) * cstride);
+                    }
+                    if (SYM) {
+                        // transposed survivors: (score, column, row) into this warp's queue
+                        if (!transposed) hits_t = 0;
+                        while (hits_t) {
+                            const int j = __ffs(hits_t) - 1;
+                            hits_t &= hits_t - 1;
+                            uint32_t bits = r[0];
+#pragma unroll
+                            for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
+                            float s, st;
+                            scores(ch * 32 + j, __uint_as_float(bits), s, st);
+                            const int slot = atomicAdd(&sm->wq_cnt[quarter], 1);
+                            if (slot < TC_WQ_CAP)
+                                sm->wq[quarter][slot] = make_uint2(__float_as_uint(st),
+                                                                   uint32_t((ch * 32 + j) << 8) | uint32_t(quarter * 32 + lane));
+                            else
+                                bucket_push(p, col0 + ch * 32 + j, int(row), __float_as_uint(st));
+                        }
                     }
                 }
                 ptx::tc_fence_before();
                 if (CG == 1) ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
                 else ptx::mbar_arrive_cluster(ptx::smem_u32(&sm->tmem_empty[buf]), 0);     // the leader's barrier
+                if (SYM) {
+                    // drain the warp's queue into the per-column buckets, one entry per lane and round
+                    __syncwarp();
+                    const int queued = min(sm->wq_cnt[quarter], TC_WQ_CAP);
+                    for (int e = lane; e < queued; e += 32) {
+                        const uint2 q = sm->wq[quarter][e];
+                        bucket_push(p, col0 + int(q.y >> 8), int(row0) + int(q.y & 0xffu), q.x);
+                    }
+                    __syncwarp();
+                    if (lane == 0) sm->wq_cnt[quarter] = 0;
+                    __syncwarp();
+                }
+                ++tile;
             }
+            // the unit's result: the threshold (pre-pass) or the candidate list of (row, split)
             if (KL > 0 && row < p.row_end) {
-                const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+                if (p.thr_out != nullptr) {
+                    float t = INFINITY;                   // the list ascends: min over q >= rank is lv[rank]
 #pragma unroll
-                for (int q = 0; q < KL; ++q) { p.part_val[o + q] = lv[q]; p.part_idx[o + q] = li[q]; }
+                    for (int q = 0; q < KLA; ++q) t = fminf(t, (q >= p.thr_rank) ? lv[q] : INFINITY);
+                    // guaranteed slack for the 3xBF16 error of a score (dropped lo*lo term <= 2^-16 |x_i||x_j|,
+                    // FP32 accumulation, both tile orientations): Euclidean / Gaussian scores n_j - 2 dot,
+                    // cosine scores -dot / |x_j|
+                    const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
+                    p.thr_out[row] = t + 4.8828125e-4f * scale;
+                } else {
+                    const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+#pragma unroll
+                    for (int q = 0; q < KLA; ++q) { p.part_val[o + q] = lv[q]; p.part_idx[o + q] = li[q]; }
+                }
             }
         }
     }
@@ -316,21 +413,18 @@ int tc_cta_group() {                       // 1 (default) or 2 = CTA pairs, HG_B
     return (e && atoi(e) == 2) ? 2 : 1;
 }
 
-TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
-    TcPlan pl{};
-    pl.cg = tc_cta_group();
+static int list_len(int k) {            // k plus slack for the exact re-rank, in the register-array sizes compiled
+    return (k + 4 <= 8) ? 8 : (k + 4 <= 16) ? 16 : (k + 8 <= 24) ? 24 : 32;
+}
+
+// Concurrency shape rc x cc = workers and the split count.  The A row blocks of the workers
+// running together must stay L2-resident while B streams through (A block = rows x d_pad x
+// (hi + lo)); keep them under ~40 MB of the 126 MB L2.  Then the fewest column splits (a
+// multiple of cc) whose last round wastes the least.  `major` = row blocks or row-block pairs,
+// `tiles` = column tiles a major unit sweeps.
+static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
     const int workers = kNumSMs / pl.cg;               // CTAs or CTA pairs
-    const int rb_rows = TC_BM * pl.cg;                 // query rows per work unit
-    pl.n_rows = n_rows;
-    pl.num_rb = int(ceil_div(n_rows, rb_rows));
-    pl.num_ct = int(ceil_div(n, TC_BN));
-    // list length: k plus slack for the exact re-rank, in the register-array sizes compiled
-    pl.kl = (k + 4 <= 8) ? 8 : (k + 4 <= 16) ? 16 : (k + 8 <= 24) ? 24 : 32;
-    // Concurrency shape rc x cc = workers: the A row blocks of the workers running together must
-    // stay L2-resident while B streams through (A block = rows x d_pad x (hi + lo)); keep them
-    // under ~40 MB of the 126 MB L2.  Then the fewest column splits (a multiple of cc) whose
-    // last round wastes the least.
-    const int64_t a_block = int64_t(rb_rows) * d_pad * 4;
+    const int64_t a_block = int64_t(TC_BM * pl.cg) * d_pad * 4;
     const int64_t rc_cap = (int64_t(40) << 20) / a_block;
     const int cc_max = 4 / pl.cg;                      // 148 = 4 * 37, 74 = 2 * 37
     int best_cc = cc_max, best_s = cc_max;
@@ -339,9 +433,11 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
         const int rc = workers / cc;
         if (rc > rc_cap && cc < cc_max) continue;
         for (int s = cc; s <= TC_MAX_SPLITS; s += cc) {
-            if (s > pl.num_ct && s > cc) break;
-            const int64_t units = int64_t(pl.num_rb) * s;
-            const double eff = double(units) / double(ceil_div(units, workers) * workers);
+            if (s > tiles && s > cc) break;
+            const int64_t units = int64_t(major) * s;
+            // a unit is ceil(tiles / s) tiles long: count the padding of the last split as waste too
+            const double fill = double(tiles) / double(ceil_div(tiles, s) * s);
+            const double eff = fill * double(units) / double(ceil_div(units, workers) * workers);
             if (eff > best_eff + 0.015) { best_eff = eff; best_cc = cc; best_s = s; }
         }
     }
@@ -353,9 +449,67 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     pl.cc = best_cc;
     pl.rc = workers / best_cc;
     pl.splits = best_s;
+    pl.grid = int(min64(workers, int64_t(major) * pl.splits)) * pl.cg;
+}
+
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
+    TcPlan pl{};
+    pl.cg = tc_cta_group();
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cg));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(n, TC_BN));
+    pl.kl = list_len(k);
+    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad);
     pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));     // trailing splits may be empty
-    pl.grid = int(min64(workers, int64_t(pl.num_rb) * pl.splits)) * pl.cg;
     return pl;
+}
+
+// Threshold pre-pass: all rows against every stride-th column, one unit per row block (the
+// bound must come from ONE list per row).
+TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
+    TcPlan pl{};
+    pl.cg = 1;
+    pl.n_rows = n;
+    pl.num_rb = int(ceil_div(n, TC_BM));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(ceil_div(n, stride), TC_BN));
+    pl.kl = list_len(k);
+    pl.cc = 1; pl.rc = kNumSMs; pl.splits = 1;
+    pl.ct_per_split = pl.num_ct;
+    pl.grid = int(min64(kNumSMs, pl.num_rb));
+    (void)d_pad;
+    return pl;
+}
+
+// Symmetric plan over the full row range: the classic unit grid, of which each unit computes
+// only the tiles it owns (about every other one).
+TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
+    TcPlan pl{};
+    pl.cg = 1;
+    pl.sym = 1;
+    pl.n_rows = n;
+    pl.num_rb = int(ceil_div(n, TC_BM));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(n, TC_BN));
+    pl.kl = list_len(k);
+    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad);
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
+    return pl;
+}
+
+// Symmetric mode pays a 1/stride pre-pass and needs enough sample columns for a useful bound.
+// HG_B200_TC_SYM=0 disables it, =<stride> forces the pre-pass stride.
+int tc_sym_stride(int64_t n, int64_t n_rows, int k) {
+    if (n_rows != n || tc_cta_group() != 1) return 0;
+    int stride = (n >= 32768) ? 16 : 8;
+    if (const char* e = getenv("HG_B200_TC_SYM")) {
+        const int v = atoi(e);
+        if (v <= 0) return 0;
+        if (v >= 2 && v <= 64) stride = v;
+    }
+    if (n < 8192 || n / stride < 4 * (k + 8)) return 0;
+    return stride;
 }
 
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
@@ -370,11 +524,13 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
     return fn;
 }
 
-static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows) {
+// row_stride > 1: a view of every row_stride-th operand row (the pre-pass column sample)
+static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows,
+                     int row_stride = 1) {
     auto enc = get_encode_fn();
     HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
-    cuuint64_t dims[3] = {cuuint64_t(d_pad), cuuint64_t(n_pad), 2};
-    cuuint64_t strides[2] = {cuuint64_t(d_pad) * 2, cuuint64_t(n_pad) * cuuint64_t(d_pad) * 2};
+    cuuint64_t dims[3] = {cuuint64_t(d_pad), cuuint64_t(ceil_div(n_pad, row_stride)), 2};
+    cuuint64_t strides[2] = {cuuint64_t(d_pad) * 2 * cuuint64_t(row_stride), cuuint64_t(n_pad) * cuuint64_t(d_pad) * 2};
     cuuint32_t box[3] = {cuuint32_t(TC_BK), cuuint32_t(box_rows), 2};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
@@ -384,10 +540,11 @@ static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, i
     return HG_OK;
 }
 
-template <int KL, bool HAS_POS, int CG>
+template <int KL, bool HAS_POS, int CG, bool SYM>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
-    auto kern = knn_tc_kernel<KL, HAS_POS, CG>;
+    auto kern = knn_tc_kernel<KL, HAS_POS, CG, SYM>;
     constexpr size_t smem = tc_smem_bytes<CG>();
+    static_assert(smem <= 232448, "over the 227 KB dynamic shared memory limit");
     HG_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(unsigned(p.plan.grid));
@@ -406,16 +563,27 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
 
 template <int KL>
 static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
+    if constexpr (KL > 0) {
+        if (p.plan.sym)
+            return p.pos4 ? launch_one<KL, true, 1, true>(ta, tb, p, st) : launch_one<KL, false, 1, true>(ta, tb, p, st);
+    }
     if (p.plan.cg == 2)
-        return p.pos4 ? launch_one<KL, true, 2>(ta, tb, p, st) : launch_one<KL, false, 2>(ta, tb, p, st);
-    return p.pos4 ? launch_one<KL, true, 1>(ta, tb, p, st) : launch_one<KL, false, 1>(ta, tb, p, st);
+        return p.pos4 ? launch_one<KL, true, 2, false>(ta, tb, p, st) : launch_one<KL, false, 2, false>(ta, tb, p, st);
+    return p.pos4 ? launch_one<KL, true, 1, false>(ta, tb, p, st) : launch_one<KL, false, 1, false>(ta, tb, p, st);
 }
 
-int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
+int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cudaStream_t st) {
+    TcParams p = p_in;
+    p.n_pad = n_pad;
+    if (p.col_stride < 1) p.col_stride = 1;
+    HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
+                               p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),
+               HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
+    HG_REQUIRE(p.col_stride == 1 || (p.plan.cg == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need cg 1");
     CUtensorMap ta, tb;
     int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg);     // a CTA of a pair stages half of the B tile
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

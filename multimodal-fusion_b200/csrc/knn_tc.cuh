@@ -20,6 +20,10 @@ struct TcPlan {
     int kl;                     // list length kept per (row, split): 8 / 16 / 24 / 32
     int grid;                   // CTAs launched
     int cg;                     // 1 = one CTA per 128-row tile, 2 = CTA pairs (cta_group::2) on 256-row tiles
+    // symmetric mode (sym = 1, full row range only): a checkerboard half of the tiles is computed
+    // and each one also serves the transposed direction (see knn_tc.cu)
+    int sym;
+    int num_u;                  // major units of the work list (= num_rb)
 };
 
 struct TcParams {
@@ -37,9 +41,30 @@ struct TcParams {
     float* dense_out;
     int64_t dense_ld;
     float lambda_h;
+    // threshold pre-pass: the kernel's column c is operand row c * col_stride (the B tensor map is
+    // strided to match); instead of candidate lists it writes thr_out[row] = the thr_rank-th best
+    // score of the sample, an upper bound of the row's final k-th best.
+    int64_t n_pad;
+    int col_stride;
+    float* thr_out;
+    int thr_rank;
+    int thr_margin_cos;         // error slack added to thr_out scales with |x_i| (cosine) or n_i + norm_max
+    const float* norm_max;      // largest squared row norm
+    // symmetric mode: transposed candidates (column j gets row i) with score < thr[j] are
+    // appended to bucket j (bkt_cap entries of (score bits, row)); *ovf is raised on overflow
+    const float* thr;
+    int32_t* bkt_cnt;
+    uint2* bkt;
+    int bkt_cap;
+    int* ovf;
+    const int* guard;           // non-null: the whole grid exits at once unless *guard != 0
 };
 
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad);
+TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad);
+TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride);
+int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride
+constexpr int TC_BKT_CAP = 512;
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
 
 struct RerankParams {
@@ -48,12 +73,18 @@ struct RerankParams {
     int metric; float lambda_h, lambda_g;
     const float* part_val; const int32_t* part_idx;
     int splits, kl; int64_t n_rows, row_begin;
+    // symmetric mode: candidates = per-(row, split) lists of the sym plan + the row's bucket;
+    // if *ovf != 0 the classic kernel re-ran and (splits, kl) above describe its lists
+    TcPlan sym_plan; const int32_t* bkt_cnt; const uint2* bkt; int bkt_cap; const int* ovf;
     int k;
     int32_t* out_idx; float* out_val;
 };
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 
+// also resets the symmetric-mode state when given: thr = NaN, bucket counts = 0, and folds the
+// largest squared norm into *norm_max (zeroed by the caller)
 int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
-                     float2* colp, float4* pos4, cudaStream_t st);
+                     float2* colp, float4* pos4, cudaStream_t st,
+                     float* thr = nullptr, int32_t* bkt_cnt = nullptr, float* norm_max = nullptr);
 
 }  // namespace hg

@@ -14,9 +14,18 @@ namespace hg {
 
 __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float* __restrict__ pos, int pos_dim,
                                  int64_t n, int64_t n_pad, int metric, float2* __restrict__ colp,
-                                 float4* __restrict__ pos4) {
+                                 float4* __restrict__ pos4, float* __restrict__ thr, int32_t* __restrict__ bkt_cnt,
+                                 float* __restrict__ norm_max) {
     const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (j >= n_pad) return;
+    if (thr != nullptr) {
+        thr[j] = __int_as_float(0x7fc00000); bkt_cnt[j] = 0;
+        // non-negative floats order like their bit patterns; one atomic per warp
+        float m = (j < n) ? sq_norms[j] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(norm_max), __float_as_int(m));
+    }
     float2 cp = make_float2(INFINITY, 0.f);          // padded columns can never be selected
     if (j < n) {
         const float nj = sq_norms[j];
@@ -36,8 +45,9 @@ __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float
 }
 
 int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
-                     float2* colp, float4* pos4, cudaStream_t st) {
-    colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, pos, pos_dim, n, n_pad, metric, colp, pos4);
+                     float2* colp, float4* pos4, cudaStream_t st, float* thr, int32_t* bkt_cnt, float* norm_max) {
+    colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, pos, pos_dim, n, n_pad, metric, colp, pos4,
+                                                                     thr, bkt_cnt, norm_max);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -48,7 +58,8 @@ __device__ __forceinline__ bool pair_less(float va, int ia, float vb, int ib) {
 }
 
 constexpr int RR_WARPS = 8;
-constexpr int RR_MAX_CAND = TC_MAX_SPLITS * 32;      // 256 candidates per row at most
+constexpr int RR_MAX_LIST = TC_MAX_SPLITS * 32;      // 256 list candidates per row at most
+constexpr int RR_MAX_CAND = RR_MAX_LIST + TC_BKT_CAP; // + the row's bucket (symmetric mode)
 
 __global__ void __launch_bounds__(RR_WARPS * 32)
 rerank_kernel(const RerankParams p) {
@@ -56,9 +67,15 @@ rerank_kernel(const RerankParams p) {
     const int64_t r = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
     if (r >= p.n_rows) return;
     const int64_t row = p.row_begin + r;
-    const int total = p.splits * p.kl;
+    // symmetric mode unless the bucket overflow flag made the classic kernel re-run
+    const bool sym = p.ovf != nullptr && *p.ovf == 0;
+    const int splits = sym ? p.sym_plan.splits : p.splits;
+    const int total = splits * p.kl;
+    const int nbkt = sym ? min(p.bkt_cnt[row], p.bkt_cap) : 0;
 
     // ---- 1. merge: the kl best approximate candidates, lane t ends up holding the t-th -------------
+    // slots [0, total) = the split lists, [total, ncand) = the bucket
+    const int ncand = total + nbkt;
     float cv[RR_MAX_CAND / 32];
     int ci[RR_MAX_CAND / 32];
 #pragma unroll
@@ -70,14 +87,19 @@ rerank_kernel(const RerankParams p) {
             const int64_t o = (int64_t(s) * p.n_rows + r) * p.kl + w;
             const int idx = p.part_idx[o];
             if (idx >= 0) { cv[q] = p.part_val[o]; ci[q] = idx; }
+        } else if (t < ncand) {
+            const uint2 b = p.bkt[row * p.bkt_cap + (t - total)];
+            cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
         }
     }
     int sel = -1;                                    // candidate column held by this lane (lane < kl)
     for (int t = 0; t < p.kl; ++t) {
         float bv = INFINITY; int bi = 0x7fffffff;
 #pragma unroll
-        for (int q = 0; q < RR_MAX_CAND / 32; ++q)
+        for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+            if (q * 32 >= ncand) break;              // warp-uniform
             if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
@@ -86,8 +108,10 @@ rerank_kernel(const RerankParams p) {
         }
         if (bi == 0x7fffffff) break;                 // fewer than kl real candidates
 #pragma unroll
-        for (int q = 0; q < RR_MAX_CAND / 32; ++q)
+        for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+            if (q * 32 >= ncand) break;
             if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }   // column ids are unique per row
+        }
         if (lane == t) sel = bi;
     }
 
@@ -196,7 +220,8 @@ rerank_kernel(const RerankParams p) {
 }
 
 int rerank_launch(const RerankParams& p, cudaStream_t st) {
-    HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_CAND, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
+    HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_LIST && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
+               p.bkt_cap <= TC_BKT_CAP, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
     rerank_kernel<<<(unsigned)ceil_div(p.n_rows, RR_WARPS), RR_WARPS * 32, 0, st>>>(p);
     HG_CHECK_LAUNCH();
     count_launches(1);

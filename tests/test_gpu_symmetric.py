@@ -1,0 +1,106 @@
+"""Symmetric mode of the fused similarity + top-k stage (knn_tc.cu): half of the tiles are computed,
+each serves (i, j) and (j, i).  Its neighbour lists must equal the full pass bit for bit, and the
+oracle on sampled rows; the bucket-overflow fallback must give the same answer too."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from hg_b200 import _lib, ops, synth
+from test_gpu_parity import _cuda, check_knn
+
+pytestmark = pytest.mark.gpu
+
+
+class _env:
+    def __init__(self, **kv):
+        self.kv = {k: str(v) for k, v in kv.items()}
+
+    def __enter__(self):
+        self.old = {k: os.environ.get(k) for k in self.kv}
+        os.environ.update(self.kv)
+
+    def __exit__(self, *exc):
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def _plan(n, d, k, r0=0, r1=None):
+    lib = _lib.load_library()
+    stride, flop = ctypes.c_int(0), ctypes.c_double(0)
+    _lib.check(lib.hg_knn_feature_plan(n, d, k, r0, n if r1 is None else r1, ctypes.byref(stride), ctypes.byref(flop)))
+    return stride.value, flop.value
+
+
+def _both(x, k, metric, **kw):
+    with _env(HG_B200_TC_SYM=0):
+        full = ops.knn_feature(x, k, metric, **kw)
+    sym = ops.knn_feature(x, k, metric, **kw)
+    torch.cuda.synchronize()
+    return full, sym
+
+
+@pytest.mark.parametrize("n,d,k,metric,with_pos", [
+    (8192, 256, 8, "gaussian", False),          # smallest symmetric shape, stride 8
+    (12345, 200, 16, "gaussian", True),         # ragged n and d, spatial term in the epilogue
+    (20000, 512, 8, "cosine", False),
+    (33000, 128, 5, "euclidean", False),        # stride 16
+])
+def test_symmetric_equals_full_pass(n, d, k, metric, with_pos):
+    stride, flop = _plan(n, d, k)
+    assert stride in (8, 16)
+    d_pad = -(-d // 64) * 64
+    assert flop < 0.66 * 3 * 2.0 * n * n * d_pad * 1.1          # about 0.56 of the full pass
+    feats, pos = synth.make_slide(n, d, 11, "cosine" if metric == "cosine" else "gaussian")
+    kw = dict(positions=_cuda(pos), lambda_h=1.0, lambda_g=1.0 / 128) if with_pos else {}
+    (fi, fv), (si, sv) = _both(_cuda(feats), k, metric, **kw)
+    assert torch.equal(fi, si)
+    assert torch.equal(fv, sv)
+    rows = np.random.default_rng(0).choice(n, 256, replace=False)
+    check_knn(si.cpu().numpy()[rows], feats, k, metric, rows=rows, pos=pos if with_pos else None,
+              lambda_h=1.0, lambda_g=1.0 / 128 if with_pos else 0.0)
+
+
+def test_row_ranges_and_small_slides_use_the_full_pass():
+    assert _plan(50000, 1024, 16, 0, 25000)[0] == 0
+    assert _plan(4096, 1024, 8)[0] == 0
+    with _env(HG_B200_TC_SYM=0):
+        assert _plan(50000, 1024, 16)[0] == 0
+    stride, flop = _plan(50000, 1024, 16)
+    assert stride == 16 and 0.5 < flop / (3 * 2.0 * 50000.0 ** 2 * 1024) < 0.6
+
+
+def test_bucket_overflow_falls_back_to_the_full_pass():
+    n, d, k = 9000, 128, 8
+    feats = synth.make_features(n, d, 5, "gaussian")
+    x = _cuda(feats)
+    with _env(HG_B200_TC_SYM=0):
+        fi, fv = ops.knn_feature(x, k, "gaussian")
+    with _env(HG_B200_TC_BKT_CAP=4):           # every bucket overflows -> guarded full pass runs
+        si, sv = ops.knn_feature(x, k, "gaussian")
+    torch.cuda.synchronize()
+    assert torch.equal(fi, si) and torch.equal(fv, sv)
+
+
+def test_symmetric_with_duplicate_rows_and_outlier_norms():
+    """Exact duplicates give score ties at the admission threshold; one huge-norm row stretches the
+    error slack of every threshold.  Sets must still match the full pass."""
+    n, d, k = 10000, 96, 8
+    rng = np.random.default_rng(3)
+    feats = synth.make_features(n, d, 9, "gaussian")
+    dup = rng.choice(n, 2000, replace=False)
+    feats[dup] = feats[rng.choice(n, 2000)]                  # many exact copies
+    feats[17] *= 300.0
+    (fi, fv), (si, sv) = _both(_cuda(feats), k, "gaussian")
+    a, b = np.sort(fi.cpu().numpy(), 1), np.sort(si.cpu().numpy(), 1)
+    differ = np.nonzero((a != b).any(1))[0]
+    # only tie rows (equal k-th and (k+1)-th exact value) may choose a different copy
+    fvn, svn = fv.cpu().numpy(), sv.cpu().numpy()
+    np.testing.assert_array_equal(fvn[~np.isin(np.arange(n), differ)], svn[~np.isin(np.arange(n), differ)])
+    for r in differ:
+        np.testing.assert_array_equal(fvn[r], svn[r])        # same values, different duplicate picked
