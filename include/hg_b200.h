@@ -95,6 +95,17 @@ int hg_knn_feature(const float* feats, int64_t n, int64_t d,
                    int32_t* out_idx, float* out_val,
                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* hg_knn_feature that also writes out_cos [rows, k] (may be NULL): cos(f_row, f_idx) of every list
+ * entry, a by-product of the exact re-rank, bit-identical to what hg_edge_weights_cosine computes
+ * for the pair -- the input of hg_edge_weights_from_knn.  Tensor-core path only. */
+int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
+                       const float* pos, int pos_dim,
+                       int metric, float lambda_h, float lambda_g,
+                       int k, int64_t row_begin, int64_t row_end, int exclude_self,
+                       int precision,
+                       int32_t* out_idx, float* out_val, float* out_cos,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- A1/A2/A7: dense (small-N / rectangular) Gaussian kernel -----------------
  * out[i, j] = exp(-lambda_h d2(a_i, b_j) - lambda_g d2(pa_i, pb_j)), un-clamped.
  * b == NULL means b = a (square).  pos_* may be NULL.
@@ -155,6 +166,14 @@ int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
 int hg_edge_weights_cosine(const float* feats, int64_t n, int64_t d,
                            const int64_t* edge_index, int64_t num_edges,
                            float* weights, void* stream);
+
+/* A6 without re-reading feature rows: w_e looked up in the feature-kNN lists (knn_idx / knn_cos
+ * [n, k] of a full-range hg_knn_feature_cos call); edges found in neither endpoint's list
+ * (spatial kNN, cliques) are computed from the rows as above.  Same values bit for bit. */
+int hg_edge_weights_from_knn(const float* feats, int64_t n, int64_t d,
+                             const int32_t* knn_idx, const float* knn_cos, int k,
+                             const int64_t* edge_index, int64_t num_edges,
+                             float* weights, void* stream);
 
 /* ---- CSR incidence of the undirected pair list ---------------------------------------
  * rowptr [n+1], col [2E] (neighbour), eid [2E] (edge id), rows sorted by neighbour.

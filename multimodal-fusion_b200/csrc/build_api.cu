@@ -8,7 +8,7 @@
 namespace hg {
 static size_t al1k(size_t b) { return (b + 1023) & ~size_t(1023); }
 
-struct BuildWs { size_t off_knn, off_spatial, off_edges, off_csr, bytes; size_t knn, spatial, edges, csr; };
+struct BuildWs { size_t off_knn, off_spatial, off_edges, off_csr, off_cos, bytes; size_t knn, spatial, edges, csr; };
 
 static int plan_build(int64_t n, int64_t d, int k, int spatial_k, int num_hyperedges, int64_t clique_pairs,
                       int64_t max_edges, bool want_csr, BuildWs* w) {
@@ -34,7 +34,9 @@ static int plan_build(int64_t n, int64_t d, int k, int spatial_k, int num_hypere
     w->off_edges = 0;
     w->off_csr = al1k(w->edges);
     const size_t stage2 = w->off_csr + al1k(w->csr);
-    w->bytes = stage1 > stage2 ? stage1 : stage2;
+    // cos(f_i, f_j) of every feature-kNN entry lives through both stages (edge weights read it)
+    w->off_cos = stage1 > stage2 ? stage1 : stage2;
+    w->bytes = w->off_cos + al1k(size_t(n) * size_t(k) * 4);
     return HG_OK;
 }
 }  // namespace hg
@@ -77,8 +79,9 @@ extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d,
                "hg_build_knn_hypergraph: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
     char* ws = static_cast<char*>(workspace);
 
-    rc = hg_knn_feature(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, 0, n, 1, 0, knn_idx, knn_val,
-                        ws + w.off_knn, w.knn, stream);
+    float* knn_cos = reinterpret_cast<float*>(ws + w.off_cos);
+    rc = hg_knn_feature_cos(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, 0, n, 1, 0, knn_idx, knn_val,
+                            knn_cos, ws + w.off_knn, w.knn, stream);
     if (rc != HG_OK) return rc;
     const int32_t* lists[2] = {knn_idx, nullptr};
     int ks[2] = {k, 0};
@@ -96,7 +99,7 @@ extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d,
     HG_REQUIRE(e <= max_edges, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: %lld edges exceed max_edges", (long long)e);
     rc = hg_edges_fill(e, edge_index, ws + w.off_edges, w.edges, stream);
     if (rc != HG_OK) return rc;
-    rc = hg_edge_weights_cosine(feats, n, d, edge_index, e, edge_weights, stream);
+    rc = hg_edge_weights_from_knn(feats, n, d, knn_idx, knn_cos, k, edge_index, e, edge_weights, stream);
     if (rc != HG_OK) return rc;
     if (want_csr) {
         rc = hg_csr_from_coo(edge_index, e, n, csr_rowptr, csr_col, csr_eid, ws + w.off_csr, w.csr, stream);

@@ -1,5 +1,6 @@
 // A6 cosine edge weights, CSR incidence, A8 dense-threshold edge builder.
 #include "common.cuh"
+#include "rowdot.cuh"
 #include "sort_scan.cuh"
 
 namespace hg {
@@ -10,38 +11,62 @@ namespace hg {
 // of `min` is re-read from L1/L2 by consecutive warps.  Algorithmic bytes per edge:
 // 16 (indices) + 4 (weight) + the two gathered rows (2 * 4 D, L2-resident when the
 // slide fits the 126 MB L2).
+__device__ __forceinline__ float warp_cosine(const float* __restrict__ feats, int64_t d, int64_t ia, int64_t ib,
+                                             int lane, bool vec) {
+    float dot, na, nb;
+    warp_dot_norms(feats + ia * d, feats + ib * d, d, lane, vec, dot, na, nb);
+    return fmaxf(0.f, cosine_from(dot, na, nb));
+}
+
 __global__ void __launch_bounds__(256)
 edge_cosine_kernel(const float* __restrict__ feats, int64_t d, const int64_t* __restrict__ edge_index,
                    int64_t num_edges, float* __restrict__ w) {
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
-    const bool vec = (d & 3) == 0 && (reinterpret_cast<uintptr_t>(feats) & 15) == 0;
+    const bool vec = rows_vectorisable(feats, d);
     for (int64_t e = warp0; e < num_edges; e += nwarps) {
-        const float* a = feats + edge_index[e] * d;
-        const float* b = feats + edge_index[num_edges + e] * d;
-        float dot = 0.f, na = 0.f, nb = 0.f;
-        if (vec) {
-            for (int64_t c = lane; c < (d >> 2); c += 32) {
-                const float4 x = __ldg(reinterpret_cast<const float4*>(a) + c);
-                const float4 y = __ldg(reinterpret_cast<const float4*>(b) + c);
-                dot = fmaf(x.x, y.x, dot); dot = fmaf(x.y, y.y, dot); dot = fmaf(x.z, y.z, dot); dot = fmaf(x.w, y.w, dot);
-                na = fmaf(x.x, x.x, na); na = fmaf(x.y, x.y, na); na = fmaf(x.z, x.z, na); na = fmaf(x.w, x.w, na);
-                nb = fmaf(y.x, y.x, nb); nb = fmaf(y.y, y.y, nb); nb = fmaf(y.z, y.z, nb); nb = fmaf(y.w, y.w, nb);
-            }
-        } else {
-            for (int64_t c = lane; c < d; c += 32) {
-                const float x = __ldg(a + c), y = __ldg(b + c);
-                dot = fmaf(x, y, dot); na = fmaf(x, x, na); nb = fmaf(y, y, nb);
-            }
+        const float c = warp_cosine(feats, d, edge_index[e], edge_index[num_edges + e], lane, vec);
+        if (lane == 0) w[e] = c;
+    }
+}
+
+// The same weights when the feature-kNN stage already produced the cosine of every list entry
+// (rerank.cu, out_cos -- bit-identical arithmetic): an edge (a, b) is looked up in a's list, then
+// in b's; only edges that come from elsewhere (spatial lists, cliques) gather their two rows.
+// Per edge: 16 B of indices + up to 2 k list entries (L1/L2-resident, edges are sorted by a)
+// instead of two feature rows.
+__global__ void __launch_bounds__(256)
+edge_weights_from_knn_kernel(const float* __restrict__ feats, int64_t d, const int32_t* __restrict__ knn_idx,
+                             const float* __restrict__ knn_cos, int k, const int64_t* __restrict__ edge_index,
+                             int64_t num_edges, float* __restrict__ w) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    const bool vec = rows_vectorisable(feats, d);
+    for (int64_t base = warp0 * 32; base < num_edges; base += nwarps * 32) {
+        const int64_t e = base + lane;
+        int64_t a = 0, b = 0;
+        bool found = true;
+        if (e < num_edges) {
+            a = edge_index[e]; b = edge_index[num_edges + e];
+            found = false;
+            float c = 0.f;
+            for (int s = 0; s < k; ++s)
+                if (__ldg(knn_idx + a * k + s) == int32_t(b)) { c = __ldg(knn_cos + a * k + s); found = true; break; }
+            if (!found)
+                for (int s = 0; s < k; ++s)
+                    if (__ldg(knn_idx + b * k + s) == int32_t(a)) { c = __ldg(knn_cos + b * k + s); found = true; break; }
+            if (found) w[e] = fmaxf(0.f, c);
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            dot += __shfl_xor_sync(0xffffffffu, dot, o);
-            na += __shfl_xor_sync(0xffffffffu, na, o);
-            nb += __shfl_xor_sync(0xffffffffu, nb, o);
+        uint32_t pending = __ballot_sync(0xffffffffu, !found);
+        while (pending) {
+            const int l = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const int64_t ia = __shfl_sync(0xffffffffu, a, l), ib = __shfl_sync(0xffffffffu, b, l);
+            const float c = warp_cosine(feats, d, ia, ib, lane, vec);
+            if (lane == 0) w[base + l] = c;
         }
-        if (lane == 0) w[e] = fmaxf(0.f, dot / (fmaxf(sqrtf(na), 1e-8f) * fmaxf(sqrtf(nb), 1e-8f)));
     }
 }
 
@@ -123,6 +148,21 @@ extern "C" int hg_edge_weights_cosine(const float* feats, int64_t n, int64_t d,
     HG_REQUIRE(edge_index && weights, HG_ERR_BAD_ARG, "hg_edge_weights_cosine: null buffer");
     const int blocks = int(min64(ceil_div(num_edges, 8), 148 * 8));
     edge_cosine_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(feats, d, edge_index, num_edges, weights);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
+extern "C" int hg_edge_weights_from_knn(const float* feats, int64_t n, int64_t d,
+                                        const int32_t* knn_idx, const float* knn_cos, int k,
+                                        const int64_t* edge_index, int64_t num_edges,
+                                        float* weights, void* stream) {
+    HG_REQUIRE(feats && n > 0 && d > 0 && num_edges >= 0 && k >= 1, HG_ERR_BAD_ARG, "hg_edge_weights_from_knn: bad argument");
+    if (num_edges == 0) return HG_OK;
+    HG_REQUIRE(edge_index && weights && knn_idx && knn_cos, HG_ERR_BAD_ARG, "hg_edge_weights_from_knn: null buffer");
+    const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 8));
+    edge_weights_from_knn_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        feats, d, knn_idx, knn_cos, k, edge_index, num_edges, weights);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

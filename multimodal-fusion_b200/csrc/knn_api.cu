@@ -24,6 +24,12 @@ static int bucket_cap() {
     return TC_BKT_CAP;
 }
 
+// the threshold pre-pass ranks with one BF16 product (hi * hi) instead of three; HG_B200_TC_PRE_HI=0/1
+static bool prepass_hi_only() {
+    if (const char* e = getenv("HG_B200_TC_PRE_HI")) return atoi(e) != 0;
+    return false;
+}
+
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
     KnnWs w{};
     w.n_pad = ops_rows(n);
@@ -45,10 +51,10 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     const size_t part = size_t(max_splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
+    w.off_ovf = take(8);                        // overflow flag, largest squared norm
     if (w.sym_stride > 0) {
         w.off_thr = take(size_t(w.n_pad) * 4);
         w.off_cnt = take(size_t(w.n_pad) * 4);
-        w.off_ovf = take(8);                    // overflow flag, largest squared norm
         w.off_bkt = take(size_t(w.n_pad) * TC_BKT_CAP * 8);
     }
     w.bytes = off;
@@ -93,7 +99,8 @@ extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begi
         return t;
     };
     const double per_tile = 3.0 * 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);     // 3 BF16 MMAs per product
-    double tiles = w.sym_stride > 0 ? tiles_of(w.sym_plan) + tiles_of(w.pre_plan) : tiles_of(w.plan) * w.plan.cg;
+    double tiles = w.sym_stride > 0 ? tiles_of(w.sym_plan) + tiles_of(w.pre_plan) / (prepass_hi_only() ? 3.0 : 1.0)
+                                    : tiles_of(w.plan) * w.plan.cg;
     if (symmetric_stride) *symmetric_stride = w.sym_stride;
     if (mma_flop) *mma_flop = tiles * per_tile;
     return HG_OK;
@@ -106,6 +113,17 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
                               int precision,
                               int32_t* out_idx, float* out_val,
                               void* workspace, size_t workspace_bytes, void* stream) {
+    return hg_knn_feature_cos(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, row_begin, row_end,
+                              exclude_self, precision, out_idx, out_val, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
+                                  const float* pos, int pos_dim,
+                                  int metric, float lambda_h, float lambda_g,
+                                  int k, int64_t row_begin, int64_t row_end, int exclude_self,
+                                  int precision,
+                                  int32_t* out_idx, float* out_val, float* out_cos,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
     HG_REQUIRE(feats && out_idx && out_val, HG_ERR_BAD_ARG, "hg_knn_feature: null buffer");
     int rc = check_knn_args(n, d, k, row_begin, row_end);
     if (rc != HG_OK) return rc;
@@ -115,6 +133,8 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     HG_REQUIRE(pos == nullptr || (pos_dim >= 1 && pos_dim <= 3), HG_ERR_UNSUPPORTED, "hg_knn_feature: pos_dim must be 1..3");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
 
+    HG_REQUIRE(out_cos == nullptr || precision == 0, HG_ERR_UNSUPPORTED,
+               "hg_knn_feature_cos: the cosine by-product needs the tensor-core path (precision 0)");
     if (precision == 1) {                                   // plain FP32 SIMT path
         SimArgs a{};
         a.a = feats; a.b = feats; a.m = n; a.n = n; a.d = d; a.pa = pos; a.pb = pos; a.pos_dim = pos_dim;
@@ -142,13 +162,13 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
     const bool sym = w.sym_stride > 0;
     float* thr = sym ? reinterpret_cast<float*>(ws + w.off_thr) : nullptr;
     int32_t* bkt_cnt = sym ? reinterpret_cast<int32_t*>(ws + w.off_cnt) : nullptr;
-    int* ovf = sym ? reinterpret_cast<int*>(ws + w.off_ovf) : nullptr;
+    int* ovf = reinterpret_cast<int*>(ws + w.off_ovf);
     uint2* bkt = sym ? reinterpret_cast<uint2*>(ws + w.off_bkt) : nullptr;
 
     rc = launch_split(feats, n, d, ops, norms, st);
     if (rc != HG_OK) return rc;
-    float* norm_max = sym ? reinterpret_cast<float*>(ws + w.off_ovf) + 1 : nullptr;
-    if (sym) HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 8, st));
+    float* norm_max = reinterpret_cast<float*>(ws + w.off_ovf) + 1;
+    HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 8, st));
     rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st, thr, bkt_cnt, norm_max);
     if (rc != HG_OK) return rc;
 
@@ -168,6 +188,7 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
         pre.plan = w.pre_plan; pre.col_stride = w.sym_stride; pre.exclude_self = 0;
         pre.thr_out = thr; pre.thr_rank = k;
         pre.thr_margin_cos = (metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
+        pre.hi_only = prepass_hi_only() ? 1 : 0;
         rc = tc_launch(ops, w.n_pad, pre, st);
         if (rc != HG_OK) return rc;
         TcParams sp = tp;
@@ -182,10 +203,11 @@ extern "C" int hg_knn_feature(const float* feats, int64_t n, int64_t d,
 
     RerankParams rp{};
     rp.feats = feats; rp.n = n; rp.d = d; rp.pos = pos; rp.pos_dim = pos_dim;
+    rp.sq_norms = norms; rp.norm_max = norm_max;
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
-    rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val;
+    rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rc = rerank_launch(rp, st);
     if (rc == HG_OK && sym && getenv("HG_B200_TC_DEBUG")) {      // tuning aid: bucket occupancy (synchronises)

@@ -171,7 +171,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         const uint32_t full = ptx::smem_u32(&sm->full[stage]);
                         const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
                         if (CG == 1) {
-                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            ptx::mbar_expect_tx(full, p.hi_only ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES);
                             ptx::tma_load_3d(dst, &tmap_a, full, kb * TC_BK, row0, 0, ptx::kEvictLast);
                             ptx::tma_load_3d(dst + 2 * TC_A_PLANE, &tmap_b, full, kb * TC_BK, ct * TC_BN, 0,
                                              ptx::kEvictNormal);
@@ -216,9 +216,13 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 #pragma unroll
                         for (int ks = 0; ks < TC_BK / 16; ++ks) {
                             const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
-                            ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
-                            ptx::mma_bf16<CG>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
-                            ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                            if (!p.hi_only) {
+                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
+                                ptx::mma_bf16<CG>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
+                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                            } else {                          // coarse pre-pass: one BF16 product
+                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kb | ks) != 0);
+                            }
                         }
                         // frees the stage (in both CTAs of a pair) when the MMAs retire
                         if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));
@@ -388,8 +392,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     // guaranteed slack for the 3xBF16 error of a score (dropped lo*lo term <= 2^-16 |x_i||x_j|,
                     // FP32 accumulation, both tile orientations): Euclidean / Gaussian scores n_j - 2 dot,
                     // cosine scores -dot / |x_j|
+                    // A hi-only pre-pass ranks with x ~ bf16(x): its k best sample columns have 3xBF16 scores at
+                    // most 2^-8 (n_i + n_j) above their coarse ones (|x - hi| <= 2^-9 |x| per element), so the
+                    // bound stays valid with that much more slack.
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
-                    p.thr_out[row] = t + 4.8828125e-4f * scale;
+                    p.thr_out[row] = t + (p.hi_only ? 4.39453125e-3f : 4.8828125e-4f) * scale;
                 } else {
                     const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
 #pragma unroll
@@ -526,12 +533,12 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 
 // row_stride > 1: a view of every row_stride-th operand row (the pre-pass column sample)
 static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows,
-                     int row_stride = 1) {
+                     int row_stride = 1, int planes = 2) {
     auto enc = get_encode_fn();
     HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
     cuuint64_t dims[3] = {cuuint64_t(d_pad), cuuint64_t(ceil_div(n_pad, row_stride)), 2};
     cuuint64_t strides[2] = {cuuint64_t(d_pad) * 2 * cuuint64_t(row_stride), cuuint64_t(n_pad) * cuuint64_t(d_pad) * 2};
-    cuuint32_t box[3] = {cuuint32_t(TC_BK), cuuint32_t(box_rows), 2};
+    cuuint32_t box[3] = {cuuint32_t(TC_BK), cuuint32_t(box_rows), cuuint32_t(planes)};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -581,9 +588,12 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
     HG_REQUIRE(p.col_stride == 1 || (p.plan.cg == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need cg 1");
     CUtensorMap ta, tb;
-    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM);
+    HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.thr_out != nullptr), HG_ERR_BAD_ARG,
+               "tc_launch: the hi-only product is for the threshold pre-pass");
+    const int planes = p.hi_only ? 1 : 2;
+    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1, planes);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride);   // a CTA of a pair stages half of the B tile
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride, planes);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

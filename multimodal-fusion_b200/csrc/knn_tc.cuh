@@ -48,6 +48,7 @@ struct TcParams {
     int col_stride;
     float* thr_out;
     int thr_rank;
+    int hi_only;                // pre-pass only: one BF16 product hi*hi (planes 0 only), wider slack
     int thr_margin_cos;         // error slack added to thr_out scales with |x_i| (cosine) or n_i + norm_max
     const float* norm_max;      // largest squared row norm
     // symmetric mode: transposed candidates (column j gets row i) with score < thr[j] are
@@ -69,6 +70,8 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaSt
 
 struct RerankParams {
     const float* feats; int64_t n, d;
+    const float* sq_norms;       // [n] squared row norms in the canonical order (split.cu)
+    const float* norm_max;       // largest of them
     const float* pos; int pos_dim;
     int metric; float lambda_h, lambda_g;
     const float* part_val; const int32_t* part_idx;
@@ -78,6 +81,7 @@ struct RerankParams {
     TcPlan sym_plan; const int32_t* bkt_cnt; const uint2* bkt; int bkt_cap; const int* ovf;
     int k;
     int32_t* out_idx; float* out_val;
+    float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
 };
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 

@@ -9,6 +9,7 @@
 // loads; the query row stays in L1 while its ~KL candidates stream from L2.
 // Algorithmic bytes per row: KL * 4 D (candidate rows) + 4 D (query) + 8 k out.
 #include "knn_tc.cuh"
+#include "rowdot.cuh"
 
 namespace hg {
 
@@ -18,8 +19,8 @@ __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float
                                  float* __restrict__ norm_max) {
     const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (j >= n_pad) return;
-    if (thr != nullptr) {
-        thr[j] = __int_as_float(0x7fc00000); bkt_cnt[j] = 0;
+    if (thr != nullptr) { thr[j] = __int_as_float(0x7fc00000); bkt_cnt[j] = 0; }
+    if (norm_max != nullptr) {
         // non-negative floats order like their bit patterns; one atomic per warp
         float m = (j < n) ? sq_norms[j] : 0.f;
 #pragma unroll
@@ -61,7 +62,10 @@ constexpr int RR_WARPS = 8;
 constexpr int RR_MAX_LIST = TC_MAX_SPLITS * 32;      // 256 list candidates per row at most
 constexpr int RR_MAX_CAND = RR_MAX_LIST + TC_BKT_CAP; // + the row's bucket (symmetric mode)
 
-__global__ void __launch_bounds__(RR_WARPS * 32)
+enum { RR_D2 = 0, RR_D2_DOT = 1, RR_DOT = 2 };       // what the exact pass accumulates per candidate
+
+template <int MODE>
+__global__ void __launch_bounds__(RR_WARPS * 32, 3)
 rerank_kernel(const RerankParams p) {
     const int lane = threadIdx.x & 31;
     const int64_t r = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
@@ -92,7 +96,14 @@ rerank_kernel(const RerankParams p) {
             cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
         }
     }
+    // Selection stops once a candidate's approximate score exceeds the k-th best by more than the
+    // guaranteed 3xBF16 error slack (both scores off by <= eps in opposite directions): such a
+    // candidate cannot enter the exact top-k, and neither can any later one.
+    const float ni = p.sq_norms[row];
+    const float slack = 4.8828125e-4f * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
     int sel = -1;                                    // candidate column held by this lane (lane < kl)
+    int nsel = 0;
+    float kth = INFINITY;
     for (int t = 0; t < p.kl; ++t) {
         float bv = INFINITY; int bi = 0x7fffffff;
 #pragma unroll
@@ -107,87 +118,86 @@ rerank_kernel(const RerankParams p) {
             if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
         }
         if (bi == 0x7fffffff) break;                 // fewer than kl real candidates
+        if (t == p.k - 1) kth = bv;
+        if (t >= p.k && bv > kth + slack) break;
 #pragma unroll
         for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
             if (q * 32 >= ncand) break;
             if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }   // column ids are unique per row
         }
         if (lane == t) sel = bi;
+        nsel = t + 1;
     }
 
-    // ---- 2. exact values ---------------------------------------------------------------------------
+    // ---- 2. exact values: sum (x_i - x_j)^2 and / or x_i . x_j in the canonical order of rowdot.cuh ----
     const float* xi = p.feats + row * p.d;
-    const bool vec = (p.d & 3) == 0 && (reinterpret_cast<uintptr_t>(p.feats) & 15) == 0;
-    float ni = 0.f;
-    if (p.metric == HG_METRIC_COSINE) {
-        for (int64_t c = lane; c < p.d; c += 32) { const float x = __ldg(xi + c); ni = fmaf(x, x, ni); }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ni += __shfl_xor_sync(0xffffffffu, ni, o);
-    }
+    const bool vec = rows_vectorisable(p.feats, p.d);
+    constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
     float my_val = INFINITY;                         // ranking key (ascending) of this lane's candidate
-    float my_out = NAN;
-    const bool is_cos = p.metric == HG_METRIC_COSINE;
-    // four candidates per pass: one read of the query row serves four distance sums and the four
-    // warp reductions overlap (the loop is latency-bound otherwise); kl is a multiple of 8
-    for (int t0 = 0; t0 < p.kl; t0 += 4) {
-        int j[4];
-        const float* xj[4];
-        bool any = false;
+    float my_out = NAN, my_cos = NAN;
+    // four candidates per pass: one read of the query row serves four rows of sums, and the four
+    // reductions overlap.  Lane l owns the float4 groups l, l + 32, ... (rowdot.cuh order).
+    constexpr int CB = 4;
+    for (int t0 = 0; t0 < nsel; t0 += CB) {
+        int j[CB];
+        const float* xj[CB];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < CB; ++q) {
             j[q] = __shfl_sync(0xffffffffu, sel, t0 + q);
-            any |= j[q] >= 0;
             xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
         }
-        if (!any) continue;                          // warp-uniform
-        float acc[4] = {0.f, 0.f, 0.f, 0.f}, nj[4] = {0.f, 0.f, 0.f, 0.f};
+        float d2[CB], dt[CB];
         if (vec) {
-            for (int64_t c = lane; c < (p.d >> 2); c += 32) {
-                const float4 x = __ldg(reinterpret_cast<const float4*>(xi) + c);
-                float4 y[4];
+            uint64_t ad[CB], at[CB];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) y[q] = __ldg(reinterpret_cast<const float4*>(xj[q]) + c);
+            for (int q = 0; q < CB; ++q) { ad[q] = 0; at[q] = 0; }
+#pragma unroll 2
+            for (int64_t v = lane; v < (p.d >> 2); v += 32) {
+                const ulonglong2 x = __ldg(reinterpret_cast<const ulonglong2*>(xi) + v);
+                ulonglong2 y[CB];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (is_cos) {
-                        acc[q] = fmaf(x.x, y[q].x, acc[q]); acc[q] = fmaf(x.y, y[q].y, acc[q]);
-                        acc[q] = fmaf(x.z, y[q].z, acc[q]); acc[q] = fmaf(x.w, y[q].w, acc[q]);
-                        nj[q] = fmaf(y[q].x, y[q].x, nj[q]); nj[q] = fmaf(y[q].y, y[q].y, nj[q]);
-                        nj[q] = fmaf(y[q].z, y[q].z, nj[q]); nj[q] = fmaf(y[q].w, y[q].w, nj[q]);
-                    } else {
-                        const float d0 = x.x - y[q].x, d1 = x.y - y[q].y, d2 = x.z - y[q].z, d3 = x.w - y[q].w;
-                        acc[q] = fmaf(d0, d0, acc[q]); acc[q] = fmaf(d1, d1, acc[q]);
-                        acc[q] = fmaf(d2, d2, acc[q]); acc[q] = fmaf(d3, d3, acc[q]);
+                for (int q = 0; q < CB; ++q) y[q] = __ldg(reinterpret_cast<const ulonglong2*>(xj[q]) + v);
+#pragma unroll
+                for (int q = 0; q < CB; ++q) {
+                    if (WANT_D2) {
+                        const uint64_t e0 = pk_sub(x.x, y[q].x), e1 = pk_sub(x.y, y[q].y);
+                        ad[q] = pk_fma(e0, e0, ad[q]); ad[q] = pk_fma(e1, e1, ad[q]);
                     }
+                    if (WANT_DOT) { at[q] = pk_fma(x.x, y[q].x, at[q]); at[q] = pk_fma(x.y, y[q].y, at[q]); }
                 }
             }
+#pragma unroll
+            for (int q = 0; q < CB; ++q) { d2[q] = pk_hsum(ad[q]); dt[q] = pk_hsum(at[q]); }
         } else {
+#pragma unroll
+            for (int q = 0; q < CB; ++q) { d2[q] = 0.f; dt[q] = 0.f; }
             for (int64_t c = lane; c < p.d; c += 32) {
                 const float x = __ldg(xi + c);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
+                for (int q = 0; q < CB; ++q) {
                     const float y = __ldg(xj[q] + c);
-                    if (is_cos) { acc[q] = fmaf(x, y, acc[q]); nj[q] = fmaf(y, y, nj[q]); }
-                    else { const float df = x - y; acc[q] = fmaf(df, df, acc[q]); }
+                    if (WANT_D2) { const float df = x - y; d2[q] = fmaf(df, df, d2[q]); }
+                    if (WANT_DOT) dt[q] = fmaf(x, y, dt[q]);
                 }
             }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
-                if (is_cos) nj[q] += __shfl_xor_sync(0xffffffffu, nj[q], o);
+            for (int q = 0; q < CB; ++q) {
+                if (WANT_D2) d2[q] += __shfl_xor_sync(0xffffffffu, d2[q], o);
+                if (WANT_DOT) dt[q] += __shfl_xor_sync(0xffffffffu, dt[q], o);
             }
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < CB; ++q) {
             if (lane != t0 + q || j[q] < 0) continue;
-            if (is_cos) {
-                const float cs = acc[q] / (fmaxf(sqrtf(ni), 1e-8f) * fmaxf(sqrtf(nj[q]), 1e-8f));
+            const float cs = WANT_DOT ? cosine_from(dt[q], ni, __ldg(p.sq_norms + j[q])) : 0.f;
+            my_cos = cs;
+            if (MODE == RR_DOT) {
                 my_val = -cs; my_out = cs;
             } else if (p.metric == HG_METRIC_EUCLIDEAN) {
-                my_val = acc[q]; my_out = acc[q];
+                my_val = d2[q]; my_out = d2[q];
             } else {
                 float d2g = 0.f;
                 if (p.pos != nullptr) {
@@ -196,7 +206,7 @@ rerank_kernel(const RerankParams p) {
                         d2g = fmaf(df, df, d2g);
                     }
                 }
-                my_val = p.lambda_h * acc[q] + p.lambda_g * d2g;
+                my_val = p.lambda_h * d2[q] + p.lambda_g * d2g;
                 my_out = expf(-my_val);
             }
         }
@@ -205,24 +215,31 @@ rerank_kernel(const RerankParams p) {
     // ---- 3. final order by (exact value, index); best k written out ----------------------------------
     const int my_idx = (sel >= 0) ? sel : 0x7fffffff;
     int rank = 0;
-    for (int t = 0; t < p.kl; ++t) {
+    for (int t = 0; t < nsel; ++t) {
         const float ov = __shfl_sync(0xffffffffu, my_val, t);
         const int oi = __shfl_sync(0xffffffffu, my_idx, t);
         rank += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
     }
-    if (lane < p.kl && sel >= 0 && rank < p.k) {
+    if (lane < nsel && sel >= 0 && rank < p.k) {
         p.out_idx[r * p.k + rank] = sel;
         p.out_val[r * p.k + rank] = my_out;
+        if (p.out_cos != nullptr) p.out_cos[r * p.k + rank] = my_cos;
     }
     // rows with fewer than k candidates: pad with (-1, NaN)
-    int have = __popc(__ballot_sync(0xffffffffu, lane < p.kl && sel >= 0));
-    for (int t = have + lane; t < p.k; t += 32) { p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN; }
+    for (int t = nsel + lane; t < p.k; t += 32) {
+        p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
+        if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+    }
 }
 
 int rerank_launch(const RerankParams& p, cudaStream_t st) {
     HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_LIST && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
                p.bkt_cap <= TC_BKT_CAP, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
-    rerank_kernel<<<(unsigned)ceil_div(p.n_rows, RR_WARPS), RR_WARPS * 32, 0, st>>>(p);
+    HG_REQUIRE(p.sq_norms && p.norm_max, HG_ERR_BAD_ARG, "rerank: row norms missing");
+    const unsigned blocks = (unsigned)ceil_div(p.n_rows, RR_WARPS);
+    if (p.metric == HG_METRIC_COSINE) rerank_kernel<RR_DOT><<<blocks, RR_WARPS * 32, 0, st>>>(p);
+    else if (p.out_cos != nullptr) rerank_kernel<RR_D2_DOT><<<blocks, RR_WARPS * 32, 0, st>>>(p);
+    else rerank_kernel<RR_D2><<<blocks, RR_WARPS * 32, 0, st>>>(p);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

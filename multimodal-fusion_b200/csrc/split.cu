@@ -9,69 +9,69 @@
 // multiple of 256 and cols to a multiple of 64 with zeros, so that TMA boxes
 // never straddle undefined memory and padded rows contribute dot = 0.
 //
-// HBM-bound: reads 4 B and writes 4 B per element; one 128-thread CTA per row,
+// HBM-bound: reads 4 B and writes 4 B per element; one warp per row (4 rows per CTA),
 // 128-bit loads, 64-bit stores.
 #include "common.cuh"
+#include "rowdot.cuh"
 
 namespace hg {
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
+constexpr int SPLIT_WARPS = 4;          // rows per CTA, one warp each
 
 template <bool VEC4>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
                   __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms) {
-    const int64_t row = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
+    if (row >= n_pad) return;
     __nv_bfloat16* hi_row = ops + row * d_pad;
     __nv_bfloat16* lo_row = ops + (n_pad + row) * d_pad;
-    float acc = 0.f;
-    if (row < n) {
-        const float* src = feats + row * d;
-        if (VEC4) {
-            const int64_t nvec = d >> 2;
-            for (int64_t v = threadIdx.x; v < (d_pad >> 2); v += blockDim.x) {
-                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (v < nvec) x = __ldg(reinterpret_cast<const float4*>(src) + v);
-                acc = fmaf(x.x, x.x, acc); acc = fmaf(x.y, x.y, acc);
-                acc = fmaf(x.z, x.z, acc); acc = fmaf(x.w, x.w, acc);
-                __nv_bfloat16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y);
-                __nv_bfloat16 h2 = __float2bfloat16_rn(x.z), h3 = __float2bfloat16_rn(x.w);
-                __nv_bfloat16 l0 = __float2bfloat16_rn(x.x - __bfloat162float(h0));
-                __nv_bfloat16 l1 = __float2bfloat16_rn(x.y - __bfloat162float(h1));
-                __nv_bfloat16 l2 = __float2bfloat16_rn(x.z - __bfloat162float(h2));
-                __nv_bfloat16 l3 = __float2bfloat16_rn(x.w - __bfloat162float(h3));
-                __nv_bfloat162 hp0(h0, h1), hp1(h2, h3), lp0(l0, l1), lp1(l2, l3);
-                uint2 hv, lv;
-                hv.x = *reinterpret_cast<uint32_t*>(&hp0); hv.y = *reinterpret_cast<uint32_t*>(&hp1);
-                lv.x = *reinterpret_cast<uint32_t*>(&lp0); lv.y = *reinterpret_cast<uint32_t*>(&lp1);
-                reinterpret_cast<uint2*>(hi_row)[v] = hv;
-                reinterpret_cast<uint2*>(lo_row)[v] = lv;
-            }
-        } else {
-            for (int64_t c = threadIdx.x; c < d_pad; c += blockDim.x) {
-                float x = (c < d) ? __ldg(src + c) : 0.f;
-                acc = fmaf(x, x, acc);
-                __nv_bfloat16 h = __float2bfloat16_rn(x);
-                hi_row[c] = h;
-                lo_row[c] = __float2bfloat16_rn(x - __bfloat162float(h));
-            }
-        }
-    } else {
-        for (int64_t v = threadIdx.x; v < (d_pad >> 2); v += blockDim.x) {
+    if (row >= n) {                              // padding rows are zero in both planes
+        for (int64_t v = lane; v < (d_pad >> 2); v += 32) {
             reinterpret_cast<uint2*>(hi_row)[v] = make_uint2(0u, 0u);
             reinterpret_cast<uint2*>(lo_row)[v] = make_uint2(0u, 0u);
         }
+        return;
     }
-    __shared__ float part[4];
-    acc = warp_sum(acc);
-    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0 && sq_norms != nullptr && row < n)
-        sq_norms[row] = (part[0] + part[1]) + (part[2] + part[3]);
+    const float* src = feats + row * d;
+    // one warp per row, lane l owns the float4 groups l, l + 32, ...: the squared norm comes out in
+    // the canonical order of rowdot.cuh in the same pass
+    float norm;
+    if (VEC4) {
+        const int64_t nvec = d >> 2;
+        float lo = 0.f, hi = 0.f;               // the two halves of the packed accumulator
+        for (int64_t v = lane; v < (d_pad >> 2); v += 32) {
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v < nvec) x = __ldg(reinterpret_cast<const float4*>(src) + v);
+            lo = fmaf(x.x, x.x, lo); hi = fmaf(x.y, x.y, hi);
+            lo = fmaf(x.z, x.z, lo); hi = fmaf(x.w, x.w, hi);
+            __nv_bfloat16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y);
+            __nv_bfloat16 h2 = __float2bfloat16_rn(x.z), h3 = __float2bfloat16_rn(x.w);
+            __nv_bfloat16 l0 = __float2bfloat16_rn(x.x - __bfloat162float(h0));
+            __nv_bfloat16 l1 = __float2bfloat16_rn(x.y - __bfloat162float(h1));
+            __nv_bfloat16 l2 = __float2bfloat16_rn(x.z - __bfloat162float(h2));
+            __nv_bfloat16 l3 = __float2bfloat16_rn(x.w - __bfloat162float(h3));
+            __nv_bfloat162 hp0(h0, h1), hp1(h2, h3), lp0(l0, l1), lp1(l2, l3);
+            uint2 hv, lv;
+            hv.x = *reinterpret_cast<uint32_t*>(&hp0); hv.y = *reinterpret_cast<uint32_t*>(&hp1);
+            lv.x = *reinterpret_cast<uint32_t*>(&lp0); lv.y = *reinterpret_cast<uint32_t*>(&lp1);
+            reinterpret_cast<uint2*>(hi_row)[v] = hv;
+            reinterpret_cast<uint2*>(lo_row)[v] = lv;
+        }
+        norm = lo + hi;
+    } else {
+        norm = 0.f;
+        for (int64_t c = lane; c < d_pad; c += 32) {
+            const float x = (c < d) ? __ldg(src + c) : 0.f;
+            norm = fmaf(x, x, norm);
+            __nv_bfloat16 h = __float2bfloat16_rn(x);
+            hi_row[c] = h;
+            lo_row[c] = __float2bfloat16_rn(x - __bfloat162float(h));
+        }
+    }
+    norm = warp_butterfly(norm);
+    if (lane == 0 && sq_norms != nullptr) sq_norms[row] = norm;
 }
 
 int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
@@ -79,9 +79,9 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (vec)
-        split_rows_kernel<true><<<(unsigned)n_pad, 128, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
+        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
     else
-        split_rows_kernel<false><<<(unsigned)n_pad, 128, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
+        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

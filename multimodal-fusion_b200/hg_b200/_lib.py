@@ -36,6 +36,9 @@ SIGNATURES = {
     "hg_knn_feature_plan": (_i32, [_i64, _i64, _i32, _i64, _i64, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
     "hg_knn_feature": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i64, _i64, _i32, _i32,
                               _vp, _vp, _vp, _sz, _vp]),
+    "hg_knn_feature_cos": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i64, _i64, _i32, _i32,
+                                  _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_edge_weights_from_knn": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _vp, _i64, _vp, _vp]),
     "hg_similarity_dense": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i32, _f32, _f32, _i32, _vp, _i64, _vp]),
     "hg_stats_workspace_bytes": (_i32, [_i64, _psz]),
     "hg_similarity_stats": (_i32, [_vp, _i64, _i64, _vp, _vp, _sz, _vp]),

@@ -104,3 +104,20 @@ def test_symmetric_with_duplicate_rows_and_outlier_norms():
     np.testing.assert_array_equal(fvn[~np.isin(np.arange(n), differ)], svn[~np.isin(np.arange(n), differ)])
     for r in differ:
         np.testing.assert_array_equal(fvn[r], svn[r])        # same values, different duplicate picked
+
+
+@pytest.mark.parametrize("n,d,k,metric", [(3000, 200, 8, "gaussian"), (9000, 256, 8, "cosine"), (2500, 130, 5, "euclidean")])
+def test_build_weights_from_knn_lists_equal_direct_cosine(n, d, k, metric):
+    """The one-call build takes edge weights from the re-rank's cosine by-product; edges that come
+    from the spatial lists or from cliques fall back to the row gather.  Must equal
+    hg_edge_weights_cosine bit for bit."""
+    import hg_b200 as hg
+    feats, pos = synth.make_slide(n, d, 21, "cosine" if metric == "cosine" else "gaussian")
+    labels = np.random.default_rng(1).integers(0, 40, n).astype(np.int32)       # 40 clusters, 6 kept as cliques
+    x = _cuda(feats)
+    out = hg.knn_hyperedges(x, _cuda(pos), k=k, kernel=metric, lambda_h=1.0, lambda_g=1.0 / 128, spatial_k=4,
+                            labels=labels, num_hyperedges=6)
+    w_direct = ops.edge_weights_cosine(x, out["edge_index"])
+    torch.cuda.synchronize()
+    assert out["edge_index"].shape[1] > n * k // 2
+    assert torch.equal(out["edge_weights"], w_direct)
