@@ -505,17 +505,20 @@ TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
     return pl;
 }
 
-// Symmetric mode pays a 1/stride pre-pass and needs enough sample columns for a useful bound.
-// HG_B200_TC_SYM=0 disables it, =<stride> forces the pre-pass stride.
+// Symmetric mode pays a 1/stride pre-pass and needs enough sample columns for a useful bound; it
+// wins from n ~ 10k up (measured break-even at 9k x 512).  HG_B200_TC_SYM=0 disables it,
+// HG_B200_TC_SYM=<stride> forces it (any n with enough sample columns) with that pre-pass stride.
 int tc_sym_stride(int64_t n, int64_t n_rows, int k) {
     if (n_rows != n || tc_cta_group() != 1) return 0;
     int stride = (n >= 32768) ? 16 : 8;
+    bool forced = false;
     if (const char* e = getenv("HG_B200_TC_SYM")) {
         const int v = atoi(e);
         if (v <= 0) return 0;
-        if (v >= 2 && v <= 64) stride = v;
+        if (v >= 2 && v <= 64) { stride = v; forced = true; }
     }
-    if (n < 8192 || n / stride < 4 * (k + 8)) return 0;
+    if (!forced && n < 12288) return 0;
+    if (n / stride < 4 * (k + 8)) return 0;
     return stride;
 }
 

@@ -37,25 +37,29 @@ def _plan(n, d, k, r0=0, r1=None):
     return stride.value, flop.value
 
 
-def _both(x, k, metric, **kw):
+def _both(x, k, metric, stride=8, **kw):
     with _env(HG_B200_TC_SYM=0):
         full = ops.knn_feature(x, k, metric, **kw)
-    sym = ops.knn_feature(x, k, metric, **kw)
+    with _env(HG_B200_TC_SYM=stride):          # forced: small test shapes are below the automatic cut-over
+        sym = ops.knn_feature(x, k, metric, **kw)
     torch.cuda.synchronize()
     return full, sym
 
 
 @pytest.mark.parametrize("n,d,k,metric,with_pos", [
-    (8192, 256, 8, "gaussian", False),          # smallest symmetric shape, stride 8
+    (3000, 256, 8, "gaussian", False),          # tiny, forced
+    (8192, 256, 8, "gaussian", False),
     (12345, 200, 16, "gaussian", True),         # ragged n and d, spatial term in the epilogue
     (20000, 512, 8, "cosine", False),
     (33000, 128, 5, "euclidean", False),        # stride 16
 ])
 def test_symmetric_equals_full_pass(n, d, k, metric, with_pos):
-    stride, flop = _plan(n, d, k)
-    assert stride in (8, 16)
-    d_pad = -(-d // 64) * 64
-    assert flop < 0.66 * 3 * 2.0 * n * n * d_pad * 1.1          # about 0.56 of the full pass
+    with _env(HG_B200_TC_SYM=8):
+        stride, flop = _plan(n, d, k)
+    assert stride == 8
+    n_pad, d_pad = -(-n // 256) * 256, -(-d // 64) * 64
+    if n >= 8192:                                                # tile granularity dominates below
+        assert flop < 0.7 * 3 * 2.0 * n_pad * n_pad * d_pad      # about 0.5 + 1/8 of the full pass
     feats, pos = synth.make_slide(n, d, 11, "cosine" if metric == "cosine" else "gaussian")
     kw = dict(positions=_cuda(pos), lambda_h=1.0, lambda_g=1.0 / 128) if with_pos else {}
     (fi, fv), (si, sv) = _both(_cuda(feats), k, metric, **kw)
@@ -69,6 +73,7 @@ def test_symmetric_equals_full_pass(n, d, k, metric, with_pos):
 def test_row_ranges_and_small_slides_use_the_full_pass():
     assert _plan(50000, 1024, 16, 0, 25000)[0] == 0
     assert _plan(4096, 1024, 8)[0] == 0
+    assert _plan(20000, 1024, 8)[0] == 8
     with _env(HG_B200_TC_SYM=0):
         assert _plan(50000, 1024, 16)[0] == 0
     stride, flop = _plan(50000, 1024, 16)
@@ -81,7 +86,7 @@ def test_bucket_overflow_falls_back_to_the_full_pass():
     x = _cuda(feats)
     with _env(HG_B200_TC_SYM=0):
         fi, fv = ops.knn_feature(x, k, "gaussian")
-    with _env(HG_B200_TC_BKT_CAP=4):           # every bucket overflows -> guarded full pass runs
+    with _env(HG_B200_TC_BKT_CAP=4, HG_B200_TC_SYM=8):      # every bucket overflows -> guarded full pass runs
         si, sv = ops.knn_feature(x, k, "gaussian")
     torch.cuda.synchronize()
     assert torch.equal(fi, si) and torch.equal(fv, sv)
