@@ -47,6 +47,7 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
         w.sym_plan = tc_make_plan_sym(n, k, w.d_pad);
         w.pre_plan = tc_make_plan_prepass(n, k, w.d_pad, w.sym_stride);
         if (w.sym_plan.splits > max_splits) max_splits = w.sym_plan.splits;
+        if (w.pre_plan.splits > max_splits) max_splits = w.pre_plan.splits;
     }
     const size_t part = size_t(max_splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
     w.off_pval = take(part * 4);
@@ -186,11 +187,17 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         //     (3) the classic full pass, which exits at once unless a bucket overflowed
         TcParams pre = tp;
         pre.plan = w.pre_plan; pre.col_stride = w.sym_stride; pre.exclude_self = 0;
-        pre.thr_out = thr; pre.thr_rank = k;
-        pre.thr_margin_cos = (metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
+        const int cosine = (metric == HG_METRIC_COSINE) ? 1 : 0;
+        pre.thr_rank = k; pre.thr_margin_cos = cosine; pre.norm_max = norm_max;
         pre.hi_only = prepass_hi_only() ? 1 : 0;
+        pre.thr_out = (w.pre_plan.splits == 1) ? thr : nullptr;     // several splits: lists, merged below
         rc = tc_launch(ops, w.n_pad, pre, st);
         if (rc != HG_OK) return rc;
+        if (w.pre_plan.splits > 1) {
+            rc = thr_merge_launch(pre.part_val, w.pre_plan.splits, n, w.pre_plan.kl, k, colp, norm_max, cosine,
+                                  pre.hi_only ? TC_SLACK_HI : TC_SLACK_3X, thr, st);
+            if (rc != HG_OK) return rc;
+        }
         TcParams sp = tp;
         sp.plan = w.sym_plan; sp.thr = thr; sp.bkt_cnt = bkt_cnt; sp.bkt = bkt; sp.bkt_cap = bucket_cap(); sp.ovf = ovf;
         rc = tc_launch(ops, w.n_pad, sp, st);

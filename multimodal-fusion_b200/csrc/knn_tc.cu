@@ -396,7 +396,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     // most 2^-8 (n_i + n_j) above their coarse ones (|x - hi| <= 2^-9 |x| per element), so the
                     // bound stays valid with that much more slack.
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
-                    p.thr_out[row] = t + (p.hi_only ? 4.39453125e-3f : 4.8828125e-4f) * scale;
+                    p.thr_out[row] = t + (p.hi_only ? TC_SLACK_HI : TC_SLACK_3X) * scale;
                 } else {
                     const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
 #pragma unroll
@@ -472,8 +472,10 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     return pl;
 }
 
-// Threshold pre-pass: all rows against every stride-th column, one unit per row block (the
-// bound must come from ONE list per row).
+// Threshold pre-pass: all rows against every stride-th column.  One unit per row block when the A
+// blocks of all 148 CTAs plus the column sample fit the L2 (the bound then comes straight out of the
+// kernel); otherwise 2 or 4 column splits run side by side on fewer row blocks and
+// thr_merge_kernel (rerank.cu) combines their lists.
 TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
     TcPlan pl{};
     pl.cg = 1;
@@ -482,10 +484,18 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(ceil_div(n, stride), TC_BN));
     pl.kl = list_len(k);
-    pl.cc = 1; pl.rc = kNumSMs; pl.splits = 1;
-    pl.ct_per_split = pl.num_ct;
-    pl.grid = int(min64(kNumSMs, pl.num_rb));
-    (void)d_pad;
+    const int64_t a_block = int64_t(TC_BM) * d_pad * 4;
+    const int64_t sample = ceil_div(n, stride) * d_pad * 4;
+    int cc = 1;
+    while (cc < 4 && (kNumSMs / cc) * a_block + sample > (int64_t(100) << 20)) cc *= 2;
+    if (const char* e = getenv("HG_B200_TC_PRE_CC")) {          // tuning / test override: 1, 2 or 4
+        const int v = atoi(e);
+        if (v == 1 || v == 2 || v == 4) cc = v;
+    }
+    if (cc > pl.num_ct) cc = 1;
+    pl.cc = cc; pl.rc = kNumSMs / cc; pl.splits = cc;
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
+    pl.grid = int(min64(kNumSMs, int64_t(pl.num_rb) * pl.splits));
     return pl;
 }
 
@@ -591,7 +601,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
     HG_REQUIRE(p.col_stride == 1 || (p.plan.cg == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need cg 1");
     CUtensorMap ta, tb;
-    HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.thr_out != nullptr), HG_ERR_BAD_ARG,
+    HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.col_stride > 1), HG_ERR_BAD_ARG,
                "tc_launch: the hi-only product is for the threshold pre-pass");
     const int planes = p.hi_only ? 1 : 2;
     int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1, planes);

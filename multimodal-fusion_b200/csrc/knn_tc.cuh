@@ -84,6 +84,10 @@ struct RerankParams {
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
 };
 int rerank_launch(const RerankParams& p, cudaStream_t st);
+int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
+                     const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st);
+constexpr float TC_SLACK_3X = 4.8828125e-4f;      // 2^-11: both 3xBF16 scores of a comparison, see knn_tc.cu
+constexpr float TC_SLACK_HI = 4.39453125e-3f;     // 2^-8 + 2^-11: a hi-only pre-pass score against a 3xBF16 one
 
 // also resets the symmetric-mode state when given: thr = NaN, bucket counts = 0, and folds the
 // largest squared norm into *norm_max (zeroed by the caller)

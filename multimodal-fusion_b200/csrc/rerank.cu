@@ -232,6 +232,46 @@ rerank_kernel(const RerankParams p) {
     }
 }
 
+// Pre-pass run with several column splits: thr[row] = the rank-th smallest score over the row's S
+// ascending lists (an upper bound of the row's final k-th best) plus the error slack the fused
+// kernel adds in its single-split path.  One thread per row, S-way merge by list heads.
+__global__ void thr_merge_kernel(const float* __restrict__ part_val, int splits, int64_t n, int kl, int rank,
+                                 const float2* __restrict__ colp, const float* __restrict__ norm_max, int cosine,
+                                 float slack, float* __restrict__ thr) {
+    const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    int head[TC_MAX_SPLITS];
+#pragma unroll
+    for (int s = 0; s < TC_MAX_SPLITS; ++s) head[s] = 0;
+    float t = INFINITY;
+    for (int step = 0; step <= rank; ++step) {
+        float best = INFINITY; int bs = -1;
+#pragma unroll
+        for (int s = 0; s < TC_MAX_SPLITS; ++s) {
+            if (s < splits && head[s] < kl) {
+                const float v = part_val[(int64_t(s) * n + row) * kl + head[s]];
+                if (v < best) { best = v; bs = s; }
+            }
+        }
+        t = best;
+        if (bs < 0) break;                            // fewer than rank + 1 finite scores: no bound
+#pragma unroll
+        for (int s = 0; s < TC_MAX_SPLITS; ++s) head[s] += (s == bs) ? 1 : 0;
+    }
+    const float2 me = colp[row];
+    const float scale = cosine ? 1.f / fmaxf(fabsf(me.y), 1e-30f) : me.x + *norm_max;
+    thr[row] = t + slack * scale;
+}
+
+int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
+                     const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st) {
+    thr_merge_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(part_val, splits, n, kl, rank, colp, norm_max, cosine,
+                                                                 slack, thr);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
 int rerank_launch(const RerankParams& p, cudaStream_t st) {
     HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_LIST && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
                p.bkt_cap <= TC_BKT_CAP, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");

@@ -70,6 +70,18 @@ def test_symmetric_equals_full_pass(n, d, k, metric, with_pos):
               lambda_h=1.0, lambda_g=1.0 / 128 if with_pos else 0.0)
 
 
+@pytest.mark.parametrize("cc", [2, 4])
+def test_prepass_with_column_splits(cc):
+    """Large D: the threshold pre-pass runs 2 or 4 column splits side by side and thr_merge_kernel
+    combines their lists (forced here on a small shape)."""
+    n, d, k = 9000, 192, 8
+    feats, pos = synth.make_slide(n, d, 13, "gaussian")
+    with _env(HG_B200_TC_PRE_CC=cc):
+        (fi, fv), (si, sv) = _both(_cuda(feats), k, "gaussian", stride=2, positions=_cuda(pos), lambda_h=1.0,
+                                   lambda_g=1.0 / 128)
+    assert torch.equal(fi, si) and torch.equal(fv, sv)
+
+
 def test_row_ranges_and_small_slides_use_the_full_pass():
     assert _plan(50000, 1024, 16, 0, 25000)[0] == 0
     assert _plan(4096, 1024, 8)[0] == 0
