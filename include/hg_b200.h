@@ -225,6 +225,21 @@ int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d, const floa
                             int64_t* num_edges_out_host,
                             void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same build, fully stream-ordered: no host synchronisation at all.  The edge count E is
+ * written to *num_edges_out_device (8 bytes of DEVICE memory) and every stage after the de-dup
+ * reads it from there, so many slides can be in flight on several streams (datasets of small
+ * slides, BASELINE config C4: the dataset loop preprocess_hypergraph.py:651-670).  Outputs have
+ * the compact layout above relative to E (edge_index row 1 at offset E, csr_col / csr_eid 2E
+ * entries); the caller reads E back when it collects the slide.  Same buffer capacities. */
+int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                    int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                    const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                                    int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                                    int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                                    int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                                    int64_t* num_edges_out_device,
+                                    void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

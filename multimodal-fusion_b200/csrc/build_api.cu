@@ -4,6 +4,7 @@
 // through the host language -- what matters for batches of small slides (BASELINE config C4).
 // Mirrors the body of the reference's build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433).
 #include "common.cuh"
+#include "sort_scan.cuh"
 
 namespace hg {
 static size_t al1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -53,16 +54,18 @@ extern "C" int hg_build_workspace_bytes(int64_t n, int64_t d, int k, int spatial
     return HG_OK;
 }
 
-extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
-                                       int metric, float lambda_h, float lambda_g, int k, int spatial_k,
-                                       const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
-                                       int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
-                                       int64_t max_edges, int64_t* edge_index, float* edge_weights,
-                                       int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
-                                       int64_t* num_edges_out_host,
-                                       void* workspace, size_t workspace_bytes, void* stream) {
-    HG_REQUIRE(feats && knn_idx && knn_val && edge_index && edge_weights && num_edges_out_host, HG_ERR_BAD_ARG,
-               "hg_build_knn_hypergraph: null buffer");
+// num_edges_out_host != null: synchronising form (compact outputs sized by the host-known count);
+// else stream-ordered form: the count stays on the device (*num_edges_out_dev), nothing blocks.
+static int build_impl(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                      int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                      const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                      int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                      int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                      int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                      int64_t* num_edges_out_host, int64_t* num_edges_out_dev,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(feats && knn_idx && knn_val && edge_index && edge_weights && (num_edges_out_host || num_edges_out_dev),
+               HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: null buffer");
     HG_REQUIRE(spatial_k == 0 || (pos && spatial_idx && spatial_d2), HG_ERR_BAD_ARG,
                "hg_build_knn_hypergraph: spatial_k > 0 needs positions and spatial output buffers");
     const bool want_csr = csr_rowptr != nullptr;
@@ -78,6 +81,7 @@ extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d,
     HG_REQUIRE(workspace && workspace_bytes >= w.bytes, HG_ERR_WORKSPACE,
                "hg_build_knn_hypergraph: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
     char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
 
     float* knn_cos = reinterpret_cast<float*>(ws + w.off_cos);
     rc = hg_knn_feature_cos(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, 0, n, 1, 0, knn_idx, knn_val,
@@ -92,18 +96,56 @@ extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d,
         if (rc != HG_OK) return rc;
         lists[1] = spatial_idx; ks[1] = spatial_k; num_lists = 2;
     }
-    rc = hg_edges_count(lists, ks, num_lists, n, labels, num_hyperedges, clique_pairs, num_edges_out_host,
-                        ws + w.off_edges, w.edges, stream);
-    if (rc != HG_OK) return rc;
-    const int64_t e = *num_edges_out_host;
-    HG_REQUIRE(e <= max_edges, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: %lld edges exceed max_edges", (long long)e);
-    rc = hg_edges_fill(e, edge_index, ws + w.off_edges, w.edges, stream);
-    if (rc != HG_OK) return rc;
-    rc = hg_edge_weights_from_knn(feats, n, d, knn_idx, knn_cos, k, edge_index, e, edge_weights, stream);
-    if (rc != HG_OK) return rc;
-    if (want_csr) {
-        rc = hg_csr_from_coo(edge_index, e, n, csr_rowptr, csr_col, csr_eid, ws + w.off_csr, w.csr, stream);
+    if (num_edges_out_host != nullptr) {
+        rc = hg_edges_count(lists, ks, num_lists, n, labels, num_hyperedges, clique_pairs, num_edges_out_host,
+                            ws + w.off_edges, w.edges, stream);
         if (rc != HG_OK) return rc;
+        const int64_t e = *num_edges_out_host;
+        HG_REQUIRE(e <= max_edges, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: %lld edges exceed max_edges", (long long)e);
+        rc = hg_edges_fill(e, edge_index, ws + w.off_edges, w.edges, stream);
+        if (rc != HG_OK) return rc;
+        rc = hg_edge_weights_from_knn(feats, n, d, knn_idx, knn_cos, k, edge_index, e, edge_weights, stream);
+        if (rc != HG_OK) return rc;
+        if (want_csr) rc = hg_csr_from_coo(edge_index, e, n, csr_rowptr, csr_col, csr_eid, ws + w.off_csr, w.csr, stream);
+        return rc;
     }
-    return HG_OK;
+    // stream-ordered: E <= bound <= max_edges by construction; every later stage reads it from the device
+    rc = edges_enqueue(lists, ks, num_lists, n, labels, num_hyperedges, clique_pairs, ws + w.off_edges, w.edges, st, nullptr);
+    if (rc != HG_OK) return rc;
+    rc = edges_fill_enqueue(bound, edge_index, ws + w.off_edges, num_edges_out_dev, st);
+    if (rc != HG_OK) return rc;
+    rc = edge_weights_from_knn_enqueue(feats, n, d, knn_idx, knn_cos, k, edge_index, num_edges_out_dev, bound, edge_weights, st);
+    if (rc != HG_OK) return rc;
+    if (want_csr)
+        rc = csr_from_coo_enqueue(edge_index, num_edges_out_dev, bound, n, csr_rowptr, csr_col, csr_eid, ws + w.off_csr,
+                                  w.csr, st);
+    return rc;
+}
+
+extern "C" int hg_build_knn_hypergraph(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                       int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                       const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                                       int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                                       int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                                       int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                                       int64_t* num_edges_out_host,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(num_edges_out_host, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: null buffer");
+    return build_impl(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, spatial_k, labels, num_hyperedges,
+                      clique_pairs, knn_idx, knn_val, spatial_idx, spatial_d2, max_edges, edge_index, edge_weights,
+                      csr_rowptr, csr_col, csr_eid, num_edges_out_host, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                               int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                               const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                                               int32_t* knn_idx, float* knn_val, int32_t* spatial_idx, float* spatial_d2,
+                                               int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                                               int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                                               int64_t* num_edges_out_device,
+                                               void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(num_edges_out_device, HG_ERR_BAD_ARG, "hg_build_knn_hypergraph_enqueue: null buffer");
+    return build_impl(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, spatial_k, labels, num_hyperedges,
+                      clique_pairs, knn_idx, knn_val, spatial_idx, spatial_d2, max_edges, edge_index, edge_weights,
+                      csr_rowptr, csr_col, csr_eid, nullptr, num_edges_out_device, workspace, workspace_bytes, stream);
 }

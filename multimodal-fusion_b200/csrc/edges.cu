@@ -111,10 +111,15 @@ __global__ void write_header_kernel(EdgesHeader* h, const unsigned long long* co
     }
 }
 
+// num_edges < 0: the count is taken from the header (stream-ordered build, no host round trip) and
+// also published to *count_out
 __global__ void decode_edges_kernel(const EdgesHeader* __restrict__ h, const char* __restrict__ ws,
-                                    int64_t num_edges, int64_t* __restrict__ edge_index) {
+                                    int64_t num_edges, int64_t* __restrict__ edge_index,
+                                    int64_t* __restrict__ count_out) {
     const uint64_t* uniq = reinterpret_cast<const uint64_t*>(ws + h->unique_off);
     const uint64_t n = h->n;
+    if (num_edges < 0) num_edges = int64_t(h->num_edges);
+    if (count_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *count_out = num_edges;
     for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < num_edges; e += int64_t(gridDim.x) * blockDim.x) {
         const uint64_t key = uniq[e];
         const uint64_t u = key / n;
@@ -189,11 +194,13 @@ extern "C" int hg_clique_pairs(const int32_t* labels, int64_t n, int num_hypered
     return HG_OK;
 }
 
-extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, int num_lists, int64_t n,
-                              const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
-                              int64_t* num_edges_out_host,
-                              void* workspace, size_t workspace_bytes, void* stream) {
-    HG_REQUIRE(n > 0 && num_edges_out_host && workspace, HG_ERR_BAD_ARG, "hg_edges_count: bad argument");
+// Everything of hg_edges_count up to (not including) the host read-back of the count: the unique keys
+// and the header are left in the workspace, *d_count_out = device address of the 64-bit count.
+int hg::edges_enqueue(const int32_t* const* knn_lists, const int* ks, int num_lists, int64_t n,
+                      const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                      void* workspace, size_t workspace_bytes, cudaStream_t st,
+                      const unsigned long long** d_count_out) {
+    HG_REQUIRE(n > 0 && workspace, HG_ERR_BAD_ARG, "hg_edges_count: bad argument");
     HG_REQUIRE(num_lists >= 0 && num_lists <= kMaxLists, HG_ERR_UNSUPPORTED, "hg_edges_count: at most %d lists", kMaxLists);
     HG_REQUIRE(n < (int64_t(1) << 31), HG_ERR_UNSUPPORTED, "hg_edges_count: n must be < 2^31");
     if (labels == nullptr) { num_hyperedges = 0; clique_pairs = 0; }
@@ -208,7 +215,6 @@ extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, in
     const EdgesPlan p = plan_edges(n, L.slot_begin[num_lists], num_hyperedges, clique_pairs);
     HG_REQUIRE(workspace_bytes >= p.bytes, HG_ERR_WORKSPACE, "hg_edges_count: workspace too small (%zu < %zu)",
                workspace_bytes, p.bytes);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* ws = static_cast<char*>(workspace);
     uint64_t* keys = reinterpret_cast<uint64_t*>(ws + p.off_keys);
     uint64_t* tmp = reinterpret_cast<uint64_t*>(ws + p.off_tmp);
@@ -256,10 +262,40 @@ extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, in
                                           (unsigned long long)(reinterpret_cast<char*>(uniq) - ws), (unsigned long long)n);
     HG_CHECK_LAUNCH();
     count_launches(1);
+    if (d_count_out) *d_count_out = d_count;
+    return HG_OK;
+}
+
+extern "C" int hg_edges_count(const int32_t* const* knn_lists, const int* ks, int num_lists, int64_t n,
+                              const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                              int64_t* num_edges_out_host,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(num_edges_out_host, HG_ERR_BAD_ARG, "hg_edges_count: bad argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned long long* d_count = nullptr;
+    int rc = edges_enqueue(knn_lists, ks, num_lists, n, labels, num_hyperedges, clique_pairs, workspace, workspace_bytes,
+                           st, &d_count);
+    if (rc != HG_OK) return rc;
     unsigned long long h_count = 0;
     HG_CHECK_CUDA(cudaMemcpyAsync(&h_count, d_count, 8, cudaMemcpyDeviceToHost, st));
     HG_CHECK_CUDA(cudaStreamSynchronize(st));
     *num_edges_out_host = int64_t(h_count);
+    return HG_OK;
+}
+
+// hg_edges_fill for a count that is still on the device: decodes h->num_edges (<= capacity) edges
+// as edge_index [2, E] (row 1 at offset E) and publishes E to *count_out_dev.
+int hg::edges_fill_enqueue(int64_t capacity, int64_t* edge_index, const void* workspace, int64_t* count_out_dev,
+                           cudaStream_t st) {
+    if (capacity <= 0) {
+        if (count_out_dev) HG_CHECK_CUDA(cudaMemsetAsync(count_out_dev, 0, 8, st));
+        return HG_OK;
+    }
+    const int blocks = int(min64(ceil_div(capacity, 256), 148 * 16));
+    decode_edges_kernel<<<blocks, 256, 0, st>>>(static_cast<const EdgesHeader*>(workspace),
+                                                static_cast<const char*>(workspace), -1, edge_index, count_out_dev);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
     return HG_OK;
 }
 
@@ -271,7 +307,7 @@ extern "C" int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
     HG_REQUIRE(edge_index, HG_ERR_BAD_ARG, "hg_edges_fill: null edge_index");
     const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 16));
     decode_edges_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const EdgesHeader*>(workspace), static_cast<const char*>(workspace), num_edges, edge_index);
+        static_cast<const EdgesHeader*>(workspace), static_cast<const char*>(workspace), num_edges, edge_index, nullptr);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

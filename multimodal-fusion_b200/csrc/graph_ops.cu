@@ -39,7 +39,8 @@ edge_cosine_kernel(const float* __restrict__ feats, int64_t d, const int64_t* __
 __global__ void __launch_bounds__(256)
 edge_weights_from_knn_kernel(const float* __restrict__ feats, int64_t d, const int32_t* __restrict__ knn_idx,
                              const float* __restrict__ knn_cos, int k, const int64_t* __restrict__ edge_index,
-                             int64_t num_edges, float* __restrict__ w) {
+                             int64_t num_edges, const int64_t* __restrict__ num_edges_dev, float* __restrict__ w) {
+    if (num_edges_dev != nullptr) num_edges = *num_edges_dev;          // stream-ordered build: count still on the device
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -71,19 +72,29 @@ edge_weights_from_knn_kernel(const float* __restrict__ feats, int64_t d, const i
 }
 
 // ---- CSR ---------------------------------------------------------------------------------
-__global__ void csr_emit_kernel(const int64_t* __restrict__ edge_index, int64_t num_edges, uint64_t n,
+// num_edges_dev != null: the count is on the device; slots [E, capacity) get the sentinel key n*n,
+// which sorts behind every real key
+__global__ void csr_emit_kernel(const int64_t* __restrict__ edge_index, int64_t num_edges,
+                                const int64_t* __restrict__ num_edges_dev, int64_t capacity, uint64_t n,
                                 uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < num_edges; e += int64_t(gridDim.x) * blockDim.x) {
-        const uint64_t u = uint64_t(edge_index[e]), v = uint64_t(edge_index[num_edges + e]);
-        keys[2 * e] = u * n + v;     vals[2 * e] = uint32_t(e);
-        keys[2 * e + 1] = v * n + u; vals[2 * e + 1] = uint32_t(e);
+    if (num_edges_dev != nullptr) num_edges = *num_edges_dev;
+    for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < capacity; e += int64_t(gridDim.x) * blockDim.x) {
+        if (e < num_edges) {
+            const uint64_t u = uint64_t(edge_index[e]), v = uint64_t(edge_index[num_edges + e]);
+            keys[2 * e] = u * n + v;     vals[2 * e] = uint32_t(e);
+            keys[2 * e + 1] = v * n + u; vals[2 * e + 1] = uint32_t(e);
+        } else {
+            keys[2 * e] = n * n;     vals[2 * e] = 0u;
+            keys[2 * e + 1] = n * n; vals[2 * e + 1] = 0u;
+        }
     }
 }
 
 // sorted (node*n + nbr, eid) -> col, eid, rowptr (first position of every node; gaps = empty rows)
 __global__ void csr_finish_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t nnz,
-                                  uint64_t n, int64_t* __restrict__ rowptr, int64_t* __restrict__ col,
-                                  int64_t* __restrict__ eid) {
+                                  const int64_t* __restrict__ num_edges_dev, uint64_t n, int64_t* __restrict__ rowptr,
+                                  int64_t* __restrict__ col, int64_t* __restrict__ eid) {
+    if (num_edges_dev != nullptr) nnz = 2 * *num_edges_dev;
     for (int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; p <= nnz; p += int64_t(gridDim.x) * blockDim.x) {
         const int64_t node = (p < nnz) ? int64_t(keys[p] / n) : int64_t(n);        // virtual end marker
         const int64_t prev = (p > 0) ? int64_t(keys[p - 1] / n) : -1;
@@ -162,7 +173,19 @@ extern "C" int hg_edge_weights_from_knn(const float* feats, int64_t n, int64_t d
     HG_REQUIRE(edge_index && weights && knn_idx && knn_cos, HG_ERR_BAD_ARG, "hg_edge_weights_from_knn: null buffer");
     const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 8));
     edge_weights_from_knn_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        feats, d, knn_idx, knn_cos, k, edge_index, num_edges, weights);
+        feats, d, knn_idx, knn_cos, k, edge_index, num_edges, nullptr, weights);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
+int hg::edge_weights_from_knn_enqueue(const float* feats, int64_t n, int64_t d, const int32_t* knn_idx,
+                                      const float* knn_cos, int k, const int64_t* edge_index,
+                                      const int64_t* num_edges_dev, int64_t capacity, float* weights, cudaStream_t st) {
+    if (capacity <= 0) return HG_OK;
+    const int blocks = int(min64(ceil_div(capacity, 256), 148 * 8));
+    edge_weights_from_knn_kernel<<<blocks, 256, 0, st>>>(feats, d, knn_idx, knn_cos, k, edge_index, 0, num_edges_dev,
+                                                         weights);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -199,13 +222,50 @@ extern "C" int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int
     uint32_t* vtmp = cv.take<uint32_t>(nnz);
     uint32_t* table = cv.take<uint32_t>(sort_table_entries(nnz));
     const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 16));
-    csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, num_edges, uint64_t(n), keys, vals);
+    csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, num_edges, nullptr, num_edges, uint64_t(n), keys, vals);
     HG_CHECK_LAUNCH();
     count_launches(1);
     uint64_t* sk; uint32_t* sv;
     int rc = radix_sort_u64(keys, tmp, vals, vtmp, nnz, bits_for(uint64_t(n) * uint64_t(n)), table, &sk, &sv, st);
     if (rc != HG_OK) return rc;
-    csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, nnz, uint64_t(n),
+    csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, nnz, nullptr, uint64_t(n),
+                                                                                         rowptr, col, eid);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
+// hg_csr_from_coo with the edge count still on the device: the directed-key sort runs over 2 * capacity
+// slots (the tail holds sentinels), the finish kernel stops at 2 E.
+int hg::csr_from_coo_enqueue(const int64_t* edge_index, const int64_t* num_edges_dev, int64_t capacity, int64_t n,
+                             int64_t* rowptr, int64_t* col, int64_t* eid, void* workspace, size_t workspace_bytes,
+                             cudaStream_t st) {
+    HG_REQUIRE(rowptr && n > 0 && capacity >= 0 && num_edges_dev, HG_ERR_BAD_ARG, "csr_from_coo_enqueue: bad argument");
+    HG_REQUIRE(n < (int64_t(1) << 31) && capacity < (int64_t(1) << 29), HG_ERR_UNSUPPORTED, "csr_from_coo_enqueue: too large");
+    size_t need = 0;
+    hg_csr_workspace_bytes(n, capacity, &need);
+    HG_REQUIRE(capacity == 0 || (workspace && workspace_bytes >= need), HG_ERR_WORKSPACE,
+               "csr_from_coo_enqueue: workspace too small (%zu < %zu)", workspace_bytes, need);
+    const int64_t nnz = 2 * capacity;
+    if (nnz == 0) {
+        HG_CHECK_CUDA(cudaMemsetAsync(rowptr, 0, size_t(n + 1) * 8, st));
+        return HG_OK;
+    }
+    HG_REQUIRE(edge_index && col && eid, HG_ERR_BAD_ARG, "csr_from_coo_enqueue: null buffer");
+    Carver cv(workspace);
+    uint64_t* keys = cv.take<uint64_t>(nnz);
+    uint64_t* tmp = cv.take<uint64_t>(nnz);
+    uint32_t* vals = cv.take<uint32_t>(nnz);
+    uint32_t* vtmp = cv.take<uint32_t>(nnz);
+    uint32_t* table = cv.take<uint32_t>(sort_table_entries(nnz));
+    const int blocks = int(min64(ceil_div(capacity, 256), 148 * 16));
+    csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, 0, num_edges_dev, capacity, uint64_t(n), keys, vals);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    uint64_t* sk; uint32_t* sv;
+    int rc = radix_sort_u64(keys, tmp, vals, vtmp, nnz, bits_for(uint64_t(n) * uint64_t(n)), table, &sk, &sv, st);
+    if (rc != HG_OK) return rc;
+    csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, 0, num_edges_dev, uint64_t(n),
                                                                                          rowptr, col, eid);
     HG_CHECK_LAUNCH();
     count_launches(1);

@@ -15,6 +15,20 @@ int unique_sorted_u64(const uint64_t* keys, int64_t count, uint64_t sentinel, ui
 // in-place exclusive scan of per-tile counts; grand total -> *total_out (device)
 int scan_tile_sums(uint32_t* sums, int64_t len, unsigned long long* total_out, cudaStream_t st);
 
+// ---- stream-ordered halves of the count -> fill pairs (build_api.cu: no host round trip) ----------
+int edges_enqueue(const int32_t* const* knn_lists, const int* ks, int num_lists, int64_t n,
+                  const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                  void* workspace, size_t workspace_bytes, cudaStream_t st, const unsigned long long** d_count_out);
+int edges_fill_enqueue(int64_t capacity, int64_t* edge_index, const void* workspace, int64_t* count_out_dev,
+                       cudaStream_t st);
+// A6 / CSR with the edge count read from *num_edges_dev; grids and the CSR sort are sized for `capacity`
+int edge_weights_from_knn_enqueue(const float* feats, int64_t n, int64_t d, const int32_t* knn_idx, const float* knn_cos,
+                                  int k, const int64_t* edge_index, const int64_t* num_edges_dev, int64_t capacity,
+                                  float* weights, cudaStream_t st);
+int csr_from_coo_enqueue(const int64_t* edge_index, const int64_t* num_edges_dev, int64_t capacity, int64_t n,
+                         int64_t* rowptr, int64_t* col, int64_t* eid, void* workspace, size_t workspace_bytes,
+                         cudaStream_t st);
+
 // ---- device-wide exclusive scan of uint32 -> uint64 totals --------------------------
 constexpr int SC_THREADS = 256;
 constexpr int SC_ITEMS = 8;
