@@ -18,20 +18,25 @@ void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed);
 
 // CUDA-event pairs recorded around the fused tensor-core kernel on its own stream, so a
 // benchmark can report that kernel's duration without a profiler attached.
-constexpr int kProfSlots = 256;
+constexpr int kProfSlots = 4096;
 static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[2 * kProfSlots];
 static bool g_prof_made = false;
-static int g_prof_used = 0;
+static std::atomic<int> g_prof_used{0};
+static thread_local int t_prof_slot = -1;          // builds may be enqueued from several host threads
 
 void prof_begin(cudaStream_t st) {
-    if (!g_prof_on || g_prof_used >= kProfSlots) return;
-    cudaEventRecord(g_prof_ev[2 * g_prof_used], st);
+    t_prof_slot = -1;
+    if (!g_prof_on) return;
+    const int slot = g_prof_used.fetch_add(1);
+    if (slot >= kProfSlots) return;
+    t_prof_slot = slot;
+    cudaEventRecord(g_prof_ev[2 * slot], st);
 }
 void prof_end(cudaStream_t st) {
-    if (!g_prof_on || g_prof_used >= kProfSlots) return;
-    cudaEventRecord(g_prof_ev[2 * g_prof_used + 1], st);
-    ++g_prof_used;
+    if (t_prof_slot < 0) return;
+    cudaEventRecord(g_prof_ev[2 * t_prof_slot + 1], st);
+    t_prof_slot = -1;
 }
 }  // namespace hg
 
@@ -45,7 +50,7 @@ extern "C" int hg_profile_enable(int on) {
         hg::g_prof_made = true;
     }
     hg::g_prof_on = on != 0;
-    hg::g_prof_used = 0;
+    hg::g_prof_used.store(0);
     return HG_OK;
 }
 
@@ -54,14 +59,15 @@ extern "C" int hg_profile_enable(int on) {
 extern "C" int hg_profile_collect(float* ms_total, int* launches) {
     HG_REQUIRE(ms_total && launches, HG_ERR_BAD_ARG, "hg_profile_collect: null");
     float sum = 0.f;
-    for (int i = 0; i < hg::g_prof_used; ++i) {
+    const int used = hg::g_prof_used.load() < hg::kProfSlots ? hg::g_prof_used.load() : hg::kProfSlots;
+    for (int i = 0; i < used; ++i) {
         float ms = 0.f;
         HG_CHECK_CUDA(cudaEventSynchronize(hg::g_prof_ev[2 * i + 1]));
         HG_CHECK_CUDA(cudaEventElapsedTime(&ms, hg::g_prof_ev[2 * i], hg::g_prof_ev[2 * i + 1]));
         sum += ms;
     }
     *ms_total = sum;
-    *launches = hg::g_prof_used;
-    hg::g_prof_used = 0;
+    *launches = used;
+    hg::g_prof_used.store(0);
     return HG_OK;
 }

@@ -72,36 +72,68 @@ edge_weights_from_knn_kernel(const float* __restrict__ feats, int64_t d, const i
 }
 
 // ---- CSR ---------------------------------------------------------------------------------
-// num_edges_dev != null: the count is on the device; slots [E, capacity) get the sentinel key n*n,
-// which sorts behind every real key
-__global__ void csr_emit_kernel(const int64_t* __restrict__ edge_index, int64_t num_edges,
-                                const int64_t* __restrict__ num_edges_dev, int64_t capacity, uint64_t n,
-                                uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+// The edge list arrives sorted by (u, v) with u < v.  Row x of the incidence holds, by ascending
+// neighbour: first the edges (u', x) in which x is the LARGER endpoint (ascending u' = ascending
+// edge id), then the edges (x, v) in which it is the smaller one (a contiguous run of the edge
+// list).  Only the first part needs data movement: ONE stable radix sort of the E pairs
+// (key = larger endpoint, log2 n bits; payload = edge id) transposes the list.  Row starts follow
+// without a scan: with first_hi[x] / first_lo[x] = number of edges whose smaller / larger endpoint
+// is < x (both found by boundary detection on a sorted run), rowptr[x] = first_hi[x] + first_lo[x].
+// num_edges_dev != null: the count is still on the device and slots [E, capacity) carry the
+// sentinel key n, which sorts behind every node.
+__global__ void csr_keys_kernel(const int64_t* __restrict__ edge_index, int64_t num_edges,
+                                const int64_t* __restrict__ num_edges_dev, int64_t capacity, int64_t n,
+                                uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ first_hi) {
     if (num_edges_dev != nullptr) num_edges = *num_edges_dev;
-    for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < capacity; e += int64_t(gridDim.x) * blockDim.x) {
-        if (e < num_edges) {
-            const uint64_t u = uint64_t(edge_index[e]), v = uint64_t(edge_index[num_edges + e]);
-            keys[2 * e] = u * n + v;     vals[2 * e] = uint32_t(e);
-            keys[2 * e + 1] = v * n + u; vals[2 * e + 1] = uint32_t(e);
-        } else {
-            keys[2 * e] = n * n;     vals[2 * e] = 0u;
-            keys[2 * e + 1] = n * n; vals[2 * e + 1] = 0u;
+    const int64_t span = capacity > num_edges ? capacity : num_edges + 1;      // e = num_edges closes first_hi
+    for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < span; e += int64_t(gridDim.x) * blockDim.x) {
+        if (e < capacity) {
+            keys[e] = (e < num_edges) ? uint64_t(edge_index[num_edges + e]) : uint64_t(n);
+            vals[e] = uint32_t(e);
+        }
+        if (e <= num_edges) {
+            const int64_t node = (e < num_edges) ? edge_index[e] : n;
+            const int64_t prev = (e > 0) ? edge_index[e - 1] : -1;
+            for (int64_t r = prev + 1; r <= node; ++r) first_hi[r] = uint32_t(e);
         }
     }
 }
 
-// sorted (node*n + nbr, eid) -> col, eid, rowptr (first position of every node; gaps = empty rows)
-__global__ void csr_finish_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t nnz,
-                                  const int64_t* __restrict__ num_edges_dev, uint64_t n, int64_t* __restrict__ rowptr,
-                                  int64_t* __restrict__ col, int64_t* __restrict__ eid) {
-    if (num_edges_dev != nullptr) nnz = 2 * *num_edges_dev;
-    for (int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; p <= nnz; p += int64_t(gridDim.x) * blockDim.x) {
-        const int64_t node = (p < nnz) ? int64_t(keys[p] / n) : int64_t(n);        // virtual end marker
-        const int64_t prev = (p > 0) ? int64_t(keys[p - 1] / n) : -1;
-        for (int64_t r = prev + 1; r <= node; ++r) rowptr[r] = p;
-        if (p < nnz) {
-            col[p] = int64_t(keys[p] - uint64_t(node) * n);
-            eid[p] = int64_t(vals[p]);
+// boundaries of the run sorted by larger endpoint -> first_lo, and the row starts
+__global__ void csr_bounds_kernel(const uint64_t* __restrict__ sorted_keys, int64_t num_edges,
+                                  const int64_t* __restrict__ num_edges_dev, int64_t n,
+                                  const uint32_t* __restrict__ first_hi, uint32_t* __restrict__ first_lo,
+                                  int64_t* __restrict__ rowptr) {
+    if (num_edges_dev != nullptr) num_edges = *num_edges_dev;
+    for (int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; p <= num_edges; p += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t node = (p < num_edges) ? int64_t(sorted_keys[p]) : n;
+        const int64_t prev = (p > 0) ? int64_t(sorted_keys[p - 1]) : -1;
+        for (int64_t r = prev + 1; r <= node; ++r) {
+            first_lo[r] = uint32_t(p);
+            rowptr[r] = int64_t(first_hi[r]) + p;
+        }
+    }
+}
+
+__global__ void csr_fill_kernel(const int64_t* __restrict__ edge_index, const uint64_t* __restrict__ sorted_keys,
+                                const uint32_t* __restrict__ sorted_eids, int64_t num_edges,
+                                const int64_t* __restrict__ num_edges_dev, const uint32_t* __restrict__ first_hi,
+                                const uint32_t* __restrict__ first_lo, const int64_t* __restrict__ rowptr,
+                                int64_t* __restrict__ col, int64_t* __restrict__ eid) {
+    if (num_edges_dev != nullptr) num_edges = *num_edges_dev;
+    for (int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; t < num_edges; t += int64_t(gridDim.x) * blockDim.x) {
+        {   // position t of the transposed run: edge (u, x) seen from its larger endpoint x
+            const int64_t x = int64_t(sorted_keys[t]);
+            const int64_t e = int64_t(sorted_eids[t]);
+            const int64_t dst = rowptr[x] + (t - int64_t(first_lo[x]));
+            col[dst] = edge_index[e];
+            eid[dst] = e;
+        }
+        {   // edge t = (u, v) seen from its smaller endpoint u, after u's first part
+            const int64_t u = edge_index[t];
+            const int64_t dst = rowptr[u] + int64_t(first_lo[u + 1] - first_lo[u]) + (t - int64_t(first_hi[u]));
+            col[dst] = edge_index[num_edges + t];
+            eid[dst] = t;
         }
     }
 }
@@ -193,83 +225,64 @@ int hg::edge_weights_from_knn_enqueue(const float* feats, int64_t n, int64_t d, 
 
 extern "C" int hg_csr_workspace_bytes(int64_t n, int64_t num_edges, size_t* bytes) {
     HG_REQUIRE(bytes && n > 0 && num_edges >= 0, HG_ERR_BAD_ARG, "hg_csr_workspace_bytes: bad argument");
-    const size_t nnz = size_t(2 * num_edges);
+    const size_t cap = size_t(num_edges);
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
-    *bytes = 2 * al(nnz * 8) + 2 * al(nnz * 4) + al(sort_table_entries(int64_t(nnz)) * 4) + 256;
+    *bytes = 2 * al(cap * 8) + 2 * al(cap * 4) + al(sort_table_entries(int64_t(cap)) * 4) + 2 * al(size_t(n + 1) * 4) + 256;
+    return HG_OK;
+}
+
+// shared by the host-count and device-count entry points (exactly one of num_edges / num_edges_dev is used)
+static int csr_build(const int64_t* edge_index, int64_t num_edges, const int64_t* num_edges_dev, int64_t capacity,
+                     int64_t n, int64_t* rowptr, int64_t* col, int64_t* eid, void* workspace, size_t workspace_bytes,
+                     cudaStream_t st) {
+    HG_REQUIRE(rowptr && n > 0 && capacity >= 0, HG_ERR_BAD_ARG, "hg_csr_from_coo: bad argument");
+    HG_REQUIRE(n < (int64_t(1) << 31) - 1 && capacity < (int64_t(1) << 30), HG_ERR_UNSUPPORTED, "hg_csr_from_coo: too large");
+    if (capacity == 0) {
+        HG_CHECK_CUDA(cudaMemsetAsync(rowptr, 0, size_t(n + 1) * 8, st));
+        return HG_OK;
+    }
+    size_t need = 0;
+    hg_csr_workspace_bytes(n, capacity, &need);
+    HG_REQUIRE(workspace && workspace_bytes >= need, HG_ERR_WORKSPACE, "hg_csr_from_coo: workspace too small (%zu < %zu)",
+               workspace_bytes, need);
+    HG_REQUIRE(edge_index && col && eid, HG_ERR_BAD_ARG, "hg_csr_from_coo: null buffer");
+    Carver cv(workspace);
+    uint64_t* keys = cv.take<uint64_t>(capacity);
+    uint64_t* tmp = cv.take<uint64_t>(capacity);
+    uint32_t* vals = cv.take<uint32_t>(capacity);
+    uint32_t* vtmp = cv.take<uint32_t>(capacity);
+    uint32_t* table = cv.take<uint32_t>(sort_table_entries(capacity));
+    uint32_t* first_hi = cv.take<uint32_t>(n + 1);
+    uint32_t* first_lo = cv.take<uint32_t>(n + 1);
+    const int blocks = int(min64(ceil_div(capacity + 1, 256), 148 * 16));
+    csr_keys_kernel<<<blocks, 256, 0, st>>>(edge_index, num_edges, num_edges_dev, capacity, n, keys, vals, first_hi);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    uint64_t* sk = keys; uint32_t* sv = vals;
+    int rc = radix_sort_u64(keys, tmp, vals, vtmp, capacity, bits_for(uint64_t(n)), table, &sk, &sv, st);
+    if (rc != HG_OK) return rc;
+    csr_bounds_kernel<<<blocks, 256, 0, st>>>(sk, num_edges, num_edges_dev, n, first_hi, first_lo, rowptr);
+    csr_fill_kernel<<<blocks, 256, 0, st>>>(edge_index, sk, sv, num_edges, num_edges_dev, first_hi, first_lo, rowptr, col, eid);
+    HG_CHECK_LAUNCH();
+    count_launches(2);
     return HG_OK;
 }
 
 extern "C" int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int64_t n,
                                int64_t* rowptr, int64_t* col, int64_t* eid,
                                void* workspace, size_t workspace_bytes, void* stream) {
-    HG_REQUIRE(rowptr && n > 0 && num_edges >= 0, HG_ERR_BAD_ARG, "hg_csr_from_coo: bad argument");
-    HG_REQUIRE(n < (int64_t(1) << 31) && num_edges < (int64_t(1) << 31), HG_ERR_UNSUPPORTED, "hg_csr_from_coo: too large");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    size_t need = 0;
-    hg_csr_workspace_bytes(n, num_edges, &need);
-    HG_REQUIRE(num_edges == 0 || (workspace && workspace_bytes >= need), HG_ERR_WORKSPACE,
-               "hg_csr_from_coo: workspace too small (%zu < %zu)", workspace_bytes, need);
-    const int64_t nnz = 2 * num_edges;
-    if (nnz == 0) {
-        HG_CHECK_CUDA(cudaMemsetAsync(rowptr, 0, size_t(n + 1) * 8, st));
-        return HG_OK;
-    }
-    HG_REQUIRE(edge_index && col && eid, HG_ERR_BAD_ARG, "hg_csr_from_coo: null buffer");
-    Carver cv(workspace);
-    uint64_t* keys = cv.take<uint64_t>(nnz);
-    uint64_t* tmp = cv.take<uint64_t>(nnz);
-    uint32_t* vals = cv.take<uint32_t>(nnz);
-    uint32_t* vtmp = cv.take<uint32_t>(nnz);
-    uint32_t* table = cv.take<uint32_t>(sort_table_entries(nnz));
-    const int blocks = int(min64(ceil_div(num_edges, 256), 148 * 16));
-    csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, num_edges, nullptr, num_edges, uint64_t(n), keys, vals);
-    HG_CHECK_LAUNCH();
-    count_launches(1);
-    uint64_t* sk; uint32_t* sv;
-    int rc = radix_sort_u64(keys, tmp, vals, vtmp, nnz, bits_for(uint64_t(n) * uint64_t(n)), table, &sk, &sv, st);
-    if (rc != HG_OK) return rc;
-    csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, nnz, nullptr, uint64_t(n),
-                                                                                         rowptr, col, eid);
-    HG_CHECK_LAUNCH();
-    count_launches(1);
-    return HG_OK;
+    HG_REQUIRE(num_edges >= 0, HG_ERR_BAD_ARG, "hg_csr_from_coo: bad argument");
+    return csr_build(edge_index, num_edges, nullptr, num_edges, n, rowptr, col, eid, workspace, workspace_bytes,
+                     static_cast<cudaStream_t>(stream));
 }
 
-// hg_csr_from_coo with the edge count still on the device: the directed-key sort runs over 2 * capacity
-// slots (the tail holds sentinels), the finish kernel stops at 2 E.
+// hg_csr_from_coo with the edge count still on the device: the sort runs over `capacity` slots (the
+// tail holds sentinels), every kernel stops at E.
 int hg::csr_from_coo_enqueue(const int64_t* edge_index, const int64_t* num_edges_dev, int64_t capacity, int64_t n,
                              int64_t* rowptr, int64_t* col, int64_t* eid, void* workspace, size_t workspace_bytes,
                              cudaStream_t st) {
-    HG_REQUIRE(rowptr && n > 0 && capacity >= 0 && num_edges_dev, HG_ERR_BAD_ARG, "csr_from_coo_enqueue: bad argument");
-    HG_REQUIRE(n < (int64_t(1) << 31) && capacity < (int64_t(1) << 29), HG_ERR_UNSUPPORTED, "csr_from_coo_enqueue: too large");
-    size_t need = 0;
-    hg_csr_workspace_bytes(n, capacity, &need);
-    HG_REQUIRE(capacity == 0 || (workspace && workspace_bytes >= need), HG_ERR_WORKSPACE,
-               "csr_from_coo_enqueue: workspace too small (%zu < %zu)", workspace_bytes, need);
-    const int64_t nnz = 2 * capacity;
-    if (nnz == 0) {
-        HG_CHECK_CUDA(cudaMemsetAsync(rowptr, 0, size_t(n + 1) * 8, st));
-        return HG_OK;
-    }
-    HG_REQUIRE(edge_index && col && eid, HG_ERR_BAD_ARG, "csr_from_coo_enqueue: null buffer");
-    Carver cv(workspace);
-    uint64_t* keys = cv.take<uint64_t>(nnz);
-    uint64_t* tmp = cv.take<uint64_t>(nnz);
-    uint32_t* vals = cv.take<uint32_t>(nnz);
-    uint32_t* vtmp = cv.take<uint32_t>(nnz);
-    uint32_t* table = cv.take<uint32_t>(sort_table_entries(nnz));
-    const int blocks = int(min64(ceil_div(capacity, 256), 148 * 16));
-    csr_emit_kernel<<<blocks, 256, 0, st>>>(edge_index, 0, num_edges_dev, capacity, uint64_t(n), keys, vals);
-    HG_CHECK_LAUNCH();
-    count_launches(1);
-    uint64_t* sk; uint32_t* sv;
-    int rc = radix_sort_u64(keys, tmp, vals, vtmp, nnz, bits_for(uint64_t(n) * uint64_t(n)), table, &sk, &sv, st);
-    if (rc != HG_OK) return rc;
-    csr_finish_kernel<<<int(min64(ceil_div(nnz + 1, 256), 148 * 16)), 256, 0, st>>>(sk, sv, 0, num_edges_dev, uint64_t(n),
-                                                                                         rowptr, col, eid);
-    HG_CHECK_LAUNCH();
-    count_launches(1);
-    return HG_OK;
+    HG_REQUIRE(num_edges_dev, HG_ERR_BAD_ARG, "csr_from_coo_enqueue: bad argument");
+    return csr_build(edge_index, 0, num_edges_dev, capacity, n, rowptr, col, eid, workspace, workspace_bytes, st);
 }
 
 extern "C" int hg_threshold_workspace_bytes(int64_t n, size_t* bytes) {

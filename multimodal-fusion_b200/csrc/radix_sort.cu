@@ -142,9 +142,11 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict
     }
 }
 
-// uint32 scratch entries: per-pass digit totals + one status array (tiles x 256) + the ticket
+// uint32 scratch entries: per-pass digit totals + one status array (tiles x 256 + the ticket) per
+// pass, so that a single memset prepares the whole sort
+static size_t rs_status_entries(int64_t count) { return size_t(rs_tiles_for(count)) * 256 + 64; }
 size_t sort_table_entries(int64_t count) {
-    return size_t(RS_MAX_PASSES) * 256 + size_t(rs_tiles_for(count)) * 256 + 64;
+    return size_t(RS_MAX_PASSES) * 256 + size_t(RS_MAX_PASSES) * rs_status_entries(count);
 }
 
 template <bool HAS_VALS>
@@ -170,16 +172,17 @@ int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t*
     HG_REQUIRE(passes <= RS_MAX_PASSES, HG_ERR_BAD_ARG, "radix sort: bad bit count %d", bits);
     const int items = rs_items_for(count), tiles = rs_tiles_for(count);
     uint32_t* hist = table;
-    uint32_t* status = table + size_t(RS_MAX_PASSES) * 256;
-    const size_t status_bytes = (size_t(tiles) * 256 + 1) * sizeof(uint32_t);
-    HG_CHECK_CUDA(cudaMemsetAsync(hist, 0, size_t(RS_MAX_PASSES) * 256 * sizeof(uint32_t), st));
+    uint32_t* status0 = table + size_t(RS_MAX_PASSES) * 256;
+    const size_t status_stride = rs_status_entries(count);
+    HG_CHECK_CUDA(cudaMemsetAsync(table, 0, (size_t(RS_MAX_PASSES) * 256 + size_t(passes) * status_stride) * sizeof(uint32_t),
+                                  st));
     const int hist_blocks = int(min64(ceil_div(count, 256 * 8), 148 * 4));
     rs_global_hist_kernel<<<hist_blocks, RS_THREADS, 0, st>>>(keys, count, passes, hist);
     count_launches(1);
     uint64_t* src = keys; uint64_t* dst = keys_tmp;
     uint32_t* vsrc = vals; uint32_t* vdst = vals_tmp;
     for (int p = 0; p < passes; ++p) {
-        HG_CHECK_CUDA(cudaMemsetAsync(status, 0, status_bytes, st));
+        uint32_t* status = status0 + size_t(p) * status_stride;
         if (vals) launch_onesweep<true>(items, tiles, src, vsrc, count, 8 * p, hist + p * 256, status, dst, vdst, st);
         else      launch_onesweep<false>(items, tiles, src, nullptr, count, 8 * p, hist + p * 256, status, dst, nullptr, st);
         HG_CHECK_LAUNCH();

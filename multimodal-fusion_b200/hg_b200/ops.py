@@ -210,12 +210,42 @@ def threshold_edges(K: torch.Tensor, threshold: float):
 
 
 # ------------------------------------------------------------------ one call per slide
+def _pack_build(b: dict, ne: int, return_csr: bool, spatial_k: int) -> dict:
+    """Views of the capacity-sized output buffers for an edge count that is now known."""
+    out = {"knn_idx": b["knn_idx"], "knn_val": b["knn_val"]}
+    if spatial_k:
+        out["spatial_idx"], out["spatial_d2"] = b["sidx"], b["sd2"]
+    out["edge_index"] = b["ei"][: 2 * ne].view(2, ne)
+    out["edge_weights"] = b["w"][:ne]
+    if return_csr:
+        out["csr_rowptr"], out["csr_col"], out["csr_eid"] = b["rowptr"], b["col"][: 2 * ne], b["eid"][: 2 * ne]
+    return out
+
+
+class PendingBuild:
+    """A slide whose build has been enqueued with hg_build_knn_hypergraph_enqueue: nothing has
+    synchronised yet.  `result()` waits for the slide's stream event, reads the edge count and
+    returns the same dict as `build_knn_hypergraph` (views of the capacity-sized buffers)."""
+
+    def __init__(self, bufs: dict, e_host: torch.Tensor, event, return_csr: bool, spatial_k: int, keep):
+        self._b, self._e_host, self.event = bufs, e_host, event
+        self._csr, self._sk, self._keep, self._out = return_csr, spatial_k, keep, None
+
+    def result(self) -> dict:
+        if self._out is None:
+            self.event.synchronize()
+            self._out = _pack_build(self._b, int(self._e_host.item()), self._csr, self._sk)
+            self._keep = None                    # inputs were only kept alive for the enqueued kernels
+        return self._out
+
+
 def build_knn_hypergraph(features: torch.Tensor, k: int, metric: str = "euclidean",
                          positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0, lambda_g: float = 0.0,
                          spatial_k: int = 0, labels: Optional[torch.Tensor] = None, num_hyperedges: int = 0,
-                         return_csr: bool = False, device=None) -> dict:
+                         return_csr: bool = False, device=None, enqueue_only: bool = False):
     """hg_build_knn_hypergraph: kNN lists, edge_index, weights (and CSR) of one slide with a single
-    host call and a single stream synchronisation."""
+    host call and a single stream synchronisation.  enqueue_only=True uses the stream-ordered entry
+    point instead (no synchronisation at all) and returns a PendingBuild."""
     lib = L.load_library()
     dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
     x = L.f32c(features, dev)
@@ -225,7 +255,6 @@ def build_knn_hypergraph(features: torch.Tensor, k: int, metric: str = "euclidea
     pos = L.f32c(positions, dev) if positions is not None else None
     if pos is None:
         spatial_k = 0
-    out = {}
     with torch.cuda.device(dev):
         st = L.stream_ptr(dev)
         lab, pairs = None, C.c_int64(0)
@@ -237,30 +266,30 @@ def build_knn_hypergraph(features: torch.Tensor, k: int, metric: str = "euclidea
         else:
             num_hyperedges = 0
         max_e = n * (k + spatial_k) + pairs.value
-        knn_idx = torch.empty((n, k), dtype=torch.int32, device=dev)
-        knn_val = torch.empty((n, k), dtype=torch.float32, device=dev)
-        sidx = torch.empty((n, spatial_k), dtype=torch.int32, device=dev) if spatial_k else None
-        sd2 = torch.empty((n, spatial_k), dtype=torch.float32, device=dev) if spatial_k else None
-        ei_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev)
-        w_buf = torch.empty(max_e, dtype=torch.float32, device=dev)
-        rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev) if return_csr else None
-        col_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None
-        eid_buf = torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None
+        b = {"knn_idx": torch.empty((n, k), dtype=torch.int32, device=dev),
+             "knn_val": torch.empty((n, k), dtype=torch.float32, device=dev),
+             "sidx": torch.empty((n, spatial_k), dtype=torch.int32, device=dev) if spatial_k else None,
+             "sd2": torch.empty((n, spatial_k), dtype=torch.float32, device=dev) if spatial_k else None,
+             "ei": torch.empty(2 * max_e, dtype=torch.int64, device=dev),
+             "w": torch.empty(max_e, dtype=torch.float32, device=dev),
+             "rowptr": torch.empty(n + 1, dtype=torch.int64, device=dev) if return_csr else None,
+             "col": torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None,
+             "eid": torch.empty(2 * max_e, dtype=torch.int64, device=dev) if return_csr else None}
         nbytes = _size(lib.hg_build_workspace_bytes, n, d, k, spatial_k, num_hyperedges, pairs.value, max_e,
                        int(return_csr))
         ws = L.Workspace.get(dev, nbytes)
+        args = (L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1], L.METRIC[metric], float(lambda_h),
+                float(lambda_g), k, spatial_k, L.ptr(lab), num_hyperedges, pairs.value,
+                L.ptr(b["knn_idx"]), L.ptr(b["knn_val"]), L.ptr(b["sidx"]), L.ptr(b["sd2"]), max_e, L.ptr(b["ei"]),
+                L.ptr(b["w"]), L.ptr(b["rowptr"]), L.ptr(b["col"]), L.ptr(b["eid"]))
+        if enqueue_only:
+            e_dev = torch.empty(1, dtype=torch.int64, device=dev)
+            e_host = torch.empty(1, dtype=torch.int64, pin_memory=True)
+            L.check(lib.hg_build_knn_hypergraph_enqueue(*args, L.ptr(e_dev), L.ptr(ws), nbytes, st))
+            e_host.copy_(e_dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            return PendingBuild(b, e_host, ev, return_csr, spatial_k, keep=(x, pos, lab, e_dev))
         e = C.c_int64(0)
-        L.check(lib.hg_build_knn_hypergraph(
-            L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1], L.METRIC[metric], float(lambda_h),
-            float(lambda_g), k, spatial_k, L.ptr(lab), num_hyperedges, pairs.value,
-            L.ptr(knn_idx), L.ptr(knn_val), L.ptr(sidx), L.ptr(sd2), max_e, L.ptr(ei_buf), L.ptr(w_buf),
-            L.ptr(rowptr), L.ptr(col_buf), L.ptr(eid_buf), C.byref(e), L.ptr(ws), nbytes, st))
-    ne = e.value
-    out["knn_idx"], out["knn_val"] = knn_idx, knn_val
-    if spatial_k:
-        out["spatial_idx"], out["spatial_d2"] = sidx, sd2
-    out["edge_index"] = ei_buf[: 2 * ne].view(2, ne)
-    out["edge_weights"] = w_buf[:ne]
-    if return_csr:
-        out["csr_rowptr"], out["csr_col"], out["csr_eid"] = rowptr, col_buf[: 2 * ne], eid_buf[: 2 * ne]
-    return out
+        L.check(lib.hg_build_knn_hypergraph(*args, C.byref(e), L.ptr(ws), nbytes, st))
+    return _pack_build(b, e.value, return_csr, spatial_k)
