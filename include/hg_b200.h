@@ -240,6 +240,38 @@ int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, co
                                     int64_t* num_edges_out_device,
                                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- batches of slides: ONE host call enqueues every build ----------------------------------
+ * The reference's dataset loop (preprocess_hypergraph.py:651-670) handles slides one at a time.
+ * A slide of a few thousand patches is only a few hundred microseconds of GPU work, so here the
+ * whole batch is enqueued stream-ordered (hg_build_knn_hypergraph_enqueue semantics, no cliques):
+ * slide i runs on lane i % num_lanes = (lane_streams[l], lane_workspaces[l]); with num_threads > 1
+ * the lanes are driven from that many host threads.  All fields are 8 bytes wide, so an array of
+ * hg_slide is also an int64 matrix [num_slides][14].  Pointers are device pointers; pos,
+ * spatial_*, csr_* may be NULL as in hg_build_knn_hypergraph. */
+typedef struct hg_slide {
+    const float* feats;            /* [n, d] */
+    int64_t n;
+    const float* pos;              /* [n, pos_dim] or NULL */
+    int32_t* knn_idx;              /* [n, k] */
+    float* knn_val;                /* [n, k] */
+    int32_t* spatial_idx;          /* [n, spatial_k] or NULL */
+    float* spatial_d2;
+    int64_t max_edges;             /* >= n * (k + spatial_k) */
+    int64_t* edge_index;           /* 2 * max_edges */
+    float* edge_weights;           /* max_edges */
+    int64_t* csr_rowptr;           /* n + 1, or NULL: no CSR */
+    int64_t* csr_col;              /* 2 * max_edges */
+    int64_t* csr_eid;              /* 2 * max_edges */
+    int64_t* num_edges_out_device; /* 1 */
+} hg_slide;
+
+int hg_build_batch_workspace_bytes(const hg_slide* slides, int num_slides, int64_t d, int k, int spatial_k,
+                                   int want_csr, size_t* bytes_per_lane);
+int hg_build_batch_enqueue(const hg_slide* slides, int num_slides, int64_t d, int pos_dim,
+                           int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                           void* const* lane_workspaces, size_t bytes_per_lane,
+                           void* const* lane_streams, int num_lanes, int num_threads);
+
 #ifdef __cplusplus
 }
 #endif

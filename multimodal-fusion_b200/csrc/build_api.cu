@@ -5,6 +5,9 @@
 // Mirrors the body of the reference's build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433).
 #include "common.cuh"
 #include "sort_scan.cuh"
+#include <string>
+#include <thread>
+#include <vector>
 
 namespace hg {
 static size_t al1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -66,6 +69,7 @@ static int build_impl(const float* feats, int64_t n, int64_t d, const float* pos
                       void* workspace, size_t workspace_bytes, void* stream) {
     HG_REQUIRE(feats && knn_idx && knn_val && edge_index && edge_weights && (num_edges_out_host || num_edges_out_dev),
                HG_ERR_BAD_ARG, "hg_build_knn_hypergraph: null buffer");
+    HG_REQUIRE(n > 1, HG_ERR_BAD_ARG, "number of nodes must be greater than 1, got N=%lld", (long long)n);
     HG_REQUIRE(spatial_k == 0 || (pos && spatial_idx && spatial_d2), HG_ERR_BAD_ARG,
                "hg_build_knn_hypergraph: spatial_k > 0 needs positions and spatial output buffers");
     const bool want_csr = csr_rowptr != nullptr;
@@ -148,4 +152,66 @@ extern "C" int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, in
     return build_impl(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, spatial_k, labels, num_hyperedges,
                       clique_pairs, knn_idx, knn_val, spatial_idx, spatial_d2, max_edges, edge_index, edge_weights,
                       csr_rowptr, csr_col, csr_eid, nullptr, num_edges_out_device, workspace, workspace_bytes, stream);
+}
+
+// ---- batches of slides ---------------------------------------------------------------------------
+// The dataset loop of the reference (preprocess_hypergraph.py:651-670) visits slides one by one; a
+// slide of a few thousand patches is a few hundred microseconds of GPU work spread over ~25 kernels,
+// so the host has to stay ahead: one C call enqueues the whole batch, slide i on lane i % num_lanes,
+// optionally from several host threads (thread t drives the lanes l with l % num_threads == t).
+extern "C" int hg_build_batch_workspace_bytes(const hg_slide* slides, int num_slides, int64_t d, int k, int spatial_k,
+                                              int want_csr, size_t* bytes_per_lane) {
+    HG_REQUIRE(slides && num_slides > 0 && bytes_per_lane, HG_ERR_BAD_ARG, "hg_build_batch_workspace_bytes: bad argument");
+    size_t need = 0;
+    for (int i = 0; i < num_slides; ++i) {
+        BuildWs w{};
+        int rc = plan_build(slides[i].n, d, k, spatial_k, 0, 0, slides[i].max_edges, want_csr != 0, &w);
+        if (rc != HG_OK) return rc;
+        if (w.bytes > need) need = w.bytes;
+    }
+    *bytes_per_lane = al1k(need);
+    return HG_OK;
+}
+
+extern "C" int hg_build_batch_enqueue(const hg_slide* slides, int num_slides, int64_t d, int pos_dim,
+                                      int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                      void* const* lane_workspaces, size_t bytes_per_lane,
+                                      void* const* lane_streams, int num_lanes, int num_threads) {
+    HG_REQUIRE(slides && num_slides > 0 && lane_workspaces && lane_streams && num_lanes > 0, HG_ERR_BAD_ARG,
+               "hg_build_batch_enqueue: bad argument");
+    if (num_threads < 1) num_threads = 1;
+    if (num_threads > num_lanes) num_threads = num_lanes;
+    int device = 0;
+    HG_CHECK_CUDA(cudaGetDevice(&device));
+    std::vector<int> rcs(size_t(num_threads), HG_OK);
+    std::vector<std::string> msgs(static_cast<size_t>(num_threads));
+    auto drive = [&](int tid) {
+        if (tid != 0 && cudaSetDevice(device) != cudaSuccess) { rcs[tid] = HG_ERR_CUDA; msgs[tid] = "cudaSetDevice failed"; return; }
+        for (int i = 0; i < num_slides; ++i) {
+            const int lane = i % num_lanes;
+            if (lane % num_threads != tid) continue;
+            const hg_slide& s = slides[i];
+            const int rc = build_impl(s.feats, s.n, d, s.pos, pos_dim, metric, lambda_h, lambda_g, k,
+                                      s.pos ? spatial_k : 0, nullptr, 0, 0, s.knn_idx, s.knn_val, s.spatial_idx, s.spatial_d2,
+                                      s.max_edges, s.edge_index, s.edge_weights, s.csr_rowptr, s.csr_col, s.csr_eid,
+                                      nullptr, s.num_edges_out_device, lane_workspaces[lane], bytes_per_lane,
+                                      lane_streams[lane]);
+            if (rc != HG_OK) {
+                rcs[tid] = rc;
+                msgs[tid] = std::string("slide ") + std::to_string(i) + ": " + get_error();
+                return;
+            }
+        }
+    };
+    if (num_threads == 1) {
+        drive(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 1; t < num_threads; ++t) pool.emplace_back(drive, t);
+        drive(0);
+        for (auto& th : pool) th.join();
+    }
+    for (int t = 0; t < num_threads; ++t)
+        if (rcs[t] != HG_OK) { set_error("hg_build_batch_enqueue: %s", msgs[t].c_str()); return rcs[t]; }
+    return HG_OK;
 }

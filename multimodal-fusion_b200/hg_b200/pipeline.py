@@ -167,68 +167,136 @@ def build_many(slides: Iterable, device=None, pipeline: Optional[SlidePipeline] 
 
 LAST_BATCH_STATS: Dict = {}          # host-side timing of the most recent build_batch call (tuning aid)
 
+# hg_slide (include/hg_b200.h): 14 fields of 8 bytes -> one int64 row per slide
+_F_FEATS, _F_N, _F_POS, _F_KIDX, _F_KVAL, _F_SIDX, _F_SD2, _F_MAXE, _F_EI, _F_W, _F_ROWPTR, _F_COL, _F_EID, _F_NE = range(14)
 
-def build_batch(slides: Iterable, device=None, lanes: int = 4, threads: Optional[int] = None, **build_kwargs) -> List[dict]:
-    """Device-resident batch (no host copies): every slide is enqueued round-robin on `lanes`
-    streams without any synchronisation, then the results (device tensors) are gathered.  The
-    calling stream is ordered before and after the batch.  threads > 1 (HG_B200_BATCH_THREADS)
-    enqueues from that many host threads, lane l driven by thread l % threads -- the C calls
-    release the GIL, so the ~30 kernel launches of different slides are issued in parallel."""
+
+class BatchResults:
+    """Sequence of per-slide result dicts (device tensors, views of one output arena); the dicts are
+    made on access.  Same keys as `knn_hyperedges`."""
+
+    def __init__(self, arena, table, offs, counts, k, spatial_k, return_csr):
+        self._arena, self._t, self._offs, self._ne = arena, table, offs, counts
+        self._k, self._sk, self._csr = k, spatial_k, return_csr
+
+    def __len__(self):
+        return len(self._ne)
+
+    def _view(self, off, count, dtype, shape):
+        nbytes = count * (8 if dtype is torch.int64 else 4)
+        return self._arena[off:off + nbytes].view(dtype).view(shape)
+
+    def __getitem__(self, i: int) -> dict:
+        if i < 0:
+            i += len(self)
+        n, ne, o = int(self._t[i, _F_N]), int(self._ne[i]), self._offs[i]
+        out = {"knn_idx": self._view(o[0], n * self._k, torch.int32, (n, self._k)),
+               "knn_val": self._view(o[1], n * self._k, torch.float32, (n, self._k))}
+        if self._sk and self._t[i, _F_SIDX]:
+            out["spatial_idx"] = self._view(o[2], n * self._sk, torch.int32, (n, self._sk))
+            out["spatial_d2"] = self._view(o[3], n * self._sk, torch.float32, (n, self._sk))
+        out["edge_index"] = self._view(o[4], 2 * ne, torch.int64, (2, ne))
+        out["edge_weights"] = self._view(o[5], ne, torch.float32, (ne,))
+        if self._csr:
+            out["csr_rowptr"] = self._view(o[6], n + 1, torch.int64, (n + 1,))
+            out["csr_col"] = self._view(o[7], 2 * ne, torch.int64, (2 * ne,))
+            out["csr_eid"] = self._view(o[8], 2 * ne, torch.int64, (2 * ne,))
+        return out
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
+def build_batch(slides: Iterable, device=None, lanes: int = 4, threads: Optional[int] = None, *, k: int = 16,
+                kernel: str = "gaussian", lambda_h: float = 1.0, lambda_g: float = 0.0, spatial_k: int = 0,
+                return_csr: bool = False) -> BatchResults:
+    """Device-resident batch of slides (`features` or `(features, positions)` CUDA tensors, same D):
+    ONE C call (hg_build_batch_enqueue) enqueues every build stream-ordered, slide i on lane
+    i % lanes, with no synchronisation; outputs live in one arena.  Returns after the edge counts
+    have arrived (one small D2H).  The calling stream is ordered before and after the batch.
+    threads (HG_B200_BATCH_THREADS) > 1 drives the lanes from that many host threads."""
+    import ctypes as C
     import time
+
+    import numpy as np
+    lib = L.load_library()
     dev = L.require_cuda(device)
-    cur = torch.cuda.current_stream(dev)
-    streams = _lane_streams(dev, lanes)
     if threads is None:
         threads = int(os.environ.get("HG_B200_BATCH_THREADS", "1"))
-    threads = max(1, min(int(threads), len(streams)))
     items = [item if isinstance(item, (tuple, list)) else (item, None) for item in slides]
-    start = torch.cuda.Event()
-    start.record(cur)
-    for s in streams:
-        s.wait_event(start)
-    pend: List = [None] * len(items)
+    num = len(items)
+    if num == 0:
+        return BatchResults(None, np.zeros((0, 14), np.int64), [], [], k, spatial_k, return_csr)
     t0 = time.perf_counter()
-
-    def drive(tid: int):
-        with torch.cuda.device(dev):
-            for i in range(len(items)):
-                lane = i % len(streams)
-                if lane % threads != tid:
-                    continue
-                with torch.cuda.stream(streams[lane]):
-                    pend[i] = _enqueue(items[i][0], items[i][1], dev, **build_kwargs)
-
-    if threads == 1:
-        drive(0)
-    else:
-        import threading
-        errs: List = []
-
-        def guarded(tid):
-            try:
-                drive(tid)
-            except BaseException as e:           # re-raised on the calling thread
-                errs.append(e)
-
-        ts = [threading.Thread(target=guarded, args=(t,)) for t in range(threads)]
-        for t in ts:
-            t.start()
-        for t in ts:
-            t.join()
-        if errs:
-            raise errs[0]
-    t1 = time.perf_counter()
-    for s in streams:
-        ev = torch.cuda.Event()
-        ev.record(s)
-        cur.wait_event(ev)
-    outs = [p.result() for p in pend]
-    for out in outs:                           # allocated on a lane stream, consumed on the caller's
-        for t in out.values():
-            t.record_stream(cur)
-    LAST_BATCH_STATS.update(enqueue_ms=(t1 - t0) * 1e3, total_ms=(time.perf_counter() - t0) * 1e3, lanes=len(streams),
-                            threads=threads, slides=len(items))
-    return outs
+    with torch.cuda.device(dev):
+        xs = [L.f32c(x, dev) for x, _ in items]
+        ps = [L.f32c(p, dev) if (p is not None and spatial_k + (lambda_g != 0)) else None for _, p in items]
+        d = xs[0].shape[1]
+        if any(x.shape[1] != d for x in xs):
+            raise ValueError("build_batch: all slides of a batch must have the same feature dimension")
+        if any(x.shape[0] <= 1 for x in xs):
+            raise ValueError("Number of nodes must be greater than 1.")
+        pds = {p.shape[1] for p in ps if p is not None}
+        if len(pds) > 1:
+            raise ValueError("build_batch: all slides of a batch must have the same position dimension")
+        pos_dim = pds.pop() if pds else 0
+        ns = np.array([x.shape[0] for x in xs], dtype=np.int64)
+        sk = np.array([spatial_k if p is not None else 0 for p in ps], dtype=np.int64)
+        cap = ns * (k + sk)
+        al = lambda b: (b + 255) // 256 * 256                                          # noqa: E731
+        sizes = np.stack([al(ns * k * 4), al(ns * k * 4), al(ns * sk * 4), al(ns * sk * 4), al(2 * cap * 8), al(cap * 4),
+                          al((ns + 1) * 8) * int(return_csr), al(2 * cap * 8) * int(return_csr),
+                          al(2 * cap * 8) * int(return_csr)], axis=1)
+        flat = np.concatenate([[0], np.cumsum(sizes.ravel())])
+        offs = flat[:-1].reshape(num, 9)
+        arena = torch.empty(int(flat[-1]) + 256, dtype=torch.uint8, device=dev)
+        base = arena.data_ptr() + (-arena.data_ptr()) % 256
+        arena = arena[base - arena.data_ptr():]
+        e_dev = torch.empty(num, dtype=torch.int64, device=dev)
+        table = np.zeros((num, 14), dtype=np.int64)
+        table[:, _F_FEATS] = [x.data_ptr() for x in xs]
+        table[:, _F_N] = ns
+        table[:, _F_POS] = [0 if p is None else p.data_ptr() for p in ps]
+        ptrs = base + offs
+        table[:, _F_KIDX], table[:, _F_KVAL] = ptrs[:, 0], ptrs[:, 1]
+        has_sp = sk > 0
+        table[:, _F_SIDX], table[:, _F_SD2] = np.where(has_sp, ptrs[:, 2], 0), np.where(has_sp, ptrs[:, 3], 0)
+        table[:, _F_MAXE], table[:, _F_EI], table[:, _F_W] = cap, ptrs[:, 4], ptrs[:, 5]
+        if return_csr:
+            table[:, _F_ROWPTR], table[:, _F_COL], table[:, _F_EID] = ptrs[:, 6], ptrs[:, 7], ptrs[:, 8]
+        table[:, _F_NE] = e_dev.data_ptr() + 8 * np.arange(num)
+        tptr = table.ctypes.data
+        nbytes = C.c_size_t(0)
+        L.check(lib.hg_build_batch_workspace_bytes(tptr, num, d, k, spatial_k, int(return_csr), C.byref(nbytes)))
+        cur = torch.cuda.current_stream(dev)
+        streams = _lane_streams(dev, min(lanes, num))
+        start = torch.cuda.Event()
+        start.record(cur)
+        wss = []
+        for s in streams:
+            s.wait_event(start)
+            with torch.cuda.stream(s):
+                wss.append(L.Workspace.get(dev, nbytes.value, "batch"))
+        arr_ws = (C.c_void_p * len(streams))(*[w.data_ptr() for w in wss])
+        arr_st = (C.c_void_p * len(streams))(*[s.cuda_stream for s in streams])
+        t1 = time.perf_counter()
+        L.check(lib.hg_build_batch_enqueue(tptr, num, d, pos_dim, L.METRIC[kernel], float(lambda_h),
+                                           float(lambda_g if kernel == "gaussian" else 0.0), k, spatial_k,
+                                           arr_ws, nbytes.value, arr_st, len(streams), max(1, int(threads))))
+        t2 = time.perf_counter()
+        for s in streams:
+            ev = torch.cuda.Event()
+            ev.record(s)
+            cur.wait_event(ev)
+            arena.record_stream(s)
+            e_dev.record_stream(s)
+        for t in xs + [p for p in ps if p is not None]:
+            for s in streams:
+                t.record_stream(s)
+        counts = e_dev.cpu().numpy()           # waits for the batch (the calling stream is ordered after every lane)
+    LAST_BATCH_STATS.update(prepare_ms=(t1 - t0) * 1e3, enqueue_ms=(t2 - t1) * 1e3, total_ms=(time.perf_counter() - t0) * 1e3,
+                            lanes=len(streams), threads=int(threads), slides=num)
+    return BatchResults(arena, table, offs, counts, k, spatial_k, return_csr)
 
 
 _LANES: Dict = {}
@@ -239,3 +307,4 @@ def _lane_streams(dev, lanes: int):
     while len(have) < lanes:
         have.append(torch.cuda.Stream(dev))
     return have[:max(1, lanes)]
+

@@ -79,3 +79,19 @@ def test_enqueue_edge_cases():
     assert out["csr_rowptr"].tolist() == [0, 1, 2] and out["csr_col"].tolist() == [1, 0]
     with pytest.raises(ValueError):
         ops.build_knn_hypergraph(x[:1], 4, "euclidean", enqueue_only=True)
+
+
+def test_build_batch_with_positions_and_threads():
+    sizes = [1500, 9000, 2200, 400]
+    slides = []
+    for i, s in enumerate(sizes):
+        f, p = synth.make_slide(s, 96, 50 + i, "gaussian")
+        slides.append((_cuda(f), _cuda(p)))
+    kw = dict(k=8, kernel="gaussian", lambda_h=1.0, lambda_g=1.0 / 128, spatial_k=8, return_csr=True)
+    outs = build_batch(slides, lanes=2, threads=2, **kw)
+    keys = KEYS + ("spatial_idx", "spatial_d2")
+    for (x, p), out in zip(slides, outs):
+        _equal(out, hg_b200.knn_hyperedges(x, p, **kw), keys)
+    with pytest.raises(ValueError):
+        build_batch([slides[0][0], _cuda(synth.make_features(100, 32, 1))], k=4)      # mixed feature dimensions
+    assert len(build_batch([], k=4)) == 0
