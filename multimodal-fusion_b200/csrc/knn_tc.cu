@@ -100,6 +100,22 @@ __device__ __forceinline__ bool owns_tile(int rb, int ct) {
     return ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0));
 }
 
+// r[j] for a run-time j without local memory: a binary tree of selects on the bits of j (31 SELs,
+// depth 5 -- a linear chain of 31 dependent selects stalls the single epilogue warp of a scheduler
+// for its whole length; ncu, N = 4096: 116 -> 109 us).
+__device__ __forceinline__ uint32_t select32(const uint32_t (&r)[32], int j) {
+    const bool b0 = (j & 1) != 0, b1 = (j & 2) != 0, b2 = (j & 4) != 0, b3 = (j & 8) != 0, b4 = (j & 16) != 0;
+    uint32_t a[16], b[8], c[4];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) a[q] = b0 ? r[2 * q + 1] : r[2 * q];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) b[q] = b1 ? a[2 * q + 1] : a[2 * q];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c[q] = b2 ? b[2 * q + 1] : b[2 * q];
+    const uint32_t d0 = b3 ? c[1] : c[0], d1 = b3 ? c[3] : c[2];
+    return b4 ? d1 : d0;
+}
+
 __device__ __forceinline__ void bucket_push(const TcParams& p, int col, int row, uint32_t score_bits) {
     const int slot = atomicAdd(p.bkt_cnt + col, 1);
     if (slot < p.bkt_cap) p.bkt[int64_t(col) * p.bkt_cap + slot] = make_uint2(score_bits, uint32_t(row));
@@ -334,16 +350,15 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         if (c == self_col) s = INFINITY;
                         hits |= (s < thr) ? (1u << j) : 0u;
                         if (SYM) hits_t |= (st < sm->thr[buf][c]) ? (1u << j) : 0u;
+                        if (!SYM) r[j] = __float_as_uint(s);      // pass 2 picks the score itself, not the dot product
                     }
                     // pass 2 (rare): ascending column order keeps the lowest index among equal scores
                     while (hits) {
                         const int j = __ffs(hits) - 1;
                         hits &= hits - 1;
-                        uint32_t bits = r[0];
-#pragma unroll
-                        for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
                         float s, st;
-                        scores(ch * 32 + j, __uint_as_float(bits), s, st);
+                        if (SYM) scores(ch * 32 + j, __uint_as_float(select32(r, j)), s, st);
+                        else s = __uint_as_float(select32(r, j));
                         if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, (col0 + ch * 32 + j) * cstride);
                     }
                     if (SYM) {
@@ -352,11 +367,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         while (hits_t) {
                             const int j = __ffs(hits_t) - 1;
                             hits_t &= hits_t - 1;
-                            uint32_t bits = r[0];
-#pragma unroll
-                            for (int q = 1; q < 32; ++q) bits = (j == q) ? r[q] : bits;
                             float s, st;
-                            scores(ch * 32 + j, __uint_as_float(bits), s, st);
+                            scores(ch * 32 + j, __uint_as_float(select32(r, j)), s, st);
                             const int slot = atomicAdd(&sm->wq_cnt[quarter], 1);
                             if (slot < TC_WQ_CAP)
                                 sm->wq[quarter][slot] = make_uint2(__float_as_uint(st),
@@ -516,7 +528,7 @@ TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
 }
 
 // Symmetric mode pays a 1/stride pre-pass and needs enough sample columns for a useful bound; it
-// wins from n ~ 10k up (measured break-even at 9k x 512).  HG_B200_TC_SYM=0 disables it,
+// wins from n ~ 9k up (measured at D = 1024: 2 % at n = 8192, 21 % at n = 10240; break-even at 9k x 512).  HG_B200_TC_SYM=0 disables it,
 // HG_B200_TC_SYM=<stride> forces it (any n with enough sample columns) with that pre-pass stride.
 int tc_sym_stride(int64_t n, int64_t n_rows, int k) {
     if (n_rows != n || tc_cta_group() != 1) return 0;
@@ -527,7 +539,7 @@ int tc_sym_stride(int64_t n, int64_t n_rows, int k) {
         if (v <= 0) return 0;
         if (v >= 2 && v <= 64) { stride = v; forced = true; }
     }
-    if (!forced && n < 12288) return 0;
+    if (!forced && n < 9216) return 0;
     if (n / stride < 4 * (k + 8)) return 0;
     return stride;
 }

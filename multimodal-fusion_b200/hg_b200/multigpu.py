@@ -71,9 +71,13 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     pos = positions if (positions is not None) else None
     if knn_fn is None:
         knn_fn = lambda x, rows: ops.knn_feature(x, k, kernel, positions=pos if lambda_g else None,   # noqa: E731
-                                                 lambda_h=lambda_h, lambda_g=lambda_g, rows=rows)
-    idx_local, val_local = knn_fn(feats, (r0, r1))
+                                                 lambda_h=lambda_h, lambda_g=lambda_g, rows=rows, return_cos=True)
+    local = knn_fn(feats, (r0, r1))
+    idx_local, val_local = local[0], local[1]
     out = {"knn_idx": all_gather_rows(idx_local, n, group), "knn_val": all_gather_rows(val_local, n, group)}
+    # cos(f_i, f_j) of every list entry travels with the lists: the edge weights are then looked up
+    # instead of gathering two feature rows per edge
+    knn_cos = all_gather_rows(local[2], n, group) if len(local) > 2 else None
     lists = [out["knn_idx"]]
     if spatial_k and pos is not None:
         sidx, sd2 = ops.knn_spatial(pos, spatial_k, rows=(r0, r1))
@@ -83,7 +87,9 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     if assemble_fn is None:
         def assemble_fn(lists, feats):
             ei = ops.build_edges(lists, n)
-            res = {"edge_index": ei, "edge_weights": ops.edge_weights_cosine(feats, ei)}
+            w = (ops.edge_weights_from_knn(feats, out["knn_idx"], knn_cos, ei) if knn_cos is not None
+                 else ops.edge_weights_cosine(feats, ei))
+            res = {"edge_index": ei, "edge_weights": w}
             if return_csr:
                 res["csr_rowptr"], res["csr_col"], res["csr_eid"] = ops.csr_from_coo(ei, n)
             return res

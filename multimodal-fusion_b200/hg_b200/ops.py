@@ -21,9 +21,10 @@ def _size(fn, *args) -> int:
 def knn_feature(features: torch.Tensor, k: int, metric: str = "euclidean",
                 positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0, lambda_g: float = 0.0,
                 rows: Optional[Tuple[int, int]] = None, exclude_self: bool = True,
-                precision: str = "tc", device=None) -> Tuple[torch.Tensor, torch.Tensor]:
+                precision: str = "tc", device=None, return_cos: bool = False):
     """Fused similarity + top-k (A1/A2/A4).  Returns (idx int32 [R,k], val float32 [R,k]);
-    val = squared distance / Gaussian K / cosine depending on `metric`."""
+    val = squared distance / Gaussian K / cosine depending on `metric`.  return_cos=True adds
+    cos(f_row, f_idx) [R,k], the by-product of the exact re-rank that edge_weights_from_knn reads."""
     lib = L.load_library()
     dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
     x = L.f32c(features, dev)
@@ -41,11 +42,12 @@ def knn_feature(features: torch.Tensor, k: int, metric: str = "euclidean",
         if prec == 0:
             nbytes = _size(lib.hg_knn_feature_workspace_bytes, n, d, k, r0, r1)
             ws = L.Workspace.get(dev, nbytes)
-        L.check(lib.hg_knn_feature(
+        out_cos = torch.empty_like(out_val) if return_cos else None
+        L.check(lib.hg_knn_feature_cos(
             L.ptr(x), n, d, L.ptr(pos), 0 if pos is None else pos.shape[1], L.METRIC[metric],
             float(lambda_h), float(lambda_g), k, r0, r1, int(exclude_self), prec,
-            L.ptr(out_idx), L.ptr(out_val), L.ptr(ws), nbytes, L.stream_ptr(dev)))
-    return out_idx, out_val
+            L.ptr(out_idx), L.ptr(out_val), L.ptr(out_cos), L.ptr(ws), nbytes, L.stream_ptr(dev)))
+    return (out_idx, out_val, out_cos) if return_cos else (out_idx, out_val)
 
 
 def knn_spatial(positions: torch.Tensor, k: int, rows: Optional[Tuple[int, int]] = None,
@@ -170,6 +172,27 @@ def edge_weights_cosine(features: torch.Tensor, edge_index: torch.Tensor) -> tor
     w = torch.empty(e, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         L.check(lib.hg_edge_weights_cosine(L.ptr(x), x.shape[0], x.shape[1], L.ptr(ei), e, L.ptr(w), L.stream_ptr(dev)))
+    return w
+
+
+def edge_weights_from_knn(features: torch.Tensor, knn_idx: torch.Tensor, knn_cos: torch.Tensor,
+                          edge_index: torch.Tensor) -> torch.Tensor:
+    """A6 without gathering feature rows: w_e looked up in the full-range kNN lists (knn_idx / knn_cos
+    [n, k] from knn_feature(..., return_cos=True)); edges in neither endpoint's list are computed from
+    the rows.  Bit-identical to edge_weights_cosine."""
+    lib = L.load_library()
+    dev = L.require_cuda(edge_index.device if edge_index.is_cuda else None)
+    x = L.f32c(features, dev)
+    ei = edge_index.to(device=dev, dtype=torch.int64).contiguous()
+    idx = knn_idx.to(device=dev, dtype=torch.int32).contiguous()
+    cs = L.f32c(knn_cos, dev)
+    if idx.shape != cs.shape or idx.shape[0] != x.shape[0]:
+        raise ValueError("knn_idx / knn_cos must be [n, k] lists of the full row range")
+    e = ei.shape[1]
+    w = torch.empty(e, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(lib.hg_edge_weights_from_knn(L.ptr(x), x.shape[0], x.shape[1], L.ptr(idx), L.ptr(cs), idx.shape[1],
+                                             L.ptr(ei), e, L.ptr(w), L.stream_ptr(dev)))
     return w
 
 
