@@ -240,6 +240,16 @@ int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, co
                                     int64_t* num_edges_out_device,
                                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- row (f)3, "next": what the consumer does with the incidence ---------------------------------
+ * One HypergraphConv propagation  out = D^-1 H B^-1 H^T x  (torch_geometric semantics without
+ * attention, unit hyperedge weights) the way downstream_survival/models/cust_omics.py:58-63,100-102
+ * applies it to the stored pair list: row 0 of edge_index = node ids, row 1 = hyperedge ids.  Takes
+ * the CSR incidence of hg_csr_from_coo (for a (min, max) pair list the members of hyperedge j are
+ * row j's neighbours < j, the hyperedges of node v its neighbours > v).  x, hyperedge_feat (scratch /
+ * by-product: B^-1 H^T x) and out are [n, f] float32; the dense Theta / bias stay with the caller. */
+int hg_hypergraph_propagate(const float* x, int64_t n, int64_t f, const int64_t* csr_rowptr,
+                            const int64_t* csr_col, float* hyperedge_feat, float* out, void* stream);
+
 /* ---- batches of slides: ONE host call enqueues every build ----------------------------------
  * The reference's dataset loop (preprocess_hypergraph.py:651-670) handles slides one at a time.
  * A slide of a few thousand patches is only a few hundred microseconds of GPU work, so here the

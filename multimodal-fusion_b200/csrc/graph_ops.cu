@@ -138,6 +138,52 @@ __global__ void csr_fill_kernel(const int64_t* __restrict__ edge_index, const ui
     }
 }
 
+// ---- (f)3: consumer-side propagation over the incidence ------------------------------------------
+// The reference's consumer hands edge_index [2, E] to torch_geometric's HypergraphConv
+// (downstream_survival/models/cust_omics.py:58-63, 100-102), which reads row 0 as NODE ids and row 1
+// as HYPEREDGE ids and computes  out = D^-1 H B^-1 H^T (X Theta)  (no attention, unit hyperedge
+// weights): m_j = (1/B_j) sum_{(i, j)} x_i over the pairs whose row 1 is j, then
+// out_v = (1/D_v) sum_{(v, j)} m_j over the pairs whose row 0 is v; B_j, D_v = pair counts, 1/0 -> 0.
+// With the (min, max) pair list this library emits, row 0 < row 1, so in the CSR incidence of node
+// x (neighbours ascending) the members of hyperedge x are exactly the neighbours < x and the
+// hyperedges incident to node x the neighbours > x: both passes are segmented gather-sums over CSR
+// rows, one warp per row, 128-bit loads, sums in ascending neighbour order (deterministic).
+// HBM/L2-bound: per pass E gathered rows of F floats + N written.
+template <bool UPPER>
+__global__ void __launch_bounds__(256)
+hconv_gather_kernel(const float* __restrict__ src, int64_t n, int64_t f, const int64_t* __restrict__ rowptr,
+                    const int64_t* __restrict__ col, float* __restrict__ dst) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (row >= n) return;
+    const int64_t b = rowptr[row], e = rowptr[row + 1];
+    // neighbours ascend: [b, mid) are < row, [mid, e) are > row
+    int64_t lo = b, hi = e;
+    while (lo < hi) {
+        const int64_t m = (lo + hi) >> 1;
+        if (col[m] < row) lo = m + 1; else hi = m;
+    }
+    const int64_t s0 = UPPER ? lo : b, s1 = UPPER ? e : lo;
+    const float inv = (s1 > s0) ? 1.f / float(s1 - s0) : 0.f;
+    const bool vec = (f & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    if (vec) {
+        for (int64_t c0 = int64_t(lane) * 4; c0 < f; c0 += 128) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int64_t p = s0; p < s1; ++p) {
+                const float4 v = __ldg(reinterpret_cast<const float4*>(src + col[p] * f + c0));
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            *reinterpret_cast<float4*>(dst + row * f + c0) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+        }
+    } else {
+        for (int64_t c = lane; c < f; c += 32) {
+            float acc = 0.f;
+            for (int64_t p = s0; p < s1; ++p) acc += __ldg(src + col[p] * f + c);
+            dst[row * f + c] = acc * inv;
+        }
+    }
+}
+
 // ---- A8: threshold compaction ----------------------------------------------------------
 __global__ void __launch_bounds__(SC_THREADS)
 thr_count_kernel(const float* __restrict__ K, int64_t count, float thr, uint32_t* __restrict__ tile_sums) {
@@ -328,5 +374,18 @@ extern "C" int hg_threshold_edges_fill(const float* K, int64_t n, float threshol
                                                                                edge_index, edge_weights);
     HG_CHECK_LAUNCH();
     count_launches(1);
+    return HG_OK;
+}
+
+extern "C" int hg_hypergraph_propagate(const float* x, int64_t n, int64_t f, const int64_t* csr_rowptr,
+                                       const int64_t* csr_col, float* hyperedge_feat, float* out, void* stream) {
+    HG_REQUIRE(x && csr_rowptr && hyperedge_feat && out && n > 0 && f > 0, HG_ERR_BAD_ARG, "hg_hypergraph_propagate: bad argument");
+    HG_REQUIRE(hyperedge_feat != out && hyperedge_feat != x, HG_ERR_BAD_ARG, "hg_hypergraph_propagate: buffers must not alias");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned blocks = unsigned(ceil_div(n * 32, 256));
+    hconv_gather_kernel<false><<<blocks, 256, 0, st>>>(x, n, f, csr_rowptr, csr_col, hyperedge_feat);
+    hconv_gather_kernel<true><<<blocks, 256, 0, st>>>(hyperedge_feat, n, f, csr_rowptr, csr_col, out);
+    HG_CHECK_LAUNCH();
+    count_launches(2);
     return HG_OK;
 }

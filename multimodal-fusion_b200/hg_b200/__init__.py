@@ -23,6 +23,8 @@ from .preprocess_hypergraph import (
     rebuild_hypergraph_from_similarity,
     batch_rebuild_hypergraph,
 )
+from .ops import hypergraph_propagate
+from .pipeline import SlidePipeline, build_batch, build_many
 
 __all__ = [
     "compute_morphological_similarity", "compute_spatial_similarity", "compute_combined_similarity",
@@ -32,5 +34,5 @@ __all__ = [
     "build_hypergraph_knn_kmeans", "save_hypergraph_to_h5", "load_similarity_matrices",
     "rebuild_hypergraph_from_similarity", "batch_rebuild_hypergraph",
     # beyond the reference surface
-    "build_hypergraph_data", "knn_hyperedges",
+    "build_hypergraph_data", "knn_hyperedges", "build_batch", "build_many", "SlidePipeline", "hypergraph_propagate",
 ]

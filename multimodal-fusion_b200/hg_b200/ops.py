@@ -213,6 +213,26 @@ def csr_from_coo(edge_index: torch.Tensor, n: int):
     return rowptr, col, eid
 
 
+def hypergraph_propagate(x: torch.Tensor, csr_rowptr: torch.Tensor, csr_col: torch.Tensor,
+                         return_hyperedge_features: bool = False):
+    """Row (f)3: out = D^-1 H B^-1 H^T x over the stored pair list read as (node, hyperedge) pairs
+    -- the sparse part of torch_geometric's HypergraphConv as the reference's consumer calls it
+    (cust_omics.py:58-63, 100-102).  x [n, F]; CSR from csr_from_coo / the build's return_csr."""
+    lib = L.load_library()
+    dev = L.require_cuda(csr_rowptr.device if csr_rowptr.is_cuda else None)
+    xx = L.f32c(x, dev)
+    n, f = xx.shape
+    rp = csr_rowptr.to(device=dev, dtype=torch.int64).contiguous()
+    cl = csr_col.to(device=dev, dtype=torch.int64).contiguous()
+    if rp.numel() != n + 1:
+        raise ValueError("csr_rowptr must have n + 1 entries")
+    m = torch.empty_like(xx)
+    out = torch.empty_like(xx)
+    with torch.cuda.device(dev):
+        L.check(lib.hg_hypergraph_propagate(L.ptr(xx), n, f, L.ptr(rp), L.ptr(cl), L.ptr(m), L.ptr(out), L.stream_ptr(dev)))
+    return (out, m) if return_hyperedge_features else out
+
+
 def threshold_edges(K: torch.Tensor, threshold: float):
     """A8: every ordered (i, j) with not (K[i,j] < threshold), row-major; (edge_index, weights)."""
     lib = L.load_library()

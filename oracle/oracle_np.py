@@ -26,7 +26,7 @@ __all__ = [
     "morphological_similarity", "spatial_similarity", "combined_similarity",
     "wsi_tma_similarity", "similarity_stats", "sq_dists_f64", "knn_feature",
     "knn_spatial", "edges_from_knn", "edge_weights_cosine", "threshold_edges",
-    "csr_from_coo", "build_hypergraph_knn", "lower_median",
+    "csr_from_coo", "build_hypergraph_knn", "lower_median", "hypergraph_conv_propagate",
 ]
 
 
@@ -308,3 +308,32 @@ def build_hypergraph_knn(wsi_features, tma_features, k=5, labels=None, num_hyper
     idx, _ = knn_feature(allf, k, metric="euclidean")
     ei = edges_from_knn(idx, labels, num_hyperedges)
     return ei, edge_weights_cosine(allf, ei)
+
+
+# --------------------------------------------------------------------------
+# (f)3: what the consumer does with edge_index (parity unpinned: torch_geometric is absent here)
+# --------------------------------------------------------------------------
+def hypergraph_conv_propagate(x, edge_index, num_nodes=None):
+    """Sparse part of torch_geometric.nn.HypergraphConv (2.x, use_attention=False, unit hyperedge
+    weights) as the reference's consumer calls it -- ``conv(x, edge_index)`` at
+    downstream_survival/models/cust_omics.py:58-63, 100-102 -- restated from its published
+    formula  out = D^-1 H B^-1 H^T x :  row 0 of edge_index = node ids, row 1 = hyperedge ids;
+    D_v = number of pairs with node v, B_j = number of pairs with hyperedge j, 1/0 -> 0;
+    m_j = B_j^-1 sum_{(i, j)} x_i;  out_v = D_v^-1 sum_{(v, j)} m_j.  float64.
+    Returns (out [N, F], m [num_hyperedges, F])."""
+    x = np.asarray(x, dtype=np.float64)
+    ei = np.asarray(edge_index, dtype=np.int64)
+    n = x.shape[0] if num_nodes is None else num_nodes
+    nodes, hedges = ei[0], ei[1]
+    num_e = int(hedges.max()) + 1 if hedges.size else 0
+    B = np.bincount(hedges, minlength=num_e).astype(np.float64)
+    D = np.bincount(nodes, minlength=n).astype(np.float64)
+    Binv = np.divide(1.0, B, out=np.zeros_like(B), where=B > 0)
+    Dinv = np.divide(1.0, D, out=np.zeros_like(D), where=D > 0)
+    m = np.zeros((num_e, x.shape[1]))
+    np.add.at(m, hedges, x[nodes])
+    m *= Binv[:, None]
+    out = np.zeros((n, x.shape[1]))
+    np.add.at(out, nodes, m[hedges])
+    out *= Dinv[:, None]
+    return out, m
