@@ -314,7 +314,8 @@ def run_ours(args):
                        "edges": num_edges, "parallelism": f"slide-per-gpu x{world}",
                        "l2": "inputs larger than L2 (205 MB FP32 features + 205 MB BF16 planes per step)"},
             "e2e": {"value": e2e_value, "unit": "patches/s", "ms_per_step": e2e_ms,
-                    "api": "hg_b200.pipeline.build_many (3-stream H2D / build / D2H overlap, wall clock, best of 3 K-step regions)",
+                    "api": f"hg_b200.pipeline.build_many (H2D stream / {pipe.lanes} stream-ordered build lanes / D2H stream, "
+                           "wall clock, best of 3 K-step regions)",
                     "sequential_ms_per_step": e2e_seq_ms, "sequential_value": world * n / (e2e_seq_ms * 1e-3),
                     "h2d_bytes_per_step": n * d * 4, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
