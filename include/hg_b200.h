@@ -76,7 +76,7 @@ int hg_split_operands(const float* feats, int64_t n, int64_t d,
  * out_idx [rows, k] int32 (-1 when fewer than k candidates exist),
  * out_val [rows, k] float32.  `precision`: 0 = 3xBF16 tensor-core candidates +
  * exact FP32 re-rank (default), 1 = plain FP32 SIMT kernel (any shape).
- * Over the full row range of a large slide (n >= 8192) the tensor-core pass exploits the symmetry
+ * Over the full row range of a large slide (n >= 9216) the tensor-core pass exploits the symmetry
  * of K: about half of the tiles are computed and each serves both (i, j) and (j, i); results are
  * identical to the full pass (HG_B200_TC_SYM=0 in the environment forces the full pass). */
 int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k,
@@ -134,7 +134,10 @@ int hg_similarity_stats_streaming(const float* feats, int64_t n, int64_t d, cons
 /* ---- A3: spatial-coordinate kNN ------------------------------------------------
  * k smallest |g_i - g_j|^2 (direct-difference FP32), self excluded, ties by
  * (d2, index).  Semantics pinned by similarity_kernel.py:57-86 (top-k of a K_g
- * row).  pos [n, pos_dim], pos_dim in {2, 3}. */
+ * row).  pos [n, pos_dim], pos_dim in {2, 3}.  2-D inputs with n >= 8192 are binned
+ * into a uniform cell grid (O(n) work); smaller or 3-D inputs, and inputs that put
+ * more than 1024 points into one cell, take the brute-force pass.  Same results
+ * bit for bit either way (HG_B200_SP_GRID=0/1 forces one path). */
 int hg_knn_spatial_workspace_bytes(int64_t n, int k, int64_t row_begin, int64_t row_end, size_t* bytes);
 int hg_knn_spatial(const float* pos, int64_t n, int pos_dim, int k,
                    int64_t row_begin, int64_t row_end,
