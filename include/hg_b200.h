@@ -54,10 +54,10 @@ int hg_profile_enable(int on);
 int hg_profile_collect(float* ms_total, int* launches);
 
 /* ---- operand preparation -------------------------------------------------
- * Splits FP32 rows into BF16 hi/lo planes (x ~= hi + lo, 16 significant bits)
- * laid out [2][n_pad][d_pad] for TMA, zero padded to n_pad = ceil256(n),
- * d_pad = ceil64(d), and writes per-row squared norms (FP32, from the original
- * data).  Replaces `torch.sum(features**2)` (similarity_kernel.py:43) and is the
+ * Splits FP32 rows into BF16 hi/lo halves (x ~= hi + lo, 16 significant bits)
+ * laid out [n_pad][d_pad / 32][2][32] for TMA (every 128 bytes = 32 hi | 32 lo values
+ * of one 32-wide k-block), zero padded to n_pad = ceil256(n), d_pad = ceil64(d), and
+ * writes per-row squared norms (FP32, from the original data).  Replaces `torch.sum(features**2)` (similarity_kernel.py:43) and is the
  * input of the tensor-core Gram product that replaces `torch.mm` (:46). */
 size_t hg_operand_bytes(int64_t n, int64_t d);
 int hg_split_operands(const float* feats, int64_t n, int64_t d,

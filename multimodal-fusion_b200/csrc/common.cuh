@@ -63,6 +63,9 @@ constexpr int kColPad = 64;    // feature dim padded to one 128-byte swizzle ato
 
 inline int64_t ops_rows(int64_t n) { return round_up(n, kRowPad); }
 inline int64_t ops_cols(int64_t d) { return round_up(d, kColPad); }
+// BF16 elements from one operand row to the next: 2 * d_pad (32 hi | 32 lo per k-block) plus a pad
+// that keeps the row pitch off multiples of 2 KB (split.cu)
+int64_t ops_row_elems(int64_t d_pad);
 
 // ---- internal launchers shared across translation units ----------------------
 // per-column epilogue parameters of the fused kernel: score = a_j + b_j * dot

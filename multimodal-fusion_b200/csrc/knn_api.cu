@@ -37,7 +37,7 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     w.plan = tc_make_plan(n, r1 - r0, k, w.d_pad);
     size_t off = 0;
     auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
-    w.off_ops = take(size_t(2) * w.n_pad * w.d_pad * 2);
+    w.off_ops = take(hg_operand_bytes(n, d));
     w.off_norms = take(size_t(w.n_pad) * 4);
     w.off_colp = take(size_t(w.n_pad) * 8);
     w.off_pos4 = take(has_pos ? size_t(w.n_pad) * 16 : 0);

@@ -6,7 +6,8 @@
 //             similarity_kernel.py:79-84,122  the spatial factor K_g
 //             preprocess_hypergraph.py:379-382  sklearn brute-force kNN
 //
-// Arithmetic: FP32 rows are pre-split into BF16 hi/lo planes (split.cu).  The dot
+// Arithmetic: FP32 rows are pre-split into BF16 hi/lo halves (split.cu), interleaved per 32-wide
+// k-block so that one 128-byte operand row carries 32 hi | 32 lo values.  The dot
 // product is accumulated in FP32 in TMEM from three tcgen05 MMAs per k-step:
 //   hi*lo^T + lo*hi^T + hi*hi^T   ("3xBF16", ~2^-17 relative per product).
 // The epilogue turns the accumulator into a ranking score  a_j + b_j * dot
@@ -15,7 +16,9 @@
 // FP32 by rerank.cu, so the tensor-core pass only has to find the right set.
 //
 // Structure (one CTA per SM, persistent over work units):
-//   warp 0      TMA producer: A tile [2 planes][128 rows][64] + B tile [2][256][64] per stage
+//   warp 0      TMA producer: A tile [128 rows][32 hi | 32 lo] + B tile [256 rows][32 hi | 32 lo] per stage
+//               (48 KB; four stages in flight: with the earlier 96 KB stages only two fitted and the
+//               reload of a stage had one stage of MMAs, 0.8 us, to land)
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
 //   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns, score, register top-k
 // Two 256-column FP32 accumulators (all 512 TMEM columns) let the epilogue of tile
@@ -52,13 +55,13 @@ namespace hg {
 // and a third pipeline stage fits.
 template <int CG>
 struct TcCfg {
-    static constexpr int STAGES = CG == 1 ? 2 : 3;
+    static constexpr int STAGES = CG == 1 ? 4 : 6;
     static constexpr int B_ROWS = TC_BN / CG;                       // B rows staged by this CTA
-    static constexpr int A_PLANE = TC_BM * TC_BK * 2;               // 16 KB
-    static constexpr int B_PLANE = B_ROWS * TC_BK * 2;              // 32 / 16 KB
-    static constexpr int STAGE_BYTES = 2 * A_PLANE + 2 * B_PLANE;   // 96 / 64 KB
+    static constexpr int A_TILE = TC_BM * 128;                      // 16 KB: 128-byte rows of 32 hi | 32 lo
+    static constexpr int B_TILE = B_ROWS * 128;                     // 32 / 16 KB
+    static constexpr int STAGE_BYTES = A_TILE + B_TILE;             // 48 / 32 KB
 };
-constexpr int TC_MAX_STAGES = 3;
+constexpr int TC_MAX_STAGES = 6;
 constexpr int TC_THREADS = 192;
 constexpr int TC_EPI_THREADS = 128;
 constexpr int TC_TMEM_COLS = 512;
@@ -128,7 +131,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
               const TcParams p) {
     using Cfg = TcCfg<CG>;
     constexpr int TC_STAGES = Cfg::STAGES;
-    constexpr int TC_A_PLANE = Cfg::A_PLANE, TC_B_PLANE = Cfg::B_PLANE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
+    constexpr int TC_A_TILE = Cfg::A_TILE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
     static_assert(!SYM || (CG == 1 && KL > 0), "symmetric mode: single-CTA tiles with candidate lists");
     if (p.guard != nullptr && *p.guard == 0) return;   // fallback launch that is not needed (grid-uniform)
     extern __shared__ uint8_t smem_raw[];
@@ -183,21 +186,25 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     if (!owns_tile<SYM, CG>(rb, ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
-                        ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
+                        if (!p.pair_stages) {
+                            ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
+                        } else if ((it & 1u) == 0) {       // stages are refilled in pairs (STAGES and num_kb are even)
+                            ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
+                            ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage + 1]), ph ^ 1u);
+                        }
                         const uint32_t full = ptx::smem_u32(&sm->full[stage]);
                         const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
                         if (CG == 1) {
-                            ptx::mbar_expect_tx(full, p.hi_only ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES);
-                            ptx::tma_load_3d(dst, &tmap_a, full, kb * TC_BK, row0, 0, ptx::kEvictLast);
-                            ptx::tma_load_3d(dst + 2 * TC_A_PLANE, &tmap_b, full, kb * TC_BK, ct * TC_BN, 0,
-                                             ptx::kEvictNormal);
+                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            ptx::tma_load_3d(dst, &tmap_a, full, kb * (2 * TC_BK), row0, 0, p.hint_a);
+                            ptx::tma_load_3d(dst + TC_A_TILE, &tmap_b, full, kb * (2 * TC_BK), ct * TC_BN, 0, p.hint_b);
                         } else {
                             // both CTAs' bytes are counted on the LEADER's barrier (peer bit cleared)
                             const uint32_t lead_full = full & 0xFEFFFFFFu;
                             if (crank == 0) ptx::mbar_expect_tx(full, 2 * TC_STAGE_BYTES);
-                            ptx::tma_load_3d_2sm(dst, &tmap_a, lead_full, kb * TC_BK, row0, 0, ptx::kEvictLast);
-                            ptx::tma_load_3d_2sm(dst + 2 * TC_A_PLANE, &tmap_b, lead_full, kb * TC_BK,
-                                                 ct * TC_BN + int(crank) * Cfg::B_ROWS, 0, ptx::kEvictNormal);
+                            ptx::tma_load_3d_2sm(dst, &tmap_a, lead_full, kb * (2 * TC_BK), row0, 0, p.hint_a);
+                            ptx::tma_load_3d_2sm(dst + TC_A_TILE, &tmap_b, lead_full, kb * (2 * TC_BK),
+                                                 ct * TC_BN + int(crank) * Cfg::B_ROWS, 0, p.hint_b);
                         }
                     }
                 }
@@ -224,11 +231,12 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         ptx::mbar_wait(ptx::smem_u32(&sm->full[stage]), ph);
                         ptx::tc_fence_after();
                         const uint32_t a_addr = smem_base + stage * TC_STAGE_BYTES;
-                        const uint32_t b_addr = a_addr + 2 * TC_A_PLANE;
+                        const uint32_t b_addr = a_addr + TC_A_TILE;
+                        // inside a 128-byte swizzled row: hi values at bytes [0, 64), lo at [64, 128)
                         const uint64_t a_hi = ptx::make_smem_desc_sw128(a_addr);
-                        const uint64_t a_lo = ptx::make_smem_desc_sw128(a_addr + TC_A_PLANE);
+                        const uint64_t a_lo = a_hi + 4;                     // + 64 bytes, in 16-byte units
                         const uint64_t b_hi = ptx::make_smem_desc_sw128(b_addr);
-                        const uint64_t b_lo = ptx::make_smem_desc_sw128(b_addr + TC_B_PLANE);
+                        const uint64_t b_lo = b_hi + 4;
 #pragma unroll
                         for (int ks = 0; ks < TC_BK / 16; ++ks) {
                             const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
@@ -558,12 +566,14 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 
 // row_stride > 1: a view of every row_stride-th operand row (the pre-pass column sample)
 static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows,
-                     int row_stride = 1, int planes = 2) {
+                     int row_stride = 1) {
     auto enc = get_encode_fn();
     HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
-    cuuint64_t dims[3] = {cuuint64_t(d_pad), cuuint64_t(ceil_div(n_pad, row_stride)), 2};
-    cuuint64_t strides[2] = {cuuint64_t(d_pad) * 2 * cuuint64_t(row_stride), cuuint64_t(n_pad) * cuuint64_t(d_pad) * 2};
-    cuuint32_t box[3] = {cuuint32_t(TC_BK), cuuint32_t(box_rows), cuuint32_t(planes)};
+    // operand row = d_pad / 32 blocks of (32 hi | 32 lo) BF16 = 4 * d_pad bytes; one box row = one such block
+    const cuuint64_t row_bytes = cuuint64_t(ops_row_elems(d_pad)) * 2;
+    cuuint64_t dims[3] = {cuuint64_t(d_pad) * 2, cuuint64_t(ceil_div(n_pad, row_stride)), 1};
+    cuuint64_t strides[2] = {row_bytes * cuuint64_t(row_stride), row_bytes * cuuint64_t(n_pad)};
+    cuuint32_t box[3] = {cuuint32_t(2 * TC_BK), cuuint32_t(box_rows), 1};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -607,6 +617,21 @@ static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cudaStream_t st) {
     TcParams p = p_in;
     p.n_pad = n_pad;
+    // A row blocks are re-read for every column tile (keep them), B tiles stream through.
+    // HG_B200_TC_HINTS=<a><b> overrides: n = normal, f = evict first, l = evict last
+    p.hint_a = ptx::kEvictLast; p.hint_b = ptx::kEvictNormal;
+    // The producer refills the four 48 KB stages two at a time: 96 KB bursts keep the CTAs that sweep the
+    // same B tiles close enough for the L2 to serve them (C3: 40.8 -> 37.6 ms; unpaired, DRAM reads were
+    // 85 GB per launch against 18 GB), while the MMAs still start on the first half as soon as it lands.
+    // HG_B200_TC_PAIR=0 refills stage by stage.
+    p.pair_stages = 1;
+    if (const char* e = getenv("HG_B200_TC_PAIR")) p.pair_stages = atoi(e) != 0 ? 1 : 0;
+    if (const char* e = getenv("HG_B200_TC_HINTS")) {
+        auto pick = [](char c, uint64_t dflt) {
+            return c == 'n' ? ptx::kEvictNormal : c == 'f' ? ptx::kEvictFirst : c == 'l' ? ptx::kEvictLast : dflt;
+        };
+        if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
+    }
     if (p.col_stride < 1) p.col_stride = 1;
     HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
                                p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),
@@ -615,10 +640,9 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
     CUtensorMap ta, tb;
     HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.col_stride > 1), HG_ERR_BAD_ARG,
                "tc_launch: the hi-only product is for the threshold pre-pass");
-    const int planes = p.hi_only ? 1 : 2;
-    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1, planes);
+    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride, planes);   // a CTA of a pair stages half of the B tile
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

@@ -6,7 +6,7 @@ namespace hg {
 
 constexpr int TC_BM = 128;      // query rows per CTA tile  (UMMA M)
 constexpr int TC_BN = 256;      // candidate columns per tile (UMMA N)
-constexpr int TC_BK = 64;       // K per pipeline stage = one 128-byte swizzle atom of BF16
+constexpr int TC_BK = 32;       // K per pipeline stage: one 128-byte operand row = 32 hi | 32 lo BF16
 constexpr int TC_MAX_SPLITS = 8;
 
 struct TcPlan {
@@ -48,7 +48,7 @@ struct TcParams {
     int col_stride;
     float* thr_out;
     int thr_rank;
-    int hi_only;                // pre-pass only: one BF16 product hi*hi (planes 0 only), wider slack
+    int hi_only;                // pre-pass only: one BF16 product hi*hi, wider slack
     int thr_margin_cos;         // error slack added to thr_out scales with |x_i| (cosine) or n_i + norm_max
     const float* norm_max;      // largest squared row norm
     // symmetric mode: transposed candidates (column j gets row i) with score < thr[j] are
@@ -59,6 +59,8 @@ struct TcParams {
     int bkt_cap;
     int* ovf;
     const int* guard;           // non-null: the whole grid exits at once unless *guard != 0
+    uint64_t hint_a, hint_b;    // L2 cache hints of the A / B tile loads (filled by tc_launch)
+    int pair_stages;            // producer refills two 48 KB stages at a time (see tc_launch)
 };
 
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad);

@@ -5,33 +5,46 @@
 // `torch.sum(features ** 2, dim=1)` (reference similarity_kernel.py:43) and
 // prepares the inputs of the MMA that replaces `torch.mm` (:46).
 //
-// Layout written: ops[plane][row][col], plane 0 = hi, 1 = lo, rows padded to a
-// multiple of 256 and cols to a multiple of 64 with zeros, so that TMA boxes
-// never straddle undefined memory and padded rows contribute dot = 0.
+// Layout written: ops[row][col / 32][half][col % 32], half 0 = hi, 1 = lo: every 128-byte run of a
+// row holds one 32-wide k-block as 32 hi | 32 lo values, which is one TMA box row and one 128-byte
+// swizzled shared-memory row of the fused kernel.  Rows are padded to a multiple of 256 and cols to
+// a multiple of 64 with zeros, so that TMA boxes never straddle undefined memory and padded rows
+// contribute dot = 0.
 //
 // HBM-bound: reads 4 B and writes 4 B per element; one warp per row (4 rows per CTA),
 // 128-bit loads, 64-bit stores.
 #include "common.cuh"
 #include "rowdot.cuh"
+#include <stdlib.h>
 
 namespace hg {
 
 constexpr int SPLIT_WARPS = 4;          // rows per CTA, one warp each
 
+// Row pitch of the operand buffer.  HG_B200_OPS_PAD_BYTES (multiple of 16) overrides the pad.
+int64_t ops_row_elems(int64_t d_pad) {
+    static const int pad_bytes = [] {
+        if (const char* e = getenv("HG_B200_OPS_PAD_BYTES")) {
+            const int v = atoi(e);
+            if (v >= 0 && v <= 4096 && v % 16 == 0) return v;
+        }
+        return 0;
+    }();
+    return 2 * d_pad + pad_bytes / 2;
+}
+
 template <bool VEC4>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
-                  __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms) {
+                  int64_t row_elems, __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms) {
     const int lane = threadIdx.x & 31;
     const int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
     if (row >= n_pad) return;
-    __nv_bfloat16* hi_row = ops + row * d_pad;
-    __nv_bfloat16* lo_row = ops + (n_pad + row) * d_pad;
-    if (row >= n) {                              // padding rows are zero in both planes
-        for (int64_t v = lane; v < (d_pad >> 2); v += 32) {
-            reinterpret_cast<uint2*>(hi_row)[v] = make_uint2(0u, 0u);
-            reinterpret_cast<uint2*>(lo_row)[v] = make_uint2(0u, 0u);
-        }
+    __nv_bfloat16* out_row = ops + row * row_elems;
+    // column c lives at (c / 32) * 64 + (c % 32) (hi) and 32 further (lo)
+    auto hi_at = [&](int64_t c) { return out_row + ((c >> 5) << 6) + (c & 31); };
+    if (row >= n) {                              // padding rows are zero in both halves
+        for (int64_t v = lane; v < (d_pad >> 1); v += 32) reinterpret_cast<uint2*>(out_row)[v] = make_uint2(0u, 0u);
         return;
     }
     const float* src = feats + row * d;
@@ -56,8 +69,9 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
             uint2 hv, lv;
             hv.x = *reinterpret_cast<uint32_t*>(&hp0); hv.y = *reinterpret_cast<uint32_t*>(&hp1);
             lv.x = *reinterpret_cast<uint32_t*>(&lp0); lv.y = *reinterpret_cast<uint32_t*>(&lp1);
-            reinterpret_cast<uint2*>(hi_row)[v] = hv;
-            reinterpret_cast<uint2*>(lo_row)[v] = lv;
+            __nv_bfloat16* dst = hi_at(v << 2);
+            *reinterpret_cast<uint2*>(dst) = hv;
+            *reinterpret_cast<uint2*>(dst + 32) = lv;
         }
         norm = lo + hi;
     } else {
@@ -66,8 +80,9 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
             const float x = (c < d) ? __ldg(src + c) : 0.f;
             norm = fmaf(x, x, norm);
             __nv_bfloat16 h = __float2bfloat16_rn(x);
-            hi_row[c] = h;
-            lo_row[c] = __float2bfloat16_rn(x - __bfloat162float(h));
+            __nv_bfloat16* dst = hi_at(c);
+            dst[0] = h;
+            dst[32] = __float2bfloat16_rn(x - __bfloat162float(h));
         }
     }
     norm = warp_butterfly(norm);
@@ -79,9 +94,9 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (vec)
-        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
+        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms);
     else
-        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops, sq_norms);
+        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -91,7 +106,7 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
 
 extern "C" size_t hg_operand_bytes(int64_t n, int64_t d) {
     if (n <= 0 || d <= 0) return 0;
-    return size_t(2) * size_t(hg::ops_rows(n)) * size_t(hg::ops_cols(d)) * sizeof(__nv_bfloat16);
+    return size_t(hg::ops_rows(n)) * size_t(hg::ops_row_elems(hg::ops_cols(d))) * sizeof(__nv_bfloat16);
 }
 
 extern "C" int hg_split_operands(const float* feats, int64_t n, int64_t d, void* ops, float* sq_norms,

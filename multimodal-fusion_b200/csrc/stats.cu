@@ -163,7 +163,7 @@ static StreamWs plan_stream(int64_t n, int64_t d, bool has_pos) {
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     size_t off = 0;
     auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
-    w.off_ops = take(size_t(2) * n_pad * d_pad * 2);
+    w.off_ops = take(hg_operand_bytes(n, d));
     w.off_norms = take(size_t(n_pad) * 4);
     w.off_colp = take(size_t(n_pad) * 8);
     w.off_pos4 = take(has_pos ? size_t(n_pad) * 16 : 0);

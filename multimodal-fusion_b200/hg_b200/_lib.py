@@ -12,7 +12,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhg_b200.so")
+# HG_B200_LIB: load another build of the same library (A/B runs of two kernel variants on one box)
+LIB_PATH = os.environ.get("HG_B200_LIB") or os.path.join(_HERE, "libhg_b200.so")
 
 HG_OK, HG_ERR_BAD_ARG, HG_ERR_UNSUPPORTED, HG_ERR_CUDA, HG_ERR_WORKSPACE = 0, -1, -2, -3, -4
 METRIC = {"euclidean": 0, "gaussian": 1, "cosine": 2}

@@ -69,8 +69,8 @@ def test_split_operands():
     norms = torch.empty(n, dtype=torch.float32, device="cuda")
     _lib.check(lib.hg_split_operands(xc.data_ptr(), n, d, ops_buf.data_ptr(), norms.data_ptr(), 0))
     torch.cuda.synchronize()
-    planes = ops_buf.view(2, n_pad, d_pad).float().cpu().numpy()
-    rec = planes[0] + planes[1]
+    blocks = ops_buf.view(n_pad, d_pad // 32, 2, 32).float().cpu().numpy()      # [row][k-block][hi | lo][32]
+    rec = (blocks[:, :, 0, :] + blocks[:, :, 1, :]).reshape(n_pad, d_pad)
     assert np.abs(rec[:n, :d] - x).max() <= 2.0 ** -16 * np.abs(x).max()
     assert (rec[n:] == 0).all() and (rec[:, d:] == 0).all()
     np.testing.assert_allclose(norms.cpu().numpy(), (x.astype(np.float64) ** 2).sum(1), rtol=1e-6)
