@@ -94,14 +94,14 @@ extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begi
         double t = 0;
         for (int rb = 0; rb < pl.num_rb; ++rb)
             for (int ct = 0; ct < pl.num_ct; ++ct) {
-                const int a = rb >> 1;
-                t += (ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0))) ? 1.0 : 0.0;
+                const int a = pl.cl == 2 ? rb : rb >> 1;
+                t += (ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0))) ? double(pl.cl) : 0.0;
             }
         return t;
     };
     const double per_tile = 3.0 * 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);     // 3 BF16 MMAs per product
     double tiles = w.sym_stride > 0 ? tiles_of(w.sym_plan) + tiles_of(w.pre_plan) / (prepass_hi_only() ? 3.0 : 1.0)
-                                    : tiles_of(w.plan) * w.plan.cg;
+                                    : tiles_of(w.plan) * w.plan.cl;
     if (symmetric_stride) *symmetric_stride = w.sym_stride;
     if (mma_flop) *mma_flop = tiles * per_tile;
     return HG_OK;

@@ -53,6 +53,10 @@ namespace hg {
 // one 256 x 256 tile: each CTA stages its own 128 A rows and HALF of the B tile, the leader issues
 // M = 256 MMAs that read both halves, so operand traffic per CTA drops from 96 to 64 KB per stage
 // and a third pipeline stage fits.
+// MC (multicast pair, CG = 1): two CTAs of a cluster work on the two 128-row halves of one 256-row block
+// against the same column tiles.  Each issues its own M = 128 MMAs from its own shared memory, but stages
+// only HALF of every B tile and multicasts it into both CTAs (TMA .multicast::cluster), so a B tile
+// crosses the L2 -> SM fabric once per pair and the two CTAs advance in lock-step by construction.
 template <int CG>
 struct TcCfg {
     static constexpr int STAGES = CG == 1 ? 4 : 6;
@@ -96,10 +100,9 @@ __device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, in
 }
 
 // Does the unit of row block rb (classic: every tile; symmetric: the checkerboard) own column tile ct?
-template <bool SYM, int CG>
-__device__ __forceinline__ bool owns_tile(int rb, int ct) {
+template <bool SYM>
+__device__ __forceinline__ bool owns_tile(int a, int ct) {          // a = 256-row super-block of the row block
     if (!SYM) return true;
-    const int a = rb >> 1;                              // 256-row super-block of a 128-row block
     return ct == a || (((a + ct) & 1) == (ct < a ? 1 : 0));
 }
 
@@ -125,7 +128,7 @@ __device__ __forceinline__ void bucket_push(const TcParams& p, int col, int row,
     else *p.ovf = 1;
 }
 
-template <int KL, bool HAS_POS, int CG, bool SYM>
+template <int KL, bool HAS_POS, int CG, bool SYM, bool MC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
               const TcParams p) {
@@ -133,6 +136,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     constexpr int TC_STAGES = Cfg::STAGES;
     constexpr int TC_A_TILE = Cfg::A_TILE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
     static_assert(!SYM || (CG == 1 && KL > 0), "symmetric mode: single-CTA tiles with candidate lists");
+    static_assert(!MC || CG == 1, "multicast pairs issue single-CTA MMAs");
+    constexpr int CL = (CG == 2 || MC) ? 2 : 1;        // CTAs per cluster = 128-row blocks per work unit
     if (p.guard != nullptr && *p.guard == 0) return;   // fallback launch that is not needed (grid-uniform)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -142,13 +147,13 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = p.d_pad / TC_BK;
     const int units = p.plan.num_u * p.plan.splits;
-    const uint32_t crank = (CG == 2) ? ptx::cluster_ctarank() : 0u;     // 0 = leader of the CTA pair
-    const int wid = blockIdx.x / CG, nworkers = gridDim.x / CG;          // a worker = one CTA or one pair
+    const uint32_t crank = (CL == 2) ? ptx::cluster_ctarank() : 0u;     // 0 = leader of the CTA pair
+    const int wid = blockIdx.x / CL, nworkers = gridDim.x / CL;          // a worker = one CTA or one pair
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_STAGES; ++s) {
             ptx::mbar_init(ptx::smem_u32(&sm->full[s]), 1);
-            ptx::mbar_init(ptx::smem_u32(&sm->empty[s]), 1);
+            ptx::mbar_init(ptx::smem_u32(&sm->empty[s]), MC ? 2 : 1);      // MC: both CTAs' MMAs release a stage
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(ptx::smem_u32(&sm->tmem_full[b]), 1);
@@ -162,7 +167,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         ptx::prefetch_tensormap(&tmap_a);
         ptx::prefetch_tensormap(&tmap_b);
     }
-    if (CG == 2) ptx::cluster_sync();                  // the peer's barriers exist before anything signals them
+    if (CL == 2) ptx::cluster_sync();                  // the peer's barriers exist before anything signals them
     if (warp == 1) {
         ptx::tmem_alloc<CG>(ptx::smem_u32(&sm->tmem_base), TC_TMEM_COLS);
         ptx::tmem_relinquish<CG>();
@@ -179,11 +184,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             for (int u = wid; u < units; u += nworkers) {
                 int split, rb;
                 decode_unit(p.plan, u, rb, split);
-                const int row0 = int(p.row_begin) + rb * (TC_BM * CG) + int(crank) * TC_BM;
+                const int row0 = int(p.row_begin) + rb * (TC_BM * CL) + int(crank) * TC_BM;
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
-                    if (!owns_tile<SYM, CG>(rb, ct)) continue;
+                    if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
                         if (!p.pair_stages) {
@@ -194,7 +199,15 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         }
                         const uint32_t full = ptx::smem_u32(&sm->full[stage]);
                         const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
-                        if (CG == 1) {
+                        if (MC) {
+                            // own A rows + the own half of the B tile, which also lands in the peer; the peer's
+                            // half arrives here the same way (its bytes may precede this expect_tx: same phase)
+                            constexpr int HALF = Cfg::B_TILE / 2;
+                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            ptx::tma_load_3d(dst, &tmap_a, full, kb * (2 * TC_BK), row0, 0, p.hint_a);
+                            ptx::tma_load_3d_mc(dst + TC_A_TILE + int(crank) * HALF, &tmap_b, full, kb * (2 * TC_BK),
+                                                ct * TC_BN + int(crank) * (TC_BN / 2), 0, uint16_t(3), p.hint_b);
+                        } else if (CG == 1) {
                             ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
                             ptx::tma_load_3d(dst, &tmap_a, full, kb * (2 * TC_BK), row0, 0, p.hint_a);
                             ptx::tma_load_3d(dst + TC_A_TILE, &tmap_b, full, kb * (2 * TC_BK), ct * TC_BN, 0, p.hint_b);
@@ -212,7 +225,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ==============================
-        if (lane == 0 && crank == 0) {
+        if (lane == 0 && (crank == 0 || MC)) {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM * CG, TC_BN);
             uint32_t it = 0, tile = 0;
             for (int u = wid; u < units; u += nworkers) {
@@ -221,7 +234,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 const int ct0 = split * p.plan.ct_per_split;
                 const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
-                    if (!owns_tile<SYM, CG>(rb, ct)) continue;
+                    if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
                     const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
                     ptx::mbar_wait(ptx::smem_u32(&sm->tmem_empty[buf]), tph ^ 1u);
                     ptx::tc_fence_after();
@@ -249,7 +262,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                             }
                         }
                         // frees the stage (in both CTAs of a pair) when the MMAs retire
-                        if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));
+                        if (MC) ptx::mma_commit_mc(ptx::smem_u32(&sm->empty[stage]), 3);
+                        else if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));
                         else ptx::mma_commit_2sm(ptx::smem_u32(&sm->empty[stage]), 3);
                     }
                     if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
@@ -269,7 +283,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         for (int u = wid; u < units; u += nworkers) {
             int split, rb;
             decode_unit(p.plan, u, rb, split);
-            const int64_t row0 = p.row_begin + int64_t(rb) * (TC_BM * CG) + int64_t(crank) * TC_BM;
+            const int64_t row0 = p.row_begin + int64_t(rb) * (TC_BM * CL) + int64_t(crank) * TC_BM;
+            const int sblk = (CL == 2) ? rb : rb >> 1;          // 256-row super-block (symmetric tile ownership)
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = split * p.plan.ct_per_split;
             const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
@@ -286,7 +301,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             // the final top-k), which removes the warm-up insertions of every unit; NaN on padded rows
             const float row_bound = SYM ? __ldg(p.thr + row) : INFINITY;
             for (int ct = ct0; ct < ct1; ++ct) {
-                if (!owns_tile<SYM, CG>(rb, ct)) continue;
+                if (!owns_tile<SYM>(sblk, ct)) continue;
                 const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
                 const int col0 = ct * TC_BN;
 #pragma unroll
@@ -303,7 +318,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 ptx::tc_fence_after();
                 const bool diag = p.exclude_self && (col0 < row0 + TC_BM) && (row0 < col0 + TC_BN) && cstride == 1;
                 const int self_col = diag ? int(row - col0) : -1;     // column inside this tile, if any
-                const bool transposed = SYM && ct != (rb >> 1);        // the diagonal tile serves rows only
+                const bool transposed = SYM && ct != sblk;             // the diagonal tile serves rows only
                 // ranking score of (this row, column c) and, SYM, of (column c, this row)
                 auto scores = [&](int c, float dot, float& s_row, float& s_tr) {
                     const float2 cp = sm->colp[buf][c];
@@ -427,7 +442,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (CG == 2) ptx::cluster_sync();                  // neither CTA may leave while its peer still reads its smem
+    if (CL == 2) ptx::cluster_sync();                  // neither CTA may leave while its peer still reads / writes its smem
     if (warp == 1) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc<CG>(tmem_base, TC_TMEM_COLS);
@@ -438,6 +453,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 int tc_cta_group() {                       // 1 (default) or 2 = CTA pairs, HG_B200_TC_CG=2
     const char* e = getenv("HG_B200_TC_CG");
     return (e && atoi(e) == 2) ? 2 : 1;
+}
+static int tc_multicast() {                // multicast pairs (cg 1 only): HG_B200_TC_MC=0/1
+    if (tc_cta_group() != 1) return 0;
+    const char* e = getenv("HG_B200_TC_MC");
+    return (e && atoi(e) != 0) ? 1 : 0;
 }
 
 static int list_len(int k) {            // k plus slack for the exact re-rank, in the register-array sizes compiled
@@ -450,10 +470,10 @@ static int list_len(int k) {            // k plus slack for the exact re-rank, i
 // multiple of cc) whose last round wastes the least.  `major` = row blocks or row-block pairs,
 // `tiles` = column tiles a major unit sweeps.
 static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
-    const int workers = kNumSMs / pl.cg;               // CTAs or CTA pairs
-    const int64_t a_block = int64_t(TC_BM * pl.cg) * d_pad * 4;
+    const int workers = kNumSMs / pl.cl;               // CTAs or CTA pairs
+    const int64_t a_block = int64_t(TC_BM * pl.cl) * d_pad * 4;
     const int64_t rc_cap = (int64_t(40) << 20) / a_block;
-    const int cc_max = 4 / pl.cg;                      // 148 = 4 * 37, 74 = 2 * 37
+    const int cc_max = 4 / pl.cl;                      // 148 = 4 * 37, 74 = 2 * 37
     int best_cc = cc_max, best_s = cc_max;
     double best_eff = -1.0;
     for (int cc = 1; cc <= cc_max; cc *= 2) {
@@ -476,14 +496,16 @@ static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
     pl.cc = best_cc;
     pl.rc = workers / best_cc;
     pl.splits = best_s;
-    pl.grid = int(min64(workers, int64_t(major) * pl.splits)) * pl.cg;
+    pl.grid = int(min64(workers, int64_t(major) * pl.splits)) * pl.cl;
 }
 
-TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists) {
     TcPlan pl{};
     pl.cg = tc_cta_group();
+    pl.mc = lists ? tc_multicast() : 0;
+    pl.cl = (pl.cg == 2 || pl.mc) ? 2 : 1;
     pl.n_rows = n_rows;
-    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cg));
+    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cl));
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(n, TC_BN));
     pl.kl = list_len(k);
@@ -498,7 +520,7 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
 // thr_merge_kernel (rerank.cu) combines their lists.
 TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
     TcPlan pl{};
-    pl.cg = 1;
+    pl.cg = 1; pl.cl = 1;
     pl.n_rows = n;
     pl.num_rb = int(ceil_div(n, TC_BM));
     pl.num_u = pl.num_rb;
@@ -524,9 +546,11 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
     TcPlan pl{};
     pl.cg = 1;
+    pl.mc = tc_multicast();
+    pl.cl = pl.mc ? 2 : 1;
     pl.sym = 1;
     pl.n_rows = n;
-    pl.num_rb = int(ceil_div(n, TC_BM));
+    pl.num_rb = int(ceil_div(n, TC_BM * pl.cl));
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(n, TC_BN));
     pl.kl = list_len(k);
@@ -582,9 +606,10 @@ static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, i
     return HG_OK;
 }
 
-template <int KL, bool HAS_POS, int CG, bool SYM>
+template <int KL, bool HAS_POS, int CG, bool SYM, bool MC = false>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
-    auto kern = knn_tc_kernel<KL, HAS_POS, CG, SYM>;
+    auto kern = knn_tc_kernel<KL, HAS_POS, CG, SYM, MC>;
+    constexpr int CL = (CG == 2 || MC) ? 2 : 1;
     constexpr size_t smem = tc_smem_bytes<CG>();
     static_assert(smem <= 232448, "over the 227 KB dynamic shared memory limit");
     HG_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
@@ -595,9 +620,9 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = (CG > 1) ? 1 : 0;
+    cfg.numAttrs = (CL > 1) ? 1 : 0;
     HG_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     count_launches(1);
     return HG_OK;
@@ -606,8 +631,12 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
 template <int KL>
 static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t st) {
     if constexpr (KL > 0) {
+        if (p.plan.sym && p.plan.mc)
+            return p.pos4 ? launch_one<KL, true, 1, true, true>(ta, tb, p, st) : launch_one<KL, false, 1, true, true>(ta, tb, p, st);
         if (p.plan.sym)
             return p.pos4 ? launch_one<KL, true, 1, true>(ta, tb, p, st) : launch_one<KL, false, 1, true>(ta, tb, p, st);
+        if (p.plan.mc)
+            return p.pos4 ? launch_one<KL, true, 1, false, true>(ta, tb, p, st) : launch_one<KL, false, 1, false, true>(ta, tb, p, st);
     }
     if (p.plan.cg == 2)
         return p.pos4 ? launch_one<KL, true, 2, false>(ta, tb, p, st) : launch_one<KL, false, 2, false>(ta, tb, p, st);
@@ -636,13 +665,14 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
     HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
                                p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
-    HG_REQUIRE(p.col_stride == 1 || (p.plan.cg == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need cg 1");
+    HG_REQUIRE(p.col_stride == 1 || (p.plan.cl == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need single CTAs");
+    HG_REQUIRE(!p.plan.mc || p.plan.kl > 0, HG_ERR_BAD_ARG, "tc_launch: multicast pairs keep lists (no dense mode)");
     CUtensorMap ta, tb;
     HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.col_stride > 1), HG_ERR_BAD_ARG,
                "tc_launch: the hi-only product is for the threshold pre-pass");
     int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cg, p.col_stride);   // a CTA of a pair stages half of the B tile
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cl, p.col_stride);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

@@ -20,6 +20,8 @@ struct TcPlan {
     int kl;                     // list length kept per (row, split): 8 / 16 / 24 / 32
     int grid;                   // CTAs launched
     int cg;                     // 1 = one CTA per 128-row tile, 2 = CTA pairs (cta_group::2) on 256-row tiles
+    int mc;                     // 1 = multicast pairs: cg 1 MMAs, the two CTAs of a cluster share every B tile
+    int cl;                     // CTAs per cluster = 128-row blocks per work unit (2 for cg 2 and for mc)
     // symmetric mode (sym = 1, full row range only): a checkerboard half of the tiles is computed
     // and each one also serves the transposed direction (see knn_tc.cu)
     int sym;
@@ -63,7 +65,7 @@ struct TcParams {
     int pair_stages;            // producer refills two 48 KB stages at a time (see tc_launch)
 };
 
-TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad);
+TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists = true);   // lists = false: dense-output mode
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad);
 TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride);
 int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride

@@ -100,6 +100,17 @@ __device__ __forceinline__ void tma_load_3d_2sm(uint32_t dst, const void* tmap, 
           "l"(cache_hint)
         : "memory");
 }
+// multicast variant: the box lands at the same CTA-relative offset in every CTA of `cta_mask`, and each of
+// them gets the complete_tx on the barrier at the same offset of its own shared memory
+__device__ __forceinline__ void tma_load_3d_mc(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2,
+                                               uint16_t cta_mask, uint64_t cache_hint) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5}], [%2], %6, %7;"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "h"(cta_mask),
+          "l"(cache_hint)
+        : "memory");
+}
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;   // CUTLASS TMA::CacheHintSm90 encodings
 constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
@@ -141,6 +152,12 @@ __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint6
 // arrive on an mbarrier once every previously issued MMA of this thread has completed
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// single-CTA MMAs, arrival multicast to the barrier at the same offset in every CTA of `cta_mask`
+__device__ __forceinline__ void mma_commit_mc(uint32_t bar, uint16_t cta_mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+        ::"r"(bar), "h"(cta_mask) : "memory");
 }
 __device__ __forceinline__ void mma_commit_2sm(uint32_t bar, uint16_t cta_mask) {
     asm volatile(

@@ -219,7 +219,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
             const int64_t r1 = min64(n, r0 + w.chunk_rows);
             TcParams tp{};
             tp.n = n; tp.row_begin = r0; tp.row_end = r1; tp.d_pad = int(d_pad);
-            tp.plan = tc_make_plan(n, r1 - r0, 1, d_pad);
+            tp.plan = tc_make_plan(n, r1 - r0, 1, d_pad, false);
             tp.plan.kl = 0;                                        // dense-output mode
             tp.colp = colp; tp.pos4 = pos4;
             tp.gscale = pos ? lambda_g / lambda_h : 0.f;

@@ -138,3 +138,24 @@ def test_build_weights_from_knn_lists_equal_direct_cosine(n, d, k, metric):
     torch.cuda.synchronize()
     assert out["edge_index"].shape[1] > n * k // 2
     assert torch.equal(out["edge_weights"], w_direct)
+
+
+@pytest.mark.parametrize("n,d,k,metric,with_pos,sym", [
+    (3000, 256, 8, "gaussian", False, 0),          # classic full pass, odd number of row blocks
+    (5000, 192, 16, "cosine", False, 0),
+    (12345, 200, 16, "gaussian", True, 8),         # symmetric half pass, ragged n and d, spatial term
+    (20000, 512, 8, "gaussian", False, 8),
+])
+def test_multicast_pairs_equal_single_ctas(n, d, k, metric, with_pos, sym):
+    """HG_B200_TC_MC=1: two CTAs of a cluster share every B tile through TMA multicast.  Same lists."""
+    feats, pos = synth.make_slide(n, d, 5 + n, "cosine" if metric == "cosine" else "gaussian")
+    x = _cuda(feats)
+    kw = dict(positions=_cuda(pos), lambda_h=1.0, lambda_g=1.0 / 128) if with_pos else {}
+    with _env(HG_B200_TC_SYM=sym, HG_B200_TC_MC=0):
+        ref = ops.knn_feature(x, k, metric, **kw)
+    with _env(HG_B200_TC_SYM=sym, HG_B200_TC_MC=1):
+        got = ops.knn_feature(x, k, metric, **kw)
+        part = ops.knn_feature(x, k, metric, rows=(1000, 2111), **kw)      # row range: classic pass on pairs
+    torch.cuda.synchronize()
+    assert torch.equal(got[0], ref[0]) and torch.equal(got[1], ref[1])
+    assert torch.equal(part[0], ref[0][1000:2111]) and torch.equal(part[1], ref[1][1000:2111])
