@@ -112,8 +112,29 @@ def cpu_reference_step(feats: np.ndarray, k: int, rows: np.ndarray, nn=None):
     return nn, ei, w
 
 
+def use_all_host_threads() -> int:
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm must run on all the host threads
+    it can use, so the BLAS / OpenMP pools are widened again at run time.  Returns the thread count."""
+    cores = os.cpu_count() or 1
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(cores)
+    try:
+        import sklearn.neighbors                   # noqa: F401 - load its OpenMP runtime before widening the pools
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=cores)            # process-wide when not used as a context manager
+    except Exception:                              # noqa: BLE001 - best effort, the count is reported either way
+        pass
+    try:
+        import torch
+        torch.set_num_threads(cores)
+    except Exception:                              # noqa: BLE001
+        pass
+    return cores
+
+
 def time_cpu_reference(feats, k, target_s=12.0, steps=1, warmup=0):
     """Bounded sample: probe 512 rows, then size the sample for ~target_s per step."""
+    use_all_host_threads()
     n = feats.shape[0]
     rng = np.random.default_rng(0)
     nn, _, _ = cpu_reference_step(feats, k, rng.choice(n, 256, replace=False))     # fit + thread-pool warm-up
