@@ -253,6 +253,27 @@ int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, co
 int hg_hypergraph_propagate(const float* x, int64_t n, int64_t f, const int64_t* csr_rowptr,
                             const int64_t* csr_col, float* hyperedge_feat, float* out, void* stream);
 
+/* ---- row (f)4, "next": super-patch aggregation without the per-cluster host loop -----------------
+ * Replaces preprocess_hypergraph.py:157-170 (mean feature / mean position of the rows of each
+ * cluster label) and :175-184 (for each cluster with m > 1 members, the mean of the off-diagonal
+ * entries of K_wsi[idx][:, idx]; 'avg_intra_cluster_similarity' = mean of those means, 0.0 if none).
+ * labels [n] int64 on the device (KMeans output); rows whose label is outside [0, num_clusters) are
+ * left out.  The intra-cluster kernel values are read from dense_k ([n, ld_k], the caller's N x N
+ * kernel) when it is given, else recomputed in FP32 tiles over same-cluster pairs only (expansion
+ * form x Gaussian of positions, as hg_similarity_dense).  want_intra = 0 skips that stage.
+ * Outputs (device): super_feats [S, d], super_pos [S, pos_dim] (pos may be NULL), counts [S] int64,
+ * intra [S] float32 (NaN for m <= 1), summary [4] float32 = {avg_intra, clusters with m > 1,
+ * first empty cluster or -1 (the reference raises ValueError there; its means are NaN here),
+ * rows with a label in range}, order_out [n] int32 or NULL = rows sorted by (label, row).
+ * Stream-ordered, deterministic (no float atomics). */
+int hg_aggregate_workspace_bytes(int64_t n, int64_t d, int num_clusters, size_t* bytes);
+int hg_aggregate_super_patches(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                               const int64_t* labels, int num_clusters, float lambda_h, float lambda_g,
+                               const float* dense_k, int64_t ld_k, int want_intra,
+                               float* super_feats, float* super_pos, int64_t* counts, float* intra,
+                               float* summary, int32_t* order_out,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- batches of slides: ONE host call enqueues every build ----------------------------------
  * The reference's dataset loop (preprocess_hypergraph.py:651-670) handles slides one at a time.
  * A slide of a few thousand patches is only a few hundred microseconds of GPU work, so here the

@@ -69,6 +69,9 @@ SIGNATURES = {
     "hg_build_batch_workspace_bytes": (_i32, [_vp, _i32, _i64, _i32, _i32, _i32, _psz]),
     "hg_build_batch_enqueue": (_i32, [_vp, _i32, _i64, _i32, _i32, _f32, _f32, _i32, _i32, _vp, _sz, _vp, _i32, _i32]),
     "hg_hypergraph_propagate": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "hg_aggregate_workspace_bytes": (_i32, [_i64, _i64, _i32, _psz]),
+    "hg_aggregate_super_patches": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _f32, _f32, _vp, _i64, _i32,
+                                          _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_threshold_edges_fill": (_i32, [_vp, _i64, _f32, _i64, _vp, _vp, _vp, _sz, _vp]),
 }
 

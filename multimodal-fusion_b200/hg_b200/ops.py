@@ -233,6 +233,45 @@ def hypergraph_propagate(x: torch.Tensor, csr_rowptr: torch.Tensor, csr_col: tor
     return (out, m) if return_hyperedge_features else out
 
 
+def aggregate_super_patches(features: torch.Tensor, positions: Optional[torch.Tensor], labels, num_clusters: int,
+                            lambda_h: float = 1.0, lambda_g: float = 0.0, dense_k: Optional[torch.Tensor] = None,
+                            want_intra: bool = True, return_order: bool = False, device=None) -> dict:
+    """Row (f)4: mean feature / position per cluster label and the intra-cluster similarity means
+    (reference preprocess_hypergraph.py:157-184) in one stream-ordered call.  Everything in the
+    returned dict stays on the device; `summary` = [avg_intra, clusters with m > 1, first empty
+    cluster or -1, rows with a label in range] is the only thing a caller needs to read back."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    n, d = x.shape
+    pos = L.f32c(positions, dev) if positions is not None else None
+    pd = 0 if pos is None else pos.shape[1]
+    lab = torch.as_tensor(np.asarray(labels) if not torch.is_tensor(labels) else labels).to(device=dev, dtype=torch.int64).contiguous()
+    if lab.numel() != n:
+        raise ValueError("labels must have one entry per row")
+    kd = L.f32c(dense_k, dev) if dense_k is not None else None
+    if kd is not None and (kd.dim() != 2 or kd.shape[0] != n or kd.shape[1] != n):
+        raise ValueError("dense_k must be [N, N]")
+    s = int(num_clusters)
+    out = {
+        "features": torch.empty((s, d), dtype=torch.float32, device=dev),
+        "positions": torch.empty((s, pd), dtype=torch.float32, device=dev) if pos is not None else None,
+        "counts": torch.empty(s, dtype=torch.int64, device=dev),
+        "intra": torch.empty(s, dtype=torch.float32, device=dev),
+        "summary": torch.empty(4, dtype=torch.float32, device=dev),
+        "order": torch.empty(n, dtype=torch.int32, device=dev) if return_order else None,
+    }
+    with torch.cuda.device(dev):
+        nbytes = _size(lib.hg_aggregate_workspace_bytes, n, d, s)
+        ws = L.Workspace.get(dev, nbytes, "agg")
+        L.check(lib.hg_aggregate_super_patches(
+            L.ptr(x), n, d, L.ptr(pos), pd, L.ptr(lab), s, float(lambda_h), float(lambda_g),
+            L.ptr(kd), 0 if kd is None else kd.stride(0), int(want_intra),
+            L.ptr(out["features"]), L.ptr(out["positions"]), L.ptr(out["counts"]), L.ptr(out["intra"]),
+            L.ptr(out["summary"]), L.ptr(out["order"]), L.ptr(ws), nbytes, L.stream_ptr(dev)))
+    return out
+
+
 def threshold_edges(K: torch.Tensor, threshold: float):
     """A8: every ordered (i, j) with not (K[i,j] < threshold), row-major; (edge_index, weights)."""
     lib = L.load_library()

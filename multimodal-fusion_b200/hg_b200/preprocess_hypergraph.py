@@ -156,28 +156,13 @@ def aggregate_wsi_super_patches(wsi_features: torch.Tensor, wsi_positions: torch
     else:
         K_wsi = None
     labels_np = _cluster(feats, num_super_patches)                              # reference :147-151
-    labels = torch.from_numpy(labels_np.astype(np.int64)).to(dev)
-    counts = torch.bincount(labels, minlength=num_super_patches)
-    empty = torch.nonzero(counts == 0)
-    if empty.numel():
-        raise ValueError(f"Cluster {int(empty[0])} is empty")                   # reference :164
-    inv = (1.0 / counts.to(torch.float32)).unsqueeze(1)
-    super_f = torch.zeros(num_super_patches, feats.shape[1], device=dev).index_add_(0, labels, feats) * inv
-    super_p = torch.zeros(num_super_patches, pos.shape[1], device=dev).index_add_(0, labels, pos) * inv
-    intra = []
-    order = torch.argsort(labels, stable=True)
-    bounds = torch.cumsum(counts, 0).tolist()
-    start = 0
-    for c in range(num_super_patches):                                          # reference :175-184
-        idx = order[start:bounds[c]]
-        start = bounds[c]
-        m = idx.numel()
-        if m > 1:
-            # large slides: the cluster's own m x m kernel block is recomputed instead of gathered
-            blk = K_wsi[idx][:, idx] if K_wsi is not None else \
-                ops.similarity_dense(feats[idx], pos_a=pos[idx], pos_b=pos[idx], lambda_h=lambda_h,
-                                     lambda_g=lambda_g, device=dev)
-            intra.append(float((blk.sum() - blk.diagonal().sum()) / (m * (m - 1))))
+    # segmented means (:157-170) and intra-cluster similarity means (:175-184): one device call
+    agg = ops.aggregate_super_patches(feats, pos, labels_np, num_super_patches, lambda_h, lambda_g,
+                                      dense_k=K_wsi, device=dev)
+    avg_intra, _, first_empty, _ = agg["summary"].tolist()
+    if first_empty >= 0:
+        raise ValueError(f"Cluster {int(first_empty)} is empty")                # reference :164
+    super_f, super_p = agg["features"], agg["positions"]
     if K_wsi is not None:
         k_stats = ops.similarity_stats(K_wsi)
     else:
@@ -185,7 +170,7 @@ def aggregate_wsi_super_patches(wsi_features: torch.Tensor, wsi_positions: torch
     stats = {
         "num_original_patches": n,
         "num_super_patches": num_super_patches,
-        "avg_intra_cluster_similarity": float(np.mean(intra)) if intra else 0.0,
+        "avg_intra_cluster_similarity": float(avg_intra),
         "wsi_similarity_matrix_stats": k_stats,
     }
     return super_f, super_p, stats, K_wsi

@@ -124,6 +124,24 @@ def main():
             num_edges=stats["num_edges"],
             sk_indices=idx.astype(np.int32), sk_distances=dist.astype(np.float64))
         print(name, "E =", ei.shape[1])
+    # ---- super-patch aggregation ((f)4): reference :87-199 with injected cluster labels ------
+    n, d, seed, s_super = 600, 96, 31, 12
+    feats, pos = synth.make_slide(n, d, seed, "gaussian")
+    rng = np.random.default_rng(seed)
+    labels = rng.integers(0, s_super - 1, size=n)
+    labels[17] = s_super - 1                               # one single-member cluster (no intra term)
+    _FixedKMeans.labels = labels
+    lam_h, lam_g = 0.5, 1.0 / 256.0
+    sf, sp, st, K = ref_pp.aggregate_wsi_super_patches(torch.from_numpy(feats), torch.from_numpy(pos), s_super,
+                                                       lam_h, lam_g)
+    np.savez_compressed(
+        os.path.join(out_dir, "aggregate_n600_d96_s12.npz"),
+        n=n, d=d, seed=seed, num_super_patches=s_super, lambda_h=lam_h, lambda_g=lam_g,
+        labels=labels.astype(np.int64), feat_sum=np.float64(feats.astype(np.float64).sum()),
+        super_features=sf.numpy(), super_positions=sp.numpy(),
+        avg_intra=np.float64(st["avg_intra_cluster_similarity"]),
+        K_stats=np.array([st["wsi_similarity_matrix_stats"][q] for q in ("mean", "std", "min", "max", "median")]))
+    print("aggregate_n600_d96_s12 avg_intra =", st["avg_intra_cluster_similarity"])
     print("golden fixtures written to", out_dir)
 
 

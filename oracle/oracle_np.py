@@ -27,6 +27,7 @@ __all__ = [
     "wsi_tma_similarity", "similarity_stats", "sq_dists_f64", "knn_feature",
     "knn_spatial", "edges_from_knn", "edge_weights_cosine", "threshold_edges",
     "csr_from_coo", "build_hypergraph_knn", "lower_median", "hypergraph_conv_propagate",
+    "aggregate_super_patches",
 ]
 
 
@@ -337,3 +338,40 @@ def hypergraph_conv_propagate(x, edge_index, num_nodes=None):
     np.add.at(out, nodes, m[hedges])
     out *= Dinv[:, None]
     return out, m
+
+
+# --------------------------------------------------------------------------
+# (f)4: super-patch aggregation by cluster label
+# --------------------------------------------------------------------------
+def aggregate_super_patches(features, positions, labels, num_super_patches, K=None,
+                            lambda_h=1.0, lambda_g=1.0, dtype=np.float64):
+    """Mean feature / position per cluster and the intra-cluster similarity statistic.
+
+    Follows build_hypergraph/preprocess_hypergraph.py:157-170 (boolean-mask mean per cluster id,
+    ValueError on an empty cluster) and :175-190 (per cluster with more than one member: mean of
+    the off-diagonal entries of K[idx][:, idx]; the statistic is the mean of those means, 0.0
+    when no cluster qualifies).  ``K`` defaults to combined_similarity(features, positions).
+    Returns (super_features, super_positions, counts, intra_per_cluster (NaN when m <= 1), avg)."""
+    x = np.asarray(features, dtype=dtype)
+    p = np.asarray(positions, dtype=dtype)
+    lab = np.asarray(labels)
+    if K is None:
+        K = combined_similarity(x, p, lambda_h, lambda_g, dtype=dtype)
+    sup_f, sup_p, counts = [], [], []
+    intra = np.full(num_super_patches, np.nan, dtype=np.float64)
+    for c in range(num_super_patches):
+        mask = lab == c
+        m = int(mask.sum())
+        if m == 0:
+            raise ValueError(f"Cluster {c} is empty")
+        counts.append(m)
+        sup_f.append(x[mask].mean(axis=0))
+        sup_p.append(p[mask].mean(axis=0))
+        if m > 1:
+            idx = np.nonzero(mask)[0]
+            blk = np.asarray(K, dtype=np.float64)[np.ix_(idx, idx)]
+            off = ~np.eye(m, dtype=bool)
+            intra[c] = blk[off].mean()
+    defined = intra[~np.isnan(intra)]
+    avg = float(defined.mean()) if defined.size else 0.0
+    return np.stack(sup_f), np.stack(sup_p), np.asarray(counts, dtype=np.int64), intra, avg
