@@ -22,7 +22,9 @@ from .preprocess_hypergraph import (
     load_similarity_matrices,
     rebuild_hypergraph_from_similarity,
     batch_rebuild_hypergraph,
+    load_similarity_topk,
 )
+from .store import open_store
 from .ops import hypergraph_propagate
 from .pipeline import SlidePipeline, build_batch, build_many
 
@@ -35,4 +37,5 @@ __all__ = [
     "rebuild_hypergraph_from_similarity", "batch_rebuild_hypergraph",
     # beyond the reference surface
     "build_hypergraph_data", "knn_hyperedges", "build_batch", "build_many", "SlidePipeline", "hypergraph_propagate",
+    "load_similarity_topk", "open_store",
 ]

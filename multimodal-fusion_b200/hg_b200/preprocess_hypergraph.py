@@ -26,16 +26,10 @@ import torch
 from . import _lib as L
 from . import ops
 from .similarity_kernel import compute_combined_similarity
+from .store import _h5py, open_store  # noqa: F401  (_h5py kept for callers of the old name)
 
 MAX_DENSE_N = int(os.environ.get("HG_B200_MAX_DENSE_N", "32768"))   # N x N FP32 = 4 GiB at 32k
-
-
-def _h5py():
-    try:
-        import h5py
-    except ModuleNotFoundError as e:       # same failure mode as the reference's module import (:15)
-        raise ModuleNotFoundError("h5py is required for the HDF5 I/O functions of hg_b200") from e
-    return h5py
+STORED_TOPK = int(os.environ.get("HG_B200_STORED_TOPK", "32"))      # per-row entries of K_wsi kept beyond that
 
 
 KMEANS_BACKEND = os.environ.get("HG_B200_KMEANS", "sklearn")        # "sklearn" (reference behaviour) | "cuda"
@@ -69,7 +63,7 @@ def _device(device, *tensors) -> torch.device:
 # ------------------------------------------------------------------------------ I/O
 def load_wsi_data(h5_path: str) -> Tuple[torch.Tensor, torch.Tensor]:
     """wsi/features [N, D] and wsi/positions [N, 2|3] as float32 CPU tensors (reference :31-62)."""
-    with _h5py().File(h5_path, "r") as f:
+    with open_store(h5_path, "r") as f:
         if "wsi" not in f or "features" not in f["wsi"]:
             raise ValueError(f"WSI features not found in {h5_path}")
         feats = torch.from_numpy(np.asarray(f["wsi"]["features"][:])).float()
@@ -83,7 +77,7 @@ def load_wsi_data(h5_path: str) -> Tuple[torch.Tensor, torch.Tensor]:
 
 def load_tma_data(h5_path: str) -> Optional[torch.Tensor]:
     """tma/features [N_tma, D] or None (reference :65-84)."""
-    with _h5py().File(h5_path, "r") as f:
+    with open_store(h5_path, "r") as f:
         if "tma" in f and "features" in f["tma"]:
             return torch.from_numpy(np.asarray(f["tma"]["features"][:])).float()
     return None
@@ -92,7 +86,7 @@ def load_tma_data(h5_path: str) -> Optional[torch.Tensor]:
 def load_similarity_matrices(h5_path: str):
     """(hypergraph/similarity/wsi_internal, .../wsi_tma) or None each (reference :726-755)."""
     wsi_sim = wsi_tma = None
-    with _h5py().File(h5_path, "r") as f:
+    with open_store(h5_path, "r") as f:
         if "hypergraph" in f and "similarity" in f["hypergraph"]:
             g = f["hypergraph"]["similarity"]
             if "wsi_internal" in g:
@@ -100,6 +94,17 @@ def load_similarity_matrices(h5_path: str):
             if "wsi_tma" in g:
                 wsi_tma = torch.from_numpy(np.asarray(g["wsi_tma"][:])).float()
     return wsi_sim, wsi_tma
+
+
+def load_similarity_topk(h5_path: str):
+    """(indices int64 [N, k], values float32 [N, k]) of hypergraph/similarity/wsi_topk_*, or None."""
+    with open_store(h5_path, "r") as f:
+        if "hypergraph" in f and "similarity" in f["hypergraph"]:
+            g = f["hypergraph"]["similarity"]
+            if "wsi_topk_indices" in g and "wsi_topk_values" in g:
+                return (torch.from_numpy(np.asarray(g["wsi_topk_indices"][:])).long(),
+                        torch.from_numpy(np.asarray(g["wsi_topk_values"][:])).float())
+    return None
 
 
 def _put(group, name, array):
@@ -112,9 +117,14 @@ def save_hypergraph_to_h5(h5_path: str, wsi_super_features: torch.Tensor, wsi_su
                           tma_features: torch.Tensor, edge_index: torch.Tensor, edge_weights: torch.Tensor,
                           group_labels: np.ndarray, stats: Dict,
                           wsi_similarity_matrix: Optional[torch.Tensor] = None,
-                          wsi_tma_similarity_matrix: Optional[torch.Tensor] = None):
-    """Write group ``hypergraph/`` (layout of reference :474-511, README.md:58-73)."""
-    with _h5py().File(h5_path, "a") as f:
+                          wsi_tma_similarity_matrix: Optional[torch.Tensor] = None,
+                          wsi_similarity_topk: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+    """Write group ``hypergraph/`` (layout of reference :474-511, README.md:58-73).  Existing
+    datasets are replaced (the reference's plain assignment fails on a file that was already
+    processed).  `wsi_similarity_topk` = (indices [N, k], values [N, k]) is what large
+    slides store in place of the dense ``similarity/wsi_internal``.  `h5_path` may be a ``.npz``
+    container (hg_b200.store)."""
+    with open_store(h5_path, "a") as f:
         hg = f.require_group("hypergraph")
         sup = hg.require_group("wsi_super")
         _put(sup, "features", wsi_super_features.cpu().numpy())
@@ -131,6 +141,10 @@ def save_hypergraph_to_h5(h5_path: str, wsi_super_features: torch.Tensor, wsi_su
             sim = hg.require_group("similarity")
             _put(sim, "wsi_tma", wsi_tma_similarity_matrix.cpu().numpy())
             sim.attrs["wsi_tma_shape"] = list(wsi_tma_similarity_matrix.shape)
+        if wsi_similarity_topk is not None:
+            sim = hg.require_group("similarity")
+            _put(sim, "wsi_topk_indices", wsi_similarity_topk[0].cpu().numpy())
+            _put(sim, "wsi_topk_values", wsi_similarity_topk[1].cpu().numpy())
         hg.attrs["stats"] = json.dumps(stats, default=float)
 
 
@@ -273,8 +287,14 @@ def process_single_file(h5_path: str, num_wsi_super_patches: int = 100, num_grou
     print("  💾 Saving to h5 (including similarity matrices for fast tuning)...")
     all_stats = {"wsi_aggregation": wsi_stats, "similarity": sim_stats, "grouping": group_stats,
                  "hypergraph": hg_stats}
+    topk = None
+    if wsi_sim is None and wsi_features.shape[0] > 1:
+        # beyond the dense limit: the k strongest entries of every row of K_wsi instead of N x N
+        kk = min(STORED_TOPK, wsi_features.shape[0] - 1)
+        topk = ops.knn_feature(wsi_features, kk, "gaussian", positions=wsi_positions, lambda_h=lambda_h,
+                               lambda_g=lambda_g, device=dev)
     save_hypergraph_to_h5(h5_path, sup_f, sup_p, tma_features, edge_index, edge_weights, group_labels, all_stats,
-                          wsi_similarity_matrix=wsi_sim, wsi_tma_similarity_matrix=sim)
+                          wsi_similarity_matrix=wsi_sim, wsi_tma_similarity_matrix=sim, wsi_similarity_topk=topk)
     print("  ✅ Done!")
     return all_stats
 
@@ -345,7 +365,7 @@ def rebuild_hypergraph_from_similarity(h5_path: str, num_wsi_super_patches: int 
             wsi_similarity_matrix=wsi_sim)
         sim, sim_stats = compute_wsi_tma_similarity(sup_f, sup_p, tma_features, 1.0, 1.0, dev)
     else:
-        with _h5py().File(h5_path, "r") as f:
+        with open_store(h5_path, "r") as f:
             if "hypergraph" not in f or "wsi_super" not in f["hypergraph"]:
                 raise ValueError("WSI super patches not found and num_wsi_super_patches not specified")
             sup_f = torch.from_numpy(np.asarray(f["hypergraph"]["wsi_super"]["features"][:])).float().to(dev)
@@ -358,7 +378,7 @@ def rebuild_hypergraph_from_similarity(h5_path: str, num_wsi_super_patches: int 
     if num_groups is not None:
         group_labels, group_stats = group_by_similarity(sim, num_groups, method="kmeans")
     else:
-        with _h5py().File(h5_path, "r") as f:
+        with open_store(h5_path, "r") as f:
             if "hypergraph" not in f or "group_labels" not in f["hypergraph"]:
                 raise ValueError("Group labels not found and num_groups not specified")
             group_labels = np.asarray(f["hypergraph"]["group_labels"][:])

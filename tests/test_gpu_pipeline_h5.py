@@ -110,3 +110,61 @@ def test_process_dataset_csv_loop(h5, tmp_path, monkeypatch):
     bad.write_text("case_id,path\nx,y\n")
     with pytest.raises(ValueError):
         hg.process_dataset(str(bad), root)
+
+
+def test_pipeline_on_npz_container_matches_h5(h5, tmp_path, monkeypatch):
+    """(f)2: the same slide through the .npz container on disk and through h5py gives the same outputs;
+    beyond the dense limit the top-k lists of K_wsi are stored instead of the N x N matrix."""
+    import hg_b200 as hg
+    from hg_b200 import preprocess_hypergraph as pp, store
+    p_h5, p_npz = str(tmp_path / "case.h5"), str(tmp_path / "case.npz")
+    feats, pos = _make_slide_file(h5, p_h5, n_wsi=500, seed=31)
+    tma = synth.make_features(90, 64, 32, "gaussian")
+    with store.open_store(p_npz, "w") as f:
+        g = f.create_group("wsi")
+        g["features"] = feats
+        g["positions"] = pos
+        f.create_group("tma")["features"] = tma
+    kw = dict(num_wsi_super_patches=16, num_groups=4, hypergraph_k=5, num_hyperedges=3, lambda_h=1.0, lambda_g=1.0 / 128)
+    s_h5 = hg.process_single_file(p_h5, **kw)
+    s_npz = hg.process_single_file(p_npz, **kw)
+    assert s_h5["hypergraph"] == s_npz["hypergraph"]
+    with h5.File(p_h5, "r") as a, store.open_store(p_npz, "r") as b:
+        for key in ("edge_index", "edge_weights", "group_labels"):
+            assert np.array_equal(a["hypergraph"][key][:], b["hypergraph"][key][:]), key
+        assert np.array_equal(a["hypergraph"]["similarity"]["wsi_internal"][:], b["hypergraph/similarity/wsi_internal"][:])
+        assert b["hypergraph"]["similarity"].attrs["wsi_shape"] == [500, 500]
+        assert json.loads(b["hypergraph"].attrs["stats"])["hypergraph"]["num_edges"] == s_npz["hypergraph"]["num_edges"]
+        assert "wsi_topk_indices" not in b["hypergraph"]["similarity"]
+    assert hg.load_similarity_topk(p_npz) is None
+    # re-processing and rebuilding an already processed container replaces its datasets
+    hg.rebuild_hypergraph_from_similarity(p_npz, num_wsi_super_patches=8, num_groups=2, hypergraph_k=3, num_hyperedges=2)
+    with store.open_store(p_npz, "r") as b:
+        assert b["hypergraph/wsi_super/features"].shape == (8, 64)
+    # large-slide layout: no dense kernel on disk, top-k lists of K_wsi instead
+    monkeypatch.setattr(pp, "MAX_DENSE_N", 400)
+    monkeypatch.setattr(pp, "STORED_TOPK", 12)
+    p_big = str(tmp_path / "big.npz")
+    with store.open_store(p_big, "w") as f:
+        g = f.create_group("wsi")
+        g["features"] = feats
+        g["positions"] = pos
+        f.create_group("tma")["features"] = tma
+    s_big = hg.process_single_file(p_big, **kw)
+    with store.open_store(p_big, "r") as b:
+        assert "wsi_internal" not in b["hypergraph"]["similarity"] and "wsi_tma" in b["hypergraph"]["similarity"]
+    idx, val = hg.load_similarity_topk(p_big)
+    assert idx.shape == (500, 12) and idx.dtype == torch.int64 and val.dtype == torch.float32
+    K = oracle.combined_similarity(feats, pos, 1.0, 1.0 / 128)
+    np.fill_diagonal(K, -np.inf)
+    exp_val = -np.sort(-K, axis=1)[:, :12]
+    np.testing.assert_allclose(val.numpy(), exp_val, rtol=1e-5)
+    np.testing.assert_allclose(K[np.arange(500)[:, None], idx.numpy()], exp_val, rtol=1e-5)
+    # streamed statistics of the kernel that was never stored, and the same edges as the dense run
+    ref = oracle.similarity_stats(oracle.combined_similarity(feats, pos, 1.0, 1.0 / 128))
+    got = s_big["wsi_aggregation"]["wsi_similarity_matrix_stats"]
+    for key in ("mean", "std", "min", "max"):
+        assert np.isclose(got[key], ref[key], rtol=1e-5, atol=1e-7), key
+    assert np.isclose(s_big["wsi_aggregation"]["avg_intra_cluster_similarity"],
+                      s_npz["wsi_aggregation"]["avg_intra_cluster_similarity"], rtol=1e-5)
+    assert s_big["hypergraph"] == s_npz["hypergraph"]
