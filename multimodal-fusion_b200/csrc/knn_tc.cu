@@ -185,8 +185,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 int split, rb;
                 decode_unit(p.plan, u, rb, split);
                 const int row0 = int(p.row_begin) + rb * (TC_BM * CL) + int(crank) * TC_BM;
-                const int ct0 = split * p.plan.ct_per_split;
-                const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+                const int ct0 = p.ct_base + split * p.plan.ct_per_split;        // ct_base: column-panel launches
+                const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
                     if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
@@ -231,8 +231,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             for (int u = wid; u < units; u += nworkers) {
                 int split, rb;
                 decode_unit(p.plan, u, rb, split);
-                const int ct0 = split * p.plan.ct_per_split;
-                const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+                const int ct0 = p.ct_base + split * p.plan.ct_per_split;        // ct_base: column-panel launches
+                const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
                 for (int ct = ct0; ct < ct1; ++ct) {
                     if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
                     const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
@@ -286,8 +286,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             const int64_t row0 = p.row_begin + int64_t(rb) * (TC_BM * CL) + int64_t(crank) * TC_BM;
             const int sblk = (CL == 2) ? rb : rb >> 1;          // 256-row super-block (symmetric tile ownership)
             const int64_t row = row0 + quarter * 32 + lane;
-            const int ct0 = split * p.plan.ct_per_split;
-            const int ct1 = min(ct0 + p.plan.ct_per_split, p.plan.num_ct);
+            const int ct0 = p.ct_base + split * p.plan.ct_per_split;
+            const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
             float lv[KLA];
             int li[KLA];
 #pragma unroll
@@ -514,6 +514,57 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists)
     return pl;
 }
 
+// Column-panel plans (staged kNN): the split count is fixed by the caller (every panel owns the same
+// number of list slots); cc = the widest power of two dividing it that keeps the A blocks in the L2.
+static int panel_cc(int splits, int cl, int64_t d_pad) {
+    const int workers = kNumSMs / cl, cc_max = 4 / cl;
+    const int64_t a_block = int64_t(TC_BM * cl) * d_pad * 4;
+    const int64_t rc_cap = (int64_t(40) << 20) / a_block;
+    int cc = 1;
+    while (cc < cc_max && workers / cc > rc_cap && splits % (cc * 2) == 0) cc *= 2;
+    return cc;
+}
+
+TcPlan tc_make_plan_panel(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int splits) {
+    TcPlan pl{};
+    pl.cg = tc_cta_group();
+    pl.mc = tc_multicast();
+    pl.cl = (pl.cg == 2 || pl.mc) ? 2 : 1;
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cl));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(panel_cols, TC_BN));
+    pl.kl = list_len(k);
+    const int workers = kNumSMs / pl.cl;
+    pl.splits = splits;
+    pl.cc = panel_cc(splits, pl.cl, d_pad);
+    pl.rc = workers / pl.cc;
+    pl.grid = int(min64(workers, int64_t(pl.num_rb) * pl.splits)) * pl.cl;
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
+    return pl;
+}
+
+// splits per panel in [1, max_splits]: the best last-round fill, mildly preferring counts whose cc
+// keeps the concurrently swept A blocks under the L2 budget
+int tc_panel_splits(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int max_splits) {
+    const int cl = (tc_cta_group() == 2 || tc_multicast()) ? 2 : 1;
+    const int workers = kNumSMs / cl;
+    const int major = int(ceil_div(n_rows, TC_BM * cl)), tiles = int(ceil_div(panel_cols, TC_BN));
+    const int64_t rc_cap = (int64_t(40) << 20) / (int64_t(TC_BM * cl) * d_pad * 4);
+    int best = 1;
+    double best_eff = -1.0;
+    for (int s = 1; s <= max_splits && s <= TC_MAX_SPLITS; ++s) {
+        if (s > tiles && s > 1) break;
+        const int64_t units = int64_t(major) * s;
+        const double fill = double(tiles) / double(ceil_div(tiles, s) * s);
+        double eff = fill * double(units) / double(ceil_div(units, workers) * workers);
+        if (workers / panel_cc(s, cl, d_pad) > rc_cap) eff *= 0.93;
+        if (eff > best_eff + 0.015) { best_eff = eff; best = s; }
+    }
+    (void)k;
+    return best;
+}
+
 // Threshold pre-pass: all rows against every stride-th column.  One unit per row block when the A
 // blocks of all 148 CTAs plus the column sample fit the L2 (the bound then comes straight out of the
 // kernel); otherwise 2 or 4 column splits run side by side on fewer row blocks and
@@ -662,6 +713,8 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
         if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
     }
     if (p.col_stride < 1) p.col_stride = 1;
+    HG_REQUIRE(p.ct_base == 0 || (!p.plan.sym && p.col_stride == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG,
+               "tc_launch: column panels are for the classic list mode");
     HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
                                p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");

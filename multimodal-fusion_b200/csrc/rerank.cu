@@ -273,7 +273,9 @@ int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int r
 }
 
 int rerank_launch(const RerankParams& p, cudaStream_t st) {
-    HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= RR_MAX_LIST && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
+    // without buckets (classic / staged lists only) the bucket slots of the merge hold list entries as well
+    const int list_cap = (p.ovf != nullptr) ? RR_MAX_LIST : RR_MAX_CAND;
+    HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= list_cap && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
                p.bkt_cap <= TC_BKT_CAP, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
     HG_REQUIRE(p.sq_norms && p.norm_max, HG_ERR_BAD_ARG, "rerank: row norms missing");
     const unsigned blocks = (unsigned)ceil_div(p.n_rows, RR_WARPS);

@@ -6,6 +6,10 @@
 * row-partitioned single slide: rank r owns rows [r*N/G, (r+1)*N/G); ONE all-gather of the
   feature row blocks (NCCL over NVLink), each rank runs the fused kernel on its row range
   against all N columns, ONE small all-gather of the [N/G, k] lists, assembly replicated.
+  With 256-aligned row blocks (`row_range_aligned`) the exchange is overlapped with the kernel:
+  every rank maps its peers' blocks (CUDA IPC), pulls them with the copy engines over NVLink on
+  a side stream, and the fused kernel sweeps each block as a column panel as soon as it is here
+  (`ops.StagedKnn`); the result is bit-identical to the gather-then-compute form.
 
 One process per GPU (`torchrun`); `torch.distributed` is plumbing only.  The host-side logic
 is backend-agnostic so world_size-2 gloo tests cover it on CPU with the kNN stage injected.
@@ -38,16 +42,27 @@ def row_range(n: int, rank: int, world_size: int) -> Tuple[int, int]:
     return r0, r0 + base + (1 if rank < extra else 0)
 
 
-def all_gather_rows(local: torch.Tensor, n: int, group=None) -> torch.Tensor:
-    """Concatenate per-rank row blocks (sizes given by row_range) into [n, ...] on every rank."""
+PANEL_ALIGN = 256     # column tile of the fused kernel: staged panels start on multiples of it
+
+
+def row_range_aligned(n: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Row blocks whose boundaries are multiples of 256 (the last block takes what is left, trailing
+    ranks may own nothing): the partition the overlapped exchange needs."""
+    chunk = -(-(-(-n // world_size)) // PANEL_ALIGN) * PANEL_ALIGN
+    r0 = min(n, rank * chunk)
+    return r0, min(n, r0 + chunk)
+
+
+def all_gather_rows(local: torch.Tensor, n: int, group=None, ranges=row_range) -> torch.Tensor:
+    """Concatenate per-rank row blocks (sizes given by `ranges`) into [n, ...] on every rank."""
     world = dist.get_world_size(group)
     shape = tuple(local.shape[1:])
-    sizes = [row_range(n, r, world)[1] - row_range(n, r, world)[0] for r in range(world)]
+    sizes = [ranges(n, r, world)[1] - ranges(n, r, world)[0] for r in range(world)]
     if len(set(sizes)) == 1:
         out = torch.empty((n,) + shape, dtype=local.dtype, device=local.device)
         dist.all_gather_into_tensor(out, local.contiguous(), group=group)
         return out
-    # ragged blocks: pad to the largest block (at most one extra row), gather, drop the padding
+    # ragged blocks: pad to the largest block, gather, drop the padding
     m = max(sizes)
     padded = torch.zeros((m,) + shape, dtype=local.dtype, device=local.device)
     padded[: local.shape[0]] = local
@@ -56,33 +71,125 @@ def all_gather_rows(local: torch.Tensor, n: int, group=None) -> torch.Tensor:
     return torch.cat([gathered[r * m: r * m + sizes[r]] for r in range(world)], 0)
 
 
+def _map_peer_blocks(local: torch.Tensor, group) -> Optional[list]:
+    """Every rank's block as a tensor usable from this process: the own block as is, the peers' blocks
+    mapped through CUDA IPC (torch's tensor sharing; the memory stays on the owning GPU).  None if any
+    rank could not export or map (all ranks agree on the outcome)."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    handle, ok = None, 1
+    try:
+        from torch.multiprocessing.reductions import reduce_tensor
+        handle = reduce_tensor(local)
+    except Exception:                      # noqa: BLE001 - allocator without IPC support, ...
+        ok = 0
+    handles = [None] * world
+    dist.all_gather_object(handles, handle, group=group)
+    blocks = []
+    if ok and all(h is not None for h in handles):
+        try:
+            for r, h in enumerate(handles):
+                blocks.append(local if r == rank else h[0](*h[1]))
+        except Exception:                  # noqa: BLE001
+            ok = 0
+    else:
+        ok = 0
+    flag = torch.tensor([ok], dtype=torch.int32, device=local.device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return blocks if int(flag.item()) == 1 else None
+
+
+def _knn_overlapped(local_features: torch.Tensor, n: int, k: int, kernel: str, lambda_h: float, lambda_g: float,
+                    pos: Optional[torch.Tensor], group):
+    """Staged kNN over peer blocks pulled by the copy engines while earlier panels are swept.
+    Returns ((idx, val, cos), feats_all) or None when the peers' memory cannot be mapped."""
+    from . import ops
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = local_features.device
+    blocks = _map_peer_blocks(local_features, group)
+    if blocks is None:
+        return None
+    ranges = [row_range_aligned(n, r, world) for r in range(world)]
+    r0, r1 = ranges[rank]
+    d = local_features.shape[1]
+    feats_all = torch.empty((n, d), dtype=torch.float32, device=dev)
+    main = torch.cuda.current_stream(dev)
+    copy_stream = torch.cuda.Stream(dev)
+    order = [(rank + s) % world for s in range(world)]            # own block first, then ring order:
+    arrived = {}                                                  # at every step each GPU serves one reader
+    copy_stream.wait_stream(main)                                 # feats_all exists, local block is ready
+    with torch.cuda.stream(copy_stream):
+        for src in order:
+            a, b = ranges[src]
+            if b > a:
+                feats_all[a:b].copy_(blocks[src], non_blocking=True)          # peer -> local over NVLink (DMA)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+            arrived[src] = ev
+    widest = max(b - a for a, b in ranges)
+    staged = ops.StagedKnn(n, d, k, kernel, (r0, r1), world, widest, positions=pos if lambda_g else None,
+                           lambda_h=lambda_h, lambda_g=lambda_g, device=dev)
+    for src in order:
+        a, b = ranges[src]
+        main.wait_event(arrived[src])
+        if b > a:
+            staged.add_panel(feats_all[a:b], a, b, src)
+    local = staged.finish(feats_all, return_cos=True)
+    feats_all.record_stream(copy_stream)
+    return local, feats_all, blocks
+
+
 def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: int = 16, kernel: str = "gaussian",
                                    lambda_h: float = 1.0, lambda_g: float = 0.0,
                                    positions: Optional[torch.Tensor] = None, spatial_k: int = 0,
-                                   return_csr: bool = False, group=None,
+                                   return_csr: bool = False, group=None, aligned: bool = False,
+                                   overlap: Optional[bool] = None,
                                    knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None) -> dict:
-    """Config C5: `local_features` is this rank's row block [r1-r0, D]; `positions` (replicated,
-    [n, 2|3]) is small.  Returns the same dict as `knn_hyperedges` on every rank."""
+    """Config C5: `local_features` is this rank's row block [r1-r0, D] (`row_range`, or
+    `row_range_aligned` with aligned=True); `positions` (replicated, [n, 2|3]) is small.  Returns
+    the same dict as `knn_hyperedges` on every rank.  With aligned blocks on CUDA the exchange of
+    the feature blocks overlaps the fused kernel (overlap=False forces gather-then-compute); the
+    dict then also carries "overlapped": True."""
     from . import ops
     rank, world = dist.get_rank(group), dist.get_world_size(group)
-    r0, r1 = row_range(n, rank, world)
-    assert local_features.shape[0] == r1 - r0, "local block does not match row_range()"
-    feats = all_gather_rows(local_features, n, group)                   # the one big collective
+    ranges = row_range_aligned if aligned else row_range
+    r0, r1 = ranges(n, rank, world)
+    assert local_features.shape[0] == r1 - r0, "local block does not match the row partition"
     pos = positions if (positions is not None) else None
-    if knn_fn is None:
-        knn_fn = lambda x, rows: ops.knn_feature(x, k, kernel, positions=pos if lambda_g else None,   # noqa: E731
-                                                 lambda_h=lambda_h, lambda_g=lambda_g, rows=rows, return_cos=True)
-    local = knn_fn(feats, (r0, r1))
+    local = feats = peer_blocks = None
+    all_have_rows = all(ranges(n, r, world)[1] > ranges(n, r, world)[0] for r in range(world))
+    if overlap is None:                    # decided from facts every rank sees alike (collectives inside)
+        overlap = aligned and knn_fn is None and local_features.is_cuda and all_have_rows and k <= 32
+    if overlap:
+        assert aligned and knn_fn is None, "the overlapped exchange needs row_range_aligned blocks"
+        res = _knn_overlapped(local_features.contiguous(), n, k, kernel, lambda_h, lambda_g, pos, group)
+        if res is not None:
+            local, feats, peer_blocks = res
+    if local is None:
+        feats = all_gather_rows(local_features, n, group, ranges)           # the one big collective
+        with_cos = knn_fn is None          # an injected knn_fn returns (idx, val)
+        if knn_fn is None:
+            knn_fn = lambda x, rows: ops.knn_feature(x, k, kernel, positions=pos if lambda_g else None,   # noqa: E731
+                                                     lambda_h=lambda_h, lambda_g=lambda_g, rows=rows, return_cos=True)
+        if r1 > r0:
+            local = knn_fn(feats, (r0, r1))
+        else:                              # more ranks than row blocks: nothing to rank here
+            local = (torch.empty((0, k), dtype=torch.int32, device=feats.device),
+                     torch.empty((0, k), dtype=torch.float32, device=feats.device))
+            if with_cos:
+                local += (torch.empty((0, k), dtype=torch.float32, device=feats.device),)
     idx_local, val_local = local[0], local[1]
-    out = {"knn_idx": all_gather_rows(idx_local, n, group), "knn_val": all_gather_rows(val_local, n, group)}
+    out = {"knn_idx": all_gather_rows(idx_local, n, group, ranges),
+           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": peer_blocks is not None}
+    # every rank is past its kNN here, i.e. has read its peers' blocks: the mappings can go
+    peer_blocks = None
     # cos(f_i, f_j) of every list entry travels with the lists: the edge weights are then looked up
     # instead of gathering two feature rows per edge
-    knn_cos = all_gather_rows(local[2], n, group) if len(local) > 2 else None
+    knn_cos = all_gather_rows(local[2], n, group, ranges) if len(local) > 2 else None
     lists = [out["knn_idx"]]
     if spatial_k and pos is not None:
         sidx, sd2 = ops.knn_spatial(pos, spatial_k, rows=(r0, r1))
-        out["spatial_idx"] = all_gather_rows(sidx, n, group)
-        out["spatial_d2"] = all_gather_rows(sd2, n, group)
+        out["spatial_idx"] = all_gather_rows(sidx, n, group, ranges)
+        out["spatial_d2"] = all_gather_rows(sd2, n, group, ranges)
         lists.append(out["spatial_idx"])
     if assemble_fn is None:
         def assemble_fn(lists, feats):

@@ -33,18 +33,29 @@ def test_row_range_partition():
         assert max(lens) - min(lens) <= 1
 
 
+def test_row_range_aligned_partition():
+    for n, world in [(250_000, 8), (20_001, 4), (300, 4), (1, 2), (512, 2), (257, 3)]:
+        edges = [multigpu.row_range_aligned(n, r, world) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+        assert all(a % 256 == 0 or a == n for a, _ in edges)          # panel boundaries of the fused kernel
+        assert all(b % 256 == 0 or b == n for _, b in edges)
+        lens = [b - a for a, b in edges]
+        assert max(lens) - (-(-n // world)) < 256                      # at most one tile more than an even share
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n, d, k, q):
+def _worker(rank, world, port, n, d, k, q, aligned=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         feats = synth.make_features(n, d, 77, "gaussian")
-        r0, r1 = multigpu.row_range(n, rank, world)
+        r0, r1 = (multigpu.row_range_aligned if aligned else multigpu.row_range)(n, rank, world)
 
         def knn_fn(x, rows):                                   # stands in for ops.knn_feature on this rank's rows
             idx, val = oracle.knn_feature(x.numpy(), k, "gaussian", rows=np.arange(rows[0], rows[1]))
@@ -55,19 +66,23 @@ def _worker(rank, world, port, n, d, k, q):
             return {"edge_index": torch.from_numpy(ei)}
 
         out = multigpu.knn_hyperedges_row_partitioned(torch.from_numpy(feats[r0:r1]), n, k=k, knn_fn=knn_fn,
-                                                      assemble_fn=assemble_fn)
+                                                      assemble_fn=assemble_fn, aligned=aligned)
+        assert out["overlapped"] is False                      # no CUDA here: gather-then-compute
         q.put((rank, out["knn_idx"].numpy(), out["edge_index"].numpy()))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.timeout(120)
-def test_row_partitioned_equals_single_process():
-    n, d, k, world = 301, 32, 4, 2                             # odd n: uneven row blocks -> all_gather of ragged chunks
+@pytest.mark.timeout(240)
+@pytest.mark.parametrize("n,aligned", [(301, False), (301, True), (200, True)])
+def test_row_partitioned_equals_single_process(n, aligned):
+    # odd n: uneven row blocks -> all_gather of ragged chunks; aligned: blocks of 256 rows, with n = 200
+    # the second rank owns nothing
+    d, k, world = 32, 4, 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, d, k, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, d, k, q, aligned)) for r in range(world)]
     for p in procs:
         p.start()
     results = [q.get(timeout=100) for _ in range(world)]
