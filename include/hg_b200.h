@@ -247,31 +247,40 @@ int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, co
  * This GPU owns the query rows [row_begin, row_end) of a slide whose other rows live on peer GPUs.
  * Instead of gathering all n rows first and then calling hg_knn_feature, the candidate columns are
  * handed over PANEL BY PANEL while the remaining ones are still in flight over NVLink: every panel is
- * split and swept by the fused kernel as soon as it is here, into its own slots of the per-row
- * candidate lists; finish merges the slots and re-ranks exactly (FP32) like the one-shot call.  The
- * result does not depend on how the columns are cut into panels nor on their order, and equals
- * hg_knn_feature(row_begin, row_end) bit for bit.
+ * split and swept by the fused kernel as soon as it is here; the per-row candidate lists are carried
+ * from one panel launch to the next, finish merges them and re-ranks exactly (FP32) like the one-shot
+ * call.  A list holds the best candidates of the columns seen so far whatever their order, so the
+ * result equals hg_knn_feature(row_begin, row_end) (tests/test_gpu_staged.py: bit for bit; arrival
+ * order could only choose between columns whose approximate scores tie exactly at the tail of a list).
  *   begin   once per slide
- *   panel   columns [col_begin, col_end) = the rows panel_feats[0 .. col_end - col_begin) of the slide;
- *           col_begin is a multiple of 256 and col_end too unless it is n; panel_index in
- *           [0, num_panels) names the panel's list slots (each index at most once).  The panel that
- *           contains the query rows must be the first one.
- *   finish  feats_all = all n rows in this GPU's memory (the re-rank gathers candidate rows from it)
- * All three are stream-ordered on `stream`; the caller orders the arrival of a panel's rows before
- * its panel call (an event of the copy stream).  The descriptor is plain data, the same for all calls. */
+ *   load    operand preparation of the columns [col_begin, col_end) = the rows
+ *           panel_feats[0 .. col_end - col_begin) of the slide (split into BF16 hi/lo, norms);
+ *           col_begin is a multiple of 256 and col_end too unless it is n
+ *   sweep   the fused kernel over those columns for the query rows, on list-slot set `lane`
+ *           (0 <= lane < num_lanes); every column is swept once.  Needs the loads of these columns
+ *           AND of the panel(s) holding the query rows to be complete.  Sweeps on the same lane must be
+ *           ordered (same stream); sweeps on different lanes may run concurrently on different
+ *           streams, which lets the next panel fill the SMs the previous sweep's tail leaves idle.
+ *   finish  after all sweeps; feats_all = all n rows in this GPU's memory (the re-rank gathers
+ *           candidate rows from it)
+ * Every call is stream-ordered on its `stream`; the caller orders the arrival of a panel's rows
+ * before its load (an event of the copy stream) and the cross-stream dependencies named above.
+ * The descriptor is plain data, the same for all calls. */
 typedef struct hg_knn_staged {
     int64_t n, d;                 /* rows of the whole slide, feature width */
     int64_t row_begin, row_end;   /* query rows of this GPU */
     int64_t max_panel_cols;       /* widest panel that will be added */
     const float* pos;             /* [n, pos_dim] positions of all rows (Gaussian metric with lambda_g) or NULL */
     int32_t pos_dim, metric, k, exclude_self;
-    int32_t num_panels, reserved;
+    int32_t num_lanes, reserved;  /* list-slot sets (1..4; 0 = 1) */
     float lambda_h, lambda_g;
 } hg_knn_staged;
 int hg_knn_staged_workspace_bytes(const hg_knn_staged* s, size_t* bytes);
 int hg_knn_staged_begin(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_staged_panel(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
-                        int panel_index, void* workspace, size_t workspace_bytes, void* stream);
+int hg_knn_staged_load(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
+                       void* workspace, size_t workspace_bytes, void* stream);
+int hg_knn_staged_sweep(const hg_knn_staged* s, int64_t col_begin, int64_t col_end, int lane,
+                        void* workspace, size_t workspace_bytes, void* stream);
 int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_all, int32_t* out_idx, float* out_val,
                          float* out_cos, void* workspace, size_t workspace_bytes, void* stream);
 

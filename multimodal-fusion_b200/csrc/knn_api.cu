@@ -235,15 +235,21 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
 // ---- staged kNN: the candidate columns arrive panel by panel -----------------------------------------
 // Row-partitioned slides: this GPU owns query rows [row_begin, row_end) and the
 // candidate rows of the other GPUs arrive over NVLink while the panels already here are being swept.
-// Every panel is split (FP32 -> BF16 hi/lo at its global operand rows) and swept by the fused kernel
-// as soon as it lands, into its own slots of the per-row candidate lists; finish merges all slots and
-// re-ranks exactly as the one-shot call does.  The candidate set a row ends up with does not depend on
-// how the columns were cut into panels or on their order: the result equals hg_knn_feature's bit for bit.
+// Every panel is loaded (FP32 -> BF16 hi/lo at its global operand rows) and swept by the fused kernel
+// as soon as it lands; the per-(row, split) candidate lists are carried from one sweep to the next
+// on the same lane (a unit starts from the list its slot already holds), so a row keeps as few lists
+// and pays as few list insertions as in the one-shot call.  Sweeps on different lanes own different
+// slots and may run on different streams: the next panel's CTAs then fill the SMs the previous
+// sweep's tail leaves idle.  finish merges the slots and re-ranks exactly as the
+// one-shot call does.  A list is the kl best of the columns that passed through its slot whatever
+// their order, so the result equals hg_knn_feature's (arrival order can only pick another one of
+// several columns whose approximate scores tie exactly at rank kl of a list).
 namespace hg {
 
 struct StagedWs {
     size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_flags, bytes;
-    int spp;                     // list slots (column splits) per panel
+    int spp;                     // list slots (column splits) per sweep
+    int lanes;                   // independent slot sets: sweeps on different lanes may run concurrently
     int kl;
     int64_t n_pad, d_pad, n_rows;
 };
@@ -253,11 +259,11 @@ static int staged_check(const hg_knn_staged* s) {
     int rc = check_knn_args(s->n, s->d, s->k, s->row_begin, s->row_end);
     if (rc != HG_OK) return rc;
     HG_REQUIRE(s->k <= 32, HG_ERR_UNSUPPORTED, "hg_knn_staged: the tensor-core path supports k <= 32 (got %d)", s->k);
-    HG_REQUIRE(s->num_panels >= 1 && s->num_panels <= 64, HG_ERR_BAD_ARG, "hg_knn_staged: 1..64 panels");
     HG_REQUIRE(s->max_panel_cols >= 1 && s->max_panel_cols <= s->n, HG_ERR_BAD_ARG, "hg_knn_staged: bad max_panel_cols");
     HG_REQUIRE(s->metric == HG_METRIC_EUCLIDEAN || s->metric == HG_METRIC_GAUSSIAN || s->metric == HG_METRIC_COSINE,
                HG_ERR_BAD_ARG, "hg_knn_staged: unknown metric %d", s->metric);
     HG_REQUIRE(s->pos == nullptr || (s->pos_dim >= 1 && s->pos_dim <= 3), HG_ERR_UNSUPPORTED, "hg_knn_staged: pos_dim must be 1..3");
+    HG_REQUIRE(s->num_lanes >= 0 && s->num_lanes <= 4, HG_ERR_BAD_ARG, "hg_knn_staged: 1..4 lanes");
     HG_REQUIRE(s->metric != HG_METRIC_GAUSSIAN || s->lambda_h > 0.f || s->pos == nullptr, HG_ERR_UNSUPPORTED,
                "hg_knn_staged: lambda_h must be > 0 when positions are given");
     return HG_OK;
@@ -273,18 +279,18 @@ static int staged_plan(const hg_knn_staged* s, StagedWs* w) {
     w->n_rows = s->row_end - s->row_begin;
     const TcPlan probe = tc_make_plan_panel(s->max_panel_cols, w->n_rows, s->k, w->d_pad, 1);
     w->kl = probe.kl;
-    // the re-rank merges at most RR_MAX_CAND = 768 candidates per row
-    const int max_spp = 768 / (w->kl * s->num_panels);
-    HG_REQUIRE(max_spp >= 1, HG_ERR_UNSUPPORTED, "hg_knn_staged: %d panels x %d candidates per row is too many",
-               s->num_panels, w->kl);
-    w->spp = tc_panel_splits(s->max_panel_cols, w->n_rows, s->k, w->d_pad, max_spp);
+    w->lanes = s->num_lanes < 1 ? 1 : s->num_lanes;
+    w->spp = tc_panel_splits(s->max_panel_cols, w->n_rows, s->k, w->d_pad, TC_MAX_SPLITS);
+    // the re-rank merges at most 768 list candidates per row
+    while (w->spp > 1 && w->lanes * w->spp * w->kl > 768) --w->spp;
+    HG_REQUIRE(w->lanes * w->spp * w->kl <= 768, HG_ERR_UNSUPPORTED, "hg_knn_staged: too many lanes (%d)", w->lanes);
     size_t off = 0;
     auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
     w->off_ops = take(hg_operand_bytes(s->n, s->d));
     w->off_norms = take(size_t(w->n_pad) * 4);
     w->off_colp = take(size_t(w->n_pad) * 8);
     w->off_pos4 = take(staged_has_pos(s) ? size_t(w->n_pad) * 16 : 0);
-    const size_t part = size_t(s->num_panels) * w->spp * size_t(w->n_rows) * size_t(w->kl);
+    const size_t part = size_t(w->lanes) * w->spp * size_t(w->n_rows) * size_t(w->kl);
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
     w->off_flags = take(8);
@@ -324,22 +330,28 @@ extern "C" int hg_knn_staged_begin(const hg_knn_staged* s, void* workspace, size
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 8, st));                  // (unused flag, largest squared norm)
-    // list slots of panels that never arrive (or have fewer tiles than slots) must read as empty
-    const size_t part = size_t(s->num_panels) * w.spp * size_t(w.n_rows) * size_t(w.kl);
+    // every list slot starts empty (index -1); the panel launches carry them forward
+    const size_t part = size_t(w.lanes) * w.spp * size_t(w.n_rows) * size_t(w.kl);
     HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_pidx, 0xff, part * 4, st));
     return HG_OK;
 }
 
-extern "C" int hg_knn_staged_panel(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
-                                   int panel_index, void* workspace, size_t workspace_bytes, void* stream) {
+static int staged_cols_ok(const hg_knn_staged* s, int64_t col_begin, int64_t col_end) {
+    HG_REQUIRE(col_begin >= 0 && col_begin < col_end && col_end <= s->n && col_end - col_begin <= s->max_panel_cols,
+               HG_ERR_BAD_ARG, "hg_knn_staged: bad column range [%lld, %lld)", (long long)col_begin, (long long)col_end);
+    HG_REQUIRE(col_begin % TC_BN == 0 && (col_end % TC_BN == 0 || col_end == s->n), HG_ERR_BAD_ARG,
+               "hg_knn_staged: panels start and end on multiples of %d columns (the last one ends at n)", TC_BN);
+    return HG_OK;
+}
+
+extern "C" int hg_knn_staged_load(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
     StagedWs w{};
     int rc = staged_ws(s, workspace, workspace_bytes, &w);
     if (rc != HG_OK) return rc;
-    HG_REQUIRE(panel_feats && panel_index >= 0 && panel_index < s->num_panels, HG_ERR_BAD_ARG, "hg_knn_staged_panel: bad argument");
-    HG_REQUIRE(col_begin >= 0 && col_begin < col_end && col_end <= s->n && col_end - col_begin <= s->max_panel_cols,
-               HG_ERR_BAD_ARG, "hg_knn_staged_panel: bad column range [%lld, %lld)", (long long)col_begin, (long long)col_end);
-    HG_REQUIRE(col_begin % TC_BN == 0 && (col_end % TC_BN == 0 || col_end == s->n), HG_ERR_BAD_ARG,
-               "hg_knn_staged_panel: panels start and end on multiples of %d columns (the last one ends at n)", TC_BN);
+    HG_REQUIRE(panel_feats, HG_ERR_BAD_ARG, "hg_knn_staged_load: null panel");
+    rc = staged_cols_ok(s, col_begin, col_end);
+    if (rc != HG_OK) return rc;
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool has_pos = staged_has_pos(s);
@@ -349,26 +361,38 @@ extern "C" int hg_knn_staged_panel(const hg_knn_staged* s, const float* panel_fe
     float4* pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
     float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
     const int64_t cols = col_end - col_begin;
-
     rc = launch_split(panel_feats, cols, s->d, ops + col_begin * ops_row_elems(w.d_pad), norms + col_begin, st);
     if (rc != HG_OK) return rc;
-    rc = launch_colparams(norms + col_begin, has_pos ? s->pos + col_begin * s->pos_dim : nullptr, s->pos_dim, cols,
-                          ops_rows(cols), s->metric, colp + col_begin, has_pos ? pos4 + col_begin : nullptr, st, nullptr,
-                          nullptr, norm_max);
-    if (rc != HG_OK) return rc;
+    return launch_colparams(norms + col_begin, has_pos ? s->pos + col_begin * s->pos_dim : nullptr, s->pos_dim, cols,
+                            ops_rows(cols), s->metric, colp + col_begin, has_pos ? pos4 + col_begin : nullptr, st, nullptr,
+                            nullptr, norm_max);
+}
 
+extern "C" int hg_knn_staged_sweep(const hg_knn_staged* s, int64_t col_begin, int64_t col_end, int lane,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+    StagedWs w{};
+    int rc = staged_ws(s, workspace, workspace_bytes, &w);
+    if (rc != HG_OK) return rc;
+    rc = staged_cols_ok(s, col_begin, col_end);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(lane >= 0 && lane < w.lanes, HG_ERR_BAD_ARG, "hg_knn_staged_sweep: lane %d of %d", lane, w.lanes);
+    char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool has_pos = staged_has_pos(s);
     TcParams tp{};
     tp.n = s->n; tp.row_begin = s->row_begin; tp.row_end = s->row_end; tp.d_pad = int(w.d_pad);
-    tp.plan = tc_make_plan_panel(cols, w.n_rows, s->k, w.d_pad, w.spp);
+    tp.plan = tc_make_plan_panel(col_end - col_begin, w.n_rows, s->k, w.d_pad, w.spp);
     tp.ct_base = int(col_begin / TC_BN);
-    tp.colp = colp; tp.pos4 = pos4;
+    tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
+    tp.pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
     tp.gscale = (has_pos && s->lambda_h > 0.f) ? s->lambda_g / s->lambda_h : 0.f;
     tp.exclude_self = s->exclude_self;
-    const size_t slot = size_t(panel_index) * w.spp * size_t(w.n_rows) * size_t(w.kl);
+    tp.carry = 1;
+    const size_t slot = size_t(lane) * w.spp * size_t(w.n_rows) * size_t(w.kl);
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval) + slot;
     tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx) + slot;
     prof_begin(st);
-    rc = tc_launch(ops, w.n_pad, tp, st);
+    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, tp, st);
     prof_end(st);
     return rc;
 }
@@ -388,7 +412,7 @@ extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_a
     rp.metric = s->metric; rp.lambda_h = s->lambda_h; rp.lambda_g = has_pos ? s->lambda_g : 0.f;
     rp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
     rp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
-    rp.splits = s->num_panels * w.spp; rp.kl = w.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
+    rp.splits = w.lanes * w.spp; rp.kl = w.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     return rerank_launch(rp, static_cast<cudaStream_t>(stream));
 }

@@ -292,6 +292,15 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             int li[KLA];
 #pragma unroll
             for (int q = 0; q < KLA; ++q) { lv[q] = INFINITY; li[q] = -1; }
+            if (KL > 0 && p.carry && row < p.row_end) {
+                // column-panel launches: go on from the list the previous panels left in this slot
+                const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+#pragma unroll
+                for (int q = 0; q < KLA; ++q) {
+                    li[q] = p.part_idx[o + q];
+                    lv[q] = li[q] >= 0 ? p.part_val[o + q] : INFINITY;
+                }
+            }
             // this row's own score parameters; padded rows: (+inf, 0)
             const float2 me = (row < p.n_pad) ? __ldg(p.colp + row) : make_float2(INFINITY, 0.f);
             const float row_norm = me.x, ta = me.x, tb = me.y;
@@ -713,7 +722,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
         if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
     }
     if (p.col_stride < 1) p.col_stride = 1;
-    HG_REQUIRE(p.ct_base == 0 || (!p.plan.sym && p.col_stride == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG,
+    HG_REQUIRE((p.ct_base == 0 && !p.carry) || (!p.plan.sym && p.col_stride == 1 && p.plan.kl > 0 && !p.thr_out), HG_ERR_BAD_ARG,
                "tc_launch: column panels are for the classic list mode");
     HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
                                p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),

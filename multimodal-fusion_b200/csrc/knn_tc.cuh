@@ -64,8 +64,10 @@ struct TcParams {
     uint64_t hint_a, hint_b;    // L2 cache hints of the A / B tile loads (filled by tc_launch)
     int pair_stages;            // producer refills two 48 KB stages at a time (see tc_launch)
     // column-panel launch (staged kNN, knn_api.cu): the plan describes the panel's own num_ct column
-    // tiles and splits; they sit ct_base tiles into the operand buffer
+    // tiles and splits; they sit ct_base tiles into the operand buffer.  carry: every unit starts from
+    // the list already stored in its (row, split) slot (index -1 = empty entry) instead of an empty one
     int ct_base;
+    int carry;
 };
 
 // plan of one column panel of `panel_cols` columns swept by n_rows rows with `splits` lists per row

@@ -27,7 +27,7 @@ class KnnStaged(C.Structure):
     """struct hg_knn_staged of include/hg_b200.h"""
     _fields_ = [("n", _i64), ("d", _i64), ("row_begin", _i64), ("row_end", _i64), ("max_panel_cols", _i64),
                 ("pos", _vp), ("pos_dim", C.c_int32), ("metric", C.c_int32), ("k", C.c_int32),
-                ("exclude_self", C.c_int32), ("num_panels", C.c_int32), ("reserved", C.c_int32),
+                ("exclude_self", C.c_int32), ("num_lanes", C.c_int32), ("reserved", C.c_int32),
                 ("lambda_h", _f32), ("lambda_g", _f32)]
 
 
@@ -81,7 +81,8 @@ SIGNATURES = {
     "hg_hypergraph_propagate": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "hg_knn_staged_workspace_bytes": (_i32, [_pst, _psz]),
     "hg_knn_staged_begin": (_i32, [_pst, _vp, _sz, _vp]),
-    "hg_knn_staged_panel": (_i32, [_pst, _vp, _i64, _i64, _i32, _vp, _sz, _vp]),
+    "hg_knn_staged_load": (_i32, [_pst, _vp, _i64, _i64, _vp, _sz, _vp]),
+    "hg_knn_staged_sweep": (_i32, [_pst, _i64, _i64, _i32, _vp, _sz, _vp]),
     "hg_knn_staged_finish": (_i32, [_pst, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_aggregate_workspace_bytes": (_i32, [_i64, _i64, _i32, _psz]),
     "hg_aggregate_super_patches": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _f32, _f32, _vp, _i64, _i32,

@@ -98,44 +98,74 @@ def _map_peer_blocks(local: torch.Tensor, group) -> Optional[list]:
     return blocks if int(flag.item()) == 1 else None
 
 
+class PeerExchange:
+    """A staging buffer [max_rows, d] float32 per rank, exported once over CUDA IPC and mapped by every
+    peer (collective constructor).  Per slide a rank writes its row block into its own buffer and the
+    peers pull it with their copy engines; nothing is pickled or synchronised with the host after
+    construction.  `blocks` is None when the mapping is not possible on this system."""
+
+    def __init__(self, max_rows: int, d: int, device, group=None):
+        self.buf = torch.empty((max_rows, d), dtype=torch.float32, device=device)
+        self.blocks = _map_peer_blocks(self.buf, group)
+        self.token = torch.zeros(1, dtype=torch.float32, device=device)
+        self.copy_stream = torch.cuda.Stream(device)
+
+
+_EXCHANGES = {}
+
+
+def peer_exchange(max_rows: int, d: int, device, group=None) -> PeerExchange:
+    """The cached exchange for this (group, shape): every rank reaches this with the same arguments, so
+    all of them create it (a collective) in the same call."""
+    key = (id(group) if group is not None else None, int(max_rows), int(d), torch.device(device).index)
+    if key not in _EXCHANGES:
+        _EXCHANGES[key] = PeerExchange(max_rows, d, device, group)
+    return _EXCHANGES[key]
+
+
 def _knn_overlapped(local_features: torch.Tensor, n: int, k: int, kernel: str, lambda_h: float, lambda_g: float,
                     pos: Optional[torch.Tensor], group):
     """Staged kNN over peer blocks pulled by the copy engines while earlier panels are swept.
-    Returns ((idx, val, cos), feats_all) or None when the peers' memory cannot be mapped."""
+    Returns ((idx, val, cos), feats_all) or None when the peers' memory cannot be mapped.
+    The caller's next collective (the all-gather of the lists) is what tells a rank that all peers
+    are done reading its staging buffer before it is overwritten for the next slide."""
     from . import ops
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     dev = local_features.device
-    blocks = _map_peer_blocks(local_features, group)
-    if blocks is None:
-        return None
     ranges = [row_range_aligned(n, r, world) for r in range(world)]
+    widest = max(b - a for a, b in ranges)
     r0, r1 = ranges[rank]
     d = local_features.shape[1]
-    feats_all = torch.empty((n, d), dtype=torch.float32, device=dev)
+    ex = peer_exchange(widest, d, dev, group)
+    if ex.blocks is None:
+        return None
     main = torch.cuda.current_stream(dev)
-    copy_stream = torch.cuda.Stream(dev)
+    if local_features.data_ptr() != ex.buf.data_ptr():
+        ex.buf[: r1 - r0].copy_(local_features, non_blocking=True)
+    dist.all_reduce(ex.token, group=group)                        # stream-ordered: every rank's block is in place
+    feats_all = torch.empty((n, d), dtype=torch.float32, device=dev)
     order = [(rank + s) % world for s in range(world)]            # own block first, then ring order:
     arrived = {}                                                  # at every step each GPU serves one reader
-    copy_stream.wait_stream(main)                                 # feats_all exists, local block is ready
-    with torch.cuda.stream(copy_stream):
+    ex.copy_stream.wait_stream(main)
+    with torch.cuda.stream(ex.copy_stream):
         for src in order:
             a, b = ranges[src]
             if b > a:
-                feats_all[a:b].copy_(blocks[src], non_blocking=True)          # peer -> local over NVLink (DMA)
+                feats_all[a:b].copy_(ex.blocks[src][: b - a], non_blocking=True)   # peer -> local over NVLink (DMA)
             ev = torch.cuda.Event()
-            ev.record(copy_stream)
+            ev.record(ex.copy_stream)
             arrived[src] = ev
-    widest = max(b - a for a, b in ranges)
-    staged = ops.StagedKnn(n, d, k, kernel, (r0, r1), world, widest, positions=pos if lambda_g else None,
+    staged = ops.StagedKnn(n, d, k, kernel, (r0, r1), widest, positions=pos if lambda_g else None,
                            lambda_h=lambda_h, lambda_g=lambda_g, device=dev)
     for src in order:
         a, b = ranges[src]
-        main.wait_event(arrived[src])
         if b > a:
-            staged.add_panel(feats_all[a:b], a, b, src)
+            staged.add_panel(feats_all[a:b], a, b, ready=arrived[src])
     local = staged.finish(feats_all, return_cos=True)
-    feats_all.record_stream(copy_stream)
-    return local, feats_all, blocks
+    feats_all.record_stream(ex.copy_stream)
+    for st in staged.streams[1:]:
+        feats_all.record_stream(st)
+    return local, feats_all
 
 
 def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: int = 16, kernel: str = "gaussian",
@@ -155,7 +185,8 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     r0, r1 = ranges(n, rank, world)
     assert local_features.shape[0] == r1 - r0, "local block does not match the row partition"
     pos = positions if (positions is not None) else None
-    local = feats = peer_blocks = None
+    local = feats = None
+    overlapped = False
     all_have_rows = all(ranges(n, r, world)[1] > ranges(n, r, world)[0] for r in range(world))
     if overlap is None:                    # decided from facts every rank sees alike (collectives inside)
         overlap = aligned and knn_fn is None and local_features.is_cuda and all_have_rows and k <= 32
@@ -163,7 +194,8 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
         assert aligned and knn_fn is None, "the overlapped exchange needs row_range_aligned blocks"
         res = _knn_overlapped(local_features.contiguous(), n, k, kernel, lambda_h, lambda_g, pos, group)
         if res is not None:
-            local, feats, peer_blocks = res
+            local, feats = res
+            overlapped = True
     if local is None:
         feats = all_gather_rows(local_features, n, group, ranges)           # the one big collective
         with_cos = knn_fn is None          # an injected knn_fn returns (idx, val)
@@ -179,9 +211,7 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                 local += (torch.empty((0, k), dtype=torch.float32, device=feats.device),)
     idx_local, val_local = local[0], local[1]
     out = {"knn_idx": all_gather_rows(idx_local, n, group, ranges),
-           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": peer_blocks is not None}
-    # every rank is past its kNN here, i.e. has read its peers' blocks: the mappings can go
-    peer_blocks = None
+           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": overlapped}
     # cos(f_i, f_j) of every list entry travels with the lists: the edge weights are then looked up
     # instead of gathering two feature rows per edge
     knn_cos = all_gather_rows(local[2], n, group, ranges) if len(local) > 2 else None

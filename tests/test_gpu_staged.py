@@ -16,13 +16,13 @@ def _panels(n, width):
     return [(a, min(n, a + width)) for a in range(0, n, width)]
 
 
-def _run_staged(x, k, metric, rows, panels, order, pos=None, lambda_h=1.0, lambda_g=0.0, return_cos=True):
+def _run_staged(x, k, metric, rows, panels, order, pos=None, lambda_h=1.0, lambda_g=0.0, return_cos=True, lanes=2):
     n, d = x.shape
-    st = ops.StagedKnn(n, d, k, metric, rows, len(panels), max(b - a for a, b in panels), positions=pos,
-                       lambda_h=lambda_h, lambda_g=lambda_g, device=x.device)
+    st = ops.StagedKnn(n, d, k, metric, rows, max(b - a for a, b in panels), positions=pos,
+                       lambda_h=lambda_h, lambda_g=lambda_g, lanes=lanes, device=x.device)
     for p in order:
         a, b = panels[p]
-        st.add_panel(x[a:b], a, b, p)
+        st.add_panel(x[a:b], a, b)
     return st.finish(x, return_cos=return_cos)
 
 
@@ -30,7 +30,7 @@ def _run_staged(x, k, metric, rows, panels, order, pos=None, lambda_h=1.0, lambd
     (3000, 128, 8, "euclidean", 768, (768, 1536)),
     (5000, 256, 16, "gaussian", 1280, (1280, 2560)),
     (4097, 96, 16, "cosine", 1024, (4096, 4097)),          # last panel: one row, owned by this "rank"
-    (2600, 64, 32, "euclidean", 512, (512, 1024)),          # k = 32: 32-entry lists, 6 panels
+    (2600, 64, 32, "euclidean", 256, (512, 768)),           # k = 32: 32-entry lists, 11 panels
     (9000, 128, 5, "gaussian", 2304, (0, 2304)),
 ])
 def test_staged_equals_one_shot(n, d, k, metric, width, rows):
@@ -41,9 +41,9 @@ def test_staged_equals_one_shot(n, d, k, metric, width, rows):
     rng = np.random.default_rng(n)
     others = [i for i in range(len(panels)) if i != own]
     ref = ops.knn_feature(x, k, metric, rows=rows, return_cos=True)
-    for trial in range(2):
+    for trial in range(3):
         order = [own] + list(rng.permutation(others))
-        got = _run_staged(x, k, metric, rows, panels, order)
+        got = _run_staged(x, k, metric, rows, panels, order, lanes=(2, 1, 3)[trial])
         for g, r, name in zip(got, ref, ("idx", "val", "cos")):
             assert torch.equal(g, r), f"{name} differs (order {order})"
     # and against the float64 oracle on the row range
@@ -73,17 +73,15 @@ def test_staged_with_positions_and_missing_panel():
 def test_staged_argument_checks():
     n, d = 3000, 64
     x = _cuda(synth.make_features(n, d, 3, "gaussian"))
-    st = ops.StagedKnn(n, d, 8, "euclidean", (0, 1024), 3, 1024, device=x.device)
+    st = ops.StagedKnn(n, d, 8, "euclidean", (0, 1024), 1024, device=x.device)
     with pytest.raises(ValueError, match="first panel"):
-        st.add_panel(x[1024:2048], 1024, 2048, 1)
-    st.add_panel(x[0:1024], 0, 1024, 0)
+        st.add_panel(x[1024:2048], 1024, 2048)
+    st.add_panel(x[0:1024], 0, 1024)
     with pytest.raises(ValueError, match="multiples of 256"):
-        st.add_panel(x[1000:2000], 1000, 2000, 1)
+        st.add_panel(x[1000:2000], 1000, 2000)
     with pytest.raises(ValueError, match="multiples of 256"):
-        st.add_panel(x[1024:2000], 1024, 2000, 1)
+        st.add_panel(x[1024:2000], 1024, 2000)
     with pytest.raises(ValueError):
-        st.add_panel(x[1024:2048], 1024, 2048, 3)            # panel index out of range
+        st.add_panel(x[0:2048], 0, 2048)                     # wider than max_panel_cols
     with pytest.raises(ValueError):
-        st.add_panel(x[0:2048], 0, 2048, 1)                  # wider than max_panel_cols
-    with pytest.raises(ValueError):
-        ops.StagedKnn(n, d, 32, "euclidean", (0, 1024), 64, 1024, device=x.device)   # 64 panels x 32 candidates
+        ops.StagedKnn(n, d, 33, "euclidean", (0, 1024), 1024, device=x.device)       # tensor-core path: k <= 32

@@ -133,18 +133,35 @@ def main():
                  slides_per_s=512 / ms * 1e3, patches_per_s=tot / ms * 1e3,
                  e2e_ms_total=e2e_ms, e2e_slides_per_s=512 / e2e_ms * 1e3, e2e_patches_per_s=tot / e2e_ms * 1e3)
         elif cfg == "c5":
-            n, d, k = 250_000, 1536, 16
-            r0, r1 = multigpu.row_range(n, rank, world)
-            # every rank generates only its own row block (same generator, block-wise seeds)
-            local_feats = torch.from_numpy(synth.make_features(r1 - r0, d, 1239 + rank, "gaussian")).to(dev)
-            if world > 1:
-                fn = lambda: multigpu.knn_hyperedges_row_partitioned(local_feats, n, k=k, kernel="gaussian",   # noqa: E731
-                                                                     lambda_h=1.0, return_csr=True)
-            else:
+            n, d, k = int(os.environ.get("HG_BENCH_C5_N", 250_000)), 1536, 16
+            if world == 1:
+                local_feats = torch.from_numpy(synth.make_features(n, d, 1239, "gaussian")).to(dev)
                 fn = lambda: hg_b200.knn_hyperedges(local_feats, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True)   # noqa: E731
-            ms, kms = timed(fn, 2, warmup=1)
-            emit(config="c5", n=n, d=d, k=k, gpus=world, ms_per_slide=ms, tc_kernel_ms=kms, patches_per_s=n / ms * 1e3,
-                 tc_tflops_algorithmic_per_gpu=2.0 * (r1 - r0) * n * d / (kms * 1e-3) / 1e12)
+                ms, kms = timed(fn, 2, warmup=1)
+                emit(config="c5", n=n, d=d, k=k, gpus=1, ms_per_slide=ms, tc_kernel_ms=kms, patches_per_s=n / ms * 1e3)
+                continue
+            # every rank generates only its own row block (same generator, block-wise seeds); two partitions:
+            # near-equal blocks with gather-then-compute, 256-aligned blocks with the overlapped exchange.
+            # The modes alternate round by round on the same box (clocks drift under the power cap).
+            modes = {}
+            for mode, ranges in (("gather_then_compute", multigpu.row_range), ("overlapped", multigpu.row_range_aligned)):
+                r0, r1 = ranges(n, rank, world)
+                modes[mode] = dict(rows=r1 - r0, aligned=mode == "overlapped", ms=[], kms=[], out=None,
+                                   feats=torch.from_numpy(synth.make_features(r1 - r0, d, 1239 + rank, "gaussian")).to(dev))
+            for rnd in range(int(os.environ.get("HG_BENCH_C5_ROUNDS", 3))):
+                for mode, m in modes.items():
+                    def fn():
+                        m["out"] = multigpu.knn_hyperedges_row_partitioned(
+                            m["feats"], n, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True, aligned=m["aligned"])
+                    ms, kms = timed(fn, 3, warmup=2 if rnd == 0 else 1)
+                    m["ms"].append(ms)
+                    m["kms"].append(kms)
+            for mode, m in modes.items():
+                ms, kms = float(np.median(m["ms"])), float(np.median(m["kms"]))
+                emit(config="c5", mode=mode, overlapped=bool(m["out"]["overlapped"]), n=n, d=d, k=k, gpus=world,
+                     rows_rank0=m["rows"], ms_per_slide=ms, ms_rounds=m["ms"], patches_per_s=n / ms * 1e3,
+                     tc_kernel_ms_sum=kms,
+                     note="tc_kernel_ms_sum adds up the launches' own durations; overlapped sweeps run side by side")
     if world > 1:
         dist.destroy_process_group()
 
