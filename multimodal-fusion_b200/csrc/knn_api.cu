@@ -281,6 +281,10 @@ static int staged_plan(const hg_knn_staged* s, StagedWs* w) {
     w->kl = probe.kl;
     w->lanes = s->num_lanes < 1 ? 1 : s->num_lanes;
     w->spp = tc_panel_splits(s->max_panel_cols, w->n_rows, s->k, w->d_pad, TC_MAX_SPLITS);
+    if (const char* e = getenv("HG_B200_STAGED_SPP")) {          // tuning override: list slots per sweep
+        const int v = atoi(e);
+        if (v >= 1 && v <= TC_MAX_SPLITS) w->spp = v;
+    }
     // the re-rank merges at most 768 list candidates per row
     while (w->spp > 1 && w->lanes * w->spp * w->kl > 768) --w->spp;
     HG_REQUIRE(w->lanes * w->spp * w->kl <= 768, HG_ERR_UNSUPPORTED, "hg_knn_staged: too many lanes (%d)", w->lanes);

@@ -553,25 +553,17 @@ TcPlan tc_make_plan_panel(int64_t panel_cols, int64_t n_rows, int k, int64_t d_p
     return pl;
 }
 
-// splits per panel in [1, max_splits]: the best last-round fill, mildly preferring counts whose cc
-// keeps the concurrently swept A blocks under the L2 budget
+// List slots per sweep in [1, max_splits].  A slide swept in P launches pays the ragged end of a launch
+// P times (the CTAs run out of units at different moments, about half a unit of idle SMs per launch),
+// so panels want SHORT units: the largest power of two that still leaves >= 8 column tiles per unit
+// (measured at 8 panels of 31k columns, D = 1536: 8 slots +2 % over the one-shot call, 4 slots +8 %,
+// 2 slots +9 %; profiles/r01_staged_panels_slots.log).
 int tc_panel_splits(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int max_splits) {
-    const int cl = (tc_cta_group() == 2 || tc_multicast()) ? 2 : 1;
-    const int workers = kNumSMs / cl;
-    const int major = int(ceil_div(n_rows, TC_BM * cl)), tiles = int(ceil_div(panel_cols, TC_BN));
-    const int64_t rc_cap = (int64_t(40) << 20) / (int64_t(TC_BM * cl) * d_pad * 4);
-    int best = 1;
-    double best_eff = -1.0;
-    for (int s = 1; s <= max_splits && s <= TC_MAX_SPLITS; ++s) {
-        if (s > tiles && s > 1) break;
-        const int64_t units = int64_t(major) * s;
-        const double fill = double(tiles) / double(ceil_div(tiles, s) * s);
-        double eff = fill * double(units) / double(ceil_div(units, workers) * workers);
-        if (workers / panel_cc(s, cl, d_pad) > rc_cap) eff *= 0.93;
-        if (eff > best_eff + 0.015) { best_eff = eff; best = s; }
-    }
-    (void)k;
-    return best;
+    const int tiles = int(ceil_div(panel_cols, TC_BN));
+    int s = 1;
+    while (s * 2 <= max_splits && s * 2 <= TC_MAX_SPLITS && tiles / (s * 2) >= 8) s *= 2;
+    (void)n_rows; (void)k; (void)d_pad;
+    return s;
 }
 
 // Threshold pre-pass: all rows against every stride-th column.  One unit per row block when the A

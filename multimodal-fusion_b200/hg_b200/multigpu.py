@@ -16,6 +16,7 @@ is backend-agnostic so world_size-2 gloo tests cover it on CPU with the kNN stag
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, List, Optional, Sequence, Tuple
 
 import torch
@@ -176,9 +177,9 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                                    knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None) -> dict:
     """Config C5: `local_features` is this rank's row block [r1-r0, D] (`row_range`, or
     `row_range_aligned` with aligned=True); `positions` (replicated, [n, 2|3]) is small.  Returns
-    the same dict as `knn_hyperedges` on every rank.  With aligned blocks on CUDA the exchange of
-    the feature blocks overlaps the fused kernel (overlap=False forces gather-then-compute); the
-    dict then also carries "overlapped": True."""
+    the same dict as `knn_hyperedges` on every rank.  overlap=True (aligned blocks on CUDA only):
+    the peers' feature blocks are pulled over NVLink while the fused kernel sweeps the blocks that are
+    already here (staged kNN, same result bit for bit); "overlapped" in the dict says whether it ran."""
     from . import ops
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     ranges = row_range_aligned if aligned else row_range
@@ -188,10 +189,14 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     local = feats = None
     overlapped = False
     all_have_rows = all(ranges(n, r, world)[1] > ranges(n, r, world)[0] for r in range(world))
-    if overlap is None:                    # decided from facts every rank sees alike (collectives inside)
+    if overlap is None:
+        # measured on 8 B200 at C5 the overlapped exchange is not faster (57.1 vs 56.2 ms: the fused kernel
+        # is power-bound, sweeping 8 panels costs 2-3 % more than one launch and the exchange it hides is
+        # ~1 ms), so gather-then-compute stays the default; HG_B200_OVERLAP=1 or overlap=True turns it on
+        overlap = os.environ.get("HG_B200_OVERLAP", "0") == "1"
+    if overlap:                            # decided from facts every rank sees alike (collectives inside)
         overlap = aligned and knn_fn is None and local_features.is_cuda and all_have_rows and k <= 32
     if overlap:
-        assert aligned and knn_fn is None, "the overlapped exchange needs row_range_aligned blocks"
         res = _knn_overlapped(local_features.contiguous(), n, k, kernel, lambda_h, lambda_g, pos, group)
         if res is not None:
             local, feats = res

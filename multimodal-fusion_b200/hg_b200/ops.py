@@ -55,13 +55,13 @@ class StagedKnn:
     handed over panel by panel (hg_knn_staged_*): the row-partitioned multi-GPU path feeds it the
     peers' row blocks as they arrive.  Panel boundaries are multiples of 256 (the last ends at n);
     the panel holding the query rows goes first.  Panels alternate between `lanes` list-slot sets,
-    each on its own stream, so the next panel's sweep fills the SMs the previous one's tail leaves
-    idle.  finish() returns what knn_feature(rows=...) does, on the stream that was current at
+    each on its own stream (measured: no gain over one lane, which is the default; short work units
+    are what keeps the ragged end of every sweep small).  finish() returns what knn_feature(rows=...) does, on the stream that was current at
     construction."""
 
     def __init__(self, n: int, d: int, k: int, metric: str, rows: Tuple[int, int],
                  max_panel_cols: int, positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0,
-                 lambda_g: float = 0.0, exclude_self: bool = True, lanes: int = 2, device=None):
+                 lambda_g: float = 0.0, exclude_self: bool = True, lanes: int = 1, device=None):
         self.lib = L.load_library()
         self.dev = L.require_cuda(device)
         self.pos = L.f32c(positions, self.dev) if positions is not None else None

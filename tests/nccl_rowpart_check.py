@@ -34,14 +34,14 @@ def main():
     # 256-aligned row blocks: peers' blocks pulled over NVLink while the fused kernel sweeps the ones that
     # are here (staged kNN); same result bit for bit, with and without the overlap
     a0, a1 = multigpu.row_range_aligned(n, rank, world)
-    for overlap in (None, False):
+    for overlap in (True, False):
         out = multigpu.knn_hyperedges_row_partitioned(x[a0:a1].contiguous(), n, k=k, kernel="gaussian", lambda_h=1.0,
                                                       lambda_g=lam_g, positions=p, spatial_k=8, return_csr=True,
                                                       aligned=True, overlap=overlap)
         for key in ("knn_idx", "knn_val", "spatial_idx", "spatial_d2", "edge_index", "edge_weights", "csr_rowptr",
                     "csr_col", "csr_eid"):
             assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, overlap={overlap})"
-        if overlap is None:
+        if overlap:
             overlapped = out["overlapped"]
     dist.barrier()
     if rank == 0:
