@@ -59,6 +59,7 @@ def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: 
         L.check(lib.hg_kmeans_workspace_bytes(d, n_clusters, C.byref(nbytes)))
         ws = L.Workspace.get(dev, nbytes.value, "kmeans")
         labels = torch.empty(n, dtype=torch.int32, device=dev)
+        prev = torch.empty(n, dtype=torch.int32, device=dev)
         d2 = torch.empty(n, dtype=torch.float32, device=dev)
         scal = torch.zeros(2, dtype=torch.float64, device=dev)          # [shift^2, inertia]
         best = None
@@ -66,12 +67,17 @@ def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: 
             gen = torch.Generator(device=dev)
             gen.manual_seed(seed + 1000003 * run)
             centers = _kmeanspp(lib, x, n_clusters, gen, st)
+            prev.fill_(-1)
             for _ in range(max_iter):
                 L.check(lib.hg_kmeans_assign(L.ptr(x), n, d, L.ptr(centers), n_clusters, L.ptr(labels), L.ptr(d2), st))
                 L.check(lib.hg_kmeans_update(L.ptr(x), n, d, L.ptr(labels), n_clusters, L.ptr(centers),
                                              scal.data_ptr(), None, L.ptr(ws), nbytes.value, st))
-                if float(scal[0]) <= tol_abs:
+                # one read-back per iteration: centre shift (scikit-learn's tol test) and whether any label
+                # moved (its strict-convergence test, which is what ends runs on nearly constant data)
+                shift, moved = torch.stack([scal[0], (labels != prev).sum().double()]).tolist()
+                if shift <= tol_abs or moved == 0:
                     break
+                prev.copy_(labels)
             L.check(lib.hg_kmeans_assign(L.ptr(x), n, d, L.ptr(centers), n_clusters, L.ptr(labels), L.ptr(d2), st))
             L.check(lib.hg_kmeans_inertia(L.ptr(d2), n, scal.data_ptr() + 8, st))
             inertia = float(scal[1])

@@ -30,10 +30,32 @@ ATTRS_KEY = "__attrs__"
 
 
 class Dataset:
-    """Read-only view of one stored array (what ``group[name]`` returns for a leaf)."""
+    """Read-only view of one stored array (what ``group[name]`` returns for a leaf).  Arrays of a file
+    opened from disk are read on first access only: loading ``tma/features`` does not pull a stored
+    N x N similarity matrix through memory."""
 
-    def __init__(self, arr: np.ndarray):
-        self._arr = arr
+    def __init__(self, arr: Optional[np.ndarray] = None, source=None, key: Optional[str] = None):
+        self._data = arr
+        self._source, self._key = source, key          # lazily read member `key`.npy of an open archive
+
+    @property
+    def loaded(self) -> bool:
+        return self._data is not None
+
+    @property
+    def _arr(self) -> np.ndarray:
+        if self._data is None:
+            self._data = self._source[self._key]
+        return self._data
+
+    def _header(self):
+        if self._data is not None:
+            return self._data.shape, self._data.dtype
+        with self._source.zip.open(self._key + ".npy") as fh:
+            version = np.lib.format.read_magic(fh)
+            reader = np.lib.format.read_array_header_1_0 if version == (1, 0) else np.lib.format.read_array_header_2_0
+            shape, _, dtype = reader(fh)
+        return shape, dtype
 
     def __getitem__(self, key):
         return self._arr[key]
@@ -42,15 +64,15 @@ class Dataset:
         return self._arr if dtype is None else self._arr.astype(dtype)
 
     def __len__(self):
-        return len(self._arr)
+        return self._header()[0][0]
 
     @property
     def shape(self):
-        return self._arr.shape
+        return self._header()[0]
 
     @property
     def dtype(self):
-        return self._arr.dtype
+        return self._header()[1]
 
 
 class Attrs(dict):
@@ -178,7 +200,7 @@ class Group:
                 groups.append(path)
                 v._flatten(arrays, attrs, groups)
             else:
-                arrays[path] = v._arr
+                arrays[path] = v
 
 
 class NpzFile(Group):
@@ -196,6 +218,7 @@ class NpzFile(Group):
         self._dirty = False
         self._closed = False
         self._loading = True
+        self._zip = None
         super().__init__(self, "")
         exists = os.path.exists(self.path)
         if mode in ("r", "r+") and not exists:
@@ -218,30 +241,46 @@ class NpzFile(Group):
             self._dirty = True
 
     def _load(self):
-        with np.load(self.path, allow_pickle=False) as z:
-            meta = json.loads(str(z[ATTRS_KEY][()])) if ATTRS_KEY in z.files else {"attrs": {}, "groups": []}
-            for g in meta.get("groups", []):
-                self.require_group(g)
-            for key in z.files:
-                if key == ATTRS_KEY:
-                    continue
-                self[key] = z[key]
-            for gname, kv in meta.get("attrs", {}).items():
-                node = self if gname == "" else self.require_group(gname)
-                for k, v in kv.items():
-                    node.attrs[k] = v
+        self._zip = np.load(self.path, allow_pickle=False)          # members are read on demand
+        z = self._zip
+        meta = json.loads(str(z[ATTRS_KEY][()])) if ATTRS_KEY in z.files else {"attrs": {}, "groups": []}
+        for g in meta.get("groups", []):
+            self.require_group(g)
+        for key in z.files:
+            if key == ATTRS_KEY:
+                continue
+            parts = [p for p in key.split("/") if p]
+            parent = self
+            for p in parts[:-1]:
+                parent = parent.require_group(p)
+            parent._items[parts[-1]] = Dataset(source=z, key=key)
+        for gname, kv in meta.get("attrs", {}).items():
+            node = self if gname == "" else self.require_group(gname)
+            for k, v in kv.items():
+                node.attrs[k] = v
 
     def flush(self):
         if not self._dirty or self.mode == "r":
             return
-        arrays, attrs, groups = {}, {}, []
-        self._flatten(arrays, attrs, groups)
-        arrays[ATTRS_KEY] = np.array(json.dumps({"attrs": attrs, "groups": groups}))
+        import shutil
+        import zipfile
+        datasets, attrs, groups = {}, {}, []
+        self._flatten(datasets, attrs, groups)
         directory = os.path.dirname(os.path.abspath(self.path))
         fd, tmp = tempfile.mkstemp(prefix=".hg_b200_", suffix=".npz", dir=directory)
         try:
-            with os.fdopen(fd, "wb") as fh:
-                np.savez(fh, **arrays)
+            with os.fdopen(fd, "wb") as raw, zipfile.ZipFile(raw, "w", zipfile.ZIP_STORED, allowZip64=True) as out:
+                def put(name, arr):
+                    with out.open(name + ".npy", "w", force_zip64=True) as fh:
+                        np.lib.format.write_array(fh, np.asanyarray(arr), allow_pickle=False)
+                for name, ds in datasets.items():
+                    if ds.loaded:
+                        put(name, ds._arr)
+                    else:                                          # untouched member: copy its bytes as they are
+                        with ds._source.zip.open(ds._key + ".npy") as fi, \
+                                out.open(name + ".npy", "w", force_zip64=True) as fo:
+                            shutil.copyfileobj(fi, fo, 1 << 24)
+                put(ATTRS_KEY, np.array(json.dumps({"attrs": attrs, "groups": groups})))
             os.replace(tmp, self.path)
         except BaseException:
             if os.path.exists(tmp):
@@ -249,10 +288,17 @@ class NpzFile(Group):
             raise
         self._dirty = False
 
+    def _release(self):
+        if self._zip is not None:
+            # arrays handed out stay valid (they are copies); unread members can no longer be read
+            self._zip.close()
+            self._zip = None
+        self._closed = True
+
     def close(self):
         if not self._closed:
             self.flush()
-            self._closed = True
+            self._release()
 
     def __enter__(self):
         return self
@@ -261,7 +307,7 @@ class NpzFile(Group):
         if exc_type is None:
             self.close()
         else:                               # leave the file on disk as it was
-            self._closed = True
+            self._release()
         return False
 
 

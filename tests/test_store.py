@@ -111,3 +111,28 @@ def test_export_and_import_h5(tmp_path, monkeypatch):
     store.import_from_h5(h5, only, groups=["wsi"])
     with store.NpzFile(only, "r") as f:
         assert sorted(f.keys()) == ["wsi"]
+
+
+def test_members_are_read_on_demand_and_copied_untouched(tmp_path):
+    path = str(tmp_path / "slide.npz")
+    big = np.random.default_rng(0).standard_normal((300, 300)).astype(np.float32)
+    with store.NpzFile(path, "w") as f:
+        f.require_group("hypergraph/similarity")["wsi_internal"] = big
+        f.require_group("tma")["features"] = np.ones((3, 4), dtype=np.float32)
+    with store.NpzFile(path, "r") as f:
+        node = f["hypergraph/similarity/wsi_internal"]
+        assert node.shape == (300, 300) and node.dtype == np.float32 and len(node) == 300   # header only
+        assert not node.loaded
+        assert f["tma"]["features"][:].sum() == 12 and not node.loaded
+    with store.NpzFile(path, "a") as f:                       # replace a small dataset: the big one is never parsed
+        del f["tma"]["features"]
+        f["tma"]["features"] = np.zeros((2, 2), dtype=np.float32)
+        node = f["hypergraph/similarity/wsi_internal"]
+    assert not node.loaded
+    with pytest.raises(Exception):
+        node[:]                                               # the file is closed, like an h5py dataset
+    with store.NpzFile(path, "r") as f:
+        assert np.array_equal(f["hypergraph/similarity/wsi_internal"][:], big)
+        assert f["tma/features"].shape == (2, 2)
+    with np.load(path) as z:                                  # still a plain numpy archive
+        assert np.array_equal(z["hypergraph/similarity/wsi_internal"], big)
