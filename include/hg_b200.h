@@ -199,8 +199,8 @@ int hg_threshold_workspace_bytes(int64_t n, size_t* bytes);
 
 /* ---- row (f)1, "next": KMeans building blocks (Lloyd assign / update, kmeans++ distances) -------
  * Replace sklearn.cluster.KMeans at preprocess_hypergraph.py:150-151, 299-300, 391-392; the
- * driver loop (n_init restarts, kmeans++ seeding, tolerance) is hg_b200/kmeans.py.  Parity with
- * scikit-learn is statistical (inertia), not label-exact. */
+ * estimator itself (n_init restarts, kmeans++ seeding, tolerance) is hg_kmeans_fit below.  Parity
+ * with scikit-learn is statistical (inertia), not label-exact. */
 int hg_kmeans_assign(const float* x, int64_t n, int64_t d, const float* centroids, int c,
                      int32_t* labels, float* d2, void* stream);
 int hg_kmeans_workspace_bytes(int64_t d, int c, size_t* bytes);
@@ -210,6 +210,18 @@ int hg_kmeans_update(const float* x, int64_t n, int64_t d, const int32_t* labels
 int hg_kmeans_inertia(const float* d2, int64_t n, double* inertia, void* stream);
 int hg_kmeans_candidate_d2(const float* x, int64_t n, int64_t d, const int64_t* cand, int t,
                            float* out, void* stream);
+/* The whole estimator in one call: KMeans(n_clusters=c, n_init, max_iter, tol, random_state=seed)
+ * .fit(x) as the reference constructs it (scikit-learn defaults: greedy k-means++ with 2 + ln(c) local
+ * trials, Lloyd until no label moves or the squared centre shift is <= tol * mean(var(x)), best restart
+ * by inertia).  Seeding, iterations and the choice of the best restart stay on the device; the host
+ * polls one flag every few iterations, so the call blocks on `stream`.  Every sum runs in a fixed
+ * order: the same seed gives the same labels bit for bit.  labels [n] int32, centroids [c, d] float,
+ * inertia (double) and n_iter (int32, may be NULL; iterations of the winning restart) are device
+ * buffers.  HG_ERR_BAD_ARG when n < c (scikit-learn's ValueError text in hg_last_error). */
+int hg_kmeans_fit_workspace_bytes(int64_t n, int64_t d, int c, size_t* bytes);
+int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_init, int max_iter, double tol,
+                  uint64_t seed, int32_t* labels, float* centroids, double* inertia, int32_t* n_iter,
+                  void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- one call per slide: A4 (+A3) -> A5 -> A6 -> CSR ---------------------------------------
  * The body of build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433) on one stream with

@@ -695,7 +695,10 @@ static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
     return p.pos4 ? launch_one<KL, true, 1, false>(ta, tb, p, st) : launch_one<KL, false, 1, false>(ta, tb, p, st);
 }
 
-int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cudaStream_t st) {
+// ops_a / ops_b: operand buffers behind the query rows and the candidate columns -- the same buffer for a
+// slide's self-kNN, two buffers for a rectangular product (rows of one matrix against another's)
+static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops, int64_t n_pad,
+                          const TcParams& p_in, cudaStream_t st) {
     TcParams p = p_in;
     p.n_pad = n_pad;
     // A row blocks are re-read for every column tile (keep them), B tiles stream through.
@@ -707,6 +710,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
     // HG_B200_TC_PAIR=0 refills stage by stage.
     p.pair_stages = 1;
     if (const char* e = getenv("HG_B200_TC_PAIR")) p.pair_stages = atoi(e) != 0 ? 1 : 0;
+    if (ops_a != ops) { p.hint_a = ptx::kEvictNormal; p.hint_b = ptx::kEvictLast; }   // rectangular: the (small) B side is the reused one
     if (const char* e = getenv("HG_B200_TC_HINTS")) {
         auto pick = [](char c, uint64_t dflt) {
             return c == 'n' ? ptx::kEvictNormal : c == 'f' ? ptx::kEvictFirst : c == 'l' ? ptx::kEvictLast : dflt;
@@ -724,7 +728,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
     CUtensorMap ta, tb;
     HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.col_stride > 1), HG_ERR_BAD_ARG,
                "tc_launch: the hi-only product is for the threshold pre-pass");
-    int rc = make_tmap(&ta, ops, n_pad, p.d_pad, TC_BM, 1);
+    int rc = make_tmap(&ta, ops_a, n_pad_a, p.d_pad, TC_BM, 1);
     if (rc != HG_OK) return rc;
     rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cl, p.col_stride);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
@@ -738,6 +742,37 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p_in, cud
     }
     set_error("tc_launch: unsupported list length %d", p.plan.kl);
     return HG_ERR_UNSUPPORTED;
+}
+
+int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
+    return tc_launch_impl(ops, n_pad, ops, n_pad, p, st);
+}
+
+// Rows of matrix A (p.row_begin .. p.row_end) against the p.n rows of matrix B: classic list mode only.
+// p.colp / p.n describe B; nothing is excluded by index.
+int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
+                   const TcParams& p, cudaStream_t st) {
+    HG_REQUIRE(ops_a != ops_b && !p.plan.sym && p.plan.cl == 1 && p.plan.kl > 0 && !p.exclude_self && !p.pos4 &&
+               !p.thr_out && !p.carry && p.ct_base == 0 && p.col_stride <= 1 && p.row_end <= n_pad_a,
+               HG_ERR_BAD_ARG, "tc_launch_rect: classic list mode without positions only");
+    return tc_launch_impl(ops_a, n_pad_a, ops_b, n_pad_b, p, st);
+}
+
+// One unit per 128-row block sweeping every column tile: the B side is small (centres), every A block is
+// used once per column tile, so neither column splits nor an L2 chunking of the rows buy anything.
+TcPlan tc_make_plan_rect(int64_t cols, int64_t n_rows, int k, int64_t d_pad) {
+    TcPlan pl{};
+    pl.cg = 1; pl.mc = 0; pl.cl = 1;
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(cols, TC_BN));
+    pl.kl = list_len(k);
+    pl.cc = 1; pl.rc = kNumSMs; pl.splits = 1;
+    pl.ct_per_split = pl.num_ct;
+    pl.grid = int(min64(kNumSMs, pl.num_rb));
+    (void)d_pad;
+    return pl;
 }
 
 }  // namespace hg

@@ -80,6 +80,10 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride);
 int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride
 constexpr int TC_BKT_CAP = 512;
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
+// rectangular product (kmeans.cu): rows of A against the rows of another matrix B, classic list mode
+TcPlan tc_make_plan_rect(int64_t cols, int64_t n_rows, int k, int64_t d_pad);
+int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
+                   const TcParams& p, cudaStream_t st);
 
 struct RerankParams {
     const float* feats; int64_t n, d;

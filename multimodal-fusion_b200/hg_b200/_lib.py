@@ -71,6 +71,8 @@ SIGNATURES = {
     "hg_kmeans_update": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_kmeans_inertia": (_i32, [_vp, _i64, _vp, _vp]),
     "hg_kmeans_candidate_d2": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp]),
+    "hg_kmeans_fit_workspace_bytes": (_i32, [_i64, _i64, _i32, _psz]),
+    "hg_kmeans_fit": (_i32, [_vp, _i64, _i64, _i32, _i32, _i32, C.c_double, C.c_uint64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_build_workspace_bytes": (_i32, [_i64, _i64, _i32, _i32, _i32, _i64, _i64, _i32, _psz]),
     "hg_build_knn_hypergraph": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i32, _vp, _i32, _i64,
                                        _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _pi64, _vp, _sz, _vp]),

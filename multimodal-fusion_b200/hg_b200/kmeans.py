@@ -1,5 +1,7 @@
-"""KMeans on the GPU (scope row (f)1, "next"): the driver loop around the C-ABI building blocks
-hg_kmeans_assign / hg_kmeans_update / hg_kmeans_candidate_d2.
+"""KMeans on the GPU (scope row (f)1, "next"): `kmeans` is one C-ABI call (hg_kmeans_fit: seeding,
+Lloyd iterations and the choice of the best restart stay on the device, deterministic for a seed);
+`kmeans_stepwise` is the same estimator driven from Python over the building blocks
+hg_kmeans_assign / hg_kmeans_update / hg_kmeans_candidate_d2 (kept for tests and tuning).
 
 Mirrors the estimator the reference constructs at preprocess_hypergraph.py:150, :299, :391 --
 ``KMeans(n_clusters, random_state=42, n_init=10)`` with scikit-learn's defaults: greedy
@@ -46,6 +48,28 @@ def _kmeanspp(lib, x, n_clusters: int, gen: torch.Generator, st) -> torch.Tensor
 def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: int = 300, tol: float = 1e-4,
            seed: int = 42, device=None) -> Tuple[np.ndarray, torch.Tensor, float]:
     """Returns (labels int64 numpy [n], centers float32 CUDA [k, d], inertia)."""
+    lib = L.load_library()
+    dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
+    x = L.f32c(features, dev)
+    n, d = x.shape
+    with torch.cuda.device(dev):
+        nbytes = C.c_size_t(0)
+        L.check(lib.hg_kmeans_fit_workspace_bytes(n, d, int(n_clusters), C.byref(nbytes)))
+        ws = L.Workspace.get(dev, nbytes.value, "kmeans_fit")
+        labels = torch.empty(n, dtype=torch.int32, device=dev)
+        centers = torch.empty((int(n_clusters), d), dtype=torch.float32, device=dev)
+        inertia = torch.zeros(1, dtype=torch.float64, device=dev)
+        n_iter = torch.zeros(1, dtype=torch.int32, device=dev)
+        L.check(lib.hg_kmeans_fit(L.ptr(x), n, d, int(n_clusters), int(n_init), int(max_iter), float(tol),
+                                  int(seed) & 0xFFFFFFFFFFFFFFFF, L.ptr(labels), L.ptr(centers), L.ptr(inertia),
+                                  L.ptr(n_iter), L.ptr(ws), nbytes.value, L.stream_ptr(dev)))
+        out = labels.cpu().numpy().astype(np.int64)
+    return out, centers, float(inertia.item())
+
+
+def kmeans_stepwise(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: int = 300, tol: float = 1e-4,
+                    seed: int = 42, device=None) -> Tuple[np.ndarray, torch.Tensor, float]:
+    """The same estimator as a Python loop over the building blocks (torch RNG; one read-back per iteration)."""
     lib = L.load_library()
     dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
     x = L.f32c(features, dev)

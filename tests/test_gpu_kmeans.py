@@ -71,3 +71,73 @@ def test_pipeline_with_cuda_kmeans(monkeypatch):
     tma = torch.from_numpy(synth.make_features(80, d, 74, "gaussian")).cuda()
     ei, w, st = pp.build_hypergraph_knn_kmeans(sf, tma, np.zeros(12), k=3, num_hyperedges=4)
     assert ei.shape[0] == 2 and w.shape[0] == ei.shape[1] == st["num_edges"]
+
+
+def _check_fit_consistent(x, labels, centers, inertia, c):
+    """labels are the nearest returned centre (up to FP32 near-ties) and the inertia matches them"""
+    cen = centers.cpu().numpy().astype(np.float64)
+    full = ((x[:, None, :].astype(np.float64) - cen[None]) ** 2).sum(-1)
+    best = full.min(1)
+    own = full[np.arange(len(x)), labels]
+    assert (own <= best + 1e-5 * np.maximum(1.0, best)).all()
+    assert np.isclose(inertia, own.sum(), rtol=1e-4, atol=1e-4)   # FP32 expansion-form distances near zero
+    assert labels.min() >= 0 and labels.max() < c
+
+
+@pytest.mark.parametrize("n,d,c", [(100, 256, 10), (356, 1024, 10), (3000, 67, 33), (40000, 64, 100), (64, 5, 64),
+                                   (500, 3, 1), (2000, 40, 300)])
+@pytest.mark.parametrize("assign", ["simt", "tc"])
+def test_native_fit_is_consistent_and_reproducible(n, d, c, assign, monkeypatch):
+    # Lloyd assignment on the FP32 SIMT kernel or on the tcgen05 kernel (rectangular launch + exact pick)
+    monkeypatch.setenv("HG_B200_KMEANS_TC", "1" if assign == "tc" else "0")
+    x = synth.make_features(n, d, 75, "gaussian")
+    xd = torch.from_numpy(x).cuda()
+    l1, c1, i1 = kmeans(xd, c, n_init=3, seed=7)
+    l2, c2, i2 = kmeans(xd, c, n_init=3, seed=7)
+    assert (l1 == l2).all() and torch.equal(c1, c2) and i1 == i2        # every sum runs in a fixed order
+    _check_fit_consistent(x, l1, c1, i1, c)
+    if n > c > 1:
+        l3, _, i3 = kmeans(xd, c, n_init=3, seed=8)
+        assert np.isfinite(i3)
+        # a converged Lloyd fit: every non-empty centre is the mean of its members
+        cen = c1.cpu().numpy()
+        for k in np.unique(l1)[:8]:
+            np.testing.assert_allclose(cen[k], x[l1 == k].astype(np.float64).mean(0), rtol=2e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("assign", ["simt", "tc"])
+def test_native_fit_matches_stepwise_quality_and_edge_cases(assign, monkeypatch):
+    from hg_b200.kmeans import kmeans_stepwise
+    monkeypatch.setenv("HG_B200_KMEANS_TC", "1" if assign == "tc" else "0")
+    x = synth.make_features(5000, 96, 76, "gaussian")
+    xd = torch.from_numpy(x).cuda()
+    _, _, native = kmeans(xd, 20, n_init=4, seed=1)
+    _, _, step = kmeans_stepwise(xd, 20, n_init=4, seed=1)
+    assert abs(native - step) <= 0.02 * step                            # different RNG streams, same estimator
+    with pytest.raises(ValueError, match="should be >= n_clusters"):
+        kmeans(xd[:5], 6)
+    # constant data: all distances are zero, one restart ends on the first "no label moved" test
+    const = torch.ones(300, 16, device="cuda")
+    labels, centers, inertia = kmeans(const, 4, n_init=2)
+    assert inertia == 0.0 and (labels == labels[0]).all()
+    # duplicated points and max_iter = 1
+    dup = torch.from_numpy(np.repeat(x[:50], 10, axis=0)).cuda()
+    labels, centers, inertia = kmeans(dup, 50, n_init=1, max_iter=1)
+    _check_fit_consistent(np.repeat(x[:50], 10, axis=0), labels, centers, inertia, 50)
+
+
+def test_both_assignment_paths_agree():
+    """same seed, same seeding (it does not depend on the assignment path): the two Lloyd loops may only
+    part ways at FP32 near-ties, so the inertias agree closely"""
+    import os
+    x = synth.make_features(20000, 256, 77, "gaussian")
+    xd = torch.from_numpy(x).cuda()
+    res = {}
+    for tc in ("0", "1"):
+        os.environ["HG_B200_KMEANS_TC"] = tc
+        try:
+            res[tc] = kmeans(xd, 50, n_init=2, seed=3)
+        finally:
+            os.environ.pop("HG_B200_KMEANS_TC")
+    assert abs(res["0"][2] - res["1"][2]) <= 2e-3 * res["0"][2]
+    assert (res["0"][0] == res["1"][0]).mean() > 0.9

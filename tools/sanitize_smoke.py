@@ -48,5 +48,9 @@ cl = hg_b200.knn_hyperedges(x, k=4, kernel="cosine", labels=labels, num_hyperedg
 K = hg_b200.compute_combined_similarity(x[:300], p[:300], 1.0, 1.0 / 128)
 ops.similarity_stats(K)
 hg_b200.build_weighted_hypergraph(x[:200], p[:200], 1.0, 1.0 / 128, 1.0)
+from hg_b200.kmeans import kmeans
+for kn, kd, kc in [(700, 96, 7), (300, 33, 40)]:
+    lab, cen, inertia = kmeans(x[:kn, :kd].contiguous(), kc, n_init=2, max_iter=20)
+    assert lab.min() >= 0 and lab.max() < kc and np.isfinite(inertia)
 torch.cuda.synchronize()
 print("sanitize_smoke ok")
