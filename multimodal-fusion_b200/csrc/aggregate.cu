@@ -41,6 +41,13 @@ __global__ void agg_bounds_kernel(const uint64_t* __restrict__ sorted_keys, int6
     }
 }
 
+int launch_cluster_bounds(const uint64_t* sorted_keys, int64_t n, int num_clusters, uint32_t* start, cudaStream_t st) {
+    agg_bounds_kernel<<<int(min64(ceil_div(n + 1, 256), int64_t(kNumSMs) * 8)), 256, 0, st>>>(sorted_keys, n, num_clusters, start);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
 // partial[z][c][col] = sum of feats[row][col] over slice z of cluster c's members (ascending row order).
 // grid (S, ceil(D / 256), split); the column block is one coalesced 1 KB read per member row.
 __global__ void __launch_bounds__(AG_THREADS)

@@ -11,6 +11,7 @@
 #include "sim_simt.cuh"
 #include "knn_tc.cuh"
 #include "rowdot.cuh"
+#include "sort_scan.cuh"
 #include <algorithm>
 #include <stdlib.h>
 
@@ -110,7 +111,7 @@ kmeans_candidate_d2_kernel(const float* __restrict__ x, int64_t n, int64_t d, co
 // The same distances for the one-call fit: the (few) candidate rows are staged in shared memory once per
 // CTA, every row of x is read once with 128-bit loads, packed FP32 pairs.  HBM-bound: 4 d bytes per row.
 template <int TMAX>
-__global__ void __launch_bounds__(256, TMAX <= 8 ? 4 : 2)
+__global__ void __launch_bounds__(256, TMAX <= 8 ? 3 : 1)
 km_cand_d2_smem_kernel(const float* __restrict__ x, int64_t n, int64_t d, const int64_t* __restrict__ cand, int t,
                        int64_t rows_per_block, float* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char km_smem_raw[];
@@ -123,26 +124,44 @@ km_cand_d2_smem_kernel(const float* __restrict__ x, int64_t n, int64_t d, const 
     }
     __syncthreads();
     const int64_t r0 = int64_t(blockIdx.x) * rows_per_block, r1 = min64(n, r0 + rows_per_block);
-    for (int64_t r = r0 + warp; r < r1; r += 8) {
-        uint64_t acc[TMAX];
+    // a warp takes two rows per pass: every candidate value read from shared memory serves both
+    for (int64_t r = r0 + 2 * warp; r < r1; r += 16) {
+        const bool two = r + 1 < r1;
+        uint64_t acc0[TMAX], acc1[TMAX];
 #pragma unroll
-        for (int q = 0; q < TMAX; ++q) acc[q] = 0ull;
-        const ulonglong2* xr = reinterpret_cast<const ulonglong2*>(x + r * d);
-#pragma unroll 2
-        for (int64_t v = lane; v < nv; v += 32) {
-            const ulonglong2 a = __ldg(xr + v);
+        for (int q = 0; q < TMAX; ++q) { acc0[q] = 0ull; acc1[q] = 0ull; }
+        const ulonglong2* xr0 = reinterpret_cast<const ulonglong2*>(x + r * d);
+        const ulonglong2* xr1 = reinterpret_cast<const ulonglong2*>(x + (two ? r + 1 : r) * d);
+        for (int64_t v0 = lane; v0 < nv; v0 += 64) {                // two 16-byte loads of each row in flight per lane
+            ulonglong2 a0[2], a1[2];
 #pragma unroll
-            for (int q = 0; q < TMAX; ++q) {
-                const ulonglong2 b = cs[q * nv + v];
-                const uint64_t e0 = pk_sub(a.x, b.x), e1 = pk_sub(a.y, b.y);
-                acc[q] = pk_fma(e0, e0, acc[q]); acc[q] = pk_fma(e1, e1, acc[q]);
+            for (int u = 0; u < 2; ++u) {
+                const bool ok = v0 + 32 * u < nv;
+                a0[u] = ok ? __ldg(xr0 + v0 + 32 * u) : make_ulonglong2(0ull, 0ull);
+                a1[u] = ok ? __ldg(xr1 + v0 + 32 * u) : make_ulonglong2(0ull, 0ull);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (v0 + 32 * u >= nv) break;
+#pragma unroll
+                for (int q = 0; q < TMAX; ++q) {
+                    const ulonglong2 b = cs[q * nv + v0 + 32 * u];
+                    uint64_t e0 = pk_sub(a0[u].x, b.x), e1 = pk_sub(a0[u].y, b.y);
+                    acc0[q] = pk_fma(e0, e0, acc0[q]); acc0[q] = pk_fma(e1, e1, acc0[q]);
+                    e0 = pk_sub(a1[u].x, b.x); e1 = pk_sub(a1[u].y, b.y);
+                    acc1[q] = pk_fma(e0, e0, acc1[q]); acc1[q] = pk_fma(e1, e1, acc1[q]);
+                }
             }
         }
 #pragma unroll
         for (int q = 0; q < TMAX; ++q) {
             if (q < t) {
-                const float a = warp_butterfly(pk_hsum(acc[q]));
-                if (lane == 0) out[int64_t(q) * n + r] = a;
+                const float s0 = warp_butterfly(pk_hsum(acc0[q]));
+                const float s1 = warp_butterfly(pk_hsum(acc1[q]));
+                if (lane == 0) {
+                    out[int64_t(q) * n + r] = s0;
+                    if (two) out[int64_t(q) * n + r + 1] = s1;
+                }
             }
         }
     }
@@ -288,15 +307,22 @@ __global__ void km_pp_sample_kernel(const double* __restrict__ tile_sums, int64_
     if (found) {
         const int64_t base = tile * KM_TILE;
         pick = min64(n, base + KM_TILE) - 1;
+        float vals[KM_TILE / 32];                    // all loads in flight at once: the scan below waits once, not 32 times
+#pragma unroll
+        for (int k = 0; k < KM_TILE / 32; ++k) {
+            const int64_t i = base + 32 * k + lane;
+            vals[k] = (i < n) ? closest[i] : 0.f;
+        }
         bool got = false;
-        for (int c0 = 0; c0 < KM_TILE && !got; c0 += 32) {
-            const int64_t i = base + c0 + lane;
-            const double v = (i < n) ? double(closest[i]) : 0.0;
-            double inc = v;
+#pragma unroll
+        for (int k = 0; k < KM_TILE / 32; ++k) {
+            if (got) continue;                       // warp-uniform
+            const int64_t i = base + 32 * k + lane;
+            double inc = double(vals[k]);
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const double y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
             const unsigned hit = __ballot_sync(0xffffffffu, i < n && before + inc >= r);
-            if (hit) { pick = base + c0 + (__ffs(hit) - 1); got = true; }
+            if (hit) { pick = base + 32 * k + (__ffs(hit) - 1); got = true; }
             else before += __shfl_sync(0xffffffffu, inc, 31);
         }
     }
@@ -358,79 +384,77 @@ __global__ void km_gather_centers_kernel(const float* __restrict__ x, int64_t d,
     for (int64_t j = threadIdx.x; j < d; j += blockDim.x) centers[int64_t(blockIdx.x) * d + j] = src[j];
 }
 
-// Lloyd update, deterministic: warp w of a CTA owns the rows r0 + 8 w .. + 7, + 8 W, ... and its own [c][32] slab of
-// shared memory (no atomics); the slabs are combined in warp order and written as this row block's partial
-// sums.  Column block 0 also counts members and the labels that moved since the previous iteration.
+// Lloyd update, deterministic.  One stable radix sort of (label, row) makes every cluster a contiguous run in
+// ascending row order (the plan of aggregate.cu); a CTA then sums one slice of one cluster, whole rows at a time
+// (256 threads x float4 = 4 KB per member row, 8 rows in flight), in registers -- no atomics, fixed order.
 __global__ void __launch_bounds__(256)
-km_accumulate_det_kernel(const float* __restrict__ x, int64_t n, int64_t d, const int32_t* __restrict__ labels,
-                         int32_t* __restrict__ prev, int c, int rows_per, float* __restrict__ part,
-                         unsigned int* __restrict__ counts_part, KmState* __restrict__ st) {
-    if (st->done) return;
-    extern __shared__ float slab[];                      // [W][c][32] floats, then [W][c] counts
-    const int W = blockDim.x >> 5;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned int* cnt = reinterpret_cast<unsigned int*>(slab + size_t(W) * c * KM_DS);
-    for (int t = threadIdx.x; t < W * c * KM_DS; t += blockDim.x) slab[t] = 0.f;
-    for (int t = threadIdx.x; t < W * c; t += blockDim.x) cnt[t] = 0u;
-    __syncthreads();
-    const int64_t r0 = int64_t(blockIdx.x) * rows_per, r1 = min64(n, r0 + rows_per);
-    const int64_t col = int64_t(blockIdx.y) * KM_DS + lane;
-    float* mine = slab + size_t(warp) * c * KM_DS;
+km_keys_kernel(const int32_t* __restrict__ labels, int32_t* __restrict__ prev, int64_t n, int c,
+               uint64_t* __restrict__ keys, uint32_t* __restrict__ rows, KmState* __restrict__ st) {
+    const bool live = st->done == 0;
     unsigned int moved = 0;
-    // a warp takes 8 consecutive rows per step: 8 independent loads in flight, sums in row order
-    for (int64_t rb = r0 + int64_t(warp) * 8; rb < r1; rb += int64_t(W) * 8) {
-        int lb[8];
-        float v[8];
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const int l = labels[i];
+        keys[i] = (l >= 0 && l < c) ? uint64_t(l) : uint64_t(c);         // strays sort last
+        rows[i] = uint32_t(i);
+        if (live) { moved += (prev[i] != l) ? 1u : 0u; prev[i] = l; }
+    }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            lb[u] = (rb + u < r1) ? labels[rb + u] : -1;
-            if (lb[u] >= c) lb[u] = -1;
-        }
+    for (int o = 16; o > 0; o >>= 1) moved += __shfl_xor_sync(0xffffffffu, moved, o);
+    if ((threadIdx.x & 31) == 0 && moved) atomicAdd(&st->moved, (unsigned long long)moved);
+}
+
+// partial[z][cc][:] = sum of the rows in slice z of cluster cc (grid (c, split))
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+km_segsum_kernel(const float* __restrict__ x, int64_t d, const uint32_t* __restrict__ order,
+                 const uint32_t* __restrict__ start, int c, float* __restrict__ partial, const KmState* __restrict__ st) {
+    if (st->done) return;
+    const int cc = blockIdx.x, z = blockIdx.y, split = gridDim.y;
+    const uint32_t s = start[cc], e = start[cc + 1];
+    const uint32_t per = (e - s + split - 1) / split;
+    const uint32_t lo = min(e, s + z * per), hi = min(e, lo + per);
+    float* out = partial + (int64_t(z) * c + cc) * d;
+    if (VEC) {
+        const int64_t nv = d >> 2;
+        for (int64_t v = threadIdx.x; v < nv; v += blockDim.x) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            uint32_t q = lo;
+            for (; q + 8 <= hi; q += 8) {
+                float4 t[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (lb[u] >= 0 && col < d) ? __ldg(x + (rb + u) * d + col) : 0.f;
+                for (int u = 0; u < 8; ++u) t[u] = __ldg(reinterpret_cast<const float4*>(x + int64_t(order[q + u]) * d) + v);
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            if (lb[u] < 0) continue;
-            mine[lb[u] * KM_DS + lane] += v[u];
-            if (blockIdx.y == 0 && lane == 0) {
-                cnt[warp * c + lb[u]] += 1u;
-                moved += (prev[rb + u] != lb[u]) ? 1u : 0u;
-                prev[rb + u] = lb[u];
+                for (int u = 0; u < 8; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
             }
+            for (; q < hi; ++q) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(x + int64_t(order[q]) * d) + v);
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
+            reinterpret_cast<float4*>(out)[v] = acc;
         }
-    }
-    __syncthreads();
-    for (int t = threadIdx.x; t < c * KM_DS; t += blockDim.x) {
-        float s = 0.f;
-        for (int w = 0; w < W; ++w) s += slab[size_t(w) * c * KM_DS + t];
-        const int64_t dc = int64_t(blockIdx.y) * KM_DS + (t % KM_DS);
-        if (dc < d) part[(int64_t(blockIdx.x) * c + t / KM_DS) * d + dc] = s;
-    }
-    if (blockIdx.y == 0) {
-        for (int t = threadIdx.x; t < c; t += blockDim.x) {
-            unsigned int s = 0;
-            for (int w = 0; w < W; ++w) s += cnt[w * c + t];
-            counts_part[int64_t(blockIdx.x) * c + t] = s;
+    } else {
+        for (int64_t col = threadIdx.x; col < d; col += blockDim.x) {
+            float acc = 0.f;
+            for (uint32_t q = lo; q < hi; ++q) acc += __ldg(x + int64_t(order[q]) * d + col);
+            out[col] = acc;
         }
-        if (lane == 0 && moved) atomicAdd(&st->moved, (unsigned long long)moved);
     }
 }
 
 // centre cc <- mean of its members (empty clusters keep their centre); shift_part[cc] = |new - old|^2
 __global__ void __launch_bounds__(128)
-km_finalize_det_kernel(const float* __restrict__ part, const unsigned int* __restrict__ counts_part, int nrb, int c,
+km_finalize_det_kernel(const float* __restrict__ partial, const uint32_t* __restrict__ start, int split, int c,
                        int64_t d, float* __restrict__ centers, double* __restrict__ shift_part,
                        const KmState* __restrict__ st) {
     if (st->done) return;
     __shared__ double sh[4];
     const int cc = blockIdx.x;
-    unsigned int cnt = 0;
-    for (int rb = 0; rb < nrb; ++rb) cnt += counts_part[int64_t(rb) * c + cc];
+    const unsigned int cnt = start[cc + 1] - start[cc];
     double local = 0.0;
     if (cnt > 0) {
         for (int64_t j = threadIdx.x; j < d; j += blockDim.x) {
             double s = 0.0;
-            for (int rb = 0; rb < nrb; ++rb) s += double(part[(int64_t(rb) * c + cc) * d + j]);
+            for (int z = 0; z < split; ++z) s += double(partial[(int64_t(z) * c + cc) * d + j]);
             const float nv = float(s / double(cnt));
             const float ov = centers[int64_t(cc) * d + j];
             local += double(nv - ov) * double(nv - ov);
@@ -492,7 +516,7 @@ __global__ void km_take_kernel(const KmState* __restrict__ st, const int32_t* __
 // KL centres with the smallest 3xBF16 scores |c|^2 - 2 x.c.  Every candidate whose score lies within the
 // guaranteed error slack of the best one is recomputed as sum (x - c)^2 in FP32 (almost always one), and the
 // smallest exact distance wins, ties to the lower centre.  One warp per row.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 km_pick_kernel(const float* __restrict__ x, const float* __restrict__ centers, int64_t n, int64_t d,
                const float* __restrict__ part_val, const int32_t* __restrict__ part_idx, int kl,
                const float* __restrict__ norms_x, const float* __restrict__ norm_max,
@@ -523,11 +547,20 @@ km_pick_kernel(const float* __restrict__ x, const float* __restrict__ centers, i
         float acc;
         if (vec) {
             uint64_t ad = 0;
-            for (int64_t v = lane; v < (d >> 2); v += 32) {
-                const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2*>(xi) + v);
-                const ulonglong2 b = *(reinterpret_cast<const ulonglong2*>(cj) + v);
-                const uint64_t e0 = pk_sub(a.x, b.x), e1 = pk_sub(a.y, b.y);
-                ad = pk_fma(e0, e0, ad); ad = pk_fma(e1, e1, ad);
+            const int64_t nv = d >> 2;
+            for (int64_t v0 = lane; v0 < nv; v0 += 128) {           // four loads of each row in flight, sums in index order
+                ulonglong2 a[4], b[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const bool ok = v0 + 32 * u < nv;
+                    a[u] = ok ? __ldg(reinterpret_cast<const ulonglong2*>(xi) + v0 + 32 * u) : make_ulonglong2(0ull, 0ull);
+                    b[u] = ok ? *(reinterpret_cast<const ulonglong2*>(cj) + v0 + 32 * u) : make_ulonglong2(0ull, 0ull);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint64_t e0 = pk_sub(a[u].x, b[u].x), e1 = pk_sub(a[u].y, b[u].y);
+                    ad = pk_fma(e0, e0, ad); ad = pk_fma(e1, e1, ad);
+                }
             }
             acc = pk_hsum(ad);
         } else {
@@ -541,9 +574,9 @@ km_pick_kernel(const float* __restrict__ x, const float* __restrict__ centers, i
 }
 
 struct KmFitPlan {
-    int rows_per, nrb, warps, trials;
+    int rows_per, nrb, split, trials;
     int64_t ntiles;
-    size_t smem, bytes;
+    size_t bytes;
     // assignment on the tensor cores (rectangular launch of the fused kNN kernel) from this much work up
     bool tc;
     int64_t n_pad_x, c_pad, d_pad;
@@ -561,14 +594,13 @@ static KmFitPlan km_fit_plan(int64_t n, int64_t d, int c) {
     KmFitPlan pl{};
     pl.rows_per = (n >= 32768) ? 2048 : 512;
     pl.nrb = int(ceil_div(n, pl.rows_per));
-    const size_t per_warp = size_t(c) * (KM_DS + 1) * 4;
-    pl.warps = int(std::max<size_t>(1, std::min<size_t>(8, (size_t(200) << 10) / per_warp)));
-    pl.smem = per_warp * pl.warps;
+    pl.split = int(std::max<int64_t>(1, std::min<int64_t>(32, ceil_div(int64_t(kNumSMs) * 4, c))));   // slices per cluster
     pl.trials = std::min(16, 2 + int(log(double(c))));   // scikit-learn: 2 + int(ln k)
     pl.ntiles = ceil_div(n, KM_TILE);
     auto al = [](size_t b) { return (b + 1023) & ~size_t(1023); };
-    const size_t part = std::max(size_t(pl.nrb) * c * d * 4, size_t(pl.nrb) * 2 * d * 8);
-    pl.bytes = al(sizeof(KmState)) + al(part) + al(size_t(pl.nrb) * c * 4) + al(size_t(c) * 8) /* shift_part */ +
+    const size_t part = std::max(size_t(pl.split) * c * d * 4, size_t(pl.nrb) * 2 * d * 8);
+    pl.bytes = al(sizeof(KmState)) + al(part) + 2 * al(size_t(n) * 8) + 2 * al(size_t(n) * 4) /* sort keys, rows */ +
+               al(sort_table_entries(n) * 4) + al((size_t(c) + 2) * 4) + al(size_t(c) * 8) /* shift_part */ +
                3 * al(size_t(n) * 4) /* cur, prev, d2 */ + al(size_t(n) * 4) /* closest */ +
                al(size_t(16) * n * 4) /* cand_d2 */ + al(size_t(pl.ntiles) * 8) + al(size_t(16) * pl.ntiles * 8) +
                al(16 * 8) + al(size_t(c) * 8) + al(size_t(c) * d * 4) + 1024;
@@ -706,7 +738,7 @@ static int km_launch_cand_d2(const float* x, int64_t n, int64_t d, const int64_t
     const size_t smem = size_t(t <= 8 ? 8 : 16) * d * 4;
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
     if (vec && smem <= 96 * 1024) {
-        const int64_t grid = std::max<int64_t>(1, std::min<int64_t>(ceil_div(n, 8), int64_t(kNumSMs) * 6));
+        const int64_t grid = std::max<int64_t>(1, std::min<int64_t>(ceil_div(n, 16), int64_t(kNumSMs) * 6));
         const int64_t rows_per_block = ceil_div(n, grid);
         if (t <= 8) {
             if (smem > 48 * 1024)
@@ -747,9 +779,14 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
     HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "hg_kmeans_fit: workspace must be 1024-byte aligned");
     KmCarver cv(workspace);
     KmState* state = cv.take<KmState>(1);
-    const size_t part_bytes = std::max(size_t(pl.nrb) * c * d * 4, size_t(pl.nrb) * 2 * d * 8);
+    const size_t part_bytes = std::max(size_t(pl.split) * c * d * 4, size_t(pl.nrb) * 2 * d * 8);
     float* part = reinterpret_cast<float*>(cv.take<char>(part_bytes));
-    unsigned int* counts_part = cv.take<unsigned int>(size_t(pl.nrb) * c);
+    uint64_t* keys = cv.take<uint64_t>(n);
+    uint64_t* keys_tmp = cv.take<uint64_t>(n);
+    uint32_t* rows = cv.take<uint32_t>(n);
+    uint32_t* rows_tmp = cv.take<uint32_t>(n);
+    uint32_t* table = cv.take<uint32_t>(sort_table_entries(n));
+    uint32_t* start = cv.take<uint32_t>(size_t(c) + 2);
     double* shift_part = cv.take<double>(c);
     int32_t* cur = cv.take<int32_t>(n);
     int32_t* prev = cv.take<int32_t>(n);
@@ -777,8 +814,9 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
         if (rc != HG_OK) return rc;
     }
 
-    if (pl.smem > 48 * 1024)
-        HG_CHECK_CUDA(cudaFuncSetAttribute(km_accumulate_det_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
+    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    const int label_bits = bits_for(uint64_t(c));
+    const int key_blocks = int(min64(ceil_div(n, 256), int64_t(kNumSMs) * 8));
     const dim3 grid_rc((unsigned)pl.nrb, (unsigned)ceil_div(d, KM_DS));
     const unsigned nt = (unsigned)pl.ntiles;
 
@@ -815,11 +853,17 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
             for (int q = 0; q < chunk; ++q) {
                 int rc = km_assign(ka, st);
                 if (rc != HG_OK) return rc;
-                km_accumulate_det_kernel<<<grid_rc, pl.warps * 32, pl.smem, st>>>(x, n, d, cur, prev, c, pl.rows_per, part,
-                                                                                 counts_part, state);
-                km_finalize_det_kernel<<<c, 128, 0, st>>>(part, counts_part, pl.nrb, c, d, centers, shift_part, state);
+                km_keys_kernel<<<key_blocks, 256, 0, st>>>(cur, prev, n, c, keys, rows, state);
+                uint64_t* sk; uint32_t* order;
+                rc = radix_sort_u64(keys, keys_tmp, rows, rows_tmp, n, label_bits, table, &sk, &order, st);
+                if (rc != HG_OK) return rc;
+                rc = launch_cluster_bounds(sk, n, c, start, st);
+                if (rc != HG_OK) return rc;
+                if (vec) km_segsum_kernel<true><<<dim3(c, pl.split), 256, 0, st>>>(x, d, order, start, c, part, state);
+                else     km_segsum_kernel<false><<<dim3(c, pl.split), 256, 0, st>>>(x, d, order, start, c, part, state);
+                km_finalize_det_kernel<<<c, 128, 0, st>>>(part, start, pl.split, c, d, centers, shift_part, state);
                 km_check_kernel<<<1, 1, 0, st>>>(shift_part, c, state);
-                count_launches(3);
+                count_launches(4);
             }
             HG_CHECK_LAUNCH();
             it += chunk;

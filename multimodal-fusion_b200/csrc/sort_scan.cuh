@@ -8,6 +8,9 @@ size_t sort_table_entries(int64_t count);     // uint32 entries needed for `tabl
 int radix_sort_u64(uint64_t* keys, uint64_t* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, int64_t count,
                    int bits, uint32_t* table, uint64_t** sorted_keys, uint32_t** sorted_vals, cudaStream_t st);
 
+// start[c] = first position of a run sorted by cluster label whose label is >= c, c in [0, num_clusters] (aggregate.cu)
+int launch_cluster_bounds(const uint64_t* sorted_keys, int64_t n, int num_clusters, uint32_t* start, cudaStream_t st);
+
 size_t unique_tiles(int64_t count);           // uint32 entries needed for `tile_sums` (SC_TILE items per tile)
 // distinct keys of a sorted run, skipping `sentinel`; *count_out (device) <- how many
 int unique_sorted_u64(const uint64_t* keys, int64_t count, uint64_t sentinel, uint64_t* out, uint32_t* tile_sums,
