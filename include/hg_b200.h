@@ -164,6 +164,9 @@ int hg_edges_count(const int32_t* const* knn_lists, const int* ks, int num_lists
                    void* workspace, size_t workspace_bytes, void* stream);
 int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
                   const void* workspace, size_t workspace_bytes, void* stream);
+/* the name SURVEY.md 8(b) lists for the second half of the count -> allocate -> fill pair; same call */
+int hg_edges_build(int64_t num_edges, int64_t* edge_index,
+                   const void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- A6: w_e = max(0, cos(f_i, f_j)), eps = 1e-8 -- preprocess_hypergraph.py:413-422 */
 int hg_edge_weights_cosine(const float* feats, int64_t n, int64_t d,
@@ -195,6 +198,9 @@ int hg_threshold_edges_count(const float* K, int64_t n, float threshold,
 int hg_threshold_edges_fill(const float* K, int64_t n, float threshold, int64_t num_edges,
                             int64_t* edge_index, float* edge_weights,
                             const void* workspace, size_t workspace_bytes, void* stream);
+int hg_threshold_edges_build(const float* K, int64_t n, float threshold, int64_t num_edges,
+                             int64_t* edge_index, float* edge_weights,
+                             const void* workspace, size_t workspace_bytes, void* stream);   /* = _fill */
 int hg_threshold_workspace_bytes(int64_t n, size_t* bytes);
 
 /* ---- row (f)1, "next": KMeans building blocks (Lloyd assign / update, kmeans++ distances) -------

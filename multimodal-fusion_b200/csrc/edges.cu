@@ -312,3 +312,8 @@ extern "C" int hg_edges_fill(int64_t num_edges, int64_t* edge_index,
     count_launches(1);
     return HG_OK;
 }
+
+extern "C" int hg_edges_build(int64_t num_edges, int64_t* edge_index,
+                              const void* workspace, size_t workspace_bytes, void* stream) {
+    return hg_edges_fill(num_edges, edge_index, workspace, workspace_bytes, stream);
+}

@@ -389,3 +389,9 @@ extern "C" int hg_hypergraph_propagate(const float* x, int64_t n, int64_t f, con
     count_launches(2);
     return HG_OK;
 }
+
+extern "C" int hg_threshold_edges_build(const float* K, int64_t n, float threshold, int64_t num_edges,
+                                        int64_t* edge_index, float* edge_weights,
+                                        const void* workspace, size_t workspace_bytes, void* stream) {
+    return hg_threshold_edges_fill(K, n, threshold, num_edges, edge_index, edge_weights, workspace, workspace_bytes, stream);
+}

@@ -61,6 +61,7 @@ SIGNATURES = {
     "hg_clique_pairs": (_i32, [_vp, _i64, _i32, _pi64, _vp]),
     "hg_edges_count": (_i32, [C.POINTER(_vp), C.POINTER(_i32), _i32, _i64, _vp, _i32, _i64, _pi64, _vp, _sz, _vp]),
     "hg_edges_fill": (_i32, [_i64, _vp, _vp, _sz, _vp]),
+    "hg_edges_build": (_i32, [_i64, _vp, _vp, _sz, _vp]),
     "hg_edge_weights_cosine": (_i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "hg_csr_workspace_bytes": (_i32, [_i64, _i64, _psz]),
     "hg_csr_from_coo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -90,6 +91,7 @@ SIGNATURES = {
     "hg_aggregate_super_patches": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _f32, _f32, _vp, _i64, _i32,
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_threshold_edges_fill": (_i32, [_vp, _i64, _f32, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "hg_threshold_edges_build": (_i32, [_vp, _i64, _f32, _i64, _vp, _vp, _vp, _sz, _vp]),
 }
 
 _lib = None

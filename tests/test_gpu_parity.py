@@ -329,6 +329,24 @@ def test_c3_combined_feature_and_spatial_sampled_rows():
     assert rowptr[-1] == 2 * ei.shape[1]
 
 
+def test_c5_row_block_of_a_giant_slide_sampled_rows():
+    """BASELINE config C5 (N=250k x 1536, row-partitioned over 8 GPUs): the row block rank 3 owns, run
+    against all N columns (what the rank holds after the all-gather), sampled rows vs the float64 oracle."""
+    from hg_b200 import multigpu
+    n, d, k = 250_000, 1536, 16
+    feats = synth.make_features(n, d, 1239, "gaussian")
+    r0, r1 = multigpu.row_range(n, 3, 8)
+    idx, val = ops.knn_feature(_cuda(feats), k, "gaussian", lambda_h=1.0, rows=(r0, r1))
+    idx, val = idx.cpu().numpy(), val.cpu().numpy()
+    assert idx.shape == (r1 - r0, k)
+    assert (np.diff(val, axis=1) <= 0).all() and (idx >= 0).all() and (idx < n).all()
+    assert (idx != np.arange(r0, r1)[:, None]).all()
+    rows = r0 + np.random.default_rng(5).choice(r1 - r0, 96, replace=False)
+    check_knn(idx[rows - r0], feats, k, "gaussian", rows=rows)
+    _, ref_val = oracle.knn_feature(feats, k, "gaussian", lambda_h=1.0, rows=rows[:16])
+    np.testing.assert_allclose(val[rows[:16] - r0], ref_val, rtol=RTOL)
+
+
 def test_streaming_stats_match_dense(monkeypatch):
     """A9 without the N x N matrix: chunked tensor-core sweep == statistics of the dense kernel."""
     n, d = 3000, 128
