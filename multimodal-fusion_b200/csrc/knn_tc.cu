@@ -481,7 +481,9 @@ static int list_len(int k) {            // k plus slack for the exact re-rank, i
 static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
     const int workers = kNumSMs / pl.cl;               // CTAs or CTA pairs
     const int64_t a_block = int64_t(TC_BM * pl.cl) * d_pad * 4;
-    const int64_t rc_cap = (int64_t(40) << 20) / a_block;
+    int64_t a_mb = 40;
+    if (const char* e = getenv("HG_B200_TC_A_MB")) { const int v = atoi(e); if (v >= 1 && v <= 512) a_mb = v; }   // tuning override
+    const int64_t rc_cap = (a_mb << 20) / a_block;
     const int cc_max = 4 / pl.cl;                      // 148 = 4 * 37, 74 = 2 * 37
     int best_cc = cc_max, best_s = cc_max;
     double best_eff = -1.0;
