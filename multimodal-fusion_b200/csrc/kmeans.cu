@@ -226,7 +226,7 @@ km_colstats_kernel(const float* __restrict__ x, int64_t n, int64_t d, int rows_p
 
 // tol_abs = tol * mean_j var(x[:, j])   (scikit-learn's _tolerance)
 __global__ void km_tol_kernel(const double* __restrict__ part, int nrb, int64_t n, int64_t d, double tol,
-                              KmState* __restrict__ st) {
+                              KmState* __restrict__ st, float* __restrict__ mean_out) {
     __shared__ double sh[32];
     double acc = 0.0;
     for (int64_t j = threadIdx.x; j < d; j += blockDim.x) {
@@ -234,9 +234,23 @@ __global__ void km_tol_kernel(const double* __restrict__ part, int nrb, int64_t 
         for (int rb = 0; rb < nrb; ++rb) { s += part[(int64_t(rb) * 2) * d + j]; q += part[(int64_t(rb) * 2 + 1) * d + j]; }
         const double mean = s / double(n);
         acc += fmax(q / double(n) - mean * mean, 0.0);
+        mean_out[j] = float(mean);
     }
     const double tot = km_block_sum(acc, sh);
     if (threadIdx.x == 0) { st->tol_abs = tol * tot / double(d); st->best_inertia = 0.0; st->best_iter = 0; }
+}
+
+// xc = x - column means: distances do not change, but the FP32 expansion |x|^2 + |c|^2 - 2 x.c and the BF16
+// split stop cancelling on data that sits far from the origin (scikit-learn's fit centres X for the same reason;
+// without it nearly constant data, e.g. a similarity matrix with entries around 0.98, never stops moving labels)
+__global__ void __launch_bounds__(256)
+km_center_kernel(const float* __restrict__ x, int64_t n, int64_t d, const float* __restrict__ mean, int rows_per,
+                 float* __restrict__ xc) {
+    const int64_t r0 = int64_t(blockIdx.x) * rows_per, r1 = min64(n, r0 + rows_per);
+    for (int64_t j = threadIdx.x; j < d; j += blockDim.x) {
+        const float m = mean[j];
+        for (int64_t r = r0; r < r1; ++r) xc[r * d + j] = x[r * d + j] - m;
+    }
 }
 
 // start of a restart: flags cleared, first centre drawn uniformly
@@ -504,12 +518,12 @@ __global__ void km_best_kernel(const double* __restrict__ tile_sums, int64_t nti
 }
 
 __global__ void km_take_kernel(const KmState* __restrict__ st, const int32_t* __restrict__ labels, int64_t n,
-                               const float* __restrict__ centers, int64_t cd, int32_t* __restrict__ labels_out,
-                               float* __restrict__ centers_out) {
+                               const float* __restrict__ centers, int64_t cd, int64_t d, const float* __restrict__ mean,
+                               int32_t* __restrict__ labels_out, float* __restrict__ centers_out) {
     if (!st->take) return;
     const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) labels_out[i] = labels[i];
-    if (i < cd) centers_out[i] = centers[i];
+    if (i < cd) centers_out[i] = centers[i] + mean[i % d];        // centres of the centred data, moved back
 }
 
 // Tensor-core assignment, second half: the fused kernel (knn_tc.cu, rectangular launch) left every row the
@@ -603,7 +617,7 @@ static KmFitPlan km_fit_plan(int64_t n, int64_t d, int c) {
                al(sort_table_entries(n) * 4) + al((size_t(c) + 2) * 4) + al(size_t(c) * 8) /* shift_part */ +
                3 * al(size_t(n) * 4) /* cur, prev, d2 */ + al(size_t(n) * 4) /* closest */ +
                al(size_t(16) * n * 4) /* cand_d2 */ + al(size_t(pl.ntiles) * 8) + al(size_t(16) * pl.ntiles * 8) +
-               al(16 * 8) + al(size_t(c) * 8) + al(size_t(c) * d * 4) + 1024;
+               al(16 * 8) + al(size_t(c) * 8) + al(size_t(c) * d * 4) + al(size_t(d) * 4) + al(size_t(n) * d * 4) /* mean, xc */ + 1024;
     pl.tc = km_use_tc(n, d, c);
     if (pl.tc) {
         pl.n_pad_x = ops_rows(n); pl.c_pad = ops_rows(c); pl.d_pad = ops_cols(d);
@@ -798,6 +812,8 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
     int64_t* cand = cv.take<int64_t>(16);
     int64_t* center_idx = cv.take<int64_t>(c);
     float* centers = cv.take<float>(size_t(c) * d);
+    float* mean = cv.take<float>(d);
+    float* xc = cv.take<float>(size_t(n) * d);
     KmAssign ka{};
     ka.tc = pl.tc;
     if (pl.tc) {
@@ -810,20 +826,24 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
         ka.part_val = cv.take<float>(size_t(n) * pl.tcplan.kl);
         ka.part_idx = cv.take<int32_t>(size_t(n) * pl.tcplan.kl);
         ka.n_pad_x = pl.n_pad_x; ka.c_pad = pl.c_pad; ka.d_pad = pl.d_pad; ka.plan = pl.tcplan;
-        int rc = launch_split(x, n, d, ka.ops_x, ka.norms_x, st);          // the rows are split once per fit
-        if (rc != HG_OK) return rc;
     }
 
-    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    const bool vec = (d % 4 == 0);                      // the segmented sums read the centred copy, which is aligned
     const int label_bits = bits_for(uint64_t(c));
     const int key_blocks = int(min64(ceil_div(n, 256), int64_t(kNumSMs) * 8));
     const dim3 grid_rc((unsigned)pl.nrb, (unsigned)ceil_div(d, KM_DS));
     const unsigned nt = (unsigned)pl.ntiles;
 
     km_colstats_kernel<<<grid_rc, 256, 0, st>>>(x, n, d, pl.rows_per, reinterpret_cast<double*>(part));
-    km_tol_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const double*>(part), pl.nrb, n, d, tol, state);
+    km_tol_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const double*>(part), pl.nrb, n, d, tol, state, mean);
+    km_center_kernel<<<(unsigned)pl.nrb, 256, 0, st>>>(x, n, d, mean, pl.rows_per, xc);
     HG_CHECK_LAUNCH();
-    count_launches(2);
+    count_launches(3);
+    x = xc;                                                                 // everything below works on the centred rows
+    if (pl.tc) {
+        int rc = launch_split(x, n, d, ka.ops_x, ka.norms_x, st);          // the rows are split once per fit
+        if (rc != HG_OK) return rc;
+    }
 
     SimArgs& a = ka.sim;
     a.a = x; a.b = centers; a.m = n; a.n = c; a.d = d; a.metric = HG_METRIC_EUCLIDEAN; a.k = 1;
@@ -878,7 +898,7 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
         km_tile_sums_kernel<<<nt, 256, 0, st>>>(d2, n, tile_sums);
         km_best_kernel<<<1, 1, 0, st>>>(tile_sums, pl.ntiles, run, state, inertia, n_iter);
         const int64_t cd = int64_t(c) * d;
-        km_take_kernel<<<(unsigned)ceil_div(std::max<int64_t>(n, cd), 256), 256, 0, st>>>(state, cur, n, centers, cd, labels, centroids);
+        km_take_kernel<<<(unsigned)ceil_div(std::max<int64_t>(n, cd), 256), 256, 0, st>>>(state, cur, n, centers, cd, d, mean, labels, centroids);
         HG_CHECK_LAUNCH();
         count_launches(3);
     }

@@ -45,9 +45,13 @@ def _kmeanspp(lib, x, n_clusters: int, gen: torch.Generator, st) -> torch.Tensor
     return x.index_select(0, centers).contiguous()
 
 
+LAST_N_ITER = 0          # Lloyd iterations of the winning restart of the most recent `kmeans` call (tests, tuning)
+
+
 def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: int = 300, tol: float = 1e-4,
            seed: int = 42, device=None) -> Tuple[np.ndarray, torch.Tensor, float]:
     """Returns (labels int64 numpy [n], centers float32 CUDA [k, d], inertia)."""
+    global LAST_N_ITER
     lib = L.load_library()
     dev = L.require_cuda(device if device is not None else (features.device if features.is_cuda else None))
     x = L.f32c(features, dev)
@@ -64,6 +68,7 @@ def kmeans(features: torch.Tensor, n_clusters: int, n_init: int = 10, max_iter: 
                                   int(seed) & 0xFFFFFFFFFFFFFFFF, L.ptr(labels), L.ptr(centers), L.ptr(inertia),
                                   L.ptr(n_iter), L.ptr(ws), nbytes.value, L.stream_ptr(dev)))
         out = labels.cpu().numpy().astype(np.int64)
+        LAST_N_ITER = int(n_iter.item())
     return out, centers, float(inertia.item())
 
 

@@ -141,3 +141,21 @@ def test_both_assignment_paths_agree():
             os.environ.pop("HG_B200_KMEANS_TC")
     assert abs(res["0"][2] - res["1"][2]) <= 2e-3 * res["0"][2]
     assert (res["0"][0] == res["1"][0]).mean() > 0.9
+
+
+@pytest.mark.parametrize("assign", ["simt", "tc"])
+def test_nearly_constant_data_far_from_the_origin_converges(assign, monkeypatch):
+    """the grouping stage clusters rows of a similarity matrix whose entries all sit near one value
+    (preprocess_hypergraph.py:299-300): the fit centres the data like scikit-learn's, so FP32 cancellation
+    cannot keep labels moving until max_iter"""
+    from sklearn.cluster import KMeans as SkKMeans
+    from hg_b200 import kmeans as km
+    monkeypatch.setenv("HG_B200_KMEANS_TC", "1" if assign == "tc" else "0")
+    rng = np.random.default_rng(5)
+    base = 0.98 + 1e-3 * rng.standard_normal((10, 256))
+    x = (base[rng.integers(0, 10, 400)] + 1e-4 * rng.standard_normal((400, 256))).astype(np.float32)
+    labels, centers, inertia = km.kmeans(torch.from_numpy(x).cuda(), 10, n_init=10, seed=42)
+    assert km.LAST_N_ITER < 50
+    sk = SkKMeans(n_clusters=10, random_state=42, n_init=10).fit(x)
+    assert inertia <= sk.inertia_ * 1.05 + 1e-9
+    np.testing.assert_allclose(np.sort(centers.cpu().numpy().mean(1)), np.sort(sk.cluster_centers_.mean(1)), atol=2e-4)
