@@ -263,14 +263,23 @@ def build_hypergraph_knn_kmeans(wsi_features: torch.Tensor, tma_features: torch.
     return edge_index, edge_weights, stats
 
 
+def _load_inputs(h5_path: str):
+    """(wsi_features, wsi_positions, tma_features | None) of one slide file -- the host half of a slide that the
+    dataset loop reads ahead while the previous slide is on the GPU."""
+    wsi_features, wsi_positions = load_wsi_data(h5_path)
+    return wsi_features, wsi_positions, load_tma_data(h5_path)
+
+
 def process_single_file(h5_path: str, num_wsi_super_patches: int = 100, num_groups: int = 10,
                         hypergraph_k: int = 5, num_hyperedges: int = 10, lambda_h: float = 1.0,
-                        lambda_g: float = 1.0, device: Optional[torch.device] = None) -> Dict:
-    """One slide end to end (reference :514-603)."""
+                        lambda_g: float = 1.0, device: Optional[torch.device] = None, *,
+                        inputs=None, writer=None) -> Dict:
+    """One slide end to end (reference :514-603).  Keyword-only extras for the dataset loop: `inputs` =
+    what `_load_inputs` returned for this file (read ahead), `writer` = an executor that takes the save;
+    the returned stats then carry the pending write under "_pending_save"."""
     dev = _device(device)
     print(f"📂 Processing: {h5_path}")
-    wsi_features, wsi_positions = load_wsi_data(h5_path)
-    tma_features = load_tma_data(h5_path)
+    wsi_features, wsi_positions, tma_features = inputs if inputs is not None else _load_inputs(h5_path)
     if tma_features is None:
         print("⚠️  TMA features not found, skipping hypergraph construction")
         return {"status": "skipped", "reason": "no_tma"}
@@ -293,38 +302,90 @@ def process_single_file(h5_path: str, num_wsi_super_patches: int = 100, num_grou
         kk = min(STORED_TOPK, wsi_features.shape[0] - 1)
         topk = ops.knn_feature(wsi_features, kk, "gaussian", positions=wsi_positions, lambda_h=lambda_h,
                                lambda_g=lambda_g, device=dev)
-    save_hypergraph_to_h5(h5_path, sup_f, sup_p, tma_features, edge_index, edge_weights, group_labels, all_stats,
-                          wsi_similarity_matrix=wsi_sim, wsi_tma_similarity_matrix=sim, wsi_similarity_topk=topk)
-    print("  ✅ Done!")
-    return all_stats
+
+    def save():
+        save_hypergraph_to_h5(h5_path, sup_f, sup_p, tma_features, edge_index, edge_weights, group_labels, all_stats,
+                              wsi_similarity_matrix=wsi_sim, wsi_tma_similarity_matrix=sim, wsi_similarity_topk=topk)
+        print(f"  ✅ Done! ({os.path.basename(h5_path)})" if writer is not None else "  ✅ Done!")
+
+    if writer is None:
+        save()
+        return all_stats
+    out = dict(all_stats)
+    out["_pending_save"] = writer.submit(save)          # D2H + file write run behind the next slide's kernels
+    return out
 
 
-def _run_over_csv(csv_path: str, data_root_dir: str, desc: str, worker, output_stats_path: Optional[str]):
-    """Sequential per-slide loop with the reference's error convention: a failing slide is
-    reported and skipped (reference :651-670, :963-982).  Under torch.distributed each rank
-    takes the slides its LPT assignment gives it (multigpu.shard_slides)."""
+IO_OVERLAP = os.environ.get("HG_B200_IO_OVERLAP", "1") != "0"
+
+
+def _run_over_csv(csv_path: str, data_root_dir: str, desc: str, worker, output_stats_path: Optional[str],
+                  loader=None):
+    """Per-slide loop with the reference's error convention: a failing slide is reported and skipped
+    (reference :651-670, :963-982).  The reference loop is strictly sequential (load -> build -> save).
+    Here, when `loader` is given (HG_B200_IO_OVERLAP=0 turns it off), the next slide's file is read by a
+    helper thread while this one is on the GPU, and saves run on a writer thread: `worker(path, inputs=...,
+    writer=...)`.  Under torch.distributed (world size > 1) every rank takes the slides of its LPT share
+    (multigpu.shard_slides on the file sizes, a proxy for N); rank 0 gathers and writes the statistics."""
     import pandas as pd
     from tqdm import tqdm
+    import torch.distributed as dist
+    from concurrent.futures import ThreadPoolExecutor
+    from .multigpu import shard_slides
     df = pd.read_csv(csv_path)
     if "h5_file_path" not in df.columns:
         raise ValueError("CSV must contain 'h5_file_path' column")
-    all_stats = []
-    for idx, row in tqdm(df.iterrows(), total=len(df), desc=desc):
+    todo = []
+    for idx, row in df.iterrows():
         rel = row["h5_file_path"]
         h5_path = os.path.join(data_root_dir, rel)
         if not os.path.exists(h5_path):
             print(f"⚠️  File not found: {h5_path}")
             continue
-        try:
-            stats = worker(h5_path)
-            stats["case_id"] = row.get("case_id", f"case_{idx}")
-            stats["h5_path"] = rel
-            all_stats.append(stats)
-        except Exception as e:                      # noqa: BLE001 -- reference behaviour
-            print(f"❌ Error processing {h5_path}: {e}")
-            import traceback
-            traceback.print_exc()
-    if output_stats_path:
+        todo.append((idx, row, rel, h5_path))
+    world, rank = 1, 0
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        world, rank = dist.get_world_size(), dist.get_rank()
+        sizes = [os.path.getsize(t[3]) if os.path.isfile(t[3]) else 1 for t in todo]
+        todo = [todo[i] for i in shard_slides(sizes, world)[rank]]
+    overlap = loader is not None and IO_OVERLAP
+    reader = ThreadPoolExecutor(1) if overlap else None
+    writer = ThreadPoolExecutor(1) if overlap else None
+    done = []                                           # (csv index, stats) of the slides that went through
+    try:
+        ahead = reader.submit(loader, todo[0][3]) if overlap and todo else None
+        for pos, (idx, row, rel, h5_path) in enumerate(tqdm(todo, total=len(todo), desc=desc)):
+            mine, ahead = ahead, None
+            if overlap and pos + 1 < len(todo):
+                ahead = reader.submit(loader, todo[pos + 1][3])
+            try:
+                stats = worker(h5_path, inputs=mine.result(), writer=writer) if overlap else worker(h5_path)
+                stats["case_id"] = row.get("case_id", f"case_{idx}")
+                stats["h5_path"] = rel
+                done.append((idx, stats))
+            except Exception as e:                      # noqa: BLE001 -- reference behaviour
+                print(f"❌ Error processing {h5_path}: {e}")
+                import traceback
+                traceback.print_exc()
+        all_stats = []
+        for idx, stats in done:                         # a save that failed drops its slide, like any other error
+            pending = stats.pop("_pending_save", None)
+            try:
+                if pending is not None:
+                    pending.result()
+                all_stats.append((idx, stats))
+            except Exception as e:                      # noqa: BLE001
+                print(f"❌ Error saving {stats.get('h5_path')}: {e}")
+    finally:
+        for ex in (reader, writer):
+            if ex is not None:
+                ex.shutdown(wait=True)
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, all_stats)
+        all_stats = sorted((item for part in parts for item in part), key=lambda t: t[0])
+    all_stats = [s for _, s in all_stats]
+    if output_stats_path and rank == 0:
         with open(output_stats_path, "w") as f:
             json.dump(all_stats, f, indent=2, default=float)
         print(f"📊 Statistics saved to: {output_stats_path}")
@@ -337,9 +398,9 @@ def process_dataset(csv_path: str, data_root_dir: str, num_wsi_super_patches: in
     """All slides of a CSV (reference :606-678)."""
     return _run_over_csv(
         csv_path, data_root_dir, "Processing files",
-        lambda p: process_single_file(p, num_wsi_super_patches, num_groups, hypergraph_k, num_hyperedges,
-                                      lambda_h, lambda_g, device),
-        output_stats_path)
+        lambda p, **io: process_single_file(p, num_wsi_super_patches, num_groups, hypergraph_k, num_hyperedges,
+                                            lambda_h, lambda_g, device, **io),
+        output_stats_path, loader=_load_inputs)
 
 
 def rebuild_hypergraph_from_similarity(h5_path: str, num_wsi_super_patches: int = None, num_groups: int = None,

@@ -95,3 +95,88 @@ def test_row_partitioned_equals_single_process(n, aligned):
     for _, idx, ei in results:
         assert (idx == ref_idx).all()
         assert (ei == ref_ei).all()
+
+
+# ---- dataset loop (preprocess_hypergraph._run_over_csv): read-ahead / writer threads, rank sharding --------
+def _dataset_files(root, sizes):
+    names = []
+    for i, sz in enumerate(sizes):
+        name = f"slide_{i}.bin"
+        with open(os.path.join(root, name), "wb") as f:
+            f.write(b"x" * sz)
+        names.append(name)
+    csv = os.path.join(root, "cases.csv")
+    with open(csv, "w") as f:
+        f.write("case_id,h5_file_path\n" + "\n".join(f"c{i},{n}" for i, n in enumerate(names + ["missing.bin"])) + "\n")
+    return csv, names
+
+
+def _fake_worker(log):
+    def worker(path, inputs=None, writer=None):
+        if path.endswith("slide_2.bin"):
+            raise RuntimeError("boom")                              # a failing slide is reported and skipped
+        stats = {"bytes": len(inputs) if inputs is not None else os.path.getsize(path)}
+        log.append(os.path.basename(path))
+        if writer is not None:
+            def save():
+                if path.endswith("slide_4.bin"):
+                    raise OSError("disk full")                      # so is a slide whose save fails
+            stats["_pending_save"] = writer.submit(save)
+        return stats
+    return worker
+
+
+def test_dataset_loop_reads_ahead_and_keeps_the_error_convention(tmp_path):
+    import json
+    from hg_b200 import preprocess_hypergraph as pp
+    csv, names = _dataset_files(str(tmp_path), [100, 400, 50, 300, 200, 10])
+    for overlap in (True, False):
+        log = []
+        out = str(tmp_path / f"stats_{overlap}.json")
+        loader = (lambda p: open(p, "rb").read()) if overlap else None
+        res = pp._run_over_csv(csv, str(tmp_path), "test", _fake_worker(log), out, loader=loader)
+        want = ["c0", "c1", "c3", "c5"] if overlap else ["c0", "c1", "c3", "c4", "c5"]   # c4 fails only in its save
+        assert [r["case_id"] for r in res] == want
+        assert [r["bytes"] for r in res][:2] == [100, 400]
+        assert all("_pending_save" not in r for r in res)
+        assert len(json.load(open(out))) == len(want)
+        assert log == [n for n in names if n != "slide_2.bin"]      # CSV order, every present file once
+
+
+def _dataset_rank(rank, world, port, root, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from hg_b200 import preprocess_hypergraph as pp
+        log = []
+        res = pp._run_over_csv(os.path.join(root, "cases.csv"), root, "test", _fake_worker(log),
+                               os.path.join(root, "stats.json"), loader=lambda p: open(p, "rb").read())
+        q.put((rank, log, [r["case_id"] for r in res]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_dataset_loop_shards_slides_over_ranks(tmp_path):
+    import json
+    sizes = [100, 400, 50, 300, 200, 10, 350]
+    csv, names = _dataset_files(str(tmp_path), sizes)
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_dataset_rank, args=(r, world, port, str(tmp_path), q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = sorted(q.get(timeout=100) for _ in range(world))
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    logs = [set(r[1]) for r in results]
+    assert not (logs[0] & logs[1])                                   # every slide on exactly one rank
+    assert logs[0] | logs[1] == {n for n in names if n != "slide_2.bin"}
+    plan = multigpu.shard_slides(sizes, world)
+    assert logs[0] == {names[i] for i in plan[0] if i != 2}          # the LPT share of rank 0
+    want = ["c0", "c1", "c3", "c5", "c6"]                            # c2 fails in the worker, c4 in its save
+    assert all(r[2] == want for r in results)                        # every rank returns the gathered statistics
+    assert [s["case_id"] for s in json.load(open(tmp_path / "stats.json"))] == want
