@@ -27,7 +27,7 @@ __all__ = [
     "wsi_tma_similarity", "similarity_stats", "sq_dists_f64", "knn_feature",
     "knn_spatial", "edges_from_knn", "edge_weights_cosine", "threshold_edges",
     "csr_from_coo", "build_hypergraph_knn", "lower_median", "hypergraph_conv_propagate",
-    "aggregate_super_patches",
+    "aggregate_super_patches", "kmeans_fit",
 ]
 
 
@@ -375,3 +375,81 @@ def aggregate_super_patches(features, positions, labels, num_super_patches, K=No
     defined = intra[~np.isnan(intra)]
     avg = float(defined.mean()) if defined.size else 0.0
     return np.stack(sup_f), np.stack(sup_p), np.asarray(counts, dtype=np.int64), intra, avg
+
+
+# --------------------------------------------------------------------------
+# (f)1: KMeans(n_clusters, random_state, n_init=10) -- preprocess_hypergraph.py:150-151, 299-300, 391-392
+# --------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+
+
+def _km_mix(z: int) -> int:                       # splitmix64 finaliser (the device RNG of hg_kmeans_fit)
+    z = (z + 0x9E3779B97F4A7C15) & _M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def _km_rand(seed: int, run: int, step: int, t: int) -> int:
+    return _km_mix(_km_mix((seed ^ (run << 40)) & _M64) ^ ((step << 8) & _M64) ^ t)
+
+
+def kmeans_fit(features, n_clusters, n_init=10, max_iter=300, tol=1e-4, seed=42):
+    """The estimator the reference constructs, as scikit-learn (1.3 / 1.9) defines it -- the library is
+    not under /root/reference, so this restates its published algorithm (sklearn/cluster/_kmeans.py):
+    X centred on its column means; tolerance = tol * mean(var(X, axis=0)); per restart greedy k-means++
+    (`_kmeans_plusplus`: 2 + int(ln k) local trials, D^2 sampling by searchsorted on the cumulative sum,
+    the candidate with the smallest potential wins) then Lloyd until no label moves or the squared centre
+    shift is <= tolerance (`_kmeans_single_lloyd`), labels of the final centres, best restart by inertia.
+    scikit-learn draws from numpy's MT19937; the CUDA path cannot share that stream, so the random numbers
+    here are the counter-based ones of hg_kmeans_fit (kmeans.cu) -- which makes this restatement comparable
+    label for label with the device result.  Empty clusters keep their centre (scikit-learn relocates them;
+    neither happens on the test data).  Returns (labels int64 [n], centres float64 [k, d], inertia)."""
+    x32 = np.ascontiguousarray(features, dtype=np.float32)
+    n, d = x32.shape
+    if n < n_clusters:
+        raise ValueError(f"n_samples={n} should be >= n_clusters={n_clusters}.")
+    mean = x32.astype(np.float64).mean(0).astype(np.float32)
+    x = (x32 - mean).astype(np.float64)            # the device centres in FP32
+    tol_abs = tol * x32.astype(np.float64).var(0).mean()
+    trials = min(16, 2 + int(np.log(n_clusters)))
+    sq = (x * x).sum(1)
+
+    def d2_to(rows):                                # [len(rows), n]
+        c = x[rows]
+        return np.maximum(sq[None, :] + (c * c).sum(1)[:, None] - 2.0 * (c @ x.T), 0.0)
+
+    best = None
+    for run in range(n_init):
+        idx = [_km_rand(seed, run, 0, 0) % n]
+        closest = d2_to(idx)[0]
+        for step in range(1, n_clusters):
+            cum = np.cumsum(closest)
+            us = np.array([(_km_rand(seed, run, step, t) >> 11) * (1.0 / 9007199254740992.0) for t in range(trials)])
+            cand = np.minimum(np.searchsorted(cum, us * cum[-1], side="left"), n - 1)
+            pot = np.minimum(closest[None, :], d2_to(cand))
+            b = int(np.argmin(pot.sum(1)))
+            closest = pot[b]
+            idx.append(int(cand[b]))
+        centers = x[idx].copy()
+        prev = np.full(n, -1)
+        for _ in range(max_iter):
+            full = sq[:, None] + (centers * centers).sum(1)[None, :] - 2.0 * (x @ centers.T)
+            labels = full.argmin(1)
+            moved = int((labels != prev).sum())
+            new = centers.copy()
+            for c in range(n_clusters):
+                m = labels == c
+                if m.any():
+                    new[c] = x[m].mean(0).astype(np.float32)       # the device stores FP32 centres
+            shift = ((new - centers) ** 2).sum()
+            centers = new
+            prev = labels
+            if shift <= tol_abs or moved == 0:
+                break
+        full = np.maximum(sq[:, None] + (centers * centers).sum(1)[None, :] - 2.0 * (x @ centers.T), 0.0)
+        labels = full.argmin(1)
+        inertia = float(full[np.arange(n), labels].sum())
+        if best is None or inertia < best[2]:
+            best = (labels.astype(np.int64), centers + mean.astype(np.float64), inertia)
+    return best

@@ -7,6 +7,7 @@ import pytest
 import torch
 
 from hg_b200 import _lib, synth
+import oracle_np as oracle
 from hg_b200.kmeans import KMeans, kmeans
 
 pytestmark = pytest.mark.gpu
@@ -159,3 +160,18 @@ def test_nearly_constant_data_far_from_the_origin_converges(assign, monkeypatch)
     sk = SkKMeans(n_clusters=10, random_state=42, n_init=10).fit(x)
     assert inertia <= sk.inertia_ * 1.05 + 1e-9
     np.testing.assert_allclose(np.sort(centers.cpu().numpy().mean(1)), np.sort(sk.cluster_centers_.mean(1)), atol=2e-4)
+
+
+@pytest.mark.parametrize("assign", ["simt", "tc"])
+@pytest.mark.parametrize("n,d,c,n_init", [(600, 32, 5, 3), (1500, 64, 12, 2), (356, 1024, 10, 2)])
+def test_native_fit_matches_the_oracle_restatement(n, d, c, n_init, assign, monkeypatch):
+    """oracle.kmeans_fit runs the same estimator with the same counter-based random numbers in float64:
+    same seeds, same Lloyd trajectory -- labels may only differ where FP32 rounding breaks a near-tie"""
+    monkeypatch.setenv("HG_B200_KMEANS_TC", "1" if assign == "tc" else "0")
+    x = synth.make_features(n, d, 78, "gaussian")
+    labels, centers, inertia = kmeans(torch.from_numpy(x).cuda(), c, n_init=n_init, seed=11)
+    ref_labels, ref_centers, ref_inertia = oracle.kmeans_fit(x, c, n_init=n_init, seed=11)
+    assert (labels == ref_labels).mean() >= 0.995
+    assert abs(inertia - ref_inertia) <= 1e-4 * ref_inertia
+    if (labels == ref_labels).all():
+        np.testing.assert_allclose(centers.cpu().numpy(), ref_centers, rtol=1e-4, atol=1e-5)
