@@ -241,3 +241,54 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
     count_launches(1);
     return HG_OK;
 }
+
+
+// ---- A1 / A2 dense output for large square inputs: the tensor-core kernel in dense-output mode ----------------
+// K[i, j] = exp(-lambda_h (|x_i|^2 + |x_j|^2 - 2 x_i.x_j) - lambda_g |p_i - p_j|^2) for one matrix against itself
+// (similarity_kernel.py:43-52, :122), the Gram product as 3xBF16 MMAs with FP32 accumulation.  13-20x the
+// throughput of hg_similarity_dense from a few thousand rows up, but its entries are within ~1.5e-5 relative of
+// float64, not 1e-5 (tests/test_gpu_parity.py::test_dense_tc_opt_in_accuracy): opt-in on the Python side.
+extern "C" int hg_similarity_dense_tc_workspace_bytes(int64_t n, int64_t d, size_t* bytes) {
+    HG_REQUIRE(bytes && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_similarity_dense_tc_workspace_bytes: bad argument");
+    const int64_t n_pad = ops_rows(n);
+    auto al = [](size_t b) { return (b + 1023) & ~size_t(1023); };
+    *bytes = al(hg_operand_bytes(n, d)) + al(size_t(n_pad) * 4) + al(size_t(n_pad) * 8) + al(size_t(n_pad) * 16);
+    return HG_OK;
+}
+
+extern "C" int hg_similarity_dense_tc(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
+                                      float lambda_h, float lambda_g, float* out, int64_t ld_out,
+                                      void* workspace, size_t workspace_bytes, void* stream) {
+    HG_REQUIRE(feats && out && n > 0 && d > 0 && ld_out >= n, HG_ERR_BAD_ARG, "hg_similarity_dense_tc: bad argument");
+    HG_REQUIRE(lambda_h > 0.f, HG_ERR_UNSUPPORTED, "hg_similarity_dense_tc: lambda_h must be > 0");
+    if (lambda_g == 0.f) pos = nullptr;
+    HG_REQUIRE(pos == nullptr || (pos_dim >= 1 && pos_dim <= 3), HG_ERR_UNSUPPORTED, "pos_dim must be 1..3");
+    size_t need = 0;
+    hg_similarity_dense_tc_workspace_bytes(n, d, &need);
+    HG_REQUIRE(workspace && workspace_bytes >= need, HG_ERR_WORKSPACE, "hg_similarity_dense_tc: workspace too small");
+    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "workspace must be 1024-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
+    char* ws = static_cast<char*>(workspace);
+    auto al = [](size_t b) { return (b + 1023) & ~size_t(1023); };
+    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws);
+    ws += al(hg_operand_bytes(n, d));
+    float* norms = reinterpret_cast<float*>(ws);
+    ws += al(size_t(n_pad) * 4);
+    float2* colp = reinterpret_cast<float2*>(ws);
+    ws += al(size_t(n_pad) * 8);
+    float4* pos4 = pos ? reinterpret_cast<float4*>(ws) : nullptr;
+    int rc = launch_split(feats, n, d, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    rc = launch_colparams(norms, pos, pos_dim, n, n_pad, HG_METRIC_GAUSSIAN, colp, pos4, st);
+    if (rc != HG_OK) return rc;
+    TcParams tp{};
+    tp.n = n; tp.row_begin = 0; tp.row_end = n; tp.d_pad = int(d_pad);
+    tp.plan = tc_make_plan(n, n, 1, d_pad, false);
+    tp.plan.kl = 0;                                            // dense-output mode
+    tp.colp = colp; tp.pos4 = pos4;
+    tp.gscale = pos ? lambda_g / lambda_h : 0.f;
+    tp.exclude_self = 0;
+    tp.dense_out = out; tp.dense_ld = ld_out; tp.lambda_h = lambda_h;
+    return tc_launch(ops, n_pad, tp, st);
+}

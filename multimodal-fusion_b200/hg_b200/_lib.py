@@ -53,6 +53,8 @@ SIGNATURES = {
     "hg_similarity_dense": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i32, _f32, _f32, _i32, _vp, _i64, _vp]),
     "hg_stats_workspace_bytes": (_i32, [_i64, _psz]),
     "hg_similarity_stats": (_i32, [_vp, _i64, _i64, _vp, _vp, _sz, _vp]),
+    "hg_similarity_dense_tc_workspace_bytes": (_i32, [_i64, _i64, _psz]),
+    "hg_similarity_dense_tc": (_i32, [_vp, _i64, _i64, _vp, _i32, _f32, _f32, _vp, _i64, _vp, _sz, _vp]),
     "hg_similarity_stats_streaming_workspace_bytes": (_i32, [_i64, _i64, _psz]),
     "hg_similarity_stats_streaming": (_i32, [_vp, _i64, _i64, _vp, _i32, _f32, _f32, _vp, _vp, _sz, _vp]),
     "hg_knn_spatial_workspace_bytes": (_i32, [_i64, _i32, _i64, _i64, _psz]),

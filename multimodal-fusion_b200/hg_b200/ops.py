@@ -3,6 +3,7 @@ passes raw pointers to libhg_b200.so.  One function per kernel family."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence, Tuple
 
 import numpy as np
@@ -139,6 +140,19 @@ def knn_spatial(positions: torch.Tensor, k: int, rows: Optional[Tuple[int, int]]
 
 
 # ------------------------------------------------------------------- dense kernels
+# Rows from which square expansion-form kernels go through the tcgen05 kernel's dense-output mode; 0 (default) =
+# never.  The mode is 13-20x faster than the FP32 SIMT tiles (N = 16,384 x 1024: 20.6 -> 1.16 ms) but its entries
+# are only within ~1.5e-5 relative of float64 (measured maximum 1.4e-5 at D = 1024: the rounding of the 3xBF16
+# product and of the tensor core's FP32 accumulation over 192 MMA steps), which misses the 1e-5 bar of the scope
+# contract -- so it is opt-in: HG_B200_DENSE_TC_MIN_N=4096.  The kNN path is not affected: it re-ranks in FP32.
+DENSE_TC_MIN_N = int(os.environ.get("HG_B200_DENSE_TC_MIN_N", "0"))
+
+
+def _dense_on_tensor_cores(xb, pb, n: int, d: int, lambda_h: float, form: int) -> bool:
+    return (DENSE_TC_MIN_N > 0 and xb is None and pb is None and form == L.FORM_EXPANSION and lambda_h > 0
+            and n >= DENSE_TC_MIN_N and d >= 64)
+
+
 def similarity_dense(a: torch.Tensor, b: Optional[torch.Tensor] = None,
                      pos_a: Optional[torch.Tensor] = None, pos_b: Optional[torch.Tensor] = None,
                      lambda_h: float = 1.0, lambda_g: float = 0.0, form: int = L.FORM_EXPANSION,
@@ -154,6 +168,14 @@ def similarity_dense(a: torch.Tensor, b: Optional[torch.Tensor] = None,
     n = m if xb is None else xb.shape[0]
     out = torch.empty((m, n), dtype=torch.float32, device=dev)
     if m == 0 or n == 0:
+        return out
+    if _dense_on_tensor_cores(xb, None if (pos_b is None or pos_b is pos_a) else pb, m, d, lambda_h, form):
+        with torch.cuda.device(dev):
+            nbytes = _size(lib.hg_similarity_dense_tc_workspace_bytes, m, d)
+            ws = L.Workspace.get(dev, nbytes, "dense_tc")
+            L.check(lib.hg_similarity_dense_tc(L.ptr(xa), m, d, L.ptr(pa), 0 if pa is None else pa.shape[1],
+                                               float(lambda_h), float(lambda_g if pa is not None else 0.0), L.ptr(out), n,
+                                               L.ptr(ws), nbytes, L.stream_ptr(dev)))
         return out
     with torch.cuda.device(dev):
         L.check(lib.hg_similarity_dense(L.ptr(xa), m, L.ptr(xb), n, d, L.ptr(pa), L.ptr(pb),

@@ -62,7 +62,9 @@ def test_python_surface_mirrors_reference():
     sig = inspect.signature(hg_b200.build_weighted_hypergraph)
     assert list(sig.parameters) == ["features", "positions", "lambda_h", "lambda_g", "threshold_median_ratio", "device"]
     sig = inspect.signature(hg_b200.process_single_file)
-    assert [p.default for p in list(sig.parameters.values())[1:]] == [100, 10, 5, 10, 1.0, 1.0, None]
+    params = list(sig.parameters.values())
+    assert [p.default for p in params[1:8]] == [100, 10, 5, 10, 1.0, 1.0, None]
+    assert all(p.kind is inspect.Parameter.KEYWORD_ONLY for p in params[8:])      # extras never shift the reference's arguments
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
