@@ -149,6 +149,94 @@ sim_tile_kernel(SimArgs p) {
     }
 }
 
+// Dense expansion-form kernel for larger outputs: 128 x 128 tile per 256-thread CTA, 8 x 8 outputs per thread (four
+// 4 x 4 blocks, 64 apart, so the shared-memory reads stay conflict-free LDS.128), BK = 16, two shared-memory
+// buffers with the next k-block prefetched into registers while the current one is multiplied.  The squared norms
+// are not re-accumulated by every thread as in the 64 x 64 kernel (8 extra FMAs per 16 there): thread t < 128 owns
+// row t's norm, thread 128 + t column t's, one FMA per k.  Every accumulator is the same k-ordered FMA chain as
+// in sim_tile_kernel, so both kernels return identical bits.
+constexpr int BM2 = 128, BN2 = 128;
+
+template <bool VEC>
+__global__ void __launch_bounds__(256, 2)
+sim_tile128_kernel(SimArgs p) {
+    __shared__ __align__(16) float As[2][BK][BM2 + PADT];
+    __shared__ __align__(16) float Bs[2][BK][BN2 + PADT];
+    __shared__ float sna[BM2], snb[BN2];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int lr = tid >> 2, lk = (tid & 3) * 4;     // loader: rows lr and lr + 64 of the tile, k offset lk
+    const int64_t row0 = int64_t(blockIdx.y) * BM2, col0 = int64_t(blockIdx.x) * BN2;
+
+    float acc[8][8] = {};
+    float nrm = 0.f;                                  // |a_row|^2 (tid < 128) or |b_col|^2 (tid >= 128)
+    float ra[2][4], rb[2][4];
+    auto fetch = [&](int64_t k0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            load4<VEC>(p.a, p.m, p.d, row0 + lr + 64 * h, k0 + lk, ra[h]);
+            load4<VEC>(p.b, p.n, p.d, col0 + lr + 64 * h, k0 + lk, rb[h]);
+        }
+    };
+    auto stash = [&](int buf) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { As[buf][lk + q][lr + 64 * h] = ra[h][q]; Bs[buf][lk + q][lr + 64 * h] = rb[h][q]; }
+    };
+    fetch(0);
+    stash(0);
+    __syncthreads();
+    int buf = 0;
+    for (int64_t k0 = 0; k0 < p.d; k0 += BK) {
+        const bool more = k0 + BK < p.d;
+        if (more) fetch(k0 + BK);                      // global loads in flight during the multiply
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][kk][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][kk][64 + ty * 4]);
+            const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][kk][tx * 4]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][kk][64 + tx * 4]);
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            const float v = (tid < BM2) ? As[buf][kk][tid] : Bs[buf][kk][tid - BM2];
+            nrm = fmaf(v, v, nrm);
+        }
+        if (more) {
+            stash(buf ^ 1);                            // nobody reads buf ^ 1 any more: its readers passed the barrier below
+            __syncthreads();
+            buf ^= 1;
+        }
+    }
+    if (tid < BM2) sna[tid] = nrm; else snb[tid - BM2] = nrm;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int li = (i < 4) ? ty * 4 + i : 64 + ty * 4 + (i - 4);
+        const int64_t r = row0 + li;
+        if (r >= p.m) continue;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int lj = (j < 4) ? tx * 4 + j : 64 + tx * 4 + (j - 4);
+            const int64_t c = col0 + lj;
+            if (c >= p.n) continue;
+            const float d2 = (sna[li] + snb[lj]) - 2.f * acc[i][j];
+            float d2g = 0.f;
+            if (p.pa != nullptr) {
+                for (int q = 0; q < p.pos_dim; ++q) {
+                    const float df = __ldg(p.pa + r * p.pos_dim + q) - __ldg(p.pb + c * p.pos_dim + q);
+                    d2g = fmaf(df, df, d2g);
+                }
+            }
+            p.out[r * p.ld_out + c] = expf(-(p.lambda_h * d2 + p.lambda_g * d2g));
+        }
+    }
+}
+
 static bool vec_ok(const float* a, const float* b, int64_t d) {
     return d % 4 == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0;
 }
@@ -156,7 +244,11 @@ static bool vec_ok(const float* a, const float* b, int64_t d) {
 int launch_dense(const SimArgs& p, int form, cudaStream_t st) {
     dim3 grid((unsigned)ceil_div(p.n, BN), (unsigned)ceil_div(p.m, BM));
     const bool v = vec_ok(p.a, p.b, p.d);
-    if (form == HG_FORM_DIRECT) {
+    if (form != HG_FORM_DIRECT && p.m >= 512 && p.n >= 512) {          // enough 128 x 128 tiles to fill the SMs
+        dim3 grid2((unsigned)ceil_div(p.n, BN2), (unsigned)ceil_div(p.m, BM2));
+        if (v) sim_tile128_kernel<true><<<grid2, 256, 0, st>>>(p);
+        else   sim_tile128_kernel<false><<<grid2, 256, 0, st>>>(p);
+    } else if (form == HG_FORM_DIRECT) {
         if (v) sim_tile_kernel<MODE_DENSE, HG_FORM_DIRECT, true, 1><<<grid, 256, 0, st>>>(p);
         else   sim_tile_kernel<MODE_DENSE, HG_FORM_DIRECT, false, 1><<<grid, 256, 0, st>>>(p);
     } else {

@@ -407,3 +407,25 @@ def test_dense_tc_opt_in_accuracy(n, d, with_pos, monkeypatch):
     if with_pos:
         Kc = hg.compute_combined_similarity(x, p, lam_h, lam_g)       # the reference-facing entry takes the same path
         assert torch.equal(Kc, K)
+
+
+@pytest.mark.parametrize("m,n,d,with_pos", [(1000, 700, 96, True), (513, 2049, 1024, False), (640, 640, 33, True), (4096, 4096, 256, False)])
+def test_dense_128_tile_kernel_equals_the_64_tile_kernel(m, n, d, with_pos):
+    """outputs of at least 512 x 512 run on the 128 x 128-tile kernel; slices below that size run on the 64 x 64 one:
+    same k-ordered FMA chains, so identical bits (and the float64 kernel within 1e-5)"""
+    a = synth.make_features(m, d, 51, "gaussian")
+    b = synth.make_features(n, d, 52, "gaussian")
+    pa, pb = (synth.make_positions(m, 53), synth.make_positions(n, 54)) if with_pos else (None, None)
+    kw = dict(lambda_h=1.0, lambda_g=1.0 / 4096 if with_pos else 0.0)
+    A, B = _cuda(a), _cuda(b)
+    PA, PB = (_cuda(pa), _cuda(pb)) if with_pos else (None, None)
+    K = ops.similarity_dense(A, B, pos_a=PA, pos_b=PB, **kw)
+    for r0 in range(0, m, 400):                                    # 400-row slices: the 64 x 64-tile kernel
+        part = ops.similarity_dense(A[r0:r0 + 400].contiguous(), B, pos_a=PA[r0:r0 + 400].contiguous() if with_pos else None,
+                                    pos_b=PB, **kw)
+        assert torch.equal(K[r0:r0 + 400], part)
+    rows = np.random.default_rng(6).choice(m, 64, replace=False)
+    d2 = oracle.sq_dists_f64(a[rows].astype(np.float64), b.astype(np.float64))
+    if with_pos:
+        d2 = d2 + kw["lambda_g"] * ((pa[rows, None, :].astype(np.float64) - pb[None, :, :].astype(np.float64)) ** 2).sum(-1)
+    np.testing.assert_allclose(K[torch.from_numpy(rows).cuda()].cpu().numpy(), np.exp(-d2), rtol=RTOL, atol=1e-30)
