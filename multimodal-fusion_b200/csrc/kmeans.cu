@@ -179,7 +179,7 @@ constexpr int KM_POLL = 4;        // Lloyd iterations enqueued between two reads
 struct KmState {                  // device scalars of a fit (one 256-byte slot of the workspace)
     double tol_abs, best_inertia;
     unsigned long long moved;
-    int done, n_iter, best_t, take, best_iter;
+    int done, n_iter, best_t, take;
 };
 
 __device__ __forceinline__ uint64_t km_mix(uint64_t z) {        // splitmix64 finaliser
@@ -237,7 +237,7 @@ __global__ void km_tol_kernel(const double* __restrict__ part, int nrb, int64_t 
         mean_out[j] = float(mean);
     }
     const double tot = km_block_sum(acc, sh);
-    if (threadIdx.x == 0) { st->tol_abs = tol * tot / double(d); st->best_inertia = 0.0; st->best_iter = 0; }
+    if (threadIdx.x == 0) { st->tol_abs = tol * tot / double(d); st->best_inertia = 0.0; }
 }
 
 // xc = x - column means: distances do not change, but the FP32 expansion |x|^2 + |c|^2 - 2 x.c and the BF16
@@ -511,7 +511,7 @@ __global__ void km_best_kernel(const double* __restrict__ tile_sums, int64_t nti
     const int take = (run == 0 || s < st->best_inertia) ? 1 : 0;
     st->take = take;
     if (take) {
-        st->best_inertia = s; st->best_iter = st->n_iter;
+        st->best_inertia = s;
         *inertia_out = s;
         if (n_iter_out) *n_iter_out = st->n_iter;
     }
@@ -836,7 +836,7 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
 
     km_colstats_kernel<<<grid_rc, 256, 0, st>>>(x, n, d, pl.rows_per, reinterpret_cast<double*>(part));
     km_tol_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const double*>(part), pl.nrb, n, d, tol, state, mean);
-    km_center_kernel<<<(unsigned)pl.nrb, 256, 0, st>>>(x, n, d, mean, pl.rows_per, xc);
+    km_center_kernel<<<(unsigned)ceil_div(n, 64), 256, 0, st>>>(x, n, d, mean, 64, xc);
     HG_CHECK_LAUNCH();
     count_launches(3);
     x = xc;                                                                 // everything below works on the centred rows
