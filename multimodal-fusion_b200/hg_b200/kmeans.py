@@ -116,15 +116,36 @@ def kmeans_stepwise(features: torch.Tensor, n_clusters: int, n_init: int = 10, m
 
 
 class KMeans:
-    """The slice of scikit-learn's estimator API the reference uses: KMeans(...).fit_predict(X)."""
+    """The slice of scikit-learn's estimator API the reference uses -- KMeans(...).fit_predict(X) -- plus
+    fit / predict and the fitted attributes (labels_, cluster_centers_, inertia_, n_iter_)."""
 
     def __init__(self, n_clusters: int = 8, random_state: int = 42, n_init: int = 10, max_iter: int = 300,
                  tol: float = 1e-4):
         self.n_clusters, self.random_state, self.n_init, self.max_iter, self.tol = \
             n_clusters, random_state, n_init, max_iter, tol
 
-    def fit_predict(self, X) -> np.ndarray:
-        t = X if isinstance(X, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
+    @staticmethod
+    def _tensor(X) -> torch.Tensor:
+        return X if isinstance(X, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
+
+    def fit(self, X) -> "KMeans":
         self.labels_, self.cluster_centers_, self.inertia_ = kmeans(
-            t, self.n_clusters, self.n_init, self.max_iter, self.tol, seed=int(self.random_state or 0))
-        return self.labels_
+            self._tensor(X), self.n_clusters, self.n_init, self.max_iter, self.tol, seed=int(self.random_state or 0))
+        self.n_iter_ = LAST_N_ITER
+        return self
+
+    def fit_predict(self, X) -> np.ndarray:
+        return self.fit(X).labels_
+
+    def predict(self, X) -> np.ndarray:
+        """nearest fitted centre of every row (hg_kmeans_assign)"""
+        lib = L.load_library()
+        cen = self.cluster_centers_
+        x = L.f32c(self._tensor(X), cen.device)
+        n, d = x.shape
+        labels = torch.empty(n, dtype=torch.int32, device=cen.device)
+        d2 = torch.empty(n, dtype=torch.float32, device=cen.device)
+        with torch.cuda.device(cen.device):
+            L.check(lib.hg_kmeans_assign(L.ptr(x), n, d, L.ptr(cen), cen.shape[0], L.ptr(labels), L.ptr(d2),
+                                         L.stream_ptr(cen.device)))
+        return labels.cpu().numpy().astype(np.int64)

@@ -58,7 +58,9 @@ def test_inertia_on_par_with_sklearn(n, d, c):
     ref = ((x.astype(np.float64) - cen[labels]) ** 2).sum()
     assert np.isclose(inertia, ref, rtol=1e-4)
     est = KMeans(n_clusters=c, random_state=42, n_init=2)
-    assert est.fit_predict(x).shape == (n,) and est.inertia_ > 0
+    assert est.fit_predict(x).shape == (n,) and est.inertia_ > 0 and 1 <= est.n_iter_ <= 300
+    again = est.predict(x)                                              # labels of a fit are its own nearest centres
+    assert (again == est.labels_).mean() > 0.999
 
 
 def test_pipeline_with_cuda_kmeans(monkeypatch):
