@@ -62,7 +62,29 @@ class ClockSampler:
         self.rows = []
         self.proc = None
 
+    # NVML is polled every few milliseconds (a 10-step timed region is ~70 ms: nvidia-smi's 100 ms loop would
+    # see it once); nvidia-smi -lms is the fallback when the binding is missing.
+    _REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
     def start(self):
+        self.nvml = None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            uuid = torch.cuda.get_device_properties(self.gpu).uuid
+            try:
+                handle = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(uuid))
+            except Exception:                                   # noqa: BLE001 -- older bindings / odd UUID form
+                handle = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            self.nvml = (pynvml, handle)
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception as e:                                  # noqa: BLE001
+            print(f"[bench] NVML polling unavailable ({type(e).__name__}: {e}); falling back to nvidia-smi", file=sys.stderr)
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
@@ -71,15 +93,33 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        pynvml, h = self.nvml
+        mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        while not self._stop.is_set():
+            try:
+                sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                mask = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)) if hasattr(
+                    pynvml, "nvmlDeviceGetCurrentClocksEventReasons") else int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                row = ["", sm, mx, "", ""] + [("Active" if mask & bit else "Not Active") for _, bit in self._REASONS]
+                self.rows.append(row)
+            except Exception:                                   # noqa: BLE001
+                pass
+            self._stop.wait(0.004)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self) -> dict:
-        if self.proc is None:
+        if self.nvml is not None:
+            self._stop.set()
+            self.thread.join(1.0)
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
         sm, mx, reasons = [], [], set()
         for r in self.rows:
             try:
@@ -88,10 +128,10 @@ class ClockSampler:
                 continue
             for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
                               ("sw_power_cap", 8)):
-                if len(r) > col and r[col].lower().startswith("active"):
+                if len(r) > col and str(r[col]).lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi", "reasons": sorted(reasons)}
 
 
 # ------------------------------------------------------------------------ reference CPU path
