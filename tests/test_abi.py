@@ -73,3 +73,20 @@ def test_no_cpu_fallback():
         hg_b200.compute_morphological_similarity(torch.randn(4, 8))
     with pytest.raises(RuntimeError):
         hg_b200.build_hypergraph_knn_kmeans(torch.randn(8, 4), torch.randn(8, 4), None)
+
+
+def test_dense_tensor_core_routing_is_opt_in(monkeypatch):
+    """A1 / A2 dense outputs stay on the FP32 kernels (1e-5 bar) unless HG_B200_DENSE_TC_MIN_N asks otherwise, and
+    even then only square expansion-form kernels of one matrix against itself qualify"""
+    from hg_b200 import _lib, ops
+    fake = object()
+    assert ops.DENSE_TC_MIN_N == 0
+    assert not ops._dense_on_tensor_cores(None, None, 50000, 1024, 1.0, _lib.FORM_EXPANSION)
+    monkeypatch.setattr(ops, "DENSE_TC_MIN_N", 4096)
+    assert ops._dense_on_tensor_cores(None, None, 4096, 1024, 1.0, _lib.FORM_EXPANSION)
+    assert not ops._dense_on_tensor_cores(None, None, 4095, 1024, 1.0, _lib.FORM_EXPANSION)     # below the cut-over
+    assert not ops._dense_on_tensor_cores(fake, None, 8192, 1024, 1.0, _lib.FORM_EXPANSION)     # rectangular (A7)
+    assert not ops._dense_on_tensor_cores(None, fake, 8192, 1024, 1.0, _lib.FORM_EXPANSION)     # other positions
+    assert not ops._dense_on_tensor_cores(None, None, 8192, 1024, 1.0, _lib.FORM_DIRECT)        # direct-difference form
+    assert not ops._dense_on_tensor_cores(None, None, 8192, 1024, 0.0, _lib.FORM_EXPANSION)     # lambda_h = 0
+    assert not ops._dense_on_tensor_cores(None, None, 8192, 2, 1.0, _lib.FORM_EXPANSION)        # K_g alone (D = 2)
