@@ -19,7 +19,7 @@ void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed);
 // CUDA-event pairs recorded around the fused tensor-core kernel on its own stream, so a
 // benchmark can report that kernel's duration without a profiler attached.
 constexpr int kProfSlots = 4096;
-static bool g_prof_on = false;
+static std::atomic<bool> g_prof_on{false};      // read by every enqueueing host thread
 static cudaEvent_t g_prof_ev[2 * kProfSlots];
 static bool g_prof_made = false;
 static std::atomic<int> g_prof_used{0};
@@ -27,7 +27,7 @@ static thread_local int t_prof_slot = -1;          // builds may be enqueued fro
 
 void prof_begin(cudaStream_t st) {
     t_prof_slot = -1;
-    if (!g_prof_on) return;
+    if (!g_prof_on.load(std::memory_order_acquire)) return;
     const int slot = g_prof_used.fetch_add(1);
     if (slot >= kProfSlots) return;
     t_prof_slot = slot;
@@ -49,8 +49,8 @@ extern "C" int hg_profile_enable(int on) {
         for (int i = 0; i < 2 * hg::kProfSlots; ++i) HG_CHECK_CUDA(cudaEventCreate(&hg::g_prof_ev[i]));
         hg::g_prof_made = true;
     }
-    hg::g_prof_on = on != 0;
     hg::g_prof_used.store(0);
+    hg::g_prof_on.store(on != 0, std::memory_order_release);
     return HG_OK;
 }
 

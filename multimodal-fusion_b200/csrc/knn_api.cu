@@ -8,7 +8,8 @@
 namespace hg {
 
 struct KnnWs {
-    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_thr, off_cnt, off_ovf, off_bkt, bytes;
+    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_thr, off_cnt, off_ovf, off_bkt, off_unc_rows,
+        off_unc_part, bytes;
     TcPlan plan;                 // classic plan (the only one, or the overflow fallback of symmetric mode)
     TcPlan sym_plan, pre_plan;   // symmetric mode: main pass and threshold pre-pass
     int sym_stride;              // 0 = classic
@@ -52,7 +53,9 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     const size_t part = size_t(max_splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
-    w.off_ovf = take(8);                        // overflow flag, largest squared norm
+    w.off_ovf = take(16);                       // overflow flag, largest squared norm, uncertified-row counter
+    w.off_unc_rows = take(size_t(w.plan.n_rows) * 4);
+    w.off_unc_part = take(rerank_unc_part_bytes(w.plan.n_rows, k));
     if (w.sym_stride > 0) {
         w.off_thr = take(size_t(w.n_pad) * 4);
         w.off_cnt = take(size_t(w.n_pad) * 4);
@@ -169,7 +172,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rc = launch_split(feats, n, d, ops, norms, st);
     if (rc != HG_OK) return rc;
     float* norm_max = reinterpret_cast<float*>(ws + w.off_ovf) + 1;
-    HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 8, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 16, st));
     rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st, thr, bkt_cnt, norm_max);
     if (rc != HG_OK) return rc;
 
@@ -216,6 +219,10 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
+    rp.unc_cnt = ovf + 2;
+    rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
+    rp.exclude_self = exclude_self;
     rc = rerank_launch(rp, st);
     if (rc == HG_OK && sym && getenv("HG_B200_TC_DEBUG")) {      // tuning aid: bucket occupancy (synchronises)
         std::vector<int32_t> cnt(static_cast<size_t>(n), 0);
@@ -228,6 +235,12 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         fprintf(stderr, "hg_b200 sym: n=%lld stride=%d splits=%d cps=%d pre_ct=%d bucket mean=%.1f max=%d ovf=%d\n",
                 (long long)n, w.sym_stride, w.sym_plan.splits, w.sym_plan.ct_per_split, w.pre_plan.num_ct,
                 double(sum) / double(n), mx, h_ovf);
+    }
+    if (rc == HG_OK && getenv("HG_B200_TC_DEBUG")) {             // tuning aid: rows sent to the exact fallback (synchronises)
+        int h_unc = 0;
+        HG_CHECK_CUDA(cudaStreamSynchronize(st));
+        HG_CHECK_CUDA(cudaMemcpy(&h_unc, ovf + 2, 4, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "hg_b200 rerank: %d of %lld rows uncertified -> exact fallback\n", h_unc, (long long)(row_end - row_begin));
     }
     return rc;
 }
@@ -247,7 +260,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
 namespace hg {
 
 struct StagedWs {
-    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_flags, bytes;
+    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_flags, off_unc_rows, off_unc_part, bytes;
     int spp;                     // list slots (column splits) per sweep
     int lanes;                   // independent slot sets: sweeps on different lanes may run concurrently
     int kl;
@@ -297,7 +310,9 @@ static int staged_plan(const hg_knn_staged* s, StagedWs* w) {
     const size_t part = size_t(w->lanes) * w->spp * size_t(w->n_rows) * size_t(w->kl);
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
-    w->off_flags = take(8);
+    w->off_flags = take(16);                     // (unused flag, largest squared norm, uncertified-row counter)
+    w->off_unc_rows = take(size_t(w->n_rows) * 4);
+    w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
     w->bytes = off;
     return HG_OK;
 }
@@ -333,7 +348,7 @@ extern "C" int hg_knn_staged_begin(const hg_knn_staged* s, void* workspace, size
     if (rc != HG_OK) return rc;
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 8, st));                  // (unused flag, largest squared norm)
+    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 16, st));
     // every list slot starts empty (index -1); the panel launches carry them forward
     const size_t part = size_t(w.lanes) * w.spp * size_t(w.n_rows) * size_t(w.kl);
     HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_pidx, 0xff, part * 4, st));
@@ -418,5 +433,9 @@ extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_a
     rp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
     rp.splits = w.lanes * w.spp; rp.kl = w.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
+    rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
+    rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
+    rp.exclude_self = s->exclude_self;
     return rerank_launch(rp, static_cast<cudaStream_t>(stream));
 }

@@ -99,7 +99,14 @@ struct RerankParams {
     int k;
     int32_t* out_idx; float* out_val;
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
+    // certification fallback (rerank.cu): rows whose lists cannot vouch for the exact top-k are appended to
+    // unc_rows (counter *unc_cnt, zeroed by the caller) and recomputed exactly against all n columns;
+    // unc_part = [n_rows][RR_UNC_SLICES][k] scratch.  All three null: no certification.
+    int32_t* unc_rows; int32_t* unc_cnt; uint2* unc_part;
+    int exclude_self;            // the fallback skips column == row (the lists already did)
 };
+constexpr int RR_UNC_SLICES = 8;
+inline size_t rerank_unc_part_bytes(int64_t n_rows, int k) { return size_t(n_rows) * RR_UNC_SLICES * size_t(k) * 8; }
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
                      const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st);

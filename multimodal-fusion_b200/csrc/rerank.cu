@@ -64,6 +64,80 @@ constexpr int RR_MAX_CAND = RR_MAX_LIST + TC_BKT_CAP; // + the row's bucket (sym
 
 enum { RR_D2 = 0, RR_D2_DOT = 1, RR_DOT = 2 };       // what the exact pass accumulates per candidate
 
+
+// Exact sums of one query row against CB candidate rows by one warp, in the canonical order of
+// rowdot.cuh (lane l owns the float4 groups l, l + 32, ...; packed FMA pairs; xor butterfly): one read
+// of the query row serves CB rows of sums and the CB reductions overlap.  Shared by the re-rank and by
+// the exact fallback of uncertified rows, so both produce the same bits for the same pair.
+template <bool WANT_D2, bool WANT_DOT, int CB>
+__device__ __forceinline__ void warp_pair_sums(const float* __restrict__ xi, const float* const (&xj)[CB], int64_t d,
+                                               int lane, bool vec, float (&d2)[CB], float (&dt)[CB]) {
+    if (vec) {
+        uint64_t ad[CB], at[CB];
+#pragma unroll
+        for (int q = 0; q < CB; ++q) { ad[q] = 0; at[q] = 0; }
+#pragma unroll 2
+        for (int64_t v = lane; v < (d >> 2); v += 32) {
+            const ulonglong2 x = __ldg(reinterpret_cast<const ulonglong2*>(xi) + v);
+            ulonglong2 y[CB];
+#pragma unroll
+            for (int q = 0; q < CB; ++q) y[q] = __ldg(reinterpret_cast<const ulonglong2*>(xj[q]) + v);
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                if (WANT_D2) {
+                    const uint64_t e0 = pk_sub(x.x, y[q].x), e1 = pk_sub(x.y, y[q].y);
+                    ad[q] = pk_fma(e0, e0, ad[q]); ad[q] = pk_fma(e1, e1, ad[q]);
+                }
+                if (WANT_DOT) { at[q] = pk_fma(x.x, y[q].x, at[q]); at[q] = pk_fma(x.y, y[q].y, at[q]); }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < CB; ++q) { d2[q] = pk_hsum(ad[q]); dt[q] = pk_hsum(at[q]); }
+    } else {
+#pragma unroll
+        for (int q = 0; q < CB; ++q) { d2[q] = 0.f; dt[q] = 0.f; }
+        for (int64_t c = lane; c < d; c += 32) {
+            const float x = __ldg(xi + c);
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                const float y = __ldg(xj[q] + c);
+                if (WANT_D2) { const float df = x - y; d2[q] = fmaf(df, df, d2[q]); }
+                if (WANT_DOT) dt[q] = fmaf(x, y, dt[q]);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int q = 0; q < CB; ++q) {
+            if (WANT_D2) d2[q] += __shfl_xor_sync(0xffffffffu, d2[q], o);
+            if (WANT_DOT) dt[q] += __shfl_xor_sync(0xffffffffu, dt[q], o);
+        }
+    }
+}
+
+// ranking key (ascending), returned value and cosine of the pair (row, j) from its exact sums
+template <int MODE>
+__device__ __forceinline__ void exact_key(const RerankParams& p, int64_t row, int j, float d2, float dot, float ni,
+                                          float& key, float& out, float& cs) {
+    cs = (MODE != RR_D2) ? cosine_from(dot, ni, __ldg(p.sq_norms + j)) : 0.f;
+    if (MODE == RR_DOT) {
+        key = -cs; out = cs;
+    } else if (p.metric == HG_METRIC_EUCLIDEAN) {
+        key = d2; out = d2;
+    } else {
+        float d2g = 0.f;
+        if (p.pos != nullptr) {
+            for (int c = 0; c < p.pos_dim; ++c) {
+                const float df = __ldg(p.pos + row * p.pos_dim + c) - __ldg(p.pos + int64_t(j) * p.pos_dim + c);
+                d2g = fmaf(df, df, d2g);
+            }
+        }
+        key = p.lambda_h * d2 + p.lambda_g * d2g;
+        out = expf(-key);
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(RR_WARPS * 32, 3)
 rerank_kernel(const RerankParams p) {
@@ -104,7 +178,8 @@ rerank_kernel(const RerankParams p) {
     int sel = -1;                                    // candidate column held by this lane (lane < kl)
     int nsel = 0;
     float kth = INFINITY;
-    for (int t = 0; t < p.kl; ++t) {
+    bool uncert = false;
+    for (int t = 0; t <= p.kl; ++t) {
         float bv = INFINITY; int bi = 0x7fffffff;
 #pragma unroll
         for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
@@ -120,6 +195,8 @@ rerank_kernel(const RerankParams p) {
         if (bi == 0x7fffffff) break;                 // fewer than kl real candidates
         if (t == p.k - 1) kth = bv;
         if (t >= p.k && bv > kth + slack) break;
+        // kl candidates taken and the next one is still inside the slack: the exact top-k may need it
+        if (t == p.kl) { uncert = true; break; }
 #pragma unroll
         for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
             if (q * 32 >= ncand) break;
@@ -127,6 +204,19 @@ rerank_kernel(const RerankParams p) {
         }
         if (lane == t) sel = bi;
         nsel = t + 1;
+    }
+    // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
+    // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still
+    // belong to the exact top-k (many near-duplicates, or k close to kl): the row goes to the exact
+    // fallback (exact_slices_kernel) instead of being returned as the approximate set re-ordered.
+    if (p.unc_cnt != nullptr) {
+        bool full_inside = false;
+        for (int s2 = lane; s2 < splits; s2 += 32) {
+            const int64_t o = (int64_t(s2) * p.n_rows + r) * p.kl + (p.kl - 1);
+            full_inside |= p.part_idx[o] >= 0 && p.part_val[o] <= kth + slack;
+        }
+        uncert = __any_sync(0xffffffffu, uncert || full_inside);
+        if (uncert && lane == 0) p.unc_rows[atomicAdd(p.unc_cnt, 1)] = int32_t(r);
     }
 
     // ---- 2. exact values: sum (x_i - x_j)^2 and / or x_i . x_j in the canonical order of rowdot.cuh ----
@@ -147,68 +237,11 @@ rerank_kernel(const RerankParams p) {
             xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
         }
         float d2[CB], dt[CB];
-        if (vec) {
-            uint64_t ad[CB], at[CB];
-#pragma unroll
-            for (int q = 0; q < CB; ++q) { ad[q] = 0; at[q] = 0; }
-#pragma unroll 2
-            for (int64_t v = lane; v < (p.d >> 2); v += 32) {
-                const ulonglong2 x = __ldg(reinterpret_cast<const ulonglong2*>(xi) + v);
-                ulonglong2 y[CB];
-#pragma unroll
-                for (int q = 0; q < CB; ++q) y[q] = __ldg(reinterpret_cast<const ulonglong2*>(xj[q]) + v);
-#pragma unroll
-                for (int q = 0; q < CB; ++q) {
-                    if (WANT_D2) {
-                        const uint64_t e0 = pk_sub(x.x, y[q].x), e1 = pk_sub(x.y, y[q].y);
-                        ad[q] = pk_fma(e0, e0, ad[q]); ad[q] = pk_fma(e1, e1, ad[q]);
-                    }
-                    if (WANT_DOT) { at[q] = pk_fma(x.x, y[q].x, at[q]); at[q] = pk_fma(x.y, y[q].y, at[q]); }
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < CB; ++q) { d2[q] = pk_hsum(ad[q]); dt[q] = pk_hsum(at[q]); }
-        } else {
-#pragma unroll
-            for (int q = 0; q < CB; ++q) { d2[q] = 0.f; dt[q] = 0.f; }
-            for (int64_t c = lane; c < p.d; c += 32) {
-                const float x = __ldg(xi + c);
-#pragma unroll
-                for (int q = 0; q < CB; ++q) {
-                    const float y = __ldg(xj[q] + c);
-                    if (WANT_D2) { const float df = x - y; d2[q] = fmaf(df, df, d2[q]); }
-                    if (WANT_DOT) dt[q] = fmaf(x, y, dt[q]);
-                }
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-            for (int q = 0; q < CB; ++q) {
-                if (WANT_D2) d2[q] += __shfl_xor_sync(0xffffffffu, d2[q], o);
-                if (WANT_DOT) dt[q] += __shfl_xor_sync(0xffffffffu, dt[q], o);
-            }
-        }
+        warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
 #pragma unroll
         for (int q = 0; q < CB; ++q) {
             if (lane != t0 + q || j[q] < 0) continue;
-            const float cs = WANT_DOT ? cosine_from(dt[q], ni, __ldg(p.sq_norms + j[q])) : 0.f;
-            my_cos = cs;
-            if (MODE == RR_DOT) {
-                my_val = -cs; my_out = cs;
-            } else if (p.metric == HG_METRIC_EUCLIDEAN) {
-                my_val = d2[q]; my_out = d2[q];
-            } else {
-                float d2g = 0.f;
-                if (p.pos != nullptr) {
-                    for (int c = 0; c < p.pos_dim; ++c) {
-                        const float df = __ldg(p.pos + row * p.pos_dim + c) - __ldg(p.pos + int64_t(j[q]) * p.pos_dim + c);
-                        d2g = fmaf(df, df, d2g);
-                    }
-                }
-                my_val = p.lambda_h * d2[q] + p.lambda_g * d2g;
-                my_out = expf(-my_val);
-            }
+            exact_key<MODE>(p, row, j[q], d2[q], dt[q], ni, my_val, my_out, my_cos);
         }
     }
 
@@ -230,6 +263,165 @@ rerank_kernel(const RerankParams p) {
         p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
         if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
     }
+}
+
+
+// ---- exact fallback for uncertified rows ------------------------------------------------------------
+// Work item = (uncertified row e, column slice): one CTA ranks the slice's columns by the exact key (the
+// same sums, in the same order, as the re-rank) and leaves its k best in unc_part[e][slice][k]; the merge
+// kernel picks the k best of the RR_UNC_SLICES lists.  Cost: one pass over the features per row, shared
+// by the CTAs working on it -- paid only by rows the approximate candidate lists cannot vouch for.
+constexpr int RR_UNC_WARPS = 8;
+
+// ascending (key, index) list of <= 32 entries spread over the lanes of a warp; lane t holds the t-th best
+__device__ __forceinline__ void warp_list_insert(float& mv, int& mi, float v, int j, int k, int lane) {
+    const bool before = pair_less(mv, mi, v, j);                     // this lane's entry stays ahead of the new one
+    const int pos = __popc(__ballot_sync(0xffffffffu, before && lane < k));
+    const float pv = __shfl_up_sync(0xffffffffu, mv, 1);
+    const int pi = __shfl_up_sync(0xffffffffu, mi, 1);
+    if (lane > pos) { mv = pv; mi = pi; }
+    else if (lane == pos) { mv = v; mi = j; }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(RR_UNC_WARPS * 32)
+exact_slices_kernel(const RerankParams p) {
+    __shared__ float s_val[RR_UNC_WARPS][32];
+    __shared__ int s_idx[RR_UNC_WARPS][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cnt = *p.unc_cnt;
+    const bool vec = rows_vectorisable(p.feats, p.d);
+    constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
+    constexpr int CB = 4;
+    const int64_t per_slice = ceil_div(p.n, RR_UNC_SLICES);
+    for (int64_t item = blockIdx.x; item < int64_t(cnt) * RR_UNC_SLICES; item += gridDim.x) {
+        const int e = int(item / RR_UNC_SLICES), slice = int(item % RR_UNC_SLICES);
+        const int64_t row = p.row_begin + p.unc_rows[e];
+        const float* xi = p.feats + row * p.d;
+        const float ni = p.sq_norms[row];
+        const int64_t c0 = slice * per_slice, c1 = min64(p.n, c0 + per_slice);
+        float mv = INFINITY; int mi = 0x7fffffff;                      // this warp's list, lane t = t-th best
+        for (int64_t j0 = c0 + warp * CB; j0 < c1; j0 += RR_UNC_WARPS * CB) {
+            const float* xj[CB];
+#pragma unroll
+            for (int q = 0; q < CB; ++q) xj[q] = p.feats + min64(j0 + q, p.n - 1) * p.d;
+            float d2[CB], dt[CB];
+            warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                const int64_t j = j0 + q;
+                if (j >= c1 || (p.exclude_self && j == row)) continue;                 // warp-uniform
+                float key, out, cs;
+                exact_key<MODE>(p, row, int(j), d2[q], dt[q], ni, key, out, cs);
+                const float kv = __shfl_sync(0xffffffffu, mv, p.k - 1);
+                const int ki = __shfl_sync(0xffffffffu, mi, p.k - 1);
+                if (pair_less(key, int(j), kv, ki)) warp_list_insert(mv, mi, key, int(j), p.k, lane);
+            }
+        }
+        s_val[warp][lane] = mv; s_idx[warp][lane] = mi;
+        __syncthreads();
+        if (warp == 0) {
+            // k best of the RR_UNC_WARPS lists: lane holds one entry per list, k rounds of warp arg-min
+            float cv[RR_UNC_WARPS]; int ci[RR_UNC_WARPS];
+#pragma unroll
+            for (int w = 0; w < RR_UNC_WARPS; ++w) {
+                const bool ok = lane < p.k;
+                cv[w] = ok ? s_val[w][lane] : INFINITY; ci[w] = ok ? s_idx[w][lane] : 0x7fffffff;
+            }
+            uint2* dst = p.unc_part + (int64_t(e) * RR_UNC_SLICES + slice) * p.k;
+            for (int t = 0; t < p.k; ++t) {
+                float bv = INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+                for (int w = 0; w < RR_UNC_WARPS; ++w)
+                    if (pair_less(cv[w], ci[w], bv, bi)) { bv = cv[w]; bi = ci[w]; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                    if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+                }
+#pragma unroll
+                for (int w = 0; w < RR_UNC_WARPS; ++w)
+                    if (ci[w] == bi) { cv[w] = INFINITY; ci[w] = 0x7fffffff; }
+                if (lane == 0) dst[t] = make_uint2(__float_as_uint(bv), uint32_t(bi));
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// one warp per uncertified row: k best of its slice lists by (exact key, index), values recomputed
+template <int MODE>
+__global__ void __launch_bounds__(RR_WARPS * 32)
+exact_merge_kernel(const RerankParams p) {
+    const int lane = threadIdx.x & 31;
+    const int cnt = *p.unc_cnt;
+    constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
+    const bool vec = rows_vectorisable(p.feats, p.d);
+    for (int e = blockIdx.x * RR_WARPS + (threadIdx.x >> 5); e < cnt; e += gridDim.x * RR_WARPS) {
+        const int64_t r = p.unc_rows[e], row = p.row_begin + r;
+        const int total = RR_UNC_SLICES * p.k;                          // <= 256
+        float cv[RR_UNC_SLICES]; int ci[RR_UNC_SLICES];
+#pragma unroll
+        for (int q = 0; q < RR_UNC_SLICES; ++q) {
+            const int t = lane + 32 * q;
+            cv[q] = INFINITY; ci[q] = 0x7fffffff;
+            if (t < total) {
+                const uint2 u = p.unc_part[int64_t(e) * total + t];
+                cv[q] = __uint_as_float(u.x); ci[q] = int(u.y);
+            }
+        }
+        int sel = 0x7fffffff;
+        int nsel = 0;
+        for (int t = 0; t < p.k; ++t) {
+            float bv = INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+            for (int q = 0; q < RR_UNC_SLICES; ++q)
+                if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+            }
+            if (bi == 0x7fffffff) break;
+#pragma unroll
+            for (int q = 0; q < RR_UNC_SLICES; ++q)
+                if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }
+            if (lane == t) sel = bi;
+            nsel = t + 1;
+        }
+        // the selection order IS the (exact key, index) order; recompute value and cosine of every winner
+        const float* xi = p.feats + row * p.d;
+        const float ni = p.sq_norms[row];
+        for (int t = 0; t < nsel; ++t) {
+            const int j = __shfl_sync(0xffffffffu, sel, t);
+            const float* xj[1] = {p.feats + int64_t(j) * p.d};
+            float d2[1], dt[1];
+            warp_pair_sums<WANT_D2, WANT_DOT, 1>(xi, xj, p.d, lane, vec, d2, dt);
+            float key, out, cs;
+            exact_key<MODE>(p, row, j, d2[0], dt[0], ni, key, out, cs);
+            if (lane == 0) {
+                p.out_idx[r * p.k + t] = j;
+                p.out_val[r * p.k + t] = out;
+                if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = cs;
+            }
+        }
+        for (int t = nsel + lane; t < p.k; t += 32) {
+            p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
+            if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+        }
+    }
+}
+
+template <int MODE>
+static int launch_exact_fallback(const RerankParams& p, cudaStream_t st) {
+    exact_slices_kernel<MODE><<<2 * kNumSMs, RR_UNC_WARPS * 32, 0, st>>>(p);
+    HG_CHECK_LAUNCH();
+    exact_merge_kernel<MODE><<<kNumSMs, RR_WARPS * 32, 0, st>>>(p);
+    HG_CHECK_LAUNCH();
+    count_launches(2);
+    return HG_OK;
 }
 
 // Pre-pass run with several column splits: thr[row] = the rank-th smallest score over the row's S
@@ -278,13 +470,19 @@ int rerank_launch(const RerankParams& p, cudaStream_t st) {
     HG_REQUIRE(p.kl <= 32 && p.splits * p.kl <= list_cap && p.sym_plan.splits * p.kl <= RR_MAX_LIST &&
                p.bkt_cap <= TC_BKT_CAP, HG_ERR_UNSUPPORTED, "rerank: too many candidates per row");
     HG_REQUIRE(p.sq_norms && p.norm_max, HG_ERR_BAD_ARG, "rerank: row norms missing");
+    HG_REQUIRE((p.unc_cnt == nullptr) == (p.unc_rows == nullptr) && (p.unc_cnt == nullptr) == (p.unc_part == nullptr),
+               HG_ERR_BAD_ARG, "rerank: incomplete fallback buffers");
     const unsigned blocks = (unsigned)ceil_div(p.n_rows, RR_WARPS);
     if (p.metric == HG_METRIC_COSINE) rerank_kernel<RR_DOT><<<blocks, RR_WARPS * 32, 0, st>>>(p);
     else if (p.out_cos != nullptr) rerank_kernel<RR_D2_DOT><<<blocks, RR_WARPS * 32, 0, st>>>(p);
     else rerank_kernel<RR_D2><<<blocks, RR_WARPS * 32, 0, st>>>(p);
     HG_CHECK_LAUNCH();
     count_launches(1);
-    return HG_OK;
+    if (p.unc_cnt == nullptr) return HG_OK;
+    // rows the lists cannot vouch for (normally none: both kernels then exit at once)
+    if (p.metric == HG_METRIC_COSINE) return launch_exact_fallback<RR_DOT>(p, st);
+    if (p.out_cos != nullptr) return launch_exact_fallback<RR_D2_DOT>(p, st);
+    return launch_exact_fallback<RR_D2>(p, st);
 }
 
 }  // namespace hg

@@ -174,7 +174,8 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                                    positions: Optional[torch.Tensor] = None, spatial_k: int = 0,
                                    return_csr: bool = False, group=None, aligned: bool = False,
                                    overlap: Optional[bool] = None,
-                                   knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None) -> dict:
+                                   knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None,
+                                   spatial_fn: Optional[Callable] = None) -> dict:
     """Config C5: `local_features` is this rank's row block [r1-r0, D] (`row_range`, or
     `row_range_aligned` with aligned=True); `positions` (replicated, [n, 2|3]) is small.  Returns
     the same dict as `knn_hyperedges` on every rank.  overlap=True (aligned blocks on CUDA only):
@@ -222,7 +223,11 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     knn_cos = all_gather_rows(local[2], n, group, ranges) if len(local) > 2 else None
     lists = [out["knn_idx"]]
     if spatial_k and pos is not None:
-        sidx, sd2 = ops.knn_spatial(pos, spatial_k, rows=(r0, r1))
+        if r1 > r0:
+            sidx, sd2 = (spatial_fn or ops.knn_spatial)(pos, spatial_k, rows=(r0, r1))
+        else:                              # a rank without rows still takes part in the gathers below
+            sidx = torch.empty((0, spatial_k), dtype=torch.int32, device=feats.device)
+            sd2 = torch.empty((0, spatial_k), dtype=torch.float32, device=feats.device)
         out["spatial_idx"] = all_gather_rows(sidx, n, group, ranges)
         out["spatial_d2"] = all_gather_rows(sd2, n, group, ranges)
         lists.append(out["spatial_idx"])

@@ -317,6 +317,38 @@ def process_single_file(h5_path: str, num_wsi_super_patches: int = 100, num_grou
 
 
 IO_OVERLAP = os.environ.get("HG_B200_IO_OVERLAP", "1") != "0"
+MAX_PENDING_SAVES = max(1, int(os.environ.get("HG_B200_MAX_PENDING_SAVES", "2")))
+
+
+class _BoundedWriter:
+    """One writer thread with at most `max_pending` saves queued or running: submit() blocks the slide loop
+    when the writer falls behind.  A queued save keeps its slide's device tensors alive (up to the dense
+    N x N K_wsi, 4 GiB at MAX_DENSE_N), so an unbounded queue could run the GPU out of memory whenever the
+    D2H + file write are slower than the GPU stages; the reference's sequential loop (:651-670) never holds
+    more than one slide."""
+
+    def __init__(self, max_pending: int = MAX_PENDING_SAVES):
+        import threading
+        from concurrent.futures import ThreadPoolExecutor
+        self._pool = ThreadPoolExecutor(1)
+        self._slots = threading.BoundedSemaphore(max_pending)
+
+    def submit(self, fn, *args, **kw):
+        self._slots.acquire()
+
+        def run():
+            try:
+                return fn(*args, **kw)
+            finally:
+                self._slots.release()
+        try:
+            return self._pool.submit(run)
+        except BaseException:
+            self._slots.release()
+            raise
+
+    def shutdown(self, wait: bool = True):
+        self._pool.shutdown(wait=wait)
 
 
 def _run_over_csv(csv_path: str, data_root_dir: str, desc: str, worker, output_stats_path: Optional[str],
@@ -350,7 +382,7 @@ def _run_over_csv(csv_path: str, data_root_dir: str, desc: str, worker, output_s
         todo = [todo[i] for i in shard_slides(sizes, world)[rank]]
     overlap = loader is not None and IO_OVERLAP
     reader = ThreadPoolExecutor(1) if overlap else None
-    writer = ThreadPoolExecutor(1) if overlap else None
+    writer = _BoundedWriter() if overlap else None
     done = []                                           # (csv index, stats) of the slides that went through
     try:
         ahead = reader.submit(loader, todo[0][3]) if overlap and todo else None

@@ -97,6 +97,8 @@ def main():
         "knn_n512_d128_k8": (400, 112, 128, 8, "cosine", 21, 0),
         "knn_n768_d256_k5_cliques": (600, 168, 256, 5, "gaussian", 22, 6),
         "knn_n1024_d1024_k8": (896, 128, 1024, 8, "cosine", 23, 0),
+        # BASELINE config C1 at full size (N = 4,096 x 1024, cosine kNN k = 8, the bench generator's seed)
+        "knn_c1_n4096_d1024_k8": (3840, 256, 1024, 8, "cosine", 1235, 0),
     }.items():
         n = n_wsi + n_tma
         feats = synth.make_features(n, d, seed, mode)

@@ -97,6 +97,56 @@ def test_row_partitioned_equals_single_process(n, aligned):
         assert (ei == ref_ei).all()
 
 
+def _worker_spatial(rank, world, port, n, d, k, ks, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        feats, pos = synth.make_slide(n, d, 78, "gaussian")
+        r0, r1 = multigpu.row_range_aligned(n, rank, world)
+
+        def knn_fn(x, rows):
+            idx, val = oracle.knn_feature(x.numpy(), k, "gaussian", rows=np.arange(rows[0], rows[1]))
+            return torch.from_numpy(idx.astype(np.int32)), torch.from_numpy(val.astype(np.float32))
+
+        def spatial_fn(p, kk, rows):                          # stands in for ops.knn_spatial: needs a non-empty range
+            assert rows[0] < rows[1]
+            idx, d2 = oracle.knn_spatial(p.numpy(), kk, rows=np.arange(rows[0], rows[1]))
+            return torch.from_numpy(idx.astype(np.int32)), torch.from_numpy(d2.astype(np.float32))
+
+        def assemble_fn(lists, x):
+            return {"edge_index": torch.from_numpy(oracle.edges_from_knn(np.concatenate([t.numpy() for t in lists], 1)))}
+
+        out = multigpu.knn_hyperedges_row_partitioned(torch.from_numpy(feats[r0:r1]), n, k=k, knn_fn=knn_fn,
+                                                      positions=torch.from_numpy(pos), spatial_k=ks, spatial_fn=spatial_fn,
+                                                      assemble_fn=assemble_fn, aligned=True)
+        q.put((rank, out["spatial_idx"].numpy(), out["edge_index"].numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_rank_without_rows_still_joins_the_spatial_gathers():
+    """n = 200 in 256-row blocks on 2 ranks: rank 1 owns nothing.  With spatial_k > 0 it used to call the spatial
+    kNN on an empty row range (ValueError) while rank 0 waited in the all-gather."""
+    n, d, k, ks, world = 200, 16, 4, 3, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_spatial, args=(r, world, port, n, d, k, ks, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=100) for _ in range(world)]
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    feats, pos = synth.make_slide(n, d, 78, "gaussian")
+    ref_idx, _ = oracle.knn_feature(feats, k, "gaussian")
+    ref_s, _ = oracle.knn_spatial(pos, ks)
+    ref_ei = oracle.edges_from_knn(np.concatenate([ref_idx, ref_s], 1))
+    for _, sidx, ei in results:
+        assert (sidx == ref_s).all() and (ei == ref_ei).all()
+
+
 # ---- dataset loop (preprocess_hypergraph._run_over_csv): read-ahead / writer threads, rank sharding --------
 def _dataset_files(root, sizes):
     names = []
@@ -141,6 +191,31 @@ def test_dataset_loop_reads_ahead_and_keeps_the_error_convention(tmp_path):
         assert all("_pending_save" not in r for r in res)
         assert len(json.load(open(out))) == len(want)
         assert log == [n for n in names if n != "slide_2.bin"]      # CSV order, every present file once
+
+
+def test_writer_never_holds_more_than_two_pending_saves():
+    """saves slower than the slide loop: submit() blocks instead of queueing device tensors without bound"""
+    import threading
+    import time
+    from hg_b200 import preprocess_hypergraph as pp
+    w = pp._BoundedWriter(max_pending=2)
+    live, peak, lock = [0], [0], threading.Lock()
+
+    def slow_save():
+        time.sleep(0.02)
+        with lock:
+            live[0] -= 1
+
+    futs = []
+    for _ in range(12):
+        with lock:                                   # "a slide's tensors are alive" from submit until its save has run
+            live[0] += 1
+            peak[0] = max(peak[0], live[0])
+        futs.append(w.submit(slow_save))
+    for f in futs:
+        f.result()
+    w.shutdown()
+    assert peak[0] <= 3                              # two pending + the one being handed over
 
 
 def _dataset_rank(rank, world, port, root, q):
