@@ -3,6 +3,7 @@
 #include "knn_tc.cuh"
 #include "sim_simt.cuh"
 #include <stdlib.h>
+#include <algorithm>
 #include <vector>
 
 namespace hg {
@@ -439,3 +440,169 @@ extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_a
     rp.exclude_self = s->exclude_self;
     return rerank_launch(rp, static_cast<cudaStream_t>(stream));
 }
+
+// ---- grouped feature kNN: many small slides, a handful of launches ------------------------------------------
+// A slide of 2-8k patches is 16-64 row blocks: launched on its own it leaves SMs idle (128 units on 148 SMs at
+// N = 4,096), pays the ragged end of a persistent launch and the empty-list warm-up with no epilogue overlap
+// behind its last tile -- 512 such slides spent 86 ms in 512 launches of the fused kernel.  Here the operands of
+// a whole group of slides sit in ONE buffer (each slide at a 256-row aligned offset, so column tiles never
+// straddle two slides) and one split launch, one column-parameter launch, ONE persistent launch of the fused
+// kernel over a unit table spanning all the slides (longest units first) and one re-rank launch do the front
+// half of every slide of the group.  Results are those of the per-slide calls bit for bit: a unit sweeps
+// exactly the column tiles of its own slide, in the same order, with the same list length.
+namespace hg {
+
+struct GroupLayout {
+    int64_t n_pad, d_pad;                  // operand rows of the whole group
+    int kl;
+    std::vector<int64_t> off;              // first operand row of every slide
+    std::vector<int> splits;               // column splits (candidate lists per row) of every slide
+    std::vector<int64_t> part_off;         // element offset of every slide's list block
+    int64_t part_elems;
+    int num_units;
+    size_t o_ops, o_norms, o_colp, o_pos4, o_pval, o_pidx, o_flags, o_unc_rows, o_unc_part, o_units, o_slides, o_map, bytes;
+};
+
+// A unit sweeps at most this many column tiles: short units keep the tail of the persistent launch short and let
+// slides of different sizes interleave; a slide of up to 4,096 rows keeps ONE list per row.
+constexpr int kGroupTilesPerUnit = 16;
+
+static GroupLayout group_layout(const KnnGroupSlide* slides, int num, int64_t d, int k, bool has_pos) {
+    GroupLayout g{};
+    g.d_pad = ops_cols(d);
+    g.kl = tc_list_len(k);
+    g.off.resize(num); g.splits.resize(num); g.part_off.resize(num);
+    int64_t rows = 0, part = 0;
+    int units = 0;
+    for (int i = 0; i < num; ++i) {
+        g.off[i] = rows;
+        rows += ops_rows(slides[i].n);
+        const int tiles = int(ceil_div(slides[i].n, TC_BN));
+        int s = int(ceil_div(tiles, kGroupTilesPerUnit));
+        if (s > TC_MAX_SPLITS) s = TC_MAX_SPLITS;
+        g.splits[i] = s;
+        g.part_off[i] = part;
+        part += int64_t(s) * slides[i].n * g.kl;
+        units += int(ceil_div(slides[i].n, TC_BM)) * s;
+    }
+    g.n_pad = rows; g.part_elems = part; g.num_units = units;
+    size_t off = 0;
+    auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
+    g.o_ops = take(size_t(g.n_pad) * size_t(ops_row_elems(g.d_pad)) * 2);
+    g.o_norms = take(size_t(g.n_pad) * 4);
+    g.o_colp = take(size_t(g.n_pad) * 8);
+    g.o_pos4 = take(has_pos ? size_t(g.n_pad) * 16 : 0);
+    g.o_pval = take(size_t(part) * 4);
+    g.o_pidx = take(size_t(part) * 4);
+    g.o_flags = take(16);
+    g.o_unc_rows = take(size_t(g.n_pad) * 4);
+    g.o_unc_part = take(rerank_unc_part_bytes(g.n_pad, k));
+    g.o_units = take(size_t(units) * sizeof(TcUnit));
+    g.o_slides = take(size_t(num) * sizeof(RrSlide));
+    g.o_map = take(size_t(g.n_pad / kRowPad) * 4);
+    g.bytes = off;
+    return g;
+}
+
+size_t knn_group_workspace_bytes(const KnnGroupSlide* slides, int num, int64_t d, int k, bool has_pos) {
+    return group_layout(slides, num, d, k, has_pos).bytes;
+}
+
+int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_dim, int metric, float lambda_h,
+                      float lambda_g, int k, int exclude_self, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    HG_REQUIRE(slides && num > 0 && d > 0 && k >= 1 && k <= 32, HG_ERR_BAD_ARG, "knn_group: bad argument");
+    bool has_pos = metric == HG_METRIC_GAUSSIAN && lambda_g != 0.f;
+    for (int i = 0; i < num; ++i) {
+        HG_REQUIRE(slides[i].feats && slides[i].n > 1 && slides[i].out_idx && slides[i].out_val, HG_ERR_BAD_ARG,
+                   "knn_group: slide %d: null buffer or fewer than 2 rows", i);
+        has_pos = has_pos && slides[i].pos != nullptr;
+    }
+    HG_REQUIRE(!has_pos || (pos_dim >= 1 && pos_dim <= 3), HG_ERR_UNSUPPORTED, "knn_group: pos_dim must be 1..3");
+    HG_REQUIRE(!has_pos || lambda_h > 0.f, HG_ERR_UNSUPPORTED, "knn_group: lambda_h must be > 0 when positions are given");
+    const GroupLayout g = group_layout(slides, num, d, k, has_pos);
+    HG_REQUIRE(g.n_pad < (int64_t(1) << 31) - 512, HG_ERR_UNSUPPORTED, "knn_group: group too large");
+    HG_REQUIRE(workspace && workspace_bytes >= g.bytes, HG_ERR_WORKSPACE, "knn_group: workspace too small (%zu < %zu)",
+               workspace_bytes, g.bytes);
+    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "knn_group: workspace must be 1024-byte aligned");
+    char* ws = static_cast<char*>(workspace);
+    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + g.o_ops);
+    float* norms = reinterpret_cast<float*>(ws + g.o_norms);
+    float2* colp = reinterpret_cast<float2*>(ws + g.o_colp);
+    float4* pos4 = has_pos ? reinterpret_cast<float4*>(ws + g.o_pos4) : nullptr;
+    int* flags = reinterpret_cast<int*>(ws + g.o_flags);
+    TcUnit* d_units = reinterpret_cast<TcUnit*>(ws + g.o_units);
+    RrSlide* d_slides = reinterpret_cast<RrSlide*>(ws + g.o_slides);
+    int32_t* d_map = reinterpret_cast<int32_t*>(ws + g.o_map);
+
+    // host tables -> device (pageable source: staged at once by the driver, no device synchronisation)
+    std::vector<TcUnit> units;
+    units.reserve(size_t(g.num_units));
+    std::vector<RrSlide> rs(static_cast<size_t>(num));
+    std::vector<int32_t> map(size_t(g.n_pad / kRowPad));
+    bool vec = d % 4 == 0;
+    int max_splits = 1;
+    for (int i = 0; i < num; ++i) {
+        const KnnGroupSlide& s = slides[i];
+        vec = vec && (reinterpret_cast<uintptr_t>(s.feats) & 15) == 0;
+        rs[i] = RrSlide{s.feats, has_pos ? s.pos : nullptr, g.off[i], s.n, g.part_off[i], g.splits[i], 0, s.out_idx, s.out_val, s.out_cos};
+        for (int64_t b = g.off[i] / kRowPad; b < (g.off[i] + ops_rows(s.n)) / kRowPad; ++b) map[size_t(b)] = i;
+        const int tiles = int(ceil_div(s.n, TC_BN)), cps = int(ceil_div(tiles, g.splits[i]));
+        const int ct_base = int(g.off[i] / TC_BN);
+        if (g.splits[i] > max_splits) max_splits = g.splits[i];
+        for (int sp = 0; sp < g.splits[i]; ++sp) {
+            const int c0 = sp * cps, c1 = std::min(tiles, c0 + cps);
+            for (int64_t rb = 0; rb < ceil_div(s.n, TC_BM); ++rb) {
+                TcUnit u{};
+                u.row0 = int32_t(g.off[i] + rb * TC_BM); u.row_end = int32_t(g.off[i] + s.n);
+                u.ct0 = ct_base + c0; u.ct1 = ct_base + std::max(c0, c1);
+                u.col_off = int32_t(g.off[i]);
+                u.part_off = g.part_off[i] + int64_t(sp) * s.n * g.kl + rb * TC_BM * g.kl;
+                units.push_back(u);
+            }
+        }
+    }
+    // longest units first (stable: units of a slide stay together, so CTAs running side by side share B tiles)
+    std::stable_sort(units.begin(), units.end(), [](const TcUnit& a, const TcUnit& b) { return (a.ct1 - a.ct0) > (b.ct1 - b.ct0); });
+    HG_CHECK_CUDA(cudaMemcpyAsync(d_units, units.data(), units.size() * sizeof(TcUnit), cudaMemcpyHostToDevice, st));
+    HG_CHECK_CUDA(cudaMemcpyAsync(d_slides, rs.data(), rs.size() * sizeof(RrSlide), cudaMemcpyHostToDevice, st));
+    HG_CHECK_CUDA(cudaMemcpyAsync(d_map, map.data(), map.size() * 4, cudaMemcpyHostToDevice, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(flags, 0, 16, st));
+
+    int rc = launch_split_group(d_slides, d_map, g.n_pad, d, vec, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    float* norm_max = reinterpret_cast<float*>(flags) + 1;
+    rc = launch_colparams_group(norms, pos_dim, g.n_pad, metric, colp, pos4, norm_max, d_slides, d_map, st);
+    if (rc != HG_OK) return rc;
+
+    TcParams tp{};
+    tp.d_pad = int(g.d_pad);
+    tp.colp = colp; tp.pos4 = pos4;
+    tp.gscale = (has_pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
+    tp.exclude_self = exclude_self;
+    tp.part_val = reinterpret_cast<float*>(ws + g.o_pval);
+    tp.part_idx = reinterpret_cast<int32_t*>(ws + g.o_pidx);
+    prof_begin(st);
+    rc = tc_launch_units(ops, g.n_pad, k, d_units, int(units.size()), tp, st);
+    prof_end(st);
+    if (rc != HG_OK) return rc;
+
+    RerankParams rp{};
+    rp.d = d; rp.n = g.n_pad; rp.pos_dim = pos_dim;
+    rp.sq_norms = norms; rp.norm_max = norm_max;
+    rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = has_pos ? lambda_g : 0.f;
+    rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
+    rp.splits = max_splits; rp.kl = g.kl; rp.n_rows = g.n_pad; rp.row_begin = 0;
+    rp.k = k;
+    bool want_cos = true;
+    for (int i = 0; i < num; ++i) want_cos = want_cos && slides[i].out_cos != nullptr;
+    rp.out_cos = want_cos ? slides[0].out_cos : nullptr;            // only selects the kernel variant; per slide below
+    rp.out_idx = slides[0].out_idx; rp.out_val = slides[0].out_val;
+    rp.unc_cnt = flags + 2;
+    rp.unc_rows = reinterpret_cast<int32_t*>(ws + g.o_unc_rows);
+    rp.unc_part = reinterpret_cast<uint2*>(ws + g.o_unc_part);
+    rp.exclude_self = exclude_self;
+    rp.g_slides = d_slides; rp.g_blk2slide = d_map;
+    return rerank_launch(rp, st);
+}
+
+}  // namespace hg

@@ -68,6 +68,11 @@ struct TcCfg {
 constexpr int TC_MAX_STAGES = 6;
 constexpr int TC_THREADS = 192;
 constexpr int TC_EPI_THREADS = 128;
+// dense-output mode: eight epilogue warps (two per TMEM lane quarter, 128 of the 256 tile columns each).  Its
+// single tile in flight (see the MMA issuer) serialises MMAs and epilogue, and the epilogue -- 256 exp + a 1 KB
+// row segment stored per thread -- was 12 us of a 25 us tile with four warps.
+constexpr int TC_THREADS_DENSE = 320;
+constexpr int TC_EPI_THREADS_DENSE = 256;
 constexpr int TC_TMEM_COLS = 512;
 
 constexpr int TC_WQ_CAP = 256;        // transposed-candidate queue entries per epilogue warp
@@ -97,6 +102,37 @@ __device__ __forceinline__ void decode_unit(const TcPlan& pl, int u, int& rb, in
     const int c = rem / rows_here;
     rb = g * pl.rc + (rem - c * rows_here);
     split = h * pl.cc + c;
+}
+
+// What one work unit covers: from the plan (row blocks x column splits of one slide) or, in a grouped launch, from the
+// unit table.
+struct UnitInfo {
+    int64_t row0, row_end;      // the CTA's 128 query rows start at row0; rows >= row_end are padding
+    int ct0, ct1;               // column tiles swept
+    int rb;                     // row block (symmetric tile ownership; plan mode only)
+    int col_off;                // subtracted from a column to get the index stored in the lists
+    int64_t list_off;           // element offset of the list of query row `row`: list_off + (row - list_row0) * kl
+    int64_t list_row0;
+};
+template <int CL>
+__device__ __forceinline__ UnitInfo unit_info(const TcParams& p, int u, uint32_t crank, int kl) {
+    UnitInfo ui;
+    if (p.unit_tab != nullptr) {
+        const TcUnit t = p.unit_tab[u];
+        ui.row0 = t.row0; ui.row_end = t.row_end; ui.ct0 = t.ct0; ui.ct1 = t.ct1; ui.rb = 0; ui.col_off = t.col_off;
+        ui.list_off = t.part_off; ui.list_row0 = t.col_off;
+        return ui;
+    }
+    int split, rb;
+    decode_unit(p.plan, u, rb, split);
+    ui.rb = rb;
+    ui.row0 = p.row_begin + int64_t(rb) * (TC_BM * CL) + int64_t(crank) * TC_BM;
+    ui.row_end = p.row_end;
+    ui.ct0 = p.ct_base + split * p.plan.ct_per_split;                            // ct_base: column-panel launches
+    ui.ct1 = min(ui.ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
+    ui.col_off = 0;
+    ui.list_off = int64_t(split) * p.plan.n_rows * kl; ui.list_row0 = p.row_begin;
+    return ui;
 }
 
 // Does the unit of row block rb (classic: every tile; symmetric: the checkerboard) own column tile ct?
@@ -129,7 +165,7 @@ __device__ __forceinline__ void bucket_push(const TcParams& p, int col, int row,
 }
 
 template <int KL, bool HAS_POS, int CG, bool SYM, bool MC>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(KL == 0 ? TC_THREADS_DENSE : TC_THREADS, 1)
 knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
               const TcParams p) {
     using Cfg = TcCfg<CG>;
@@ -138,6 +174,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     static_assert(!SYM || (CG == 1 && KL > 0), "symmetric mode: single-CTA tiles with candidate lists");
     static_assert(!MC || CG == 1, "multicast pairs issue single-CTA MMAs");
     constexpr int CL = (CG == 2 || MC) ? 2 : 1;        // CTAs per cluster = 128-row blocks per work unit
+    constexpr bool DENSE = KL == 0;                    // dense-output mode: K written out, no candidate lists
     if (p.guard != nullptr && *p.guard == 0) return;   // fallback launch that is not needed (grid-uniform)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -146,7 +183,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = p.d_pad / TC_BK;
-    const int units = p.plan.num_u * p.plan.splits;
+    const int units = p.unit_tab != nullptr ? p.num_tab_units : p.plan.num_u * p.plan.splits;
     const uint32_t crank = (CL == 2) ? ptx::cluster_ctarank() : 0u;     // 0 = leader of the CTA pair
     const int wid = blockIdx.x / CL, nworkers = gridDim.x / CL;          // a worker = one CTA or one pair
 
@@ -157,7 +194,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(ptx::smem_u32(&sm->tmem_full[b]), 1);
-            ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), TC_EPI_THREADS * CG);
+            ptx::mbar_init(ptx::smem_u32(&sm->tmem_empty[b]), (DENSE ? TC_EPI_THREADS_DENSE : TC_EPI_THREADS) * CG);
         }
         for (int q = 0; q < 4; ++q) sm->wq_cnt[q] = 0;
         ptx::fence_barrier_init();
@@ -182,12 +219,9 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
         if (lane == 0) {
             uint32_t it = 0;
             for (int u = wid; u < units; u += nworkers) {
-                int split, rb;
-                decode_unit(p.plan, u, rb, split);
-                const int row0 = int(p.row_begin) + rb * (TC_BM * CL) + int(crank) * TC_BM;
-                const int ct0 = p.ct_base + split * p.plan.ct_per_split;        // ct_base: column-panel launches
-                const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
-                for (int ct = ct0; ct < ct1; ++ct) {
+                const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
+                const int row0 = int(ui.row0), rb = ui.rb;
+                for (int ct = ui.ct0; ct < ui.ct1; ++ct) {
                     if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
@@ -229,16 +263,21 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM * CG, TC_BN);
             uint32_t it = 0, tile = 0;
             for (int u = wid; u < units; u += nworkers) {
-                int split, rb;
-                decode_unit(p.plan, u, rb, split);
-                const int ct0 = p.ct_base + split * p.plan.ct_per_split;        // ct_base: column-panel launches
-                const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
-                for (int ct = ct0; ct < ct1; ++ct) {
+                const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
+                const int rb = ui.rb;
+                for (int ct = ui.ct0; ct < ui.ct1; ++ct) {
                     if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
-                    const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
+                    // dense-output mode: ONE tile in flight, its two accumulators fill the 512 columns (see below)
+                    const uint32_t buf = DENSE ? 0u : (tile & 1u), tph = DENSE ? (tile & 1u) : ((tile >> 1) & 1u);
                     ptx::mbar_wait(ptx::smem_u32(&sm->tmem_empty[buf]), tph ^ 1u);
                     ptx::tc_fence_after();
                     const uint32_t d_tmem = tmem_base + buf * TC_BN;
+                    // The tensor core adds every MMA into the FP32 accumulator with a truncating add, so a long chain
+                    // drifts by ~1 ulp of the running sum per step (1.4e-5 relative on exp(-d2) after 192 steps at
+                    // D = 1024).  List mode does not care (exact FP32 re-rank).  Dense mode sums the two cross terms
+                    // (2^-8 of the magnitude) in an accumulator of their own and adds the two in FP32 in the epilogue:
+                    // the large accumulator sees D / 16 steps instead of 3 D / 16.
+                    const uint32_t d_cross = DENSE ? d_tmem + TC_BN : d_tmem;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
                         ptx::mbar_wait(ptx::smem_u32(&sm->full[stage]), ph);
@@ -254,9 +293,12 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         for (int ks = 0; ks < TC_BK / 16; ++ks) {
                             const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
                             if (!p.hi_only) {
-                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_lo + off, idesc, (kb | ks) != 0);
-                                ptx::mma_bf16<CG>(d_tmem, a_lo + off, b_hi + off, idesc, 1u);
-                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                                // dense mode also adds lo*lo: on the diagonal and for near-duplicate rows the dropped
+                                // term is a sum of squares (no cancellation), 5e-6 of exp(-d2) on its own
+                                if (DENSE) ptx::mma_bf16<CG>(d_cross, a_lo + off, b_lo + off, idesc, (kb | ks) != 0);
+                                ptx::mma_bf16<CG>(d_cross, a_hi + off, b_lo + off, idesc, DENSE ? 1u : uint32_t((kb | ks) != 0));
+                                ptx::mma_bf16<CG>(d_cross, a_lo + off, b_hi + off, idesc, 1u);
+                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, DENSE ? uint32_t((kb | ks) != 0) : 1u);
                             } else {                          // coarse pre-pass: one BF16 product
                                 ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kb | ks) != 0);
                             }
@@ -267,34 +309,35 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         else ptx::mma_commit_2sm(ptx::smem_u32(&sm->empty[stage]), 3);
                     }
                     if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
-                    else ptx::mma_commit_2sm(ptx::smem_u32(&sm->tmem_full[buf]), 3);
+                    else ptx::mma_commit_2sm(ptx::smem_u32(&sm->tmem_full[buf]), 3);     // (buf = 0 in dense mode)
                     ++tile;
                 }
             }
         }
     } else {
         // ============================ epilogue ================================
-        const int et = threadIdx.x - 64;                 // 0..127
+        constexpr int EPI = DENSE ? TC_EPI_THREADS_DENSE : TC_EPI_THREADS;
+        const int et = threadIdx.x - 64;                 // 0..EPI-1
         const int quarter = warp & 3;                    // TMEM lane quarter this warp may read
+        const int chalf = DENSE ? (warp - 2) >> 2 : 0;   // dense mode: which 128 columns of the tile this warp writes
         const uint32_t lane_base = uint32_t(quarter * 32) << 16;
         constexpr int KLA = KL > 0 ? KL : 1;             // KL == 0: dense-output mode, no lists
         const int cstride = p.col_stride;
         uint32_t tile = 0;
         for (int u = wid; u < units; u += nworkers) {
-            int split, rb;
-            decode_unit(p.plan, u, rb, split);
-            const int64_t row0 = p.row_begin + int64_t(rb) * (TC_BM * CL) + int64_t(crank) * TC_BM;
+            const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
+            const int rb = ui.rb;
+            const int64_t row0 = ui.row0;
             const int sblk = (CL == 2) ? rb : rb >> 1;          // 256-row super-block (symmetric tile ownership)
             const int64_t row = row0 + quarter * 32 + lane;
-            const int ct0 = p.ct_base + split * p.plan.ct_per_split;
-            const int ct1 = min(ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
+            const int ct0 = ui.ct0, ct1 = ui.ct1;
             float lv[KLA];
             int li[KLA];
 #pragma unroll
             for (int q = 0; q < KLA; ++q) { lv[q] = INFINITY; li[q] = -1; }
-            if (KL > 0 && p.carry && row < p.row_end) {
+            if (KL > 0 && p.carry && row < ui.row_end) {
                 // column-panel launches: go on from the list the previous panels left in this slot
-                const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+                const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
 #pragma unroll
                 for (int q = 0; q < KLA; ++q) {
                     li[q] = p.part_idx[o + q];
@@ -305,25 +348,25 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             const float2 me = (row < p.n_pad) ? __ldg(p.colp + row) : make_float2(INFINITY, 0.f);
             const float row_norm = me.x, ta = me.x, tb = me.y;
             float4 mypos = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (HAS_POS && row < p.n) mypos = __ldg(p.pos4 + row);
+            if (HAS_POS && row < ui.row_end) mypos = __ldg(p.pos4 + row);
             // SYM: the pre-pass bound of this row also gates its own list (nothing above it can be in
             // the final top-k), which removes the warm-up insertions of every unit; NaN on padded rows
             const float row_bound = SYM ? __ldg(p.thr + row) : INFINITY;
             for (int ct = ct0; ct < ct1; ++ct) {
                 if (!owns_tile<SYM>(sblk, ct)) continue;
-                const uint32_t buf = tile & 1u, tph = (tile >> 1) & 1u;
+                const uint32_t tbuf = DENSE ? 0u : (tile & 1u), tph = DENSE ? (tile & 1u) : ((tile >> 1) & 1u);
+                const uint32_t buf = tile & 1u;                           // shared-memory column parameters alternate
                 const int col0 = ct * TC_BN;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int c = et + 128 * h;
+                for (int c = et; c < TC_BN; c += EPI) {
                     const int64_t src = int64_t(col0 + c) * cstride;      // operand row behind column c
                     const bool ok = src < p.n_pad;
                     sm->colp[buf][c] = ok ? __ldg(p.colp + src) : make_float2(INFINITY, 0.f);
                     if (HAS_POS) sm->cpos[buf][c] = ok ? __ldg(p.pos4 + src) : make_float4(0.f, 0.f, 0.f, 0.f);
                     if (SYM) sm->thr[buf][c] = __ldg(p.thr + col0 + c);    // NaN beyond n: never admitted
                 }
-                ptx::named_bar_sync(1, TC_EPI_THREADS);
-                ptx::mbar_wait(ptx::smem_u32(&sm->tmem_full[buf]), tph);
+                ptx::named_bar_sync(1, EPI);
+                ptx::mbar_wait(ptx::smem_u32(&sm->tmem_full[tbuf]), tph);
                 ptx::tc_fence_after();
                 const bool diag = p.exclude_self && (col0 < row0 + TC_BM) && (row0 < col0 + TC_BN) && cstride == 1;
                 const int self_col = diag ? int(row - col0) : -1;     // column inside this tile, if any
@@ -342,10 +385,18 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     }
                 };
 #pragma unroll 1
-                for (int ch = 0; ch < TC_BN / 32; ++ch) {
+                for (int ch = DENSE ? chalf * 4 : 0; ch < (DENSE ? chalf * 4 + 4 : TC_BN / 32); ++ch) {
                     uint32_t r[32];
-                    ptx::tmem_ld_32x32(tmem_base + lane_base + buf * TC_BN + ch * 32, r);
-                    ptx::tmem_ld_wait();
+                    ptx::tmem_ld_32x32(tmem_base + lane_base + tbuf * TC_BN + ch * 32, r);
+                    if constexpr (DENSE) {
+                        uint32_t rx[32];                                   // the cross-term accumulator of the tile
+                        ptx::tmem_ld_32x32(tmem_base + lane_base + TC_BN + ch * 32, rx);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(rx[j]));
+                    } else {
+                        ptx::tmem_ld_wait();
+                    }
                     if constexpr (KL == 0) {
                         // dense mode: K = exp(-lambda_h (n_i + n_j - 2 dot + g d2_g)), 128 contiguous bytes per thread
                         float* dst = p.dense_out + (row - p.row_begin) * p.dense_ld + col0 + ch * 32;
@@ -358,7 +409,9 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                             for (int q = 0; q < 4; ++q) {
                                 float s, unused;
                                 scores(ch * 32 + j + q, __uint_as_float(r[j + q]), s, unused);
-                                v[q] = expf(-p.lambda_h * (row_norm + s));
+                                // a row against itself: d2 = 0 exactly, whatever the split product left of it
+                                const bool self = p.dense_self && row == int64_t(col0 + ch * 32 + j + q);
+                                v[q] = self ? 1.f : expf(-p.lambda_h * (row_norm + s));
                             }
                             if (full) {
                                 *reinterpret_cast<float4*>(dst + j) = make_float4(v[0], v[1], v[2], v[3]);
@@ -391,7 +444,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                         float s, st;
                         if (SYM) scores(ch * 32 + j, __uint_as_float(select32(r, j)), s, st);
                         else s = __uint_as_float(select32(r, j));
-                        if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, (col0 + ch * 32 + j) * cstride);
+                        if (s < lv[KLA - 1]) list_insert<KLA>(lv, li, s, (col0 + ch * 32 + j) * cstride - ui.col_off);
                     }
                     if (SYM) {
                         // transposed survivors: (score, column, row) into this warp's queue
@@ -411,8 +464,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     }
                 }
                 ptx::tc_fence_before();
-                if (CG == 1) ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[buf]));
-                else ptx::mbar_arrive_cluster(ptx::smem_u32(&sm->tmem_empty[buf]), 0);     // the leader's barrier
+                if (CG == 1) ptx::mbar_arrive(ptx::smem_u32(&sm->tmem_empty[tbuf]));
+                else ptx::mbar_arrive_cluster(ptx::smem_u32(&sm->tmem_empty[tbuf]), 0);    // the leader's barrier
                 if (SYM) {
                     // drain the warp's queue into the per-column buckets, one entry per lane and round
                     __syncwarp();
@@ -428,7 +481,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 ++tile;
             }
             // the unit's result: the threshold (pre-pass) or the candidate list of (row, split)
-            if (KL > 0 && row < p.row_end) {
+            if (KL > 0 && row < ui.row_end) {
                 if (p.thr_out != nullptr) {
                     float t = INFINITY;                   // the list ascends: min over q >= rank is lv[rank]
 #pragma unroll
@@ -442,7 +495,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
                     p.thr_out[row] = t + (p.hi_only ? TC_SLACK_HI : TC_SLACK_3X) * scale;
                 } else {
-                    const int64_t o = (int64_t(split) * p.plan.n_rows + (row - p.row_begin)) * KL;
+                    const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
 #pragma unroll
                     for (int q = 0; q < KLA; ++q) { p.part_val[o + q] = lv[q]; p.part_idx[o + q] = li[q]; }
                 }
@@ -669,7 +722,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
     HG_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(unsigned(p.plan.grid));
-    cfg.blockDim = dim3(TC_THREADS);
+    cfg.blockDim = dim3(KL == 0 ? TC_THREADS_DENSE : TC_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -749,6 +802,23 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
     return tc_launch_impl(ops, n_pad, ops, n_pad, p, st);
 }
+
+// Grouped launch: the units of several slides that share one operand buffer (TcUnit, knn_tc.cuh).  Classic list
+// mode on single CTAs; p carries colp / pos4 / gscale / exclude_self / part_val / part_idx / d_pad, and n = n_pad =
+// the rows of the whole group.
+int tc_launch_units(const __nv_bfloat16* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
+                    const TcParams& p_in, cudaStream_t st) {
+    HG_REQUIRE(unit_tab != nullptr && num_units > 0 && !p_in.thr_out && !p_in.carry && p_in.col_stride <= 1, HG_ERR_BAD_ARG,
+               "tc_launch_units: bad argument");
+    TcParams p = p_in;
+    p.plan = TcPlan{};
+    p.plan.cg = 1; p.plan.cl = 1; p.plan.kl = list_len(k);
+    p.plan.grid = int(min64(kNumSMs, num_units));
+    p.unit_tab = unit_tab; p.num_tab_units = num_units;
+    p.n = n_pad; p.row_begin = 0; p.row_end = n_pad;
+    return tc_launch_impl(ops, n_pad, ops, n_pad, p, st);
+}
+int tc_list_len(int k) { return list_len(k); }
 
 // Rows of matrix A (p.row_begin .. p.row_end) against the p.n rows of matrix B: classic list mode only.
 // p.colp / p.n describe B; nothing is excluded by index.

@@ -28,6 +28,18 @@ struct TcPlan {
     int num_u;                  // major units of the work list (= num_rb)
 };
 
+// One work unit of a GROUPED launch: several (small) slides share one operand buffer, each at a 256-row aligned
+// offset, and one persistent launch sweeps the units of all of them (reference loop over slides:
+// preprocess_hypergraph.py:651-670).  All row / tile numbers are in group coordinates.
+struct TcUnit {
+    int32_t row0;               // first operand row of the unit's 128-row block
+    int32_t row_end;            // one past the slide's last real row
+    int32_t ct0, ct1;           // column tiles [ct0, ct1) of the slide's own columns swept by the unit
+    int32_t col_off;            // the slide's first operand row: a list entry is (column - col_off)
+    int32_t reserved;
+    int64_t part_off;           // element offset of the unit's (slide, split) list block; local row r at + r * kl
+};
+
 struct TcParams {
     int64_t n, row_begin, row_end;
     int d_pad;
@@ -43,6 +55,7 @@ struct TcParams {
     float* dense_out;
     int64_t dense_ld;
     float lambda_h;
+    int dense_self;             // rows and columns are the same matrix: K[i, i] = 1 exactly
     // threshold pre-pass: the kernel's column c is operand row c * col_stride (the B tensor map is
     // strided to match); instead of candidate lists it writes thr_out[row] = the thr_rank-th best
     // score of the sample, an upper bound of the row's final k-th best.
@@ -68,6 +81,9 @@ struct TcParams {
     // the list already stored in its (row, split) slot (index -1 = empty entry) instead of an empty one
     int ct_base;
     int carry;
+    // grouped launch: non-null unit table (classic list mode, single CTAs); the plan then only carries kl
+    const TcUnit* unit_tab;
+    int num_tab_units;
 };
 
 // plan of one column panel of `panel_cols` columns swept by n_rows rows with `splits` lists per row
@@ -80,10 +96,23 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride);
 int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride
 constexpr int TC_BKT_CAP = 512;
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
+int tc_launch_units(const __nv_bfloat16* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
+                    const TcParams& p, cudaStream_t st);
+int tc_list_len(int k);
 // rectangular product (kmeans.cu): rows of A against the rows of another matrix B, classic list mode
 TcPlan tc_make_plan_rect(int64_t cols, int64_t n_rows, int k, int64_t d_pad);
 int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
                    const TcParams& p, cudaStream_t st);
+
+struct RrSlide {                 // one slide of a grouped launch, as the re-rank sees it
+    const float* feats;          // [n, d] the slide's own FP32 rows
+    const float* pos;            // [n, pos_dim] or null
+    int64_t off;                 // first operand row of the slide in the group (multiple of 256)
+    int64_t n;
+    int64_t part_off;            // element offset of the slide's [splits][n][kl] candidate lists
+    int32_t splits, reserved;
+    int32_t* out_idx; float* out_val; float* out_cos;
+};
 
 struct RerankParams {
     const float* feats; int64_t n, d;
@@ -104,6 +133,9 @@ struct RerankParams {
     // unc_part = [n_rows][RR_UNC_SLICES][k] scratch.  All three null: no certification.
     int32_t* unc_rows; int32_t* unc_cnt; uint2* unc_part;
     int exclude_self;            // the fallback skips column == row (the lists already did)
+    // grouped launch: n_rows = the group's operand rows, sq_norms / part_* = the group's arrays, everything else
+    // per slide from g_slides[g_blk2slide[row / 256]]
+    const RrSlide* g_slides; const int32_t* g_blk2slide;
 };
 constexpr int RR_UNC_SLICES = 8;
 inline size_t rerank_unc_part_bytes(int64_t n_rows, int k) { return size_t(n_rows) * RR_UNC_SLICES * size_t(k) * 8; }
@@ -118,5 +150,16 @@ constexpr float TC_SLACK_HI = 4.39453125e-3f;     // 2^-8 + 2^-11: a hi-only pre
 int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
                      float2* colp, float4* pos4, cudaStream_t st,
                      float* thr = nullptr, int32_t* bkt_cnt = nullptr, float* norm_max = nullptr);
+
+int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
+                       __nv_bfloat16* ops, float* sq_norms, cudaStream_t st);
+int launch_colparams_group(const float* sq_norms, int pos_dim, int64_t n_pad, int metric, float2* colp, float4* pos4,
+                           float* norm_max, const RrSlide* g_slides, const int32_t* g_blk2slide, cudaStream_t st);
+
+// ---- grouped feature kNN (knn_api.cu): the front half of a batch of small slides in a handful of launches ----
+struct KnnGroupSlide { const float* feats; const float* pos; int64_t n; int32_t* out_idx; float* out_val; float* out_cos; };
+size_t knn_group_workspace_bytes(const KnnGroupSlide* slides, int num, int64_t d, int k, bool has_pos);
+int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_dim, int metric, float lambda_h,
+                      float lambda_g, int k, int exclude_self, void* workspace, size_t workspace_bytes, cudaStream_t st);
 
 }  // namespace hg

@@ -16,19 +16,26 @@ namespace hg {
 __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float* __restrict__ pos, int pos_dim,
                                  int64_t n, int64_t n_pad, int metric, float2* __restrict__ colp,
                                  float4* __restrict__ pos4, float* __restrict__ thr, int32_t* __restrict__ bkt_cnt,
-                                 float* __restrict__ norm_max) {
+                                 float* __restrict__ norm_max, const RrSlide* __restrict__ g_slides,
+                                 const int32_t* __restrict__ g_blk2slide) {
     const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (j >= n_pad) return;
+    int64_t jl = j;                                  // row of `pos` behind operand row j
+    bool real = j < n;
+    if (g_slides != nullptr) {                       // grouped launch: per-slide row count and positions
+        const RrSlide sl = g_slides[g_blk2slide[j >> 8]];
+        jl = j - sl.off; real = jl < sl.n; pos = sl.pos;
+    }
     if (thr != nullptr) { thr[j] = __int_as_float(0x7fc00000); bkt_cnt[j] = 0; }
     if (norm_max != nullptr) {
         // non-negative floats order like their bit patterns; one atomic per warp
-        float m = (j < n) ? sq_norms[j] : 0.f;
+        float m = real ? sq_norms[j] : 0.f;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
         if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(norm_max), __float_as_int(m));
     }
     float2 cp = make_float2(INFINITY, 0.f);          // padded columns can never be selected
-    if (j < n) {
+    if (real) {
         const float nj = sq_norms[j];
         if (metric == HG_METRIC_COSINE) cp = make_float2(0.f, -1.f / fmaxf(sqrtf(nj), 1e-8f));
         else cp = make_float2(nj, -2.f);             // n_j - 2 dot (+ the row constant n_i, irrelevant to ranking)
@@ -36,10 +43,10 @@ __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float
     colp[j] = cp;
     if (pos4 != nullptr) {
         float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (j < n) {
-            q.x = pos[j * pos_dim];
-            if (pos_dim > 1) q.y = pos[j * pos_dim + 1];
-            if (pos_dim > 2) q.z = pos[j * pos_dim + 2];
+        if (real && pos != nullptr) {
+            q.x = pos[jl * pos_dim];
+            if (pos_dim > 1) q.y = pos[jl * pos_dim + 1];
+            if (pos_dim > 2) q.z = pos[jl * pos_dim + 2];
         }
         pos4[j] = q;
     }
@@ -48,7 +55,16 @@ __global__ void colparams_kernel(const float* __restrict__ sq_norms, const float
 int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64_t n, int64_t n_pad, int metric,
                      float2* colp, float4* pos4, cudaStream_t st, float* thr, int32_t* bkt_cnt, float* norm_max) {
     colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, pos, pos_dim, n, n_pad, metric, colp, pos4,
-                                                                     thr, bkt_cnt, norm_max);
+                                                                     thr, bkt_cnt, norm_max, nullptr, nullptr);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
+int launch_colparams_group(const float* sq_norms, int pos_dim, int64_t n_pad, int metric, float2* colp, float4* pos4,
+                           float* norm_max, const RrSlide* g_slides, const int32_t* g_blk2slide, cudaStream_t st) {
+    colparams_kernel<<<(unsigned)ceil_div(n_pad, 256), 256, 0, st>>>(sq_norms, nullptr, pos_dim, n_pad, n_pad, metric, colp, pos4,
+                                                                     nullptr, nullptr, norm_max, g_slides, g_blk2slide);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -64,6 +80,21 @@ constexpr int RR_MAX_CAND = RR_MAX_LIST + TC_BKT_CAP; // + the row's bucket (sym
 
 enum { RR_D2 = 0, RR_D2_DOT = 1, RR_DOT = 2 };       // what the exact pass accumulates per candidate
 
+
+// Grouped launches (several slides in one operand buffer, knn_tc.cuh TcUnit): the row `rg` of the group belongs to
+// slide blk2slide[rg / 256]; every per-slide quantity of the parameter block is switched to that slide, after
+// which the kernels below run unchanged on the slide's local row.  Returns false for padding rows.
+__device__ __forceinline__ bool select_group_row(RerankParams& p, int64_t rg, int64_t& r, int64_t& row) {
+    if (p.g_slides == nullptr) { r = rg; row = p.row_begin + rg; return true; }
+    const RrSlide sl = p.g_slides[p.g_blk2slide[rg >> 8]];
+    r = rg - sl.off; row = r;
+    if (r >= sl.n) return false;
+    p.feats = sl.feats; p.pos = sl.pos; p.n = sl.n; p.n_rows = sl.n; p.splits = sl.splits;
+    p.sq_norms += sl.off;
+    p.part_val += sl.part_off; p.part_idx += sl.part_off;
+    p.out_idx = sl.out_idx; p.out_val = sl.out_val; p.out_cos = sl.out_cos;
+    return true;
+}
 
 // Exact sums of one query row against CB candidate rows by one warp, in the canonical order of
 // rowdot.cuh (lane l owns the float4 groups l, l + 32, ...; packed FMA pairs; xor butterfly): one read
@@ -140,131 +171,181 @@ __device__ __forceinline__ void exact_key(const RerankParams& p, int64_t row, in
 
 template <int MODE>
 __global__ void __launch_bounds__(RR_WARPS * 32, 3)
-rerank_kernel(const RerankParams p) {
+rerank_kernel(const RerankParams p_in) {
     const int lane = threadIdx.x & 31;
-    const int64_t r = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
-    if (r >= p.n_rows) return;
-    const int64_t row = p.row_begin + r;
+    const int64_t rg = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
+    if (rg >= p_in.n_rows) return;
+    RerankParams p = p_in;
+    int64_t r, row;                                  // r: row of the lists / outputs, row: row of the features
+    if (!select_group_row(p, rg, r, row)) return;
     // symmetric mode unless the bucket overflow flag made the classic kernel re-run
     const bool sym = p.ovf != nullptr && *p.ovf == 0;
     const int splits = sym ? p.sym_plan.splits : p.splits;
     const int total = splits * p.kl;
     const int nbkt = sym ? min(p.bkt_cnt[row], p.bkt_cap) : 0;
 
-    // ---- 1. merge: the kl best approximate candidates, lane t ends up holding the t-th -------------
-    // slots [0, total) = the split lists, [total, ncand) = the bucket
     const int ncand = total + nbkt;
-    float cv[RR_MAX_CAND / 32];
-    int ci[RR_MAX_CAND / 32];
-#pragma unroll
-    for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
-        const int t = lane + 32 * q;
-        cv[q] = INFINITY; ci[q] = 0x7fffffff;
-        if (t < total) {
-            const int s = t / p.kl, w = t - s * p.kl;
-            const int64_t o = (int64_t(s) * p.n_rows + r) * p.kl + w;
-            const int idx = p.part_idx[o];
-            if (idx >= 0) { cv[q] = p.part_val[o]; ci[q] = idx; }
-        } else if (t < ncand) {
-            const uint2 b = p.bkt[row * p.bkt_cap + (t - total)];
-            cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
-        }
-    }
     // Selection stops once a candidate's approximate score exceeds the k-th best by more than the
     // guaranteed 3xBF16 error slack (both scores off by <= eps in opposite directions): such a
     // candidate cannot enter the exact top-k, and neither can any later one.
     const float ni = p.sq_norms[row];
     const float slack = 4.8828125e-4f * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
-    int sel = -1;                                    // candidate column held by this lane (lane < kl)
-    int nsel = 0;
-    float kth = INFINITY;
-    bool uncert = false;
-    for (int t = 0; t <= p.kl; ++t) {
-        float bv = INFINITY; int bi = 0x7fffffff;
-#pragma unroll
-        for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
-            if (q * 32 >= ncand) break;              // warp-uniform
-            if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
-        }
-        if (bi == 0x7fffffff) break;                 // fewer than kl real candidates
-        if (t == p.k - 1) kth = bv;
-        if (t >= p.k && bv > kth + slack) break;
-        // kl candidates taken and the next one is still inside the slack: the exact top-k may need it
-        if (t == p.kl) { uncert = true; break; }
-#pragma unroll
-        for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
-            if (q * 32 >= ncand) break;
-            if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }   // column ids are unique per row
-        }
-        if (lane == t) sel = bi;
-        nsel = t + 1;
-    }
     // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
     // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still
-    // belong to the exact top-k (many near-duplicates, or k close to kl): the row goes to the exact
-    // fallback (exact_slices_kernel) instead of being returned as the approximate set re-ordered.
+    // belong to the exact top-k (many near-duplicates): the row goes to the exact fallback
+    // (exact_slices_kernel).  Everything else is decided here, however many candidates sit inside the
+    // slack: they are taken 32 at a time (almost always one round).
+    const float* xi = p.feats + row * p.d;
+    const bool vec = rows_vectorisable(p.feats, p.d);
+    constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
+    constexpr int CB = 4;
+    float kth = INFINITY;
+    int taken = 0;
+    float last_v = -INFINITY;                            // the last candidate a round selected
+    int last_i = -1;
+    // running exact top-k, lane t = the t-th best by (key, index); materialised only from a second round on
+    float bk = INFINITY, bo = NAN, bc = NAN;
+    int bidx = 0x7fffffff, nbest = 0;
+    for (int round = 0;; ++round) {
+        // ---- 1. the next (up to 32) best approximate candidates; lane t holds the t-th of them --------
+        // slots [0, total) = the split lists, [total, ncand) = the bucket.  The pool lives in registers only while
+        // a round selects; a later round (rare) reloads it and drops what the earlier ones took: selection
+        // runs in (score, index) order, so "taken" = everything up to the last candidate selected
+        float cv[RR_MAX_CAND / 32];
+        int ci[RR_MAX_CAND / 32];
+#pragma unroll
+        for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+            const int t = lane + 32 * q;
+            cv[q] = INFINITY; ci[q] = 0x7fffffff;
+            if (t < total) {
+                const int s = t / p.kl, w = t - s * p.kl;
+                const int64_t o = (int64_t(s) * p.n_rows + r) * p.kl + w;
+                const int idx = p.part_idx[o];
+                if (idx >= 0) { cv[q] = p.part_val[o]; ci[q] = idx; }
+            } else if (t < ncand) {
+                const uint2 b = p.bkt[row * p.bkt_cap + (t - total)];
+                cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
+            }
+            if (round > 0 && !pair_less(last_v, last_i, cv[q], ci[q])) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }
+        }
+        int sel = -1, nsel = 0;
+        bool last = false;
+        for (int t = 0; t < 32; ++t) {
+            float bv = INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+            for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+                if (q * 32 >= ncand) break;              // warp-uniform
+                if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+            }
+            if (bi == 0x7fffffff) { last = true; break; }                  // no candidates left
+            if (taken + t == p.k - 1) kth = bv;
+            if (taken + t >= p.k && bv > kth + slack) { last = true; break; }
+#pragma unroll
+            for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
+                if (q * 32 >= ncand) break;
+                if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }   // column ids are unique per row
+            }
+            if (lane == t) sel = bi;
+            nsel = t + 1;
+            last_v = bv; last_i = bi;
+        }
+        taken += nsel;
+
+        // ---- 2. exact values: sum (x_i - x_j)^2 and / or x_i . x_j in the canonical order of rowdot.cuh ----
+        float my_val = INFINITY;                         // ranking key (ascending) of this lane's candidate
+        float my_out = NAN, my_cos = NAN;
+        for (int t0 = 0; t0 < nsel; t0 += CB) {
+            int j[CB];
+            const float* xj[CB];
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                j[q] = __shfl_sync(0xffffffffu, sel, t0 + q);
+                xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
+            }
+            float d2[CB], dt[CB];
+            warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                if (lane != t0 + q || j[q] < 0) continue;
+                exact_key<MODE>(p, row, j[q], d2[q], dt[q], ni, my_val, my_out, my_cos);
+            }
+        }
+        const int my_idx = (sel >= 0) ? sel : 0x7fffffff;
+
+        if (round == 0 && last) {
+            // ---- 3. (the usual case) final order by (exact value, index); best k written out ----------------
+            int rank = 0;
+            for (int t = 0; t < nsel; ++t) {
+                const float ov = __shfl_sync(0xffffffffu, my_val, t);
+                const int oi = __shfl_sync(0xffffffffu, my_idx, t);
+                rank += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
+            }
+            if (lane < nsel && sel >= 0 && rank < p.k) {
+                p.out_idx[r * p.k + rank] = sel;
+                p.out_val[r * p.k + rank] = my_out;
+                if (p.out_cos != nullptr) p.out_cos[r * p.k + rank] = my_cos;
+            }
+            nbest = min(nsel, p.k);
+            break;
+        }
+        // ---- 3'. more than 32 candidates inside the slack: merge this round into the running top-k ----------
+        int r_old = lane, r_new = 0;
+        for (int t = 0; t < nsel; ++t) {
+            const float ov = __shfl_sync(0xffffffffu, my_val, t);
+            const int oi = __shfl_sync(0xffffffffu, my_idx, t);
+            r_old += pair_less(ov, oi, bk, bidx) ? 1 : 0;
+            r_new += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
+        }
+        for (int t = 0; t < nbest; ++t) {
+            const float ov = __shfl_sync(0xffffffffu, bk, t);
+            const int oi = __shfl_sync(0xffffffffu, bidx, t);
+            r_new += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
+        }
+        if (lane >= nbest) r_old = 1 << 20;
+        if (lane >= nsel) r_new = 1 << 20;
+        const int total_best = min(p.k, nbest + nsel);
+        float nk = INFINITY, no = NAN, nc = NAN;
+        int nidx = 0x7fffffff;
+        for (int t = 0; t < total_best; ++t) {          // lane t takes the entry of rank t (indices are unique: no ties)
+            const unsigned mo = __ballot_sync(0xffffffffu, r_old == t);
+            const unsigned mn = __ballot_sync(0xffffffffu, r_new == t);
+            const int src = __ffs(mo ? mo : mn) - 1;
+            const float vk = __shfl_sync(0xffffffffu, mo ? bk : my_val, src);
+            const float vo = __shfl_sync(0xffffffffu, mo ? bo : my_out, src);
+            const float vc = __shfl_sync(0xffffffffu, mo ? bc : my_cos, src);
+            const int vi = __shfl_sync(0xffffffffu, mo ? bidx : my_idx, src);
+            if (lane == t) { nk = vk; no = vo; nc = vc; nidx = vi; }
+        }
+        bk = nk; bo = no; bc = nc; bidx = nidx; nbest = total_best;
+        if (last) {
+            if (lane < nbest) {
+                p.out_idx[r * p.k + lane] = bidx;
+                p.out_val[r * p.k + lane] = bo;
+                if (p.out_cos != nullptr) p.out_cos[r * p.k + lane] = bc;
+            }
+            break;
+        }
+    }
+    // rows with fewer than k candidates: pad with (-1, NaN)
+    for (int t = nbest + lane; t < p.k; t += 32) {
+        p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
+        if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+    }
     if (p.unc_cnt != nullptr) {
         bool full_inside = false;
         for (int s2 = lane; s2 < splits; s2 += 32) {
             const int64_t o = (int64_t(s2) * p.n_rows + r) * p.kl + (p.kl - 1);
             full_inside |= p.part_idx[o] >= 0 && p.part_val[o] <= kth + slack;
         }
-        uncert = __any_sync(0xffffffffu, uncert || full_inside);
-        if (uncert && lane == 0) p.unc_rows[atomicAdd(p.unc_cnt, 1)] = int32_t(r);
-    }
-
-    // ---- 2. exact values: sum (x_i - x_j)^2 and / or x_i . x_j in the canonical order of rowdot.cuh ----
-    const float* xi = p.feats + row * p.d;
-    const bool vec = rows_vectorisable(p.feats, p.d);
-    constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
-    float my_val = INFINITY;                         // ranking key (ascending) of this lane's candidate
-    float my_out = NAN, my_cos = NAN;
-    // four candidates per pass: one read of the query row serves four rows of sums, and the four
-    // reductions overlap.  Lane l owns the float4 groups l, l + 32, ... (rowdot.cuh order).
-    constexpr int CB = 4;
-    for (int t0 = 0; t0 < nsel; t0 += CB) {
-        int j[CB];
-        const float* xj[CB];
-#pragma unroll
-        for (int q = 0; q < CB; ++q) {
-            j[q] = __shfl_sync(0xffffffffu, sel, t0 + q);
-            xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
-        }
-        float d2[CB], dt[CB];
-        warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
-#pragma unroll
-        for (int q = 0; q < CB; ++q) {
-            if (lane != t0 + q || j[q] < 0) continue;
-            exact_key<MODE>(p, row, j[q], d2[q], dt[q], ni, my_val, my_out, my_cos);
-        }
-    }
-
-    // ---- 3. final order by (exact value, index); best k written out ----------------------------------
-    const int my_idx = (sel >= 0) ? sel : 0x7fffffff;
-    int rank = 0;
-    for (int t = 0; t < nsel; ++t) {
-        const float ov = __shfl_sync(0xffffffffu, my_val, t);
-        const int oi = __shfl_sync(0xffffffffu, my_idx, t);
-        rank += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
-    }
-    if (lane < nsel && sel >= 0 && rank < p.k) {
-        p.out_idx[r * p.k + rank] = sel;
-        p.out_val[r * p.k + rank] = my_out;
-        if (p.out_cos != nullptr) p.out_cos[r * p.k + rank] = my_cos;
-    }
-    // rows with fewer than k candidates: pad with (-1, NaN)
-    for (int t = nsel + lane; t < p.k; t += 32) {
-        p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
-        if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+        if (__any_sync(0xffffffffu, full_inside) && lane == 0) p.unc_rows[atomicAdd(p.unc_cnt, 1)] = int32_t(rg);
     }
 }
-
 
 // ---- exact fallback for uncertified rows ------------------------------------------------------------
 // Work item = (uncertified row e, column slice): one CTA ranks the slice's columns by the exact key (the
@@ -285,18 +366,20 @@ __device__ __forceinline__ void warp_list_insert(float& mv, int& mi, float v, in
 
 template <int MODE>
 __global__ void __launch_bounds__(RR_UNC_WARPS * 32)
-exact_slices_kernel(const RerankParams p) {
+exact_slices_kernel(const RerankParams p_in) {
     __shared__ float s_val[RR_UNC_WARPS][32];
     __shared__ int s_idx[RR_UNC_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cnt = *p.unc_cnt;
-    const bool vec = rows_vectorisable(p.feats, p.d);
+    const int cnt = *p_in.unc_cnt;
     constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
     constexpr int CB = 4;
-    const int64_t per_slice = ceil_div(p.n, RR_UNC_SLICES);
     for (int64_t item = blockIdx.x; item < int64_t(cnt) * RR_UNC_SLICES; item += gridDim.x) {
         const int e = int(item / RR_UNC_SLICES), slice = int(item % RR_UNC_SLICES);
-        const int64_t row = p.row_begin + p.unc_rows[e];
+        RerankParams p = p_in;
+        int64_t r, row;
+        select_group_row(p, p_in.unc_rows[e], r, row);
+        const bool vec = rows_vectorisable(p.feats, p.d);
+        const int64_t per_slice = ceil_div(p.n, RR_UNC_SLICES);
         const float* xi = p.feats + row * p.d;
         const float ni = p.sq_norms[row];
         const int64_t c0 = slice * per_slice, c1 = min64(p.n, c0 + per_slice);
@@ -353,13 +436,15 @@ exact_slices_kernel(const RerankParams p) {
 // one warp per uncertified row: k best of its slice lists by (exact key, index), values recomputed
 template <int MODE>
 __global__ void __launch_bounds__(RR_WARPS * 32)
-exact_merge_kernel(const RerankParams p) {
+exact_merge_kernel(const RerankParams p_in) {
     const int lane = threadIdx.x & 31;
-    const int cnt = *p.unc_cnt;
+    const int cnt = *p_in.unc_cnt;
     constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
-    const bool vec = rows_vectorisable(p.feats, p.d);
     for (int e = blockIdx.x * RR_WARPS + (threadIdx.x >> 5); e < cnt; e += gridDim.x * RR_WARPS) {
-        const int64_t r = p.unc_rows[e], row = p.row_begin + r;
+        RerankParams p = p_in;
+        int64_t r, row;
+        select_group_row(p, p_in.unc_rows[e], r, row);
+        const bool vec = rows_vectorisable(p.feats, p.d);
         const int total = RR_UNC_SLICES * p.k;                          // <= 256
         float cv[RR_UNC_SLICES]; int ci[RR_UNC_SLICES];
 #pragma unroll

@@ -13,7 +13,7 @@
 //
 // HBM-bound: reads 4 B and writes 4 B per element; one warp per row (4 rows per CTA),
 // 128-bit loads, 64-bit stores.
-#include "common.cuh"
+#include "knn_tc.cuh"
 #include "rowdot.cuh"
 #include <stdlib.h>
 
@@ -36,11 +36,17 @@ int64_t ops_row_elems(int64_t d_pad) {
 template <bool VEC4>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
-                  int64_t row_elems, __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms) {
+                  int64_t row_elems, __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms,
+                  const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide) {
     const int lane = threadIdx.x & 31;
-    const int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
+    int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
     if (row >= n_pad) return;
     __nv_bfloat16* out_row = ops + row * row_elems;
+    float* norm_out = sq_norms != nullptr ? sq_norms + row : nullptr;
+    if (g_slides != nullptr) {                   // grouped launch: operand row `row` is row (row - off) of its slide
+        const RrSlide sl = g_slides[g_blk2slide[row >> 8]];
+        feats = sl.feats; n = sl.n; row -= sl.off;
+    }
     // column c lives at (c / 32) * 64 + (c % 32) (hi) and 32 further (lo)
     auto hi_at = [&](int64_t c) { return out_row + ((c >> 5) << 6) + (c & 31); };
     if (row >= n) {                              // padding rows are zero in both halves
@@ -86,7 +92,7 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
         }
     }
     norm = warp_butterfly(norm);
-    if (lane == 0 && sq_norms != nullptr) sq_norms[row] = norm;
+    if (lane == 0 && norm_out != nullptr) *norm_out = norm;
 }
 
 int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
@@ -94,9 +100,23 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (vec)
-        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms);
+        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr);
     else
-        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms);
+        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr);
+    HG_CHECK_LAUNCH();
+    count_launches(1);
+    return HG_OK;
+}
+
+// the rows of a whole group of slides (device tables, knn_tc.cuh) in one launch; n_pad = the group's operand rows
+int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
+                       __nv_bfloat16* ops, float* sq_norms, cudaStream_t st) {
+    const int64_t d_pad = ops_cols(d);
+    const unsigned blocks = (unsigned)ceil_div(n_pad, SPLIT_WARPS);
+    if (vec)
+        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide);
+    else
+        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

@@ -224,7 +224,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
             tp.colp = colp; tp.pos4 = pos4;
             tp.gscale = pos ? lambda_g / lambda_h : 0.f;
             tp.exclude_self = 0;
-            tp.dense_out = chunk; tp.dense_ld = n; tp.lambda_h = lambda_h;
+            tp.dense_out = chunk; tp.dense_ld = n; tp.lambda_h = lambda_h; tp.dense_self = 1;
             rc = tc_launch(ops, n_pad, tp, st);
             if (rc != HG_OK) return rc;
             const int64_t cnt = (r1 - r0) * n;
@@ -289,6 +289,6 @@ extern "C" int hg_similarity_dense_tc(const float* feats, int64_t n, int64_t d, 
     tp.colp = colp; tp.pos4 = pos4;
     tp.gscale = pos ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = 0;
-    tp.dense_out = out; tp.dense_ld = ld_out; tp.lambda_h = lambda_h;
+    tp.dense_out = out; tp.dense_ld = ld_out; tp.lambda_h = lambda_h; tp.dense_self = 1;
     return tc_launch(ops, n_pad, tp, st);
 }
