@@ -373,6 +373,24 @@ int hg_build_batch_enqueue(const hg_slide* slides, int num_slides, int64_t d, in
                            void* const* lane_workspaces, size_t bytes_per_lane,
                            void* const* lane_streams, int num_lanes, int num_threads);
 
+/* The same batch with a GROUPED front half, for slides of a few thousand patches (BASELINE config C4): consecutive
+ * slides are packed into groups of up to max_group_rows operand rows (every slide padded to a multiple of 256); a
+ * group's feature kNN is four launches on front_stream -- operand split, column parameters, ONE persistent launch
+ * of the fused tcgen05 kernel over a unit table spanning all the slides of the group, exact re-rank -- and the
+ * slides' back halves (spatial kNN, edge assembly, weights, CSR) run on the lanes behind it, next to the following
+ * group's fused kernel.  front_workspaces[0..1] (front_bytes each) alternate between groups.  Slides of 9,216
+ * rows or more take the per-slide path on a lane.  Results equal hg_build_batch_enqueue's bit for bit.
+ * Replaces the reference's one-slide-at-a-time loop, preprocess_hypergraph.py:651-670. */
+int hg_build_batch_grouped_workspace_bytes(const hg_slide* slides, int num_slides, int64_t d, int k, int spatial_k,
+                                           int want_csr, int64_t max_group_rows, size_t* front_bytes,
+                                           size_t* bytes_per_lane);
+int hg_build_batch_grouped_enqueue(const hg_slide* slides, int num_slides, int64_t d, int pos_dim,
+                                   int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                   int64_t max_group_rows,
+                                   void* const* front_workspaces, size_t front_bytes, void* front_stream,
+                                   void* const* lane_workspaces, size_t bytes_per_lane,
+                                   void* const* lane_streams, int num_lanes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -3,7 +3,7 @@
 // one host call and one stream synchronisation (the edge count) instead of a dozen round trips
 // through the host language -- what matters for batches of small slides (BASELINE config C4).
 // Mirrors the body of the reference's build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433).
-#include "common.cuh"
+#include "knn_tc.cuh"
 #include "sort_scan.cuh"
 #include <string>
 #include <thread>
@@ -57,6 +57,14 @@ extern "C" int hg_build_workspace_bytes(int64_t n, int64_t d, int k, int spatial
     return HG_OK;
 }
 
+static int build_back_half(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim, int k, int spatial_k,
+                           const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                           const int32_t* knn_idx, const float* knn_cos, int32_t* spatial_idx, float* spatial_d2,
+                           int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                           int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                           int64_t* num_edges_out_host, int64_t* num_edges_out_dev,
+                           char* ws, const BuildWs& w, void* stream);
+
 // num_edges_out_host != null: synchronising form (compact outputs sized by the host-known count);
 // else stream-ordered form: the count stays on the device (*num_edges_out_dev), nothing blocks.
 static int build_impl(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim,
@@ -91,6 +99,23 @@ static int build_impl(const float* feats, int64_t n, int64_t d, const float* pos
     rc = hg_knn_feature_cos(feats, n, d, pos, pos_dim, metric, lambda_h, lambda_g, k, 0, n, 1, 0, knn_idx, knn_val,
                             knn_cos, ws + w.off_knn, w.knn, stream);
     if (rc != HG_OK) return rc;
+    return build_back_half(feats, n, d, pos, pos_dim, k, spatial_k, labels, num_hyperedges, clique_pairs, knn_idx, knn_cos,
+                           spatial_idx, spatial_d2, max_edges, edge_index, edge_weights, csr_rowptr, csr_col, csr_eid,
+                           num_edges_out_host, num_edges_out_dev, ws, w, stream);
+}
+
+// everything behind the feature kNN: spatial kNN, edge assembly, weights, CSR (knn_cos: cos of every list entry)
+static int build_back_half(const float* feats, int64_t n, int64_t d, const float* pos, int pos_dim, int k, int spatial_k,
+                           const int32_t* labels, int num_hyperedges, int64_t clique_pairs,
+                           const int32_t* knn_idx, const float* knn_cos, int32_t* spatial_idx, float* spatial_d2,
+                           int64_t max_edges, int64_t* edge_index, float* edge_weights,
+                           int64_t* csr_rowptr, int64_t* csr_col, int64_t* csr_eid,
+                           int64_t* num_edges_out_host, int64_t* num_edges_out_dev,
+                           char* ws, const BuildWs& w, void* stream) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool want_csr = csr_rowptr != nullptr;
+    const int64_t bound = n * int64_t(k) + n * int64_t(spatial_k) + clique_pairs;
+    int rc = HG_OK;
     const int32_t* lists[2] = {knn_idx, nullptr};
     int ks[2] = {k, 0};
     int num_lists = 1;
@@ -214,4 +239,178 @@ extern "C" int hg_build_batch_enqueue(const hg_slide* slides, int num_slides, in
     for (int t = 0; t < num_threads; ++t)
         if (rcs[t] != HG_OK) { set_error("hg_build_batch_enqueue: %s", msgs[t].c_str()); return rcs[t]; }
     return HG_OK;
+}
+
+// ---- batches of SMALL slides: grouped front half ----------------------------------------------------------------
+// hg_build_batch_enqueue runs ~25 launches per slide, one of them the persistent fused kernel, which a slide of a
+// few thousand rows cannot fill.  Here consecutive slides are packed into groups of up to max_group_rows operand
+// rows; a group's feature kNN is FOUR launches on the front stream (knn_group_enqueue, knn_api.cu) and the slides'
+// back halves (spatial kNN, edge assembly, weights, CSR) then run on the lanes, next to the following group's
+// fused kernel.  Two front workspaces alternate, so group g + 2 waits for the back halves of group g.  Slides of
+// more than kGroupMaxN rows (where the symmetric single-slide kernel wins) take the per-slide path on a lane.
+namespace hg {
+constexpr int64_t kGroupMaxN = 9215;              // tc_sym_stride: symmetric mode from 9,216 rows up
+
+struct BatchGroup { int first, count; int64_t rows; };
+
+static std::vector<BatchGroup> make_groups(const hg_slide* slides, int num, int64_t max_group_rows) {
+    std::vector<BatchGroup> groups;
+    BatchGroup cur{0, 0, 0};
+    for (int i = 0; i < num; ++i) {
+        const bool big = slides[i].n > kGroupMaxN;
+        const int64_t rows = ops_rows(slides[i].n);
+        if (cur.count > 0 && (big || cur.rows + rows > max_group_rows)) { groups.push_back(cur); cur = BatchGroup{i, 0, 0}; }
+        if (big) { groups.push_back(BatchGroup{i, 1, -1}); cur = BatchGroup{i + 1, 0, 0}; continue; }     // rows = -1: per-slide path
+        if (cur.count == 0) cur.first = i;
+        cur.count++; cur.rows += rows;
+    }
+    if (cur.count > 0) groups.push_back(cur);
+    return groups;
+}
+
+static int plan_back(int64_t n, int k, int spatial_k, int64_t max_edges, bool want_csr, BuildWs* w) {
+    *w = BuildWs{};
+    int rc = HG_OK;
+    if (spatial_k > 0) {
+        rc = hg_knn_spatial_workspace_bytes(n, spatial_k, 0, n, &w->spatial);
+        if (rc != HG_OK) return rc;
+    }
+    rc = hg_edges_workspace_bytes(n, n * int64_t(k) + n * int64_t(spatial_k), 0, 0, &w->edges);
+    if (rc != HG_OK) return rc;
+    if (want_csr) {
+        rc = hg_csr_workspace_bytes(n, max_edges, &w->csr);
+        if (rc != HG_OK) return rc;
+    }
+    // the spatial search is over before the edge stage starts: both at offset 0
+    w->off_spatial = 0; w->off_edges = 0; w->off_csr = al1k(w->edges);
+    const size_t a = al1k(w->spatial), b = w->off_csr + al1k(w->csr);
+    w->bytes = a > b ? a : b;
+    return HG_OK;
+}
+
+static std::vector<KnnGroupSlide> group_slides(const hg_slide* slides, const BatchGroup& g, int k, char* cos_base,
+                                               size_t* cos_bytes) {
+    std::vector<KnnGroupSlide> gs(static_cast<size_t>(g.count));
+    size_t off = 0;
+    for (int j = 0; j < g.count; ++j) {
+        const hg_slide& s = slides[g.first + j];
+        gs[size_t(j)] = KnnGroupSlide{s.feats, s.pos, s.n, s.knn_idx, s.knn_val,
+                                      cos_base ? reinterpret_cast<float*>(cos_base + off) : nullptr};
+        off += al1k(size_t(s.n) * size_t(k) * 4);
+    }
+    if (cos_bytes) *cos_bytes = off;
+    return gs;
+}
+}  // namespace hg
+
+extern "C" int hg_build_batch_grouped_workspace_bytes(const hg_slide* slides, int num_slides, int64_t d, int k, int spatial_k,
+                                                      int want_csr, int64_t max_group_rows, size_t* front_bytes,
+                                                      size_t* bytes_per_lane) {
+    HG_REQUIRE(slides && num_slides > 0 && front_bytes && bytes_per_lane && max_group_rows >= 256, HG_ERR_BAD_ARG,
+               "hg_build_batch_grouped_workspace_bytes: bad argument");
+    size_t front = 0, lane = 0;
+    for (const BatchGroup& g : make_groups(slides, num_slides, max_group_rows)) {
+        if (g.rows < 0) {                                            // a big slide: whole build on a lane
+            BuildWs w{};
+            const hg_slide& s = slides[g.first];
+            int rc = plan_build(s.n, d, k, s.pos ? spatial_k : 0, 0, 0, s.max_edges, want_csr != 0, &w);
+            if (rc != HG_OK) return rc;
+            if (w.bytes > lane) lane = w.bytes;
+            continue;
+        }
+        size_t cos_bytes = 0;
+        const std::vector<KnnGroupSlide> gs = group_slides(slides, g, k, nullptr, &cos_bytes);
+        bool has_pos = true;
+        for (const KnnGroupSlide& s : gs) has_pos = has_pos && s.pos != nullptr;
+        const size_t need = al1k(knn_group_workspace_bytes(gs.data(), g.count, d, k, has_pos)) + cos_bytes;
+        if (need > front) front = need;
+        for (int j = 0; j < g.count; ++j) {
+            BuildWs w{};
+            const hg_slide& s = slides[g.first + j];
+            int rc = plan_back(s.n, k, s.pos ? spatial_k : 0, s.max_edges, want_csr != 0, &w);
+            if (rc != HG_OK) return rc;
+            if (w.bytes > lane) lane = w.bytes;
+        }
+    }
+    *front_bytes = al1k(front);
+    *bytes_per_lane = al1k(lane);
+    return HG_OK;
+}
+
+extern "C" int hg_build_batch_grouped_enqueue(const hg_slide* slides, int num_slides, int64_t d, int pos_dim,
+                                              int metric, float lambda_h, float lambda_g, int k, int spatial_k,
+                                              int64_t max_group_rows,
+                                              void* const* front_workspaces, size_t front_bytes, void* front_stream,
+                                              void* const* lane_workspaces, size_t bytes_per_lane,
+                                              void* const* lane_streams, int num_lanes) {
+    HG_REQUIRE(slides && num_slides > 0 && front_workspaces && front_workspaces[0] && front_workspaces[1] &&
+               lane_workspaces && lane_streams && num_lanes > 0 && max_group_rows >= 256, HG_ERR_BAD_ARG,
+               "hg_build_batch_grouped_enqueue: bad argument");
+    cudaStream_t fst = static_cast<cudaStream_t>(front_stream);
+    const std::vector<BatchGroup> groups = make_groups(slides, num_slides, max_group_rows);
+    std::vector<cudaEvent_t> events;                                  // destroyed at the end: CUDA defers the release
+    auto new_event = [&](cudaEvent_t* ev) {
+        cudaError_t e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+        if (e == cudaSuccess) events.push_back(*ev);
+        return e;
+    };
+    // back-half events of the last group that used each front workspace
+    std::vector<cudaEvent_t> busy[2];
+    int rc = HG_OK, slot = 0, lane_rr = 0;
+    for (size_t gi = 0; gi < groups.size() && rc == HG_OK; ++gi) {
+        const BatchGroup& g = groups[gi];
+        if (g.rows < 0) {                                            // big slide: the per-slide build on the next lane
+            const hg_slide& s = slides[g.first];
+            const int lane = lane_rr++ % num_lanes;
+            rc = build_impl(s.feats, s.n, d, s.pos, pos_dim, metric, lambda_h, lambda_g, k, s.pos ? spatial_k : 0, nullptr, 0, 0,
+                            s.knn_idx, s.knn_val, s.spatial_idx, s.spatial_d2, s.max_edges, s.edge_index, s.edge_weights,
+                            s.csr_rowptr, s.csr_col, s.csr_eid, nullptr, s.num_edges_out_device, lane_workspaces[lane],
+                            bytes_per_lane, lane_streams[lane]);
+            continue;
+        }
+        char* fws = static_cast<char*>(front_workspaces[slot]);
+        for (cudaEvent_t ev : busy[slot]) HG_CHECK_CUDA(cudaStreamWaitEvent(fst, ev, 0));
+        busy[slot].clear();
+        size_t cos_bytes = 0;
+        group_slides(slides, g, k, nullptr, &cos_bytes);
+        bool has_pos = true;
+        for (int j = 0; j < g.count; ++j) has_pos = has_pos && slides[g.first + j].pos != nullptr;
+        HG_REQUIRE(front_bytes >= cos_bytes, HG_ERR_WORKSPACE, "hg_build_batch_grouped_enqueue: front workspace too small");
+        const std::vector<KnnGroupSlide> gs = group_slides(slides, g, k, fws, nullptr);
+        const size_t knn_ws = front_bytes - cos_bytes;
+        rc = knn_group_enqueue(gs.data(), g.count, d, pos_dim, metric, lambda_h, lambda_g, k, 1, fws + cos_bytes, knn_ws, fst);
+        if (rc != HG_OK) break;
+        cudaEvent_t front_done;
+        HG_CHECK_CUDA(new_event(&front_done));
+        HG_CHECK_CUDA(cudaEventRecord(front_done, fst));
+        std::vector<char> lane_used(size_t(num_lanes), 0);
+        for (int j = 0; j < g.count && rc == HG_OK; ++j) {
+            const hg_slide& s = slides[g.first + j];
+            const int lane = lane_rr++ % num_lanes;
+            cudaStream_t lst = static_cast<cudaStream_t>(lane_streams[lane]);
+            if (!lane_used[size_t(lane)]) { HG_CHECK_CUDA(cudaStreamWaitEvent(lst, front_done, 0)); lane_used[size_t(lane)] = 1; }
+            BuildWs w{};
+            const int sk = s.pos ? spatial_k : 0;
+            rc = plan_back(s.n, k, sk, s.max_edges, s.csr_rowptr != nullptr, &w);
+            if (rc != HG_OK) break;
+            HG_REQUIRE(bytes_per_lane >= w.bytes, HG_ERR_WORKSPACE, "hg_build_batch_grouped_enqueue: lane workspace too small");
+            HG_REQUIRE(s.edge_index && s.edge_weights && s.num_edges_out_device && s.max_edges >= s.n * int64_t(k + sk),
+                       HG_ERR_BAD_ARG, "hg_build_batch_grouped_enqueue: slide %d: bad output buffers", g.first + j);
+            rc = build_back_half(s.feats, s.n, d, s.pos, pos_dim, k, sk, nullptr, 0, 0, s.knn_idx, gs[size_t(j)].out_cos,
+                                 s.spatial_idx, s.spatial_d2, s.max_edges, s.edge_index, s.edge_weights, s.csr_rowptr,
+                                 s.csr_col, s.csr_eid, nullptr, s.num_edges_out_device,
+                                 static_cast<char*>(lane_workspaces[lane]), w, lane_streams[lane]);
+        }
+        if (rc != HG_OK) break;
+        for (int l = 0; l < num_lanes; ++l) {
+            if (!lane_used[size_t(l)]) continue;
+            cudaEvent_t ev;
+            HG_CHECK_CUDA(new_event(&ev));
+            HG_CHECK_CUDA(cudaEventRecord(ev, static_cast<cudaStream_t>(lane_streams[l])));
+            busy[slot].push_back(ev);
+        }
+        slot ^= 1;
+    }
+    for (cudaEvent_t ev : events) cudaEventDestroy(ev);
+    return rc;
 }

@@ -4,6 +4,8 @@
 #include "sim_simt.cuh"
 #include <stdlib.h>
 #include <algorithm>
+#include <mutex>
+#include <string.h>
 #include <vector>
 
 namespace hg {
@@ -452,6 +454,39 @@ extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_a
 // exactly the column tiles of its own slide, in the same order, with the same list length.
 namespace hg {
 
+// Pinned host staging for the per-group tables.  cudaMemcpyAsync from PAGEABLE memory is staged by a driver worker
+// thread some time after the call returns, so the source must outlive the call; a small ring of pinned buffers,
+// each guarded by an event recorded behind its copy, gives a source that does and a copy that is a plain DMA.
+struct StageSlot { void* host = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; };
+static std::mutex g_stage_mu;
+static StageSlot g_stage[8];
+static int g_stage_next = 0;
+
+static int stage_acquire(size_t bytes, StageSlot** out) {
+    std::lock_guard<std::mutex> lock(g_stage_mu);
+    StageSlot& s = g_stage[g_stage_next];
+    g_stage_next = (g_stage_next + 1) % 8;
+    if (s.done != nullptr) {                       // the copy that last read this slot
+        HG_CHECK_CUDA(cudaEventSynchronize(s.done));
+        HG_CHECK_CUDA(cudaEventDestroy(s.done));
+        s.done = nullptr;
+    }
+    if (s.cap < bytes) {
+        if (s.host != nullptr) HG_CHECK_CUDA(cudaFreeHost(s.host));
+        s.host = nullptr; s.cap = 0;
+        const size_t cap = (bytes + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
+        HG_CHECK_CUDA(cudaHostAlloc(&s.host, cap, cudaHostAllocPortable));
+        s.cap = cap;
+    }
+    *out = &s;
+    return HG_OK;
+}
+static int stage_release(StageSlot* s, cudaStream_t st) {
+    HG_CHECK_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
+    HG_CHECK_CUDA(cudaEventRecord(s->done, st));
+    return HG_OK;
+}
+
 struct GroupLayout {
     int64_t n_pad, d_pad;                  // operand rows of the whole group
     int kl;
@@ -504,6 +539,27 @@ static GroupLayout group_layout(const KnnGroupSlide* slides, int num, int64_t d,
     return g;
 }
 
+// HG_B200_GROUP_DEBUG: print the slide table as the device sees it and check every list entry's range
+__global__ void group_debug_kernel(const RrSlide* sl, const int32_t* map, int num, int64_t n_pad, const float* part_val,
+                                   const int32_t* part_idx, int kl) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int i = 0; i < num; ++i)
+            printf("slide %d: feats %p pos %p off %lld n %lld part_off %lld splits %d out %p %p %p\n", i, (const void*)sl[i].feats,
+                   (const void*)sl[i].pos, (long long)sl[i].off, (long long)sl[i].n, (long long)sl[i].part_off, sl[i].splits,
+                   (void*)sl[i].out_idx, (void*)sl[i].out_val, (void*)sl[i].out_cos);
+        for (int64_t b = 0; b < n_pad / 256; ++b) printf("map[%lld] = %d\n", (long long)b, map[b]);
+    }
+    for (int i = 0; i < num; ++i) {
+        const int64_t cnt = int64_t(sl[i].splits) * sl[i].n * kl;
+        for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < cnt; e += int64_t(gridDim.x) * blockDim.x) {
+            const int idx = part_idx[sl[i].part_off + e];
+            if (idx < -1 || idx >= sl[i].n)
+                printf("slide %d list entry %lld: index %d out of [-1, %lld) score %f\n", i, (long long)e, idx, (long long)sl[i].n,
+                       part_val[sl[i].part_off + e]);
+        }
+    }
+}
+
 size_t knn_group_workspace_bytes(const KnnGroupSlide* slides, int num, int64_t d, int k, bool has_pos) {
     return group_layout(slides, num, d, k, has_pos).bytes;
 }
@@ -534,11 +590,17 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     RrSlide* d_slides = reinterpret_cast<RrSlide*>(ws + g.o_slides);
     int32_t* d_map = reinterpret_cast<int32_t*>(ws + g.o_map);
 
-    // host tables -> device (pageable source: staged at once by the driver, no device synchronisation)
+    // host tables (unit table, slide table, row-block -> slide map) in one pinned staging block laid out like the
+    // device side, so a single DMA moves them
+    StageSlot* stage = nullptr;
+    const size_t tab_bytes = g.bytes - g.o_units;
+    int rc = stage_acquire(tab_bytes, &stage);
+    if (rc != HG_OK) return rc;
+    char* hs = static_cast<char*>(stage->host);
+    RrSlide* rs = reinterpret_cast<RrSlide*>(hs + (g.o_slides - g.o_units));
+    int32_t* map = reinterpret_cast<int32_t*>(hs + (g.o_map - g.o_units));
     std::vector<TcUnit> units;
     units.reserve(size_t(g.num_units));
-    std::vector<RrSlide> rs(static_cast<size_t>(num));
-    std::vector<int32_t> map(size_t(g.n_pad / kRowPad));
     bool vec = d % 4 == 0;
     int max_splits = 1;
     for (int i = 0; i < num; ++i) {
@@ -556,23 +618,35 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
                 u.row0 = int32_t(g.off[i] + rb * TC_BM); u.row_end = int32_t(g.off[i] + s.n);
                 u.ct0 = ct_base + c0; u.ct1 = ct_base + std::max(c0, c1);
                 u.col_off = int32_t(g.off[i]);
-                u.part_off = g.part_off[i] + int64_t(sp) * s.n * g.kl + rb * TC_BM * g.kl;
+                u.part_off = g.part_off[i] + int64_t(sp) * s.n * g.kl;         // the kernel adds (row - col_off) * kl
                 units.push_back(u);
             }
         }
     }
     // longest units first (stable: units of a slide stay together, so CTAs running side by side share B tiles)
     std::stable_sort(units.begin(), units.end(), [](const TcUnit& a, const TcUnit& b) { return (a.ct1 - a.ct0) > (b.ct1 - b.ct0); });
-    HG_CHECK_CUDA(cudaMemcpyAsync(d_units, units.data(), units.size() * sizeof(TcUnit), cudaMemcpyHostToDevice, st));
-    HG_CHECK_CUDA(cudaMemcpyAsync(d_slides, rs.data(), rs.size() * sizeof(RrSlide), cudaMemcpyHostToDevice, st));
-    HG_CHECK_CUDA(cudaMemcpyAsync(d_map, map.data(), map.size() * 4, cudaMemcpyHostToDevice, st));
+    memcpy(hs, units.data(), units.size() * sizeof(TcUnit));
+    HG_CHECK_CUDA(cudaMemcpyAsync(d_units, hs, tab_bytes, cudaMemcpyHostToDevice, st));
+    rc = stage_release(stage, st);
+    if (rc != HG_OK) return rc;
     HG_CHECK_CUDA(cudaMemsetAsync(flags, 0, 16, st));
 
-    int rc = launch_split_group(d_slides, d_map, g.n_pad, d, vec, ops, norms, st);
+    const bool dbg = getenv("HG_B200_GROUP_DEBUG") != nullptr;      // synchronise after every phase and say which one failed
+    auto phase = [&](const char* what) {
+        if (!dbg) return HG_OK;
+        const cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { set_error("knn_group: %s failed: %s", what, cudaGetErrorString(e)); return int(HG_ERR_CUDA); }
+        return int(HG_OK);
+    };
+    rc = phase("table upload");
     if (rc != HG_OK) return rc;
+    rc = launch_split_group(d_slides, d_map, g.n_pad, d, vec, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    if ((rc = phase("operand split")) != HG_OK) return rc;
     float* norm_max = reinterpret_cast<float*>(flags) + 1;
     rc = launch_colparams_group(norms, pos_dim, g.n_pad, metric, colp, pos4, norm_max, d_slides, d_map, st);
     if (rc != HG_OK) return rc;
+    if ((rc = phase("column parameters")) != HG_OK) return rc;
 
     TcParams tp{};
     tp.d_pad = int(g.d_pad);
@@ -585,6 +659,11 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     rc = tc_launch_units(ops, g.n_pad, k, d_units, int(units.size()), tp, st);
     prof_end(st);
     if (rc != HG_OK) return rc;
+    if ((rc = phase("fused kernel")) != HG_OK) return rc;
+    if (dbg) {
+        group_debug_kernel<<<32, 256, 0, st>>>(d_slides, d_map, num, g.n_pad, tp.part_val, tp.part_idx, g.kl);
+        if ((rc = phase("list check")) != HG_OK) return rc;
+    }
 
     RerankParams rp{};
     rp.d = d; rp.n = g.n_pad; rp.pos_dim = pos_dim;
@@ -593,9 +672,9 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = max_splits; rp.kl = g.kl; rp.n_rows = g.n_pad; rp.row_begin = 0;
     rp.k = k;
-    bool want_cos = true;
-    for (int i = 0; i < num; ++i) want_cos = want_cos && slides[i].out_cos != nullptr;
-    rp.out_cos = want_cos ? slides[0].out_cos : nullptr;            // only selects the kernel variant; per slide below
+    const float* any_cos = nullptr;
+    for (int i = 0; i < num; ++i) if (slides[i].out_cos != nullptr) any_cos = slides[i].out_cos;
+    rp.out_cos = const_cast<float*>(any_cos);                       // only selects the kernel variant; per slide in the kernel
     rp.out_idx = slides[0].out_idx; rp.out_val = slides[0].out_val;
     rp.unc_cnt = flags + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + g.o_unc_rows);

@@ -81,18 +81,36 @@ constexpr int RR_MAX_CAND = RR_MAX_LIST + TC_BKT_CAP; // + the row's bucket (sym
 enum { RR_D2 = 0, RR_D2_DOT = 1, RR_DOT = 2 };       // what the exact pass accumulates per candidate
 
 
-// Grouped launches (several slides in one operand buffer, knn_tc.cuh TcUnit): the row `rg` of the group belongs to
-// slide blk2slide[rg / 256]; every per-slide quantity of the parameter block is switched to that slide, after
-// which the kernels below run unchanged on the slide's local row.  Returns false for padding rows.
-__device__ __forceinline__ bool select_group_row(RerankParams& p, int64_t rg, int64_t& r, int64_t& row) {
-    if (p.g_slides == nullptr) { r = rg; row = p.row_begin + rg; return true; }
-    const RrSlide sl = p.g_slides[p.g_blk2slide[rg >> 8]];
-    r = rg - sl.off; row = r;
-    if (r >= sl.n) return false;
-    p.feats = sl.feats; p.pos = sl.pos; p.n = sl.n; p.n_rows = sl.n; p.splits = sl.splits;
-    p.sq_norms += sl.off;
-    p.part_val += sl.part_off; p.part_idx += sl.part_off;
-    p.out_idx = sl.out_idx; p.out_val = sl.out_val; p.out_cos = sl.out_cos;
+// The per-row view of the parameter block.  Plain launches: the block's own fields.  Grouped launches (several
+// slides in one operand buffer, knn_tc.cuh TcUnit): row `rg` of the group belongs to slide blk2slide[rg / 256] and
+// every per-slide quantity comes from that slide's table entry.
+struct RowCtx {
+    const float* feats; const float* pos; const float* sq_norms;
+    const float* part_val; const int32_t* part_idx;
+    int64_t n, n_rows;            // rows of the slide; row stride between two splits' lists
+    int splits;
+    int32_t* out_idx; float* out_val; float* out_cos;
+    int64_t r, row;               // r: row of the lists / outputs, row: row of the features
+};
+// false for the padding rows of a group.  Deliberately NOT inlined: inlined into the kernels, nvcc 12.9 replaced the
+// grouped branch's c.feats by p.feats (null in a grouped parameter block) -- the PTX simply had no load of the table's
+// first field; behind a call the struct is written to local memory and read back as written.
+__device__ __noinline__ bool row_ctx(const RerankParams& p, int64_t rg, RowCtx& c) {
+    if (p.g_slides == nullptr) {
+        c.feats = p.feats; c.pos = p.pos; c.sq_norms = p.sq_norms; c.part_val = p.part_val; c.part_idx = p.part_idx;
+        c.n = p.n; c.n_rows = p.n_rows; c.splits = p.splits;
+        c.out_idx = p.out_idx; c.out_val = p.out_val; c.out_cos = p.out_cos;
+        c.r = rg; c.row = p.row_begin + rg;
+        return true;
+    }
+    const RrSlide* sl = p.g_slides + p.g_blk2slide[rg >> 8];
+    const int64_t off = sl->off;
+    c.n = sl->n; c.n_rows = c.n; c.splits = sl->splits;
+    c.r = rg - off; c.row = c.r;
+    if (c.r >= c.n) return false;
+    c.feats = sl->feats; c.pos = sl->pos; c.sq_norms = p.sq_norms + off;
+    c.part_val = p.part_val + sl->part_off; c.part_idx = p.part_idx + sl->part_off;
+    c.out_idx = sl->out_idx; c.out_val = sl->out_val; c.out_cos = sl->out_cos;
     return true;
 }
 
@@ -149,18 +167,19 @@ __device__ __forceinline__ void warp_pair_sums(const float* __restrict__ xi, con
 
 // ranking key (ascending), returned value and cosine of the pair (row, j) from its exact sums
 template <int MODE>
-__device__ __forceinline__ void exact_key(const RerankParams& p, int64_t row, int j, float d2, float dot, float ni,
+__device__ __forceinline__ void exact_key(const RerankParams& p, const RowCtx& c, int j, float d2, float dot, float ni,
                                           float& key, float& out, float& cs) {
-    cs = (MODE != RR_D2) ? cosine_from(dot, ni, __ldg(p.sq_norms + j)) : 0.f;
+    const int64_t row = c.row;
+    cs = (MODE != RR_D2) ? cosine_from(dot, ni, __ldg(c.sq_norms + j)) : 0.f;
     if (MODE == RR_DOT) {
         key = -cs; out = cs;
     } else if (p.metric == HG_METRIC_EUCLIDEAN) {
         key = d2; out = d2;
     } else {
         float d2g = 0.f;
-        if (p.pos != nullptr) {
-            for (int c = 0; c < p.pos_dim; ++c) {
-                const float df = __ldg(p.pos + row * p.pos_dim + c) - __ldg(p.pos + int64_t(j) * p.pos_dim + c);
+        if (c.pos != nullptr) {
+            for (int q = 0; q < p.pos_dim; ++q) {
+                const float df = __ldg(c.pos + row * p.pos_dim + q) - __ldg(c.pos + int64_t(j) * p.pos_dim + q);
                 d2g = fmaf(df, df, d2g);
             }
         }
@@ -170,17 +189,17 @@ __device__ __forceinline__ void exact_key(const RerankParams& p, int64_t row, in
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(RR_WARPS * 32, 3)
-rerank_kernel(const RerankParams p_in) {
+__global__ void __launch_bounds__(RR_WARPS * 32, 2)
+rerank_kernel(const RerankParams p) {
     const int lane = threadIdx.x & 31;
     const int64_t rg = int64_t(blockIdx.x) * RR_WARPS + (threadIdx.x >> 5);
-    if (rg >= p_in.n_rows) return;
-    RerankParams p = p_in;
-    int64_t r, row;                                  // r: row of the lists / outputs, row: row of the features
-    if (!select_group_row(p, rg, r, row)) return;
+    if (rg >= p.n_rows) return;
+    RowCtx c;
+    if (!row_ctx(p, rg, c)) return;
+    const int64_t r = c.r, row = c.row;
     // symmetric mode unless the bucket overflow flag made the classic kernel re-run
     const bool sym = p.ovf != nullptr && *p.ovf == 0;
-    const int splits = sym ? p.sym_plan.splits : p.splits;
+    const int splits = sym ? p.sym_plan.splits : c.splits;
     const int total = splits * p.kl;
     const int nbkt = sym ? min(p.bkt_cnt[row], p.bkt_cap) : 0;
 
@@ -188,15 +207,15 @@ rerank_kernel(const RerankParams p_in) {
     // Selection stops once a candidate's approximate score exceeds the k-th best by more than the
     // guaranteed 3xBF16 error slack (both scores off by <= eps in opposite directions): such a
     // candidate cannot enter the exact top-k, and neither can any later one.
-    const float ni = p.sq_norms[row];
+    const float ni = c.sq_norms[row];
     const float slack = 4.8828125e-4f * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
     // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
     // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still
     // belong to the exact top-k (many near-duplicates): the row goes to the exact fallback
     // (exact_slices_kernel).  Everything else is decided here, however many candidates sit inside the
     // slack: they are taken 32 at a time (almost always one round).
-    const float* xi = p.feats + row * p.d;
-    const bool vec = rows_vectorisable(p.feats, p.d);
+    const float* xi = c.feats + row * p.d;
+    const bool vec = rows_vectorisable(c.feats, p.d);
     constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
     constexpr int CB = 4;
     float kth = INFINITY;
@@ -219,9 +238,9 @@ rerank_kernel(const RerankParams p_in) {
             cv[q] = INFINITY; ci[q] = 0x7fffffff;
             if (t < total) {
                 const int s = t / p.kl, w = t - s * p.kl;
-                const int64_t o = (int64_t(s) * p.n_rows + r) * p.kl + w;
-                const int idx = p.part_idx[o];
-                if (idx >= 0) { cv[q] = p.part_val[o]; ci[q] = idx; }
+                const int64_t o = (int64_t(s) * c.n_rows + r) * p.kl + w;
+                const int idx = c.part_idx[o];
+                if (idx >= 0) { cv[q] = c.part_val[o]; ci[q] = idx; }
             } else if (t < ncand) {
                 const uint2 b = p.bkt[row * p.bkt_cap + (t - total)];
                 cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
@@ -266,14 +285,14 @@ rerank_kernel(const RerankParams p_in) {
 #pragma unroll
             for (int q = 0; q < CB; ++q) {
                 j[q] = __shfl_sync(0xffffffffu, sel, t0 + q);
-                xj[q] = p.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
+                xj[q] = c.feats + int64_t(j[q] >= 0 ? j[q] : row) * p.d;     // dummy read of the own row if absent
             }
             float d2[CB], dt[CB];
             warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
 #pragma unroll
             for (int q = 0; q < CB; ++q) {
                 if (lane != t0 + q || j[q] < 0) continue;
-                exact_key<MODE>(p, row, j[q], d2[q], dt[q], ni, my_val, my_out, my_cos);
+                exact_key<MODE>(p, c, j[q], d2[q], dt[q], ni, my_val, my_out, my_cos);
             }
         }
         const int my_idx = (sel >= 0) ? sel : 0x7fffffff;
@@ -287,9 +306,9 @@ rerank_kernel(const RerankParams p_in) {
                 rank += pair_less(ov, oi, my_val, my_idx) ? 1 : 0;
             }
             if (lane < nsel && sel >= 0 && rank < p.k) {
-                p.out_idx[r * p.k + rank] = sel;
-                p.out_val[r * p.k + rank] = my_out;
-                if (p.out_cos != nullptr) p.out_cos[r * p.k + rank] = my_cos;
+                c.out_idx[r * p.k + rank] = sel;
+                c.out_val[r * p.k + rank] = my_out;
+                if (c.out_cos != nullptr) c.out_cos[r * p.k + rank] = my_cos;
             }
             nbest = min(nsel, p.k);
             break;
@@ -325,23 +344,23 @@ rerank_kernel(const RerankParams p_in) {
         bk = nk; bo = no; bc = nc; bidx = nidx; nbest = total_best;
         if (last) {
             if (lane < nbest) {
-                p.out_idx[r * p.k + lane] = bidx;
-                p.out_val[r * p.k + lane] = bo;
-                if (p.out_cos != nullptr) p.out_cos[r * p.k + lane] = bc;
+                c.out_idx[r * p.k + lane] = bidx;
+                c.out_val[r * p.k + lane] = bo;
+                if (c.out_cos != nullptr) c.out_cos[r * p.k + lane] = bc;
             }
             break;
         }
     }
     // rows with fewer than k candidates: pad with (-1, NaN)
     for (int t = nbest + lane; t < p.k; t += 32) {
-        p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
-        if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+        c.out_idx[r * p.k + t] = -1; c.out_val[r * p.k + t] = NAN;
+        if (c.out_cos != nullptr) c.out_cos[r * p.k + t] = NAN;
     }
     if (p.unc_cnt != nullptr) {
         bool full_inside = false;
         for (int s2 = lane; s2 < splits; s2 += 32) {
-            const int64_t o = (int64_t(s2) * p.n_rows + r) * p.kl + (p.kl - 1);
-            full_inside |= p.part_idx[o] >= 0 && p.part_val[o] <= kth + slack;
+            const int64_t o = (int64_t(s2) * c.n_rows + r) * p.kl + (p.kl - 1);
+            full_inside |= c.part_idx[o] >= 0 && c.part_val[o] <= kth + slack;
         }
         if (__any_sync(0xffffffffu, full_inside) && lane == 0) p.unc_rows[atomicAdd(p.unc_cnt, 1)] = int32_t(rg);
     }
@@ -366,28 +385,28 @@ __device__ __forceinline__ void warp_list_insert(float& mv, int& mi, float v, in
 
 template <int MODE>
 __global__ void __launch_bounds__(RR_UNC_WARPS * 32)
-exact_slices_kernel(const RerankParams p_in) {
+exact_slices_kernel(const RerankParams p) {
     __shared__ float s_val[RR_UNC_WARPS][32];
     __shared__ int s_idx[RR_UNC_WARPS][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cnt = *p_in.unc_cnt;
+    const int cnt = *p.unc_cnt;
     constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
     constexpr int CB = 4;
     for (int64_t item = blockIdx.x; item < int64_t(cnt) * RR_UNC_SLICES; item += gridDim.x) {
         const int e = int(item / RR_UNC_SLICES), slice = int(item % RR_UNC_SLICES);
-        RerankParams p = p_in;
-        int64_t r, row;
-        select_group_row(p, p_in.unc_rows[e], r, row);
-        const bool vec = rows_vectorisable(p.feats, p.d);
-        const int64_t per_slice = ceil_div(p.n, RR_UNC_SLICES);
-        const float* xi = p.feats + row * p.d;
-        const float ni = p.sq_norms[row];
-        const int64_t c0 = slice * per_slice, c1 = min64(p.n, c0 + per_slice);
+        RowCtx c;
+        row_ctx(p, p.unc_rows[e], c);
+        const int64_t row = c.row;
+        const bool vec = rows_vectorisable(c.feats, p.d);
+        const int64_t per_slice = ceil_div(c.n, RR_UNC_SLICES);
+        const float* xi = c.feats + row * p.d;
+        const float ni = c.sq_norms[row];
+        const int64_t c0 = slice * per_slice, c1 = min64(c.n, c0 + per_slice);
         float mv = INFINITY; int mi = 0x7fffffff;                      // this warp's list, lane t = t-th best
         for (int64_t j0 = c0 + warp * CB; j0 < c1; j0 += RR_UNC_WARPS * CB) {
             const float* xj[CB];
 #pragma unroll
-            for (int q = 0; q < CB; ++q) xj[q] = p.feats + min64(j0 + q, p.n - 1) * p.d;
+            for (int q = 0; q < CB; ++q) xj[q] = c.feats + min64(j0 + q, c.n - 1) * p.d;
             float d2[CB], dt[CB];
             warp_pair_sums<WANT_D2, WANT_DOT, CB>(xi, xj, p.d, lane, vec, d2, dt);
 #pragma unroll
@@ -395,7 +414,7 @@ exact_slices_kernel(const RerankParams p_in) {
                 const int64_t j = j0 + q;
                 if (j >= c1 || (p.exclude_self && j == row)) continue;                 // warp-uniform
                 float key, out, cs;
-                exact_key<MODE>(p, row, int(j), d2[q], dt[q], ni, key, out, cs);
+                exact_key<MODE>(p, c, int(j), d2[q], dt[q], ni, key, out, cs);
                 const float kv = __shfl_sync(0xffffffffu, mv, p.k - 1);
                 const int ki = __shfl_sync(0xffffffffu, mi, p.k - 1);
                 if (pair_less(key, int(j), kv, ki)) warp_list_insert(mv, mi, key, int(j), p.k, lane);
@@ -436,15 +455,15 @@ exact_slices_kernel(const RerankParams p_in) {
 // one warp per uncertified row: k best of its slice lists by (exact key, index), values recomputed
 template <int MODE>
 __global__ void __launch_bounds__(RR_WARPS * 32)
-exact_merge_kernel(const RerankParams p_in) {
+exact_merge_kernel(const RerankParams p) {
     const int lane = threadIdx.x & 31;
-    const int cnt = *p_in.unc_cnt;
+    const int cnt = *p.unc_cnt;
     constexpr bool WANT_D2 = MODE != RR_DOT, WANT_DOT = MODE != RR_D2;
     for (int e = blockIdx.x * RR_WARPS + (threadIdx.x >> 5); e < cnt; e += gridDim.x * RR_WARPS) {
-        RerankParams p = p_in;
-        int64_t r, row;
-        select_group_row(p, p_in.unc_rows[e], r, row);
-        const bool vec = rows_vectorisable(p.feats, p.d);
+        RowCtx c;
+        row_ctx(p, p.unc_rows[e], c);
+        const int64_t r = c.r, row = c.row;
+        const bool vec = rows_vectorisable(c.feats, p.d);
         const int total = RR_UNC_SLICES * p.k;                          // <= 256
         float cv[RR_UNC_SLICES]; int ci[RR_UNC_SLICES];
 #pragma unroll
@@ -477,24 +496,24 @@ exact_merge_kernel(const RerankParams p_in) {
             nsel = t + 1;
         }
         // the selection order IS the (exact key, index) order; recompute value and cosine of every winner
-        const float* xi = p.feats + row * p.d;
-        const float ni = p.sq_norms[row];
+        const float* xi = c.feats + row * p.d;
+        const float ni = c.sq_norms[row];
         for (int t = 0; t < nsel; ++t) {
             const int j = __shfl_sync(0xffffffffu, sel, t);
-            const float* xj[1] = {p.feats + int64_t(j) * p.d};
+            const float* xj[1] = {c.feats + int64_t(j) * p.d};
             float d2[1], dt[1];
             warp_pair_sums<WANT_D2, WANT_DOT, 1>(xi, xj, p.d, lane, vec, d2, dt);
             float key, out, cs;
-            exact_key<MODE>(p, row, j, d2[0], dt[0], ni, key, out, cs);
+            exact_key<MODE>(p, c, j, d2[0], dt[0], ni, key, out, cs);
             if (lane == 0) {
-                p.out_idx[r * p.k + t] = j;
-                p.out_val[r * p.k + t] = out;
-                if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = cs;
+                c.out_idx[r * p.k + t] = j;
+                c.out_val[r * p.k + t] = out;
+                if (c.out_cos != nullptr) c.out_cos[r * p.k + t] = cs;
             }
         }
         for (int t = nsel + lane; t < p.k; t += 32) {
-            p.out_idx[r * p.k + t] = -1; p.out_val[r * p.k + t] = NAN;
-            if (p.out_cos != nullptr) p.out_cos[r * p.k + t] = NAN;
+            c.out_idx[r * p.k + t] = -1; c.out_val[r * p.k + t] = NAN;
+            if (c.out_cos != nullptr) c.out_cos[r * p.k + t] = NAN;
         }
     }
 }

@@ -83,6 +83,9 @@ SIGNATURES = {
                                                _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_build_batch_workspace_bytes": (_i32, [_vp, _i32, _i64, _i32, _i32, _i32, _psz]),
     "hg_build_batch_enqueue": (_i32, [_vp, _i32, _i64, _i32, _i32, _f32, _f32, _i32, _i32, _vp, _sz, _vp, _i32, _i32]),
+    "hg_build_batch_grouped_workspace_bytes": (_i32, [_vp, _i32, _i64, _i32, _i32, _i32, _i64, _psz, _psz]),
+    "hg_build_batch_grouped_enqueue": (_i32, [_vp, _i32, _i64, _i32, _i32, _f32, _f32, _i32, _i32, _i64,
+                                              _vp, _sz, _vp, _vp, _sz, _vp, _i32]),
     "hg_hypergraph_propagate": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "hg_knn_staged_workspace_bytes": (_i32, [_pst, _psz]),
     "hg_knn_staged_begin": (_i32, [_pst, _vp, _sz, _vp]),

@@ -209,12 +209,17 @@ class BatchResults:
 
 def build_batch(slides: Iterable, device=None, lanes: int = 4, threads: Optional[int] = None, *, k: int = 16,
                 kernel: str = "gaussian", lambda_h: float = 1.0, lambda_g: float = 0.0, spatial_k: int = 0,
-                return_csr: bool = False) -> BatchResults:
+                return_csr: bool = False, grouped: Optional[bool] = None, group_rows: Optional[int] = None) -> BatchResults:
     """Device-resident batch of slides (`features` or `(features, positions)` CUDA tensors, same D):
-    ONE C call (hg_build_batch_enqueue) enqueues every build stream-ordered, slide i on lane
-    i % lanes, with no synchronisation; outputs live in one arena.  Returns after the edge counts
-    have arrived (one small D2H).  The calling stream is ordered before and after the batch.
-    threads (HG_B200_BATCH_THREADS) > 1 drives the lanes from that many host threads."""
+    ONE C call enqueues every build stream-ordered with no synchronisation; outputs live in one arena.
+    Returns after the edge counts have arrived (one small D2H).  The calling stream is ordered before
+    and after the batch.
+
+    grouped (default on, HG_B200_BATCH_GROUPED=0 turns it off; needs k <= 32): hg_build_batch_grouped_enqueue --
+    the feature kNN of up to `group_rows` (HG_B200_GROUP_ROWS, default 131,072) operand rows of consecutive
+    slides is ONE persistent launch of the fused kernel, the back halves run on `lanes` streams behind it.
+    Otherwise hg_build_batch_enqueue: slide i entirely on lane i % lanes; threads (HG_B200_BATCH_THREADS) > 1
+    drives the lanes from that many host threads.  Both give the same results bit for bit."""
     import ctypes as C
     import time
 
@@ -266,23 +271,46 @@ def build_batch(slides: Iterable, device=None, lanes: int = 4, threads: Optional
             table[:, _F_ROWPTR], table[:, _F_COL], table[:, _F_EID] = ptrs[:, 6], ptrs[:, 7], ptrs[:, 8]
         table[:, _F_NE] = e_dev.data_ptr() + 8 * np.arange(num)
         tptr = table.ctypes.data
-        nbytes = C.c_size_t(0)
-        L.check(lib.hg_build_batch_workspace_bytes(tptr, num, d, k, spatial_k, int(return_csr), C.byref(nbytes)))
+        if grouped is None:
+            grouped = os.environ.get("HG_B200_BATCH_GROUPED", "1") != "0"
+        grouped = bool(grouped) and k <= 32
+        if group_rows is None:
+            group_rows = int(os.environ.get("HG_B200_GROUP_ROWS", str(128 * 1024)))
+        nbytes, fbytes = C.c_size_t(0), C.c_size_t(0)
+        if grouped:
+            L.check(lib.hg_build_batch_grouped_workspace_bytes(tptr, num, d, k, spatial_k, int(return_csr), group_rows,
+                                                               C.byref(fbytes), C.byref(nbytes)))
+        else:
+            L.check(lib.hg_build_batch_workspace_bytes(tptr, num, d, k, spatial_k, int(return_csr), C.byref(nbytes)))
         cur = torch.cuda.current_stream(dev)
-        streams = _lane_streams(dev, min(lanes, num))
+        streams = _lane_streams(dev, min(lanes, num) + (1 if grouped else 0))
         start = torch.cuda.Event()
         start.record(cur)
         wss = []
-        for s in streams:
+        for i, s in enumerate(streams):
             s.wait_event(start)
             with torch.cuda.stream(s):
-                wss.append(L.Workspace.get(dev, nbytes.value, "batch"))
-        arr_ws = (C.c_void_p * len(streams))(*[w.data_ptr() for w in wss])
-        arr_st = (C.c_void_p * len(streams))(*[s.cuda_stream for s in streams])
+                if grouped and i == 0:         # the front stream owns the two alternating group workspaces
+                    wss.append((L.Workspace.get(dev, max(fbytes.value, 1), "batch_front0"),
+                                L.Workspace.get(dev, max(fbytes.value, 1), "batch_front1")))
+                else:
+                    wss.append(L.Workspace.get(dev, max(nbytes.value, 1), "batch"))
         t1 = time.perf_counter()
-        L.check(lib.hg_build_batch_enqueue(tptr, num, d, pos_dim, L.METRIC[kernel], float(lambda_h),
-                                           float(lambda_g if kernel == "gaussian" else 0.0), k, spatial_k,
-                                           arr_ws, nbytes.value, arr_st, len(streams), max(1, int(threads))))
+        if grouped:
+            front, lane_st, lane_ws = streams[0], streams[1:], wss[1:]
+            arr_f = (C.c_void_p * 2)(wss[0][0].data_ptr(), wss[0][1].data_ptr())
+            arr_ws = (C.c_void_p * len(lane_st))(*[w.data_ptr() for w in lane_ws])
+            arr_st = (C.c_void_p * len(lane_st))(*[s.cuda_stream for s in lane_st])
+            L.check(lib.hg_build_batch_grouped_enqueue(tptr, num, d, pos_dim, L.METRIC[kernel], float(lambda_h),
+                                                       float(lambda_g if kernel == "gaussian" else 0.0), k, spatial_k,
+                                                       group_rows, arr_f, fbytes.value, front.cuda_stream,
+                                                       arr_ws, nbytes.value, arr_st, len(lane_st)))
+        else:
+            arr_ws = (C.c_void_p * len(streams))(*[w.data_ptr() for w in wss])
+            arr_st = (C.c_void_p * len(streams))(*[s.cuda_stream for s in streams])
+            L.check(lib.hg_build_batch_enqueue(tptr, num, d, pos_dim, L.METRIC[kernel], float(lambda_h),
+                                               float(lambda_g if kernel == "gaussian" else 0.0), k, spatial_k,
+                                               arr_ws, nbytes.value, arr_st, len(streams), max(1, int(threads))))
         t2 = time.perf_counter()
         for s in streams:
             ev = torch.cuda.Event()
@@ -295,7 +323,7 @@ def build_batch(slides: Iterable, device=None, lanes: int = 4, threads: Optional
                 t.record_stream(s)
         counts = e_dev.cpu().numpy()           # waits for the batch (the calling stream is ordered after every lane)
     LAST_BATCH_STATS.update(prepare_ms=(t1 - t0) * 1e3, enqueue_ms=(t2 - t1) * 1e3, total_ms=(time.perf_counter() - t0) * 1e3,
-                            lanes=len(streams), threads=int(threads), slides=num)
+                            lanes=len(streams) - int(grouped), threads=int(threads), slides=num, grouped=bool(grouped))
     return BatchResults(arena, table, offs, counts, k, spatial_k, return_csr)
 
 

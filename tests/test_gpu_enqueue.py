@@ -57,6 +57,37 @@ def test_build_batch_many_small_slides_on_four_streams():
         _equal(a, b)
 
 
+@pytest.mark.parametrize("group_rows,with_pos", [(4096, False), (128 * 1024, False), (16384, True)])
+def test_build_batch_grouped_front_half_equals_per_slide_builds(group_rows, with_pos):
+    """hg_build_batch_grouped_enqueue: the slides of a group share one operand buffer and ONE launch of the fused
+    kernel (unit table); small groups force many groups, alternating front workspaces and single-slide groups; the
+    9,500-row slide takes the per-slide (symmetric) path in the middle of the batch.  Bit-equal to the ungrouped
+    batch and to one-by-one builds."""
+    sizes = [300, 5000, 2049, 9500, 256, 257, 4096, 8192, 1000, 3000, 2, 700, 6000, 2304]
+    slides = []
+    for i, s in enumerate(sizes):
+        f, p = synth.make_slide(int(s), 128, 300 + i, "gaussian")
+        slides.append((_cuda(f), _cuda(p)) if with_pos else _cuda(f))
+    kw = dict(k=16, kernel="gaussian", lambda_h=1.0, return_csr=True)
+    keys = KEYS
+    if with_pos:
+        kw.update(lambda_g=1.0 / 128, spatial_k=4)
+        keys = KEYS + ("spatial_idx", "spatial_d2")
+    grouped = build_batch(slides, lanes=3, grouped=True, group_rows=group_rows, **kw)
+    from hg_b200 import pipeline
+    assert pipeline.LAST_BATCH_STATS["grouped"] is True
+    plain = build_batch(slides, lanes=3, grouped=False, **kw)
+    torch.cuda.synchronize()
+    for a, b in zip(grouped, plain):
+        _equal(a, b, keys)
+    for i in (0, 3, 7, 10):
+        x, p = slides[i] if with_pos else (slides[i], None)
+        _equal(grouped[i], hg_b200.knn_hyperedges(x, p, **kw), keys)
+    again = build_batch(slides, lanes=2, grouped=True, group_rows=group_rows, **kw)     # workspaces reused
+    for a, b in zip(grouped, again):
+        _equal(a, b, keys)
+
+
 @pytest.mark.parametrize("lanes", [1, 3])
 def test_pipeline_lanes_from_host_memory(lanes):
     sizes = [700, 4100, 900, 2600, 3300, 512, 6000]
