@@ -197,6 +197,21 @@ int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int64_t n,
                     int64_t* rowptr, int64_t* col, int64_t* eid,
                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* hg_csr_from_coo for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO counterpart in the reference.  Same inputs,
+ * outputs and result as hg_csr_from_coo, but the scratch lives in a file-scope device array of
+ * HG_CSR_STATIC_SCRATCH_BYTES (18 MiB) that every GPU loading the library holds until exit; the call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine).  Limits: n <= HG_CSR_STATIC_MAX_N and
+ * num_edges <= HG_CSR_STATIC_MAX_EDGES, beyond which it returns HG_ERR_UNSUPPORTED.  All calls on a device share
+ * the array (it keeps the previous call's contents; the build initialises what it reads): calls that overlap on
+ * the GPU race -- keep them on one stream or order them with events.  The device must be current. */
+#define HG_CSR_STATIC_MAX_N           131072
+#define HG_CSR_STATIC_MAX_EDGES       524288
+#define HG_CSR_STATIC_SCRATCH_BYTES   (18 * 1024 * 1024)
+int hg_csr_from_coo_static(const int64_t* edge_index, int64_t num_edges, int64_t n,
+                           int64_t* rowptr, int64_t* col, int64_t* eid, void* stream);
+
+
 /* ---- A8: dense-threshold builder -------------------------------------------------------
  * Keep every ordered (i, j), diagonal included, with K[i, j] >= threshold, row
  * major.  similarity_kernel.py:193-210.  K is a dense n x n matrix (small N). */

@@ -1,6 +1,7 @@
 // A6 cosine edge weights, CSR incidence, A8 dense-threshold edge builder.
 #include "common.cuh"
 #include "rowdot.cuh"
+#include <mutex>
 #include "sort_scan.cuh"
 
 namespace hg {
@@ -320,6 +321,52 @@ extern "C" int hg_csr_from_coo(const int64_t* edge_index, int64_t num_edges, int
     HG_REQUIRE(num_edges >= 0, HG_ERR_BAD_ARG, "hg_csr_from_coo: bad argument");
     return csr_build(edge_index, num_edges, nullptr, num_edges, n, rowptr, col, eid, workspace, workspace_bytes,
                      static_cast<cudaStream_t>(stream));
+}
+
+// ---- hg_csr_from_coo without any allocation on the caller's side ------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the scratch of the CSR build --
+// sort keys and payloads, digit tables, first_hi / first_lo -- lives in a file-scope device array instead of a
+// caller-provided workspace.  Every GPU that loads the library holds HG_CSR_STATIC_SCRATCH_BYTES (18 MiB) until
+// the process exits.  The array is shared by every call on a device and keeps the last call's contents: the build
+// initialises everything it reads (the same kernels run on an uninitialised caller workspace in hg_csr_from_coo),
+// but two calls that overlap on the GPU (different streams, or threads) race on it -- serialise them.
+// In host code the array's name is only a stand-in for the symbol, not a device address: the address is looked up
+// once per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+static __device__ __align__(256) unsigned char g_csr_static_scratch[HG_CSR_STATIC_SCRATCH_BYTES];
+
+static std::mutex g_csr_static_mu;
+static void* g_csr_static_addr[64] = {};          // per device
+
+extern "C" int hg_csr_from_coo_static(const int64_t* edge_index, int64_t num_edges, int64_t n,
+                                      int64_t* rowptr, int64_t* col, int64_t* eid, void* stream) {
+    HG_REQUIRE(num_edges >= 0 && n > 0, HG_ERR_BAD_ARG, "hg_csr_from_coo_static: bad argument");
+    HG_REQUIRE(n <= HG_CSR_STATIC_MAX_N && num_edges <= HG_CSR_STATIC_MAX_EDGES, HG_ERR_UNSUPPORTED,
+               "hg_csr_from_coo_static: n = %lld / num_edges = %lld beyond the static scratch (n <= %lld, num_edges <= %lld); "
+               "use hg_csr_from_coo with a caller workspace", (long long)n, (long long)num_edges,
+               (long long)HG_CSR_STATIC_MAX_N, (long long)HG_CSR_STATIC_MAX_EDGES);
+    size_t need = 0;
+    int rc = hg_csr_workspace_bytes(n, num_edges, &need);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(need <= size_t(HG_CSR_STATIC_SCRATCH_BYTES), HG_ERR_UNSUPPORTED,
+               "hg_csr_from_coo_static: %zu bytes of scratch needed, %zu available", need, size_t(HG_CSR_STATIC_SCRATCH_BYTES));
+    int dev = 0;
+    HG_CHECK_CUDA(cudaGetDevice(&dev));
+    HG_REQUIRE(dev >= 0 && dev < 64, HG_ERR_UNSUPPORTED, "hg_csr_from_coo_static: device ordinal %d", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_csr_static_mu);
+        if (g_csr_static_addr[dev] == nullptr) {
+            void* ptr = nullptr;
+            HG_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_csr_static_scratch));       // this device's copy of the array
+            HG_REQUIRE(ptr != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 255) == 0, HG_ERR_CUDA,
+                       "hg_csr_from_coo_static: bad symbol address");
+            g_csr_static_addr[dev] = ptr;
+        }
+        scratch = g_csr_static_addr[dev];
+    }
+    return csr_build(edge_index, num_edges, nullptr, num_edges, n, rowptr, col, eid, scratch,
+                     size_t(HG_CSR_STATIC_SCRATCH_BYTES), static_cast<cudaStream_t>(stream));
 }
 
 // hg_csr_from_coo with the edge count still on the device: the sort runs over `capacity` slots (the

@@ -67,6 +67,7 @@ SIGNATURES = {
     "hg_edge_weights_cosine": (_i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "hg_csr_workspace_bytes": (_i32, [_i64, _i64, _psz]),
     "hg_csr_from_coo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_csr_from_coo_static": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
     "hg_threshold_workspace_bytes": (_i32, [_i64, _psz]),
     "hg_threshold_edges_count": (_i32, [_vp, _i64, _f32, _pi64, _vp, _sz, _vp]),
     "hg_kmeans_assign": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _vp, _vp]),
