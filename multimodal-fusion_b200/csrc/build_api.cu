@@ -5,6 +5,7 @@
 // Mirrors the body of the reference's build_hypergraph_knn_kmeans (preprocess_hypergraph.py:374-433).
 #include "knn_tc.cuh"
 #include "sort_scan.cuh"
+#include <stdlib.h>
 #include <string>
 #include <thread>
 #include <vector>
@@ -301,6 +302,41 @@ static std::vector<KnnGroupSlide> group_slides(const hg_slide* slides, const Bat
     if (cos_bytes) *cos_bytes = off;
     return gs;
 }
+// the group's slides as the grouped back half (group_back.cu) wants them; cos_base as in group_slides
+static std::vector<GbSlide> back_slides(const hg_slide* slides, const BatchGroup& g, int k, int spatial_k, char* cos_base) {
+    std::vector<GbSlide> gb(static_cast<size_t>(g.count));
+    size_t off = 0;
+    for (int j = 0; j < g.count; ++j) {
+        const hg_slide& s = slides[g.first + j];
+        const bool sp = spatial_k > 0 && s.pos != nullptr;
+        gb[size_t(j)] = GbSlide{s.n, s.feats, s.knn_idx, reinterpret_cast<const float*>(cos_base + off), sp ? s.spatial_idx : nullptr,
+                                s.edge_index, s.edge_weights, s.num_edges_out_device, s.csr_rowptr, s.csr_col, s.csr_eid};
+        off += al1k(size_t(s.n) * size_t(k) * 4);
+    }
+    return gb;
+}
+
+// HG_B200_GROUP_BACK=0: per-slide back halves on the lanes (the first version; kept for A/B runs)
+static bool grouped_back_half() {
+    const char* e = getenv("HG_B200_GROUP_BACK");
+    return !(e && atoi(e) == 0);
+}
+
+// scratch of the largest spatial search of a group (the searches of a group run one after the other on its lane)
+static int group_spatial_bytes(const hg_slide* slides, const BatchGroup& g, int spatial_k, size_t* bytes) {
+    *bytes = 0;
+    if (spatial_k <= 0) return HG_OK;
+    for (int j = 0; j < g.count; ++j) {
+        const hg_slide& s = slides[g.first + j];
+        if (s.pos == nullptr) continue;
+        size_t b = 0;
+        int rc = hg_knn_spatial_workspace_bytes(s.n, spatial_k, 0, s.n, &b);
+        if (rc != HG_OK) return rc;
+        if (b > *bytes) *bytes = b;
+    }
+    *bytes = al1k(*bytes);
+    return HG_OK;
+}
 }  // namespace hg
 
 extern "C" int hg_build_batch_grouped_workspace_bytes(const hg_slide* slides, int num_slides, int64_t d, int k, int spatial_k,
@@ -331,6 +367,13 @@ extern "C" int hg_build_batch_grouped_workspace_bytes(const hg_slide* slides, in
             if (rc != HG_OK) return rc;
             if (w.bytes > lane) lane = w.bytes;
         }
+        // grouped back half: the spatial searches' scratch, then the group's sort / CSR scratch
+        size_t sp_bytes = 0;
+        int rc = group_spatial_bytes(slides, g, spatial_k, &sp_bytes);
+        if (rc != HG_OK) return rc;
+        const std::vector<GbSlide> gb = back_slides(slides, g, k, spatial_k, nullptr);
+        const size_t back = sp_bytes + al1k(group_back_workspace_bytes(gb.data(), g.count, k, spatial_k));
+        if (back > lane) lane = back;
     }
     *front_bytes = al1k(front);
     *bytes_per_lane = al1k(lane);
@@ -378,12 +421,42 @@ extern "C" int hg_build_batch_grouped_enqueue(const hg_slide* slides, int num_sl
         HG_REQUIRE(front_bytes >= cos_bytes, HG_ERR_WORKSPACE, "hg_build_batch_grouped_enqueue: front workspace too small");
         const std::vector<KnnGroupSlide> gs = group_slides(slides, g, k, fws, nullptr);
         const size_t knn_ws = front_bytes - cos_bytes;
-        rc = knn_group_enqueue(gs.data(), g.count, d, pos_dim, metric, lambda_h, lambda_g, k, 1, fws + cos_bytes, knn_ws, fst);
+        // the fused kernel on the front stream, the exact re-rank on the group's lane (next to the next group's sweep)
+        const int lane0 = lane_rr % num_lanes;
+        cudaStream_t lst0 = static_cast<cudaStream_t>(lane_streams[lane0]);
+        rc = knn_group_enqueue(gs.data(), g.count, d, pos_dim, metric, lambda_h, lambda_g, k, 1, fws + cos_bytes, knn_ws, fst, lst0);
         if (rc != HG_OK) break;
         cudaEvent_t front_done;
         HG_CHECK_CUDA(new_event(&front_done));
-        HG_CHECK_CUDA(cudaEventRecord(front_done, fst));
+        HG_CHECK_CUDA(cudaEventRecord(front_done, lst0));
         std::vector<char> lane_used(size_t(num_lanes), 0);
+        if (grouped_back_half()) {
+            // the whole group's back half on ONE lane: spatial searches slide by slide, then group_back.cu
+            const int lane = lane_rr++ % num_lanes;
+            cudaStream_t lst = static_cast<cudaStream_t>(lane_streams[lane]);
+            char* lws = static_cast<char*>(lane_workspaces[lane]);
+            HG_CHECK_CUDA(cudaStreamWaitEvent(lst, front_done, 0));
+            lane_used[size_t(lane)] = 1;
+            size_t sp_bytes = 0;
+            rc = group_spatial_bytes(slides, g, spatial_k, &sp_bytes);
+            if (rc != HG_OK) break;
+            for (int j = 0; j < g.count && rc == HG_OK; ++j) {
+                const hg_slide& s = slides[g.first + j];
+                HG_REQUIRE(s.edge_index && s.edge_weights && s.num_edges_out_device &&
+                           s.max_edges >= s.n * int64_t(k + (s.pos ? spatial_k : 0)), HG_ERR_BAD_ARG,
+                           "hg_build_batch_grouped_enqueue: slide %d: bad output buffers", g.first + j);
+                if (spatial_k > 0 && s.pos != nullptr) {
+                    HG_REQUIRE(s.spatial_idx && s.spatial_d2, HG_ERR_BAD_ARG,
+                               "hg_build_batch_grouped_enqueue: slide %d: spatial output buffers missing", g.first + j);
+                    rc = hg_knn_spatial(s.pos, s.n, pos_dim, spatial_k, 0, s.n, s.spatial_idx, s.spatial_d2, lws, sp_bytes, lst);
+                }
+            }
+            if (rc != HG_OK) break;
+            const std::vector<GbSlide> gb = back_slides(slides, g, k, spatial_k, fws);
+            HG_REQUIRE(bytes_per_lane >= sp_bytes, HG_ERR_WORKSPACE, "hg_build_batch_grouped_enqueue: lane workspace too small");
+            rc = group_back_enqueue(gb.data(), g.count, d, k, spatial_k, lws + sp_bytes, bytes_per_lane - sp_bytes, lst);
+            if (rc != HG_OK) break;
+        } else {
         for (int j = 0; j < g.count && rc == HG_OK; ++j) {
             const hg_slide& s = slides[g.first + j];
             const int lane = lane_rr++ % num_lanes;
@@ -400,6 +473,7 @@ extern "C" int hg_build_batch_grouped_enqueue(const hg_slide* slides, int num_sl
                                  s.spatial_idx, s.spatial_d2, s.max_edges, s.edge_index, s.edge_weights, s.csr_rowptr,
                                  s.csr_col, s.csr_eid, nullptr, s.num_edges_out_device,
                                  static_cast<char*>(lane_workspaces[lane]), w, lane_streams[lane]);
+        }
         }
         if (rc != HG_OK) break;
         for (int l = 0; l < num_lanes; ++l) {

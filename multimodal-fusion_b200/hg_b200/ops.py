@@ -140,12 +140,14 @@ def knn_spatial(positions: torch.Tensor, k: int, rows: Optional[Tuple[int, int]]
 
 
 # ------------------------------------------------------------------- dense kernels
-# Rows from which square expansion-form kernels go through the tcgen05 kernel's dense-output mode; 0 (default) =
-# never.  The mode is 13-20x faster than the FP32 SIMT tiles (N = 16,384 x 1024: 20.6 -> 1.16 ms) but its entries
-# are only within ~1.5e-5 relative of float64 (measured maximum 1.4e-5 at D = 1024: the rounding of the 3xBF16
-# product and of the tensor core's FP32 accumulation over 192 MMA steps), which misses the 1e-5 bar of the scope
-# contract -- so it is opt-in: HG_B200_DENSE_TC_MIN_N=4096.  The kNN path is not affected: it re-ranks in FP32.
-DENSE_TC_MIN_N = int(os.environ.get("HG_B200_DENSE_TC_MIN_N", "0"))
+# Rows from which square expansion-form kernels (A1 / A2 as the reference returns them, similarity_kernel.py:43-52,
+# 79-84, 122) go through the tcgen05 kernel's dense-output mode; below that the FP32 SIMT tiles are as fast as the
+# operand split + launch.  The mode is 6-7x faster than the SIMT tiles (N = 16,384 x 1024: 11.6 -> 1.8 ms) and holds
+# the 1e-5 bar of the scope contract: hi*hi accumulates in one TMEM accumulator, the three small products
+# (hi*lo, lo*hi, lo*lo) in a second one, added in FP32 in the epilogue, and the diagonal is exact -- measured maximum
+# over ALL entries of a 16,384^2 output against float64: 4.4e-6 relative at D = 1024, 6.0e-6 at D = 1536 (the SIMT
+# tiles: 4.8e-6 / 6.6e-6; profiles/r02_dense_tc_accuracy.jsonl).  HG_B200_DENSE_TC_MIN_N=0 turns the routing off.
+DENSE_TC_MIN_N = int(os.environ.get("HG_B200_DENSE_TC_MIN_N", "4096"))
 
 
 def _dense_on_tensor_cores(xb, pb, n: int, d: int, lambda_h: float, form: int) -> bool:

@@ -43,9 +43,25 @@ def main():
             assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, overlap={overlap})"
         if overlap:
             overlapped = out["overlapped"]
+    E_small = int(ref["edge_index"].shape[1])
     dist.barrier()
+    # the same at C5's width and beyond C3's row count: n = 100,003 x 1536 (ragged blocks), every rank generates
+    # the whole slide from the seed, ranks > 0 drop everything but their block before the build
+    big = None
+    if os.environ.get("HG_NCCL_CHECK_BIG", "1") == "1":
+        del x, p, out, ref
+        nb, db = 100_003, 1536
+        fb = torch.from_numpy(synth.make_features(nb, db, 1240, "gaussian")).to(dev)
+        b0, b1 = multigpu.row_range(nb, rank, world)
+        outb = multigpu.knn_hyperedges_row_partitioned(fb[b0:b1].contiguous(), nb, k=k, kernel="gaussian", lambda_h=1.0,
+                                                       return_csr=True)
+        refb = hg_b200.knn_hyperedges(fb, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True)     # symmetric single-GPU pass
+        for key in ("knn_idx", "knn_val", "edge_index", "edge_weights", "csr_rowptr", "csr_col", "csr_eid"):
+            assert torch.equal(outb[key], refb[key]), f"rank {rank}: {key} differs at n = {nb}"
+        big = (nb, db, int(refb["edge_index"].shape[1]))
+        dist.barrier()
     if rank == 0:
-        print(f"NCCL_ROWPART_OK world={world} n={n} E={ref['edge_index'].shape[1]} overlapped={overlapped}")
+        print(f"NCCL_ROWPART_OK world={world} n={n} E={E_small} overlapped={overlapped} big={big}")
     dist.destroy_process_group()
 
 

@@ -75,12 +75,14 @@ def test_no_cpu_fallback():
         hg_b200.build_hypergraph_knn_kmeans(torch.randn(8, 4), torch.randn(8, 4), None)
 
 
-def test_dense_tensor_core_routing_is_opt_in(monkeypatch):
-    """A1 / A2 dense outputs stay on the FP32 kernels (1e-5 bar) unless HG_B200_DENSE_TC_MIN_N asks otherwise, and
-    even then only square expansion-form kernels of one matrix against itself qualify"""
+def test_dense_tensor_core_routing_is_square_only(monkeypatch):
+    """A1 / A2 dense outputs of 4,096 rows and more run on the tensor cores (1e-5 bar held, test_gpu_parity.py);
+    HG_B200_DENSE_TC_MIN_N=0 keeps them on the FP32 kernels; only square expansion-form kernels of one matrix
+    against itself qualify"""
     from hg_b200 import _lib, ops
     fake = object()
-    assert ops.DENSE_TC_MIN_N == 0
+    assert ops.DENSE_TC_MIN_N == 4096
+    monkeypatch.setattr(ops, "DENSE_TC_MIN_N", 0)
     assert not ops._dense_on_tensor_cores(None, None, 50000, 1024, 1.0, _lib.FORM_EXPANSION)
     monkeypatch.setattr(ops, "DENSE_TC_MIN_N", 4096)
     assert ops._dense_on_tensor_cores(None, None, 4096, 1024, 1.0, _lib.FORM_EXPANSION)

@@ -455,20 +455,24 @@ def test_aggregate_large_slide_streams_stats(monkeypatch):
     assert np.isclose(stats["avg_intra_cluster_similarity"], stats_dense["avg_intra_cluster_similarity"], rtol=1e-5)
 
 
-@pytest.mark.parametrize("n,d,with_pos", [(4096, 1024, False), (5000, 256, True), (4100, 100, True)])
-def test_dense_tc_opt_in_accuracy(n, d, with_pos, monkeypatch):
-    """A1 / A2 through the tensor-core kernel's dense-output mode (opt-in, HG_B200_DENSE_TC_MIN_N): entries within
-    3e-5 relative of the float64 kernel (measured maximum 1.4e-5) -- the 3xBF16 product does not reach the 1e-5
-    the default FP32 SIMT path holds, which is why it is not the default."""
+@pytest.mark.parametrize("n,d,with_pos", [(4096, 1024, False), (5000, 256, True), (4100, 100, True), (6000, 1536, True)])
+def test_dense_tc_default_routing_accuracy(n, d, with_pos, monkeypatch):
+    """A1 / A2 of square inputs from 4,096 rows up run on the tensor cores by default (dense-output mode of the
+    fused kernel: hi*hi in one TMEM accumulator, the small products in a second one, exact diagonal) and hold the
+    same 1e-5 relative bar against float64 as the FP32 SIMT tiles they replace; HG_B200_DENSE_TC_MIN_N=0 (here:
+    the module attribute) switches back."""
     feats, pos = synth.make_slide(n, d, 41, "gaussian")
     lam_h, lam_g = 1.0, (1.0 / 4096 if with_pos else 0.0)          # exponents stay below ~10: FP32 resolves them to 1e-6
     x, p = _cuda(feats), (_cuda(pos) if with_pos else None)
-    assert ops.DENSE_TC_MIN_N == 0 and not ops._dense_on_tensor_cores(None, None, n, d, lam_h, _lib.FORM_EXPANSION)
+    assert ops.DENSE_TC_MIN_N == 4096 and ops._dense_on_tensor_cores(None, None, n, d, lam_h, _lib.FORM_EXPANSION)
+    assert not ops._dense_on_tensor_cores(None, None, 4095, d, lam_h, _lib.FORM_EXPANSION)
+    K = ops.similarity_dense(x, pos_a=p, pos_b=p, lambda_h=lam_h, lambda_g=lam_g)
+    monkeypatch.setattr(ops, "DENSE_TC_MIN_N", 0)
     K_simt = ops.similarity_dense(x, pos_a=p, pos_b=p, lambda_h=lam_h, lambda_g=lam_g)
     monkeypatch.setattr(ops, "DENSE_TC_MIN_N", 4096)
-    K = ops.similarity_dense(x, pos_a=p, pos_b=p, lambda_h=lam_h, lambda_g=lam_g)
     assert not torch.equal(K, K_simt)                                 # two different kernels ran
-    rows = np.random.default_rng(2).choice(n, 256, replace=False)
+    assert bool((torch.diagonal(K) == 1.0).all())                     # d2(i, i) = 0 exactly
+    rows = np.random.default_rng(2).choice(n, 512, replace=False)
     x64 = feats.astype(np.float64)
     d2 = oracle.sq_dists_f64(x64[rows], x64)
     if with_pos:
@@ -476,8 +480,8 @@ def test_dense_tc_opt_in_accuracy(n, d, with_pos, monkeypatch):
         d2 = lam_h * d2 + lam_g * ((p64[rows, None, :] - p64[None, :, :]) ** 2).sum(-1)
     ref = np.exp(-d2)
     sel = torch.from_numpy(rows).cuda()
-    np.testing.assert_allclose(K_simt[sel].cpu().numpy(), ref, rtol=RTOL, atol=1e-30)      # the default path holds 1e-5
-    np.testing.assert_allclose(K[sel].cpu().numpy(), ref, rtol=3e-5, atol=1e-30)
+    np.testing.assert_allclose(K_simt[sel].cpu().numpy(), ref, rtol=RTOL, atol=1e-30)
+    np.testing.assert_allclose(K[sel].cpu().numpy(), ref, rtol=RTOL, atol=1e-30)         # the same bar on the tensor cores
     if with_pos:
         Kc = hg.compute_combined_similarity(x, p, lam_h, lam_g)       # the reference-facing entry takes the same path
         assert torch.equal(Kc, K)
