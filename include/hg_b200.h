@@ -325,6 +325,45 @@ int hg_knn_staged_sweep(const hg_knn_staged* s, int64_t col_begin, int64_t col_e
 int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_all, int32_t* out_idx, float* out_val,
                          float* out_cos, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- row-partitioned slides in SYMMETRIC mode ---------------------------------------------
+ * hg_knn_feature on a row block computes every tile of its rows (classic pass).  Here the GPUs share the
+ * checkerboard of the single-GPU symmetric mode: the owner of a row block computes about half of its tiles, keeps
+ * the row direction locally and pushes the transposed survivors into per-row buckets ON THE GPU THAT OWNS THE ROW
+ * (remote atomics + stores over NVLink; the caller maps the peers' bucket arrays, e.g. with CUDA IPC).  Row blocks
+ * are chunks of `chunk` rows, chunk a multiple of 256 (the last one may be shorter).  Per slide, stream-ordered:
+ *   prepass  (all n rows in feats_all) operand split, column parameters, own bucket counters + flags cleared,
+ *            threshold pre-pass of the own rows -> thr_all[row_begin, row_end)   (thr_all: [ceil256(n)] floats)
+ *   caller   all-gather of thr_all (entries beyond n = NaN); it is also the barrier behind which every GPU has
+ *            cleared its buckets
+ *   sweep    symmetric kernel over the own rows; peer_bkt_cnt[r] / peer_bkt[r] = the arrays of GPU r
+ *            ([chunk] int32, [chunk * 512] pairs of uint32; r = own rank: the own arrays)
+ *   caller   all-reduce(max) of own_flags[0] over the GPUs: the barrier behind which all pushes have landed
+ *   finish   classic pass if any bucket overflowed (any_overflow[0] != 0, then on every GPU alike), merge, exact
+ *            re-rank -> out_idx / out_val / out_cos [row_end - row_begin, k], equal to hg_knn_feature_cos's.
+ * The descriptor is hg_knn_staged (max_panel_cols / num_lanes unused).  Replaces the reference's sklearn kNN call,
+ * preprocess_hypergraph.py:379-382, for slides too large for one GPU's time budget. */
+/* peer access from the current device to `peer_device` (kernels of hg_knn_sympart_sweep store into mapped peer memory) */
+int hg_enable_peer_access(int peer_device);
+/* map an allocation another process exported (64-byte cudaIpcMemHandle_t) for kernels of the CURRENT device; the
+ * library maps, it does not allocate.  One open per exported allocation and process. */
+int hg_ipc_open(const void* handle64, void** base_out);
+/* a cudaMalloc'ed exchange buffer on the current device plus its 64-byte IPC handle, for peers to hg_ipc_open (the
+ * ONE allocation this library makes, on explicit request: framework allocators may return memory whose handles are
+ * not cudaIpcMemHandle_t); hg_peer_free releases it */
+int hg_peer_alloc(size_t bytes, void** ptr_out, void* handle64_out);
+int hg_peer_free(void* ptr);
+int hg_ipc_close(void* base);
+int hg_knn_sympart_workspace_bytes(const hg_knn_staged* s, size_t* bytes);
+int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
+                           int* own_flags, void* workspace, size_t workspace_bytes, void* stream);
+int hg_knn_sympart_sweep(const hg_knn_staged* s, const float* thr_all, int64_t chunk, int num_peers,
+                         void* const* peer_bkt_cnt, void* const* peer_bkt, int* own_flags,
+                         void* workspace, size_t workspace_bytes, void* stream);
+int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_all, const int* any_overflow,
+                          const int32_t* own_bkt_cnt, const void* own_bkt,
+                          int32_t* out_idx, float* out_val, float* out_cos,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- row (f)3, "next": what the consumer does with the incidence ---------------------------------
  * One HypergraphConv propagation  out = D^-1 H B^-1 H^T x  (torch_geometric semantics without
  * attention, unit hyperedge weights) the way downstream_survival/models/cust_omics.py:58-63,100-102

@@ -1,6 +1,7 @@
 // Error state, version, launch counter and the optional in-stream kernel timer of the C ABI.
 #include "common.cuh"
 #include <atomic>
+#include <string.h>
 
 namespace hg {
 static thread_local char g_err[512] = "";
@@ -69,5 +70,68 @@ extern "C" int hg_profile_collect(float* ms_total, int* launches) {
     *ms_total = sum;
     *launches = used;
     hg::g_prof_used.store(0);
+    return HG_OK;
+}
+
+// Maps a peer process's allocation (the 64-byte cudaIpcMemHandle_t it exported) into THIS process for the CURRENT
+// device, with peer access enabled lazily: the returned base is what kernels on this device may load / store.
+// (torch rebuilds shared tensors with the EXPORTING device current -- fine for copies, not for kernels running on
+// another device, hence this pair.)  One open per exported allocation and process; hg_ipc_close unmaps.
+extern "C" int hg_ipc_open(const void* handle64, void** base_out) {
+    HG_REQUIRE(handle64 && base_out, HG_ERR_BAD_ARG, "hg_ipc_open: null");
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(&h, handle64, sizeof(h));
+    const cudaError_t e = cudaIpcOpenMemHandle(base_out, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaGetLastError();                          // do not leave the error for the next launch check to find
+        hg::set_error("hg_ipc_open: cudaIpcOpenMemHandle -> %s", cudaGetErrorString(e));
+        return HG_ERR_CUDA;
+    }
+    return HG_OK;
+}
+// A device buffer that peers can map: plain cudaMalloc (torch's caching allocator may hand out expandable-segment
+// memory, whose handles cudaIpcOpenMemHandle does not take) + its IPC handle.  The one place where the library
+// allocates: a long-lived exchange buffer the caller asks for explicitly and frees with hg_peer_free.
+extern "C" int hg_peer_alloc(size_t bytes, void** ptr_out, void* handle64_out) {
+    HG_REQUIRE(bytes > 0 && ptr_out && handle64_out, HG_ERR_BAD_ARG, "hg_peer_alloc: bad argument");
+    void* p = nullptr;
+    HG_CHECK_CUDA(cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(p);
+        hg::set_error("hg_peer_alloc: cudaIpcGetMemHandle -> %s", cudaGetErrorString(e));
+        return HG_ERR_CUDA;
+    }
+    memcpy(handle64_out, &h, sizeof(h));
+    *ptr_out = p;
+    return HG_OK;
+}
+extern "C" int hg_peer_free(void* ptr) {
+    HG_REQUIRE(ptr, HG_ERR_BAD_ARG, "hg_peer_free: null");
+    HG_CHECK_CUDA(cudaFree(ptr));
+    return HG_OK;
+}
+extern "C" int hg_ipc_close(void* base) {
+    HG_REQUIRE(base, HG_ERR_BAD_ARG, "hg_ipc_close: null");
+    HG_CHECK_CUDA(cudaIpcCloseMemHandle(base));
+    return HG_OK;
+}
+
+// Lets kernels running on the CURRENT device dereference memory of `peer_device` that this process has mapped (its own
+// allocations there, or CUDA-IPC mappings opened in that device's context): the bucket pushes of the partitioned
+// symmetric pass (hg_knn_sympart_sweep) store straight into the owning GPU's arrays over NVLink.
+extern "C" int hg_enable_peer_access(int peer_device) {
+    int dev = 0;
+    HG_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev == peer_device) return HG_OK;
+    int can = 0;
+    HG_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer_device));
+    HG_REQUIRE(can != 0, HG_ERR_UNSUPPORTED, "hg_enable_peer_access: device %d cannot access device %d", dev, peer_device);
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return HG_OK; }
+    HG_CHECK_CUDA(e);
     return HG_OK;
 }

@@ -696,3 +696,184 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
 }
 
 }  // namespace hg
+
+// ---- symmetric pass over a slide whose ROWS are partitioned over several GPUs (C5) ---------------------------------
+// hg_knn_feature on a row block runs the classic full pass: every rank computes all tiles of its rows although the
+// tile (a, c) on the owner of a and the tile (c, a) on the owner of c hold the same products.  Here the checkerboard
+// of the single-GPU symmetric mode (knn_tc.cu) is cut along the row blocks instead: the rank that owns row block a
+// computes the tiles (a, c) of the checkerboard only (about half), keeps the row direction in its register lists and
+// sends the transposed survivors -- (score, row i) for column j -- into bucket j ON THE GPU THAT OWNS ROW j, with a
+// remote atomic + an 8-byte store over NVLink (peer memory mapped by the host side).  Per slide:
+//   prepass  operand split of all n rows (every rank holds them after the all-gather), column parameters, own bucket
+//            counters cleared, threshold pre-pass for the own rows -> thr[row_begin, row_end)
+//   (host)   all-gather of thr: every rank needs the bound of every column; also the barrier behind which all
+//            bucket counters are cleared
+//   sweep    the symmetric kernel over the own rows; pushes into the peers' buckets
+//   (host)   all-reduce(max) of the overflow flags: the barrier behind which all pushes have landed, and every rank
+//            learns whether ANY bucket overflowed (then all of them take the classic pass, as on one GPU)
+//   finish   classic pass guarded by the flag, merge of lists + own buckets, exact re-rank
+// Row blocks are 256-aligned chunks of `chunk` rows (multigpu.row_range_aligned); results equal hg_knn_feature's.
+namespace hg {
+
+struct SymPartWs {
+    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_flags, off_unc_rows, off_unc_part, bytes;
+    TcPlan plan, sym_plan, pre_plan;
+    int stride;
+    int64_t n_pad, d_pad, n_rows;
+};
+
+static int sympart_plan(const hg_knn_staged* s, SymPartWs* w) {
+    int rc = staged_check(s);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(s->row_begin % 256 == 0, HG_ERR_BAD_ARG, "hg_knn_sympart: row_begin must be a multiple of 256");
+    w->n_pad = ops_rows(s->n);
+    w->d_pad = ops_cols(s->d);
+    w->n_rows = s->row_end - s->row_begin;
+    w->stride = (s->n >= 32768) ? 16 : 8;
+    HG_REQUIRE(s->n / w->stride >= 4 * (s->k + 8), HG_ERR_UNSUPPORTED, "hg_knn_sympart: slide too small for the symmetric pass");
+    w->plan = tc_make_plan(s->n, w->n_rows, s->k, w->d_pad);
+    w->sym_plan = tc_make_plan_sym_rows(s->n, w->n_rows, s->k, w->d_pad);
+    w->pre_plan = tc_make_plan_prepass_rows(s->n, w->n_rows, s->k, w->d_pad, w->stride);
+    const int max_splits = std::max(w->plan.splits, w->sym_plan.splits);
+    size_t off = 0;
+    auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
+    w->off_ops = take(hg_operand_bytes(s->n, s->d));
+    w->off_norms = take(size_t(w->n_pad) * 4);
+    w->off_colp = take(size_t(w->n_pad) * 8);
+    w->off_pos4 = take(staged_has_pos(s) ? size_t(w->n_pad) * 16 : 0);
+    const size_t part = size_t(max_splits) * size_t(w->n_rows) * size_t(w->plan.kl);
+    w->off_pval = take(part * 4);
+    w->off_pidx = take(part * 4);
+    w->off_flags = take(16);
+    w->off_unc_rows = take(size_t(w->n_rows) * 4);
+    w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
+    w->bytes = off;
+    return HG_OK;
+}
+
+static int sympart_ws(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, SymPartWs* w) {
+    int rc = sympart_plan(s, w);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(workspace && workspace_bytes >= w->bytes, HG_ERR_WORKSPACE, "hg_knn_sympart: workspace too small (%zu < %zu)",
+               workspace_bytes, w->bytes);
+    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "hg_knn_sympart: workspace must be 1024-byte aligned");
+    return HG_OK;
+}
+
+static TcParams sympart_params(const hg_knn_staged* s, const SymPartWs& w, char* ws) {
+    const bool has_pos = staged_has_pos(s);
+    TcParams tp{};
+    tp.n = s->n; tp.row_begin = s->row_begin; tp.row_end = s->row_end; tp.d_pad = int(w.d_pad);
+    tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
+    tp.pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
+    tp.gscale = (has_pos && s->lambda_h > 0.f) ? s->lambda_g / s->lambda_h : 0.f;
+    tp.exclude_self = s->exclude_self;
+    tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
+    tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
+    return tp;
+}
+}  // namespace hg
+
+extern "C" int hg_knn_sympart_workspace_bytes(const hg_knn_staged* s, size_t* bytes) {
+    HG_REQUIRE(bytes, HG_ERR_BAD_ARG, "hg_knn_sympart_workspace_bytes: null");
+    SymPartWs w{};
+    int rc = sympart_plan(s, &w);
+    if (rc != HG_OK) return rc;
+    *bytes = w.bytes;
+    return HG_OK;
+}
+
+extern "C" int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
+                                      int* own_flags, void* workspace, size_t workspace_bytes, void* stream) {
+    SymPartWs w{};
+    int rc = sympart_ws(s, workspace, workspace_bytes, &w);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(feats_all && thr_all && own_bkt_cnt && own_flags, HG_ERR_BAD_ARG, "hg_knn_sympart_prepass: null buffer");
+    char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool has_pos = staged_has_pos(s);
+    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    float* norms = reinterpret_cast<float*>(ws + w.off_norms);
+    float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
+    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 16, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(own_flags, 0, 8, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(own_bkt_cnt, 0, size_t(w.n_rows) * 4, st));
+    rc = launch_split(feats_all, s->n, s->d, ops, norms, st);
+    if (rc != HG_OK) return rc;
+    TcParams tp = sympart_params(s, w, ws);
+    rc = launch_colparams(norms, has_pos ? s->pos : nullptr, s->pos_dim, s->n, w.n_pad, s->metric,
+                          const_cast<float2*>(tp.colp), const_cast<float4*>(tp.pos4), st, nullptr, nullptr, norm_max);
+    if (rc != HG_OK) return rc;
+    TcParams pre = tp;
+    pre.plan = w.pre_plan; pre.col_stride = w.stride; pre.exclude_self = 0;
+    pre.thr_rank = s->k; pre.thr_margin_cos = (s->metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
+    pre.thr_out = thr_all;                                    // indexed by the global row
+    prof_begin(st);
+    rc = tc_launch(ops, w.n_pad, pre, st);
+    prof_end(st);
+    return rc;
+}
+
+extern "C" int hg_knn_sympart_sweep(const hg_knn_staged* s, const float* thr_all, int64_t chunk, int num_peers,
+                                    void* const* peer_bkt_cnt, void* const* peer_bkt, int* own_flags,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
+    SymPartWs w{};
+    int rc = sympart_ws(s, workspace, workspace_bytes, &w);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(thr_all && peer_bkt_cnt && peer_bkt && own_flags && num_peers >= 1 && num_peers <= 8 && chunk > 0 &&
+               chunk % 256 == 0 && chunk * num_peers >= s->n && w.n_rows <= chunk, HG_ERR_BAD_ARG,
+               "hg_knn_sympart_sweep: bad partition (1..8 peers, 256-aligned chunks covering n)");
+    char* ws = static_cast<char*>(workspace);
+    TcParams sp = sympart_params(s, w, ws);
+    sp.plan = w.sym_plan;
+    sp.thr = thr_all; sp.bkt_cap = bucket_cap(); sp.ovf = own_flags;
+    sp.sblk_base = int(s->row_begin / 256);
+    sp.peer_chunk = chunk;
+    for (int r = 0; r < num_peers; ++r) {
+        HG_REQUIRE(peer_bkt_cnt[r] && peer_bkt[r], HG_ERR_BAD_ARG, "hg_knn_sympart_sweep: null peer buffer");
+        sp.peer_cnt[r] = static_cast<int32_t*>(peer_bkt_cnt[r]);
+        sp.peer_bkt[r] = static_cast<uint2*>(peer_bkt[r]);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    prof_begin(st);
+    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, sp, st);
+    prof_end(st);
+    return rc;
+}
+
+extern "C" int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_all, const int* any_overflow,
+                                     const int32_t* own_bkt_cnt, const void* own_bkt,
+                                     int32_t* out_idx, float* out_val, float* out_cos,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+    SymPartWs w{};
+    int rc = sympart_ws(s, workspace, workspace_bytes, &w);
+    if (rc != HG_OK) return rc;
+    HG_REQUIRE(feats_all && any_overflow && own_bkt_cnt && own_bkt && out_idx && out_val, HG_ERR_BAD_ARG,
+               "hg_knn_sympart_finish: null buffer");
+    char* ws = static_cast<char*>(workspace);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool has_pos = staged_has_pos(s);
+    // the classic pass over the own rows, which exits at once unless a bucket overflowed somewhere
+    TcParams tp = sympart_params(s, w, ws);
+    tp.plan = w.plan;
+    tp.guard = any_overflow;
+    prof_begin(st);
+    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, tp, st);
+    prof_end(st);
+    if (rc != HG_OK) return rc;
+    RerankParams rp{};
+    rp.feats = feats_all; rp.n = s->n; rp.d = s->d; rp.pos = has_pos ? s->pos : nullptr; rp.pos_dim = s->pos_dim;
+    rp.sq_norms = reinterpret_cast<float*>(ws + w.off_norms);
+    rp.norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
+    rp.metric = s->metric; rp.lambda_h = s->lambda_h; rp.lambda_g = has_pos ? s->lambda_g : 0.f;
+    rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
+    rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
+    rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
+    rp.sym_plan = w.sym_plan; rp.bkt_cnt = own_bkt_cnt; rp.bkt = static_cast<const uint2*>(own_bkt); rp.bkt_cap = bucket_cap();
+    rp.ovf = any_overflow; rp.bkt_row0 = s->row_begin;
+    rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
+    rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
+    rp.exclude_self = s->exclude_self;
+    return rerank_launch(rp, st);
+}

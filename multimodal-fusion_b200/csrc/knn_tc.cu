@@ -159,6 +159,16 @@ __device__ __forceinline__ uint32_t select32(const uint32_t (&r)[32], int j) {
 }
 
 __device__ __forceinline__ void bucket_push(const TcParams& p, int col, int row, uint32_t score_bits) {
+    if (p.peer_chunk > 0) {
+        // partitioned slide: column col is a row of GPU `owner`; the slot counter is a remote atomic over NVLink,
+        // the entry a remote 8-byte store (peer memory mapped by the host side, or the own arrays)
+        const int owner = int(col / p.peer_chunk);
+        const int64_t local = col - owner * p.peer_chunk;
+        const int slot = atomicAdd_system(p.peer_cnt[owner] + local, 1);
+        if (slot < p.bkt_cap) p.peer_bkt[owner][local * p.bkt_cap + slot] = make_uint2(score_bits, uint32_t(row));
+        else *p.ovf = 1;
+        return;
+    }
     const int slot = atomicAdd(p.bkt_cnt + col, 1);
     if (slot < p.bkt_cap) p.bkt[int64_t(col) * p.bkt_cap + slot] = make_uint2(score_bits, uint32_t(row));
     else *p.ovf = 1;
@@ -222,7 +232,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
                 const int row0 = int(ui.row0), rb = ui.rb;
                 for (int ct = ui.ct0; ct < ui.ct1; ++ct) {
-                    if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
+                    if (!owns_tile<SYM>(p.sblk_base + (CL == 2 ? rb : rb >> 1), ct)) continue;
                     for (int kb = 0; kb < num_kb; ++kb, ++it) {
                         const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
                         if (!p.pair_stages) {
@@ -266,7 +276,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
                 const int rb = ui.rb;
                 for (int ct = ui.ct0; ct < ui.ct1; ++ct) {
-                    if (!owns_tile<SYM>(CL == 2 ? rb : rb >> 1, ct)) continue;
+                    if (!owns_tile<SYM>(p.sblk_base + (CL == 2 ? rb : rb >> 1), ct)) continue;
                     // dense-output mode: ONE tile in flight, its two accumulators fill the 512 columns (see below)
                     const uint32_t buf = DENSE ? 0u : (tile & 1u), tph = DENSE ? (tile & 1u) : ((tile >> 1) & 1u);
                     ptx::mbar_wait(ptx::smem_u32(&sm->tmem_empty[buf]), tph ^ 1u);
@@ -328,7 +338,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
             const int rb = ui.rb;
             const int64_t row0 = ui.row0;
-            const int sblk = (CL == 2) ? rb : rb >> 1;          // 256-row super-block (symmetric tile ownership)
+            const int sblk = p.sblk_base + ((CL == 2) ? rb : rb >> 1);   // 256-row super-block (symmetric tile ownership)
             const int64_t row = row0 + quarter * 32 + lane;
             const int ct0 = ui.ct0, ct1 = ui.ct1;
             float lv[KLA];
@@ -666,6 +676,36 @@ TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
     return pl;
 }
 
+TcPlan tc_make_plan_sym_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
+    TcPlan pl{};
+    pl.cg = 1; pl.mc = 0; pl.cl = 1;
+    pl.sym = 1;
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(n, TC_BN));
+    pl.kl = list_len(k);
+    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad);
+    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
+    return pl;
+}
+
+// one unit per row block, every stride-th column: the bound comes straight out of the kernel (thr_out)
+TcPlan tc_make_plan_prepass_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad, int stride) {
+    TcPlan pl{};
+    pl.cg = 1; pl.cl = 1;
+    pl.n_rows = n_rows;
+    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_u = pl.num_rb;
+    pl.num_ct = int(ceil_div(ceil_div(n, stride), TC_BN));
+    pl.kl = list_len(k);
+    pl.cc = 1; pl.rc = kNumSMs; pl.splits = 1;
+    pl.ct_per_split = pl.num_ct;
+    pl.grid = int(min64(kNumSMs, pl.num_rb));
+    (void)d_pad;
+    return pl;
+}
+
 // Symmetric mode pays a 1/stride pre-pass and needs enough sample columns for a useful bound; it
 // wins from n ~ 9k up (measured at D = 1024: 2 % at n = 8192, 21 % at n = 10240; break-even at 9k x 512).  HG_B200_TC_SYM=0 disables it,
 // HG_B200_TC_SYM=<stride> forces it (any n with enough sample columns) with that pre-pass stride.
@@ -775,8 +815,9 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
     if (p.col_stride < 1) p.col_stride = 1;
     HG_REQUIRE((p.ct_base == 0 && !p.carry) || (!p.plan.sym && p.col_stride == 1 && p.plan.kl > 0 && !p.thr_out), HG_ERR_BAD_ARG,
                "tc_launch: column panels are for the classic list mode");
-    HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.row_begin == 0 &&
-                               p.row_end == p.n && p.thr && p.bkt_cnt && p.bkt && p.ovf),
+    HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.thr &&
+                               ((p.peer_chunk == 0 && p.row_begin == 0 && p.row_end == p.n && p.bkt_cnt && p.bkt && p.ovf) ||
+                                (p.peer_chunk > 0 && p.ovf && p.row_begin % 256 == 0 && p.sblk_base == p.row_begin / 256))),
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
     HG_REQUIRE(p.col_stride == 1 || (p.plan.cl == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need single CTAs");
     HG_REQUIRE(!p.plan.mc || p.plan.kl > 0, HG_ERR_BAD_ARG, "tc_launch: multicast pairs keep lists (no dense mode)");

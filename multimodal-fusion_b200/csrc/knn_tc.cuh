@@ -73,6 +73,14 @@ struct TcParams {
     uint2* bkt;
     int bkt_cap;
     int* ovf;
+    // symmetric mode over a ROW BLOCK of a slide whose rows are partitioned over several GPUs (C5): sblk_base =
+    // row_begin / 256; the bucket of column j lives on the GPU that owns row j = peer j / peer_chunk, whose arrays
+    // (mapped over NVLink, or local for the own block) are peer_cnt / peer_bkt[owner], indexed by
+    // j - owner * peer_chunk.  peer_chunk = 0: one GPU, bkt_cnt / bkt / ovf above.
+    int sblk_base;
+    int64_t peer_chunk;
+    int32_t* peer_cnt[8];
+    uint2* peer_bkt[8];         // an overflow raises the PUSHING GPU's own flag (ovf): the owner may already be past its sweep
     const int* guard;           // non-null: the whole grid exits at once unless *guard != 0
     uint64_t hint_a, hint_b;    // L2 cache hints of the A / B tile loads (filled by tc_launch)
     int pair_stages;            // producer refills two 48 KB stages at a time (see tc_launch)
@@ -93,6 +101,9 @@ int tc_panel_splits(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, in
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists = true);   // lists = false: dense-output mode
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad);
 TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride);
+// symmetric mode over the row block [row_begin, row_end) of a partitioned slide (row_begin a multiple of 256)
+TcPlan tc_make_plan_sym_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad);
+TcPlan tc_make_plan_prepass_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad, int stride);
 int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride
 constexpr int TC_BKT_CAP = 512;
 int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
@@ -125,6 +136,7 @@ struct RerankParams {
     // symmetric mode: candidates = per-(row, split) lists of the sym plan + the row's bucket;
     // if *ovf != 0 the classic kernel re-ran and (splits, kl) above describe its lists
     TcPlan sym_plan; const int32_t* bkt_cnt; const uint2* bkt; int bkt_cap; const int* ovf;
+    int64_t bkt_row0;            // bkt_cnt / bkt are indexed by (row - bkt_row0): 0, or row_begin for a partitioned slide
     int k;
     int32_t* out_idx; float* out_val;
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)

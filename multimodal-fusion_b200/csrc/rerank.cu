@@ -201,7 +201,7 @@ rerank_kernel(const RerankParams p) {
     const bool sym = p.ovf != nullptr && *p.ovf == 0;
     const int splits = sym ? p.sym_plan.splits : c.splits;
     const int total = splits * p.kl;
-    const int nbkt = sym ? min(p.bkt_cnt[row], p.bkt_cap) : 0;
+    const int nbkt = sym ? min(p.bkt_cnt[row - p.bkt_row0], p.bkt_cap) : 0;
 
     const int ncand = total + nbkt;
     // Selection stops once a candidate's approximate score exceeds the k-th best by more than the
@@ -242,7 +242,7 @@ rerank_kernel(const RerankParams p) {
                 const int idx = c.part_idx[o];
                 if (idx >= 0) { cv[q] = c.part_val[o]; ci[q] = idx; }
             } else if (t < ncand) {
-                const uint2 b = p.bkt[row * p.bkt_cap + (t - total)];
+                const uint2 b = p.bkt[(row - p.bkt_row0) * p.bkt_cap + (t - total)];
                 cv[q] = __uint_as_float(b.x); ci[q] = int(b.y);
             }
             if (round > 0 && !pair_less(last_v, last_i, cv[q], ci[q])) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }

@@ -93,6 +93,15 @@ SIGNATURES = {
     "hg_knn_staged_load": (_i32, [_pst, _vp, _i64, _i64, _vp, _sz, _vp]),
     "hg_knn_staged_sweep": (_i32, [_pst, _i64, _i64, _i32, _vp, _sz, _vp]),
     "hg_knn_staged_finish": (_i32, [_pst, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_enable_peer_access": (_i32, [_i32]),
+    "hg_ipc_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
+    "hg_ipc_close": (_i32, [_vp]),
+    "hg_peer_alloc": (_i32, [_sz, C.POINTER(_vp), C.c_char_p]),
+    "hg_peer_free": (_i32, [_vp]),
+    "hg_knn_sympart_workspace_bytes": (_i32, [_pst, _psz]),
+    "hg_knn_sympart_prepass": (_i32, [_pst, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_knn_sympart_sweep": (_i32, [_pst, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hg_knn_sympart_finish": (_i32, [_pst, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_aggregate_workspace_bytes": (_i32, [_i64, _i64, _i32, _psz]),
     "hg_aggregate_super_patches": (_i32, [_vp, _i64, _i64, _vp, _i32, _vp, _i32, _f32, _f32, _vp, _i64, _i32,
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -169,11 +169,126 @@ def _knn_overlapped(local_features: torch.Tensor, n: int, k: int, kernel: str, l
     return local, feats_all
 
 
+class _SymPartState:
+    """Per-(group, chunk) buffers of the partitioned symmetric pass: the own bucket arrays in ONE allocation, exported
+    once over CUDA IPC and mapped by every peer FOR ITS OWN DEVICE (collective constructor; hg_ipc_open -- torch's
+    own tensor sharing maps with the exporting device current, which serves copies but not kernels running on
+    another GPU), and the flag word.  `peer_cnt` / `peer_bkt` = raw device pointers per rank, None when the mapping
+    is not possible on this system (all ranks agree)."""
+
+    BKT_CAP = 512                                      # TC_BKT_CAP (knn_tc.cuh)
+
+    def __init__(self, chunk: int, device, group=None):
+        import ctypes as C
+        from . import _lib as L
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        cnt_bytes = -(-chunk * 4 // 256) * 256
+        self.flags = torch.zeros(2, dtype=torch.int32, device=device)
+        self.peer_cnt = self.peer_bkt = None
+        self.why = ""                                  # what kept the mapping from working, for diagnostics
+        self._mapped = []
+        self.own = None                                # raw device pointer of the own arrays (hg_peer_alloc)
+        lib = L.load_library()
+        ok, handle = 1, None
+        with torch.cuda.device(device):
+            ptr, hbuf = C.c_void_p(0), C.create_string_buffer(64)
+            if lib.hg_peer_alloc(cnt_bytes + chunk * self.BKT_CAP * 8, C.byref(ptr), hbuf) == 0 and ptr.value:
+                self.own = ptr.value
+                handle = (hbuf.raw, 0)
+            else:
+                self.why = f"export failed: {L.last_error()}"
+                ok = 0
+        handles = [None] * world
+        dist.all_gather_object(handles, handle, group=group)
+        bases = [None] * world
+        if ok and all(h is not None for h in handles):
+            with torch.cuda.device(device):
+                for r, (hbytes, off) in enumerate(handles):
+                    if r == rank:
+                        bases[r] = self.own
+                        continue
+                    base = C.c_void_p(0)
+                    if lib.hg_ipc_open(hbytes, C.byref(base)) != 0 or not base.value:
+                        self.why = L.last_error()
+                        ok = 0
+                        break
+                    self._mapped.append(base.value)
+                    bases[r] = base.value + off
+        else:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 1:
+            self.peer_cnt = bases
+            self.peer_bkt = [b + cnt_bytes for b in bases]
+            self.cnt_ptr, self.bkt_ptr = self.own, self.own + cnt_bytes
+
+
+_SYMPART = {}
+
+
+def _sympart_state(chunk: int, device, group=None) -> _SymPartState:
+    key = (id(group) if group is not None else None, int(chunk), torch.device(device).index)
+    if key not in _SYMPART:
+        _SYMPART[key] = _SymPartState(chunk, device, group)
+    return _SYMPART[key]
+
+
+def _knn_sympart(feats: torch.Tensor, n: int, k: int, kernel: str, lambda_h: float, lambda_g: float,
+                 pos: Optional[torch.Tensor], group):
+    """Feature kNN of this rank's aligned row block in SYMMETRIC mode (hg_knn_sympart_*): the ranks share the
+    checkerboard of tile pairs, transposed survivors travel into the owning rank's buckets over NVLink.  `feats` =
+    all n rows (after the all-gather).  Returns (idx, val, cos) of the own rows, or None when peer memory cannot be
+    mapped (all ranks agree)."""
+    import ctypes as C
+    from . import _lib as L
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = feats.device
+    chunk = row_range_aligned(n, 0, world)[1]
+    r0, r1 = row_range_aligned(n, rank, world)
+    st = _sympart_state(chunk, dev, group)
+    if st.peer_bkt is None:
+        if os.environ.get("HG_B200_SYMPART_DEBUG"):
+            print(f"[hg_b200] rank {rank}: symmetric row partition unavailable ({st.why or 'a peer could not map'})", flush=True)
+        return None
+    lib = L.load_library()
+    d = feats.shape[1]
+    use_pos = pos is not None and kernel == "gaussian" and lambda_g != 0.0
+    p = L.f32c(pos, dev) if use_pos else None
+    desc = L.KnnStaged(n=n, d=d, row_begin=r0, row_end=r1, max_panel_cols=n, pos=L.ptr(p),
+                       pos_dim=0 if p is None else p.shape[1], metric=L.METRIC[kernel], k=k, exclude_self=1,
+                       num_lanes=1, reserved=0, lambda_h=float(lambda_h), lambda_g=float(lambda_g if use_pos else 0.0))
+    n_pad = -(-n // 256) * 256
+    with torch.cuda.device(dev):
+        nbytes = C.c_size_t(0)
+        L.check(lib.hg_knn_sympart_workspace_bytes(C.byref(desc), C.byref(nbytes)))
+        ws = L.Workspace.get(dev, nbytes.value, "sympart")
+        stream = L.stream_ptr(dev)
+        thr = torch.full((n_pad,), float("nan"), dtype=torch.float32, device=dev)
+        L.check(lib.hg_knn_sympart_prepass(C.byref(desc), L.ptr(feats), L.ptr(thr), st.cnt_ptr, L.ptr(st.flags),
+                                           L.ptr(ws), nbytes.value, stream))
+        # every rank needs every column's bound; behind this collective all bucket counters are cleared
+        thr[:n] = all_gather_rows(thr[r0:r1].clone(), n, group, row_range_aligned)
+        arr_cnt = (C.c_void_p * world)(*st.peer_cnt)
+        arr_bkt = (C.c_void_p * world)(*st.peer_bkt)
+        L.check(lib.hg_knn_sympart_sweep(C.byref(desc), L.ptr(thr), chunk, world, arr_cnt, arr_bkt, L.ptr(st.flags),
+                                         L.ptr(ws), nbytes.value, stream))
+        # behind this collective all pushes have landed, and every rank knows whether any bucket overflowed
+        dist.all_reduce(st.flags, op=dist.ReduceOp.MAX, group=group)
+        rows = r1 - r0
+        out_idx = torch.empty((rows, k), dtype=torch.int32, device=dev)
+        out_val = torch.empty((rows, k), dtype=torch.float32, device=dev)
+        out_cos = torch.empty((rows, k), dtype=torch.float32, device=dev)
+        L.check(lib.hg_knn_sympart_finish(C.byref(desc), L.ptr(feats), L.ptr(st.flags), st.cnt_ptr, st.bkt_ptr,
+                                          L.ptr(out_idx), L.ptr(out_val), L.ptr(out_cos), L.ptr(ws), nbytes.value, stream))
+    return out_idx, out_val, out_cos
+
+
 def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: int = 16, kernel: str = "gaussian",
                                    lambda_h: float = 1.0, lambda_g: float = 0.0,
                                    positions: Optional[torch.Tensor] = None, spatial_k: int = 0,
                                    return_csr: bool = False, group=None, aligned: bool = False,
-                                   overlap: Optional[bool] = None,
+                                   overlap: Optional[bool] = None, symmetric: Optional[bool] = None,
                                    knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None,
                                    spatial_fn: Optional[Callable] = None) -> dict:
     """Config C5: `local_features` is this rank's row block [r1-r0, D] (`row_range`, or
@@ -202,8 +317,22 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
         if res is not None:
             local, feats = res
             overlapped = True
-    if local is None:
+    # symmetric mode over aligned row blocks (default on CUDA; HG_B200_SYMPART=0 or symmetric=False: classic pass):
+    # the ranks share the checkerboard of tile pairs instead of each computing every tile of its rows
+    mode = "overlapped staged panels" if overlapped else "classic row blocks"
+    if symmetric is None:
+        symmetric = os.environ.get("HG_B200_SYMPART", "1") != "0"
+    stride = 16 if n >= 32768 else 8
+    symmetric = (symmetric and local is None and aligned and knn_fn is None and local_features.is_cuda and world > 1
+                 and world <= 8 and all_have_rows and k <= 32 and n // stride >= 4 * (k + 8))
+    if symmetric:
         feats = all_gather_rows(local_features, n, group, ranges)           # the one big collective
+        local = _knn_sympart(feats, n, k, kernel, lambda_h, lambda_g, pos, group)
+        if local is not None:
+            mode = "symmetric tile pairs (buckets over NVLink)"
+    if local is None:
+        if feats is None:
+            feats = all_gather_rows(local_features, n, group, ranges)       # the one big collective
         with_cos = knn_fn is None          # an injected knn_fn returns (idx, val)
         if knn_fn is None:
             knn_fn = lambda x, rows: ops.knn_feature(x, k, kernel, positions=pos if lambda_g else None,   # noqa: E731
@@ -217,7 +346,7 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                 local += (torch.empty((0, k), dtype=torch.float32, device=feats.device),)
     idx_local, val_local = local[0], local[1]
     out = {"knn_idx": all_gather_rows(idx_local, n, group, ranges),
-           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": overlapped}
+           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": overlapped, "mode": mode}
     # cos(f_i, f_j) of every list entry travels with the lists: the edge weights are then looked up
     # instead of gathering two feature rows per edge
     knn_cos = all_gather_rows(local[2], n, group, ranges) if len(local) > 2 else None

@@ -13,6 +13,11 @@ import hg_b200                                   # noqa: E402
 from hg_b200 import multigpu, synth              # noqa: E402
 
 
+def _lib_err():
+    from hg_b200 import _lib
+    return _lib.last_error()
+
+
 def main():
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -34,15 +39,21 @@ def main():
     # 256-aligned row blocks: peers' blocks pulled over NVLink while the fused kernel sweeps the ones that
     # are here (staged kNN); same result bit for bit, with and without the overlap
     a0, a1 = multigpu.row_range_aligned(n, rank, world)
-    for overlap in (True, False):
+    modes = []
+    for overlap, symmetric in ((True, False), (False, False), (False, True), (False, True)):
         out = multigpu.knn_hyperedges_row_partitioned(x[a0:a1].contiguous(), n, k=k, kernel="gaussian", lambda_h=1.0,
                                                       lambda_g=lam_g, positions=p, spatial_k=8, return_csr=True,
-                                                      aligned=True, overlap=overlap)
+                                                      aligned=True, overlap=overlap, symmetric=symmetric)
         for key in ("knn_idx", "knn_val", "spatial_idx", "spatial_d2", "edge_index", "edge_weights", "csr_rowptr",
                     "csr_col", "csr_eid"):
-            assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, overlap={overlap})"
+            assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, overlap={overlap}, symmetric={symmetric})"
+        modes.append(out["mode"])
+        torch.cuda.synchronize()
+        if rank == 0 and os.environ.get("HG_NCCL_CHECK_VERBOSE"):
+            print(f"phase ok: overlap={overlap} symmetric={symmetric} mode={out['mode']}", flush=True)
         if overlap:
             overlapped = out["overlapped"]
+    assert modes[2].startswith("symmetric") and modes[3].startswith("symmetric"), (modes, _lib_err())     # twice: buffers reused
     E_small = int(ref["edge_index"].shape[1])
     dist.barrier()
     # the same at C5's width and beyond C3's row count: n = 100,003 x 1536 (ragged blocks), every rank generates
@@ -53,11 +64,16 @@ def main():
         nb, db = 100_003, 1536
         fb = torch.from_numpy(synth.make_features(nb, db, 1240, "gaussian")).to(dev)
         b0, b1 = multigpu.row_range(nb, rank, world)
-        outb = multigpu.knn_hyperedges_row_partitioned(fb[b0:b1].contiguous(), nb, k=k, kernel="gaussian", lambda_h=1.0,
-                                                       return_csr=True)
         refb = hg_b200.knn_hyperedges(fb, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True)     # symmetric single-GPU pass
+        outb = multigpu.knn_hyperedges_row_partitioned(fb[b0:b1].contiguous(), nb, k=k, kernel="gaussian", lambda_h=1.0,
+                                                       return_csr=True)                                # ragged blocks: classic
+        c0, c1 = multigpu.row_range_aligned(nb, rank, world)
+        outs = multigpu.knn_hyperedges_row_partitioned(fb[c0:c1].contiguous(), nb, k=k, kernel="gaussian", lambda_h=1.0,
+                                                       return_csr=True, aligned=True)                  # aligned: symmetric
+        assert outs["mode"].startswith("symmetric"), outs["mode"]
         for key in ("knn_idx", "knn_val", "edge_index", "edge_weights", "csr_rowptr", "csr_col", "csr_eid"):
             assert torch.equal(outb[key], refb[key]), f"rank {rank}: {key} differs at n = {nb}"
+            assert torch.equal(outs[key], refb[key]), f"rank {rank}: {key} differs at n = {nb} (symmetric tile pairs)"
         big = (nb, db, int(refb["edge_index"].shape[1]))
         dist.barrier()
     if rank == 0:
