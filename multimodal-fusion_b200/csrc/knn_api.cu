@@ -57,7 +57,7 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
     w.off_ovf = take(16);                       // overflow flag, largest squared norm, uncertified-row counter
-    w.off_unc_rows = take(size_t(w.plan.n_rows) * 4);
+    w.off_unc_rows = take(size_t(w.plan.n_rows) * 8);        // uncertified rows | rows of the multi-round re-rank
     w.off_unc_part = take(rerank_unc_part_bytes(w.plan.n_rows, k));
     if (w.sym_stride > 0) {
         w.off_thr = take(size_t(w.n_pad) * 4);
@@ -224,6 +224,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rp.unc_cnt = ovf + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.more_cnt = ovf + 3; rp.more_rows = rp.unc_rows + w.plan.n_rows;
     rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
     rp.exclude_self = exclude_self;
     rc = rerank_launch(rp, st);
@@ -314,7 +315,7 @@ static int staged_plan(const hg_knn_staged* s, StagedWs* w) {
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
     w->off_flags = take(16);                     // (unused flag, largest squared norm, uncertified-row counter)
-    w->off_unc_rows = take(size_t(w->n_rows) * 4);
+    w->off_unc_rows = take(size_t(w->n_rows) * 8);
     w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
     w->bytes = off;
     return HG_OK;
@@ -438,6 +439,7 @@ extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_a
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.more_cnt = rp.unc_cnt + 1; rp.more_rows = rp.unc_rows + w.n_rows;
     rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
     rp.exclude_self = s->exclude_self;
     return rerank_launch(rp, static_cast<cudaStream_t>(stream));
@@ -529,7 +531,7 @@ static GroupLayout group_layout(const KnnGroupSlide* slides, int num, int64_t d,
     g.o_pval = take(size_t(part) * 4);
     g.o_pidx = take(size_t(part) * 4);
     g.o_flags = take(16);
-    g.o_unc_rows = take(size_t(g.n_pad) * 4);
+    g.o_unc_rows = take(size_t(g.n_pad) * 8);
     g.o_unc_part = take(rerank_unc_part_bytes(g.n_pad, k));
     g.o_units = take(size_t(units) * sizeof(TcUnit));
     g.o_slides = take(size_t(num) * sizeof(RrSlide));
@@ -681,6 +683,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     rp.out_idx = slides[0].out_idx; rp.out_val = slides[0].out_val;
     rp.unc_cnt = flags + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + g.o_unc_rows);
+    rp.more_cnt = flags + 3; rp.more_rows = rp.unc_rows + g.n_pad;
     rp.unc_part = reinterpret_cast<uint2*>(ws + g.o_unc_part);
     rp.exclude_self = exclude_self;
     rp.g_slides = d_slides; rp.g_blk2slide = d_map;
@@ -745,7 +748,7 @@ static int sympart_plan(const hg_knn_staged* s, SymPartWs* w) {
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
     w->off_flags = take(16);
-    w->off_unc_rows = take(size_t(w->n_rows) * 4);
+    w->off_unc_rows = take(size_t(w->n_rows) * 8);
     w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
     w->bytes = off;
     return HG_OK;
@@ -873,6 +876,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_
     rp.ovf = any_overflow; rp.bkt_row0 = s->row_begin;
     rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
+    rp.more_cnt = rp.unc_cnt + 1; rp.more_rows = rp.unc_rows + w.n_rows;
     rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
     rp.exclude_self = s->exclude_self;
     return rerank_launch(rp, st);

@@ -144,6 +144,9 @@ struct RerankParams {
     // unc_rows (counter *unc_cnt, zeroed by the caller) and recomputed exactly against all n columns;
     // unc_part = [n_rows][RR_UNC_SLICES][k] scratch.  All three null: no certification.
     int32_t* unc_rows; int32_t* unc_cnt; uint2* unc_part;
+    // rows with more than 32 candidates inside the slack: worklist of the multi-round re-rank kernel (counter zeroed
+    // by the caller, list of n_rows entries)
+    int32_t* more_rows; int32_t* more_cnt;
     int exclude_self;            // the fallback skips column == row (the lists already did)
     // grouped launch: n_rows = the group's operand rows, sq_norms / part_* = the group's arrays, everything else
     // per slide from g_slides[g_blk2slide[row / 256]]

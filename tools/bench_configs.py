@@ -144,25 +144,27 @@ def main():
             # near-equal blocks with gather-then-compute, 256-aligned blocks with the overlapped exchange.
             # The modes alternate round by round on the same box (clocks drift under the power cap).
             modes = {}
-            for mode, ranges in (("gather_then_compute", multigpu.row_range), ("overlapped", multigpu.row_range_aligned)):
+            for mode, ranges, kwm in (("classic_row_blocks", multigpu.row_range, dict(aligned=False, symmetric=False)),
+                                      ("symmetric_tile_pairs", multigpu.row_range_aligned, dict(aligned=True, symmetric=True)),
+                                      ("overlapped_staged", multigpu.row_range_aligned, dict(aligned=True, overlap=True, symmetric=False))):
                 r0, r1 = ranges(n, rank, world)
-                modes[mode] = dict(rows=r1 - r0, aligned=mode == "overlapped", ms=[], kms=[], out=None,
+                modes[mode] = dict(rows=r1 - r0, kw=kwm, ms=[], kms=[], out=None,
                                    feats=torch.from_numpy(synth.make_features(r1 - r0, d, 1239 + rank, "gaussian")).to(dev))
             for rnd in range(int(os.environ.get("HG_BENCH_C5_ROUNDS", 3))):
                 for mode, m in modes.items():
                     def fn():
                         m["out"] = multigpu.knn_hyperedges_row_partitioned(
-                            m["feats"], n, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True, aligned=m["aligned"],
-                            overlap=m["aligned"])
+                            m["feats"], n, k=k, kernel="gaussian", lambda_h=1.0, return_csr=True, **m["kw"])
                     ms, kms = timed(fn, 3, warmup=2 if rnd == 0 else 1)
                     m["ms"].append(ms)
                     m["kms"].append(kms)
             for mode, m in modes.items():
                 ms, kms = float(np.median(m["ms"])), float(np.median(m["kms"]))
-                emit(config="c5", mode=mode, overlapped=bool(m["out"]["overlapped"]), n=n, d=d, k=k, gpus=world,
+                emit(config="c5", mode=mode, ran_as=m["out"]["mode"], n=n, d=d, k=k, gpus=world,
                      rows_rank0=m["rows"], ms_per_slide=ms, ms_rounds=m["ms"], patches_per_s=n / ms * 1e3,
-                     tc_kernel_ms_sum=kms,
-                     note="tc_kernel_ms_sum adds up the launches' own durations; overlapped sweeps run side by side")
+                     tc_kernel_ms_sum=kms, tc_tflops_algorithmic_per_gpu=2.0 * m["rows"] * n * d / (kms * 1e-3) / 1e12,
+                     edges=int(m["out"]["edge_index"].shape[1]),
+                     note="tc_kernel_ms_sum adds up the fused kernel's launches on rank 0 (pre-pass + sweep + guarded pass)")
     if world > 1:
         dist.destroy_process_group()
 
