@@ -284,46 +284,16 @@ int hg_build_knn_hypergraph_enqueue(const float* feats, int64_t n, int64_t d, co
                                     int64_t* num_edges_out_device,
                                     void* workspace, size_t workspace_bytes, void* stream);
 
-/* ---- row-partitioned slides: kNN in stages --------------------------------
- * This GPU owns the query rows [row_begin, row_end) of a slide whose other rows live on peer GPUs.
- * Instead of gathering all n rows first and then calling hg_knn_feature, the candidate columns are
- * handed over PANEL BY PANEL while the remaining ones are still in flight over NVLink: every panel is
- * split and swept by the fused kernel as soon as it is here; the per-row candidate lists are carried
- * from one panel launch to the next, finish merges them and re-ranks exactly (FP32) like the one-shot
- * call.  A list holds the best candidates of the columns seen so far whatever their order, so the
- * result equals hg_knn_feature(row_begin, row_end) (tests/test_gpu_staged.py: bit for bit; arrival
- * order could only choose between columns whose approximate scores tie exactly at the tail of a list).
- *   begin   once per slide
- *   load    operand preparation of the columns [col_begin, col_end) = the rows
- *           panel_feats[0 .. col_end - col_begin) of the slide (split into BF16 hi/lo, norms);
- *           col_begin is a multiple of 256 and col_end too unless it is n
- *   sweep   the fused kernel over those columns for the query rows, on list-slot set `lane`
- *           (0 <= lane < num_lanes); every column is swept once.  Needs the loads of these columns
- *           AND of the panel(s) holding the query rows to be complete.  Sweeps on the same lane must be
- *           ordered (same stream); sweeps on different lanes may run concurrently on different
- *           streams, which lets the next panel fill the SMs the previous sweep's tail leaves idle.
- *   finish  after all sweeps; feats_all = all n rows in this GPU's memory (the re-rank gathers
- *           candidate rows from it)
- * Every call is stream-ordered on its `stream`; the caller orders the arrival of a panel's rows
- * before its load (an event of the copy stream) and the cross-stream dependencies named above.
- * The descriptor is plain data, the same for all calls. */
-typedef struct hg_knn_staged {
+/* ---- descriptor of the feature kNN of a ROW BLOCK of a slide (plain data, the same for all calls of a slide) ---- */
+typedef struct hg_knn_part {
     int64_t n, d;                 /* rows of the whole slide, feature width */
     int64_t row_begin, row_end;   /* query rows of this GPU */
-    int64_t max_panel_cols;       /* widest panel that will be added */
+    int64_t reserved0;
     const float* pos;             /* [n, pos_dim] positions of all rows (Gaussian metric with lambda_g) or NULL */
     int32_t pos_dim, metric, k, exclude_self;
-    int32_t num_lanes, reserved;  /* list-slot sets (1..4; 0 = 1) */
+    int32_t reserved1, reserved2;
     float lambda_h, lambda_g;
-} hg_knn_staged;
-int hg_knn_staged_workspace_bytes(const hg_knn_staged* s, size_t* bytes);
-int hg_knn_staged_begin(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_staged_load(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
-                       void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_staged_sweep(const hg_knn_staged* s, int64_t col_begin, int64_t col_end, int lane,
-                        void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_all, int32_t* out_idx, float* out_val,
-                         float* out_cos, void* workspace, size_t workspace_bytes, void* stream);
+} hg_knn_part;
 
 /* ---- row-partitioned slides in SYMMETRIC mode ---------------------------------------------
  * hg_knn_feature on a row block computes every tile of its rows (classic pass).  Here the GPUs share the
@@ -340,7 +310,7 @@ int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_all, int32_t
  *   caller   all-reduce(max) of own_flags[0] over the GPUs: the barrier behind which all pushes have landed
  *   finish   classic pass if any bucket overflowed (any_overflow[0] != 0, then on every GPU alike), merge, exact
  *            re-rank -> out_idx / out_val / out_cos [row_end - row_begin, k], equal to hg_knn_feature_cos's.
- * The descriptor is hg_knn_staged (max_panel_cols / num_lanes unused).  Replaces the reference's sklearn kNN call,
+ * Replaces the reference's sklearn kNN call,
  * preprocess_hypergraph.py:379-382, for slides too large for one GPU's time budget. */
 /* peer access from the current device to `peer_device` (kernels of hg_knn_sympart_sweep store into mapped peer memory) */
 int hg_enable_peer_access(int peer_device);
@@ -353,13 +323,13 @@ int hg_ipc_open(const void* handle64, void** base_out);
 int hg_peer_alloc(size_t bytes, void** ptr_out, void* handle64_out);
 int hg_peer_free(void* ptr);
 int hg_ipc_close(void* base);
-int hg_knn_sympart_workspace_bytes(const hg_knn_staged* s, size_t* bytes);
-int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
+int hg_knn_sympart_workspace_bytes(const hg_knn_part* s, size_t* bytes);
+int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
                            int* own_flags, void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_sympart_sweep(const hg_knn_staged* s, const float* thr_all, int64_t chunk, int num_peers,
+int hg_knn_sympart_sweep(const hg_knn_part* s, const float* thr_all, int64_t chunk, int num_peers,
                          void* const* peer_bkt_cnt, void* const* peer_bkt, int* own_flags,
                          void* workspace, size_t workspace_bytes, void* stream);
-int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_all, const int* any_overflow,
+int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_all, const int* any_overflow,
                           const int32_t* own_bkt_cnt, const void* own_bkt,
                           int32_t* out_idx, float* out_val, float* out_cos,
                           void* workspace, size_t workspace_bytes, void* stream);

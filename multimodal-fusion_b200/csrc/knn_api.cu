@@ -249,201 +249,27 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     return rc;
 }
 
-// ---- staged kNN: the candidate columns arrive panel by panel -----------------------------------------
-// Row-partitioned slides: this GPU owns query rows [row_begin, row_end) and the
-// candidate rows of the other GPUs arrive over NVLink while the panels already here are being swept.
-// Every panel is loaded (FP32 -> BF16 hi/lo at its global operand rows) and swept by the fused kernel
-// as soon as it lands; the per-(row, split) candidate lists are carried from one sweep to the next
-// on the same lane (a unit starts from the list its slot already holds), so a row keeps as few lists
-// and pays as few list insertions as in the one-shot call.  Sweeps on different lanes own different
-// slots and may run on different streams: the next panel's CTAs then fill the SMs the previous
-// sweep's tail leaves idle.  finish merges the slots and re-ranks exactly as the
-// one-shot call does.  A list is the kl best of the columns that passed through its slot whatever
-// their order, so the result equals hg_knn_feature's (arrival order can only pick another one of
-// several columns whose approximate scores tie exactly at rank kl of a list).
+// ---- descriptor checks shared by the row-block entry points (symmetric pass over partitioned rows, below) --------
 namespace hg {
 
-struct StagedWs {
-    size_t off_ops, off_norms, off_colp, off_pos4, off_pval, off_pidx, off_flags, off_unc_rows, off_unc_part, bytes;
-    int spp;                     // list slots (column splits) per sweep
-    int lanes;                   // independent slot sets: sweeps on different lanes may run concurrently
-    int kl;
-    int64_t n_pad, d_pad, n_rows;
-};
-
-static int staged_check(const hg_knn_staged* s) {
-    HG_REQUIRE(s, HG_ERR_BAD_ARG, "hg_knn_staged: null descriptor");
+static int part_check(const hg_knn_part* s) {
+    HG_REQUIRE(s, HG_ERR_BAD_ARG, "hg_knn_part: null descriptor");
     int rc = check_knn_args(s->n, s->d, s->k, s->row_begin, s->row_end);
     if (rc != HG_OK) return rc;
-    HG_REQUIRE(s->k <= 32, HG_ERR_UNSUPPORTED, "hg_knn_staged: the tensor-core path supports k <= 32 (got %d)", s->k);
-    HG_REQUIRE(s->max_panel_cols >= 1 && s->max_panel_cols <= s->n, HG_ERR_BAD_ARG, "hg_knn_staged: bad max_panel_cols");
+    HG_REQUIRE(s->k <= 32, HG_ERR_UNSUPPORTED, "hg_knn_part: the tensor-core path supports k <= 32 (got %d)", s->k);
     HG_REQUIRE(s->metric == HG_METRIC_EUCLIDEAN || s->metric == HG_METRIC_GAUSSIAN || s->metric == HG_METRIC_COSINE,
-               HG_ERR_BAD_ARG, "hg_knn_staged: unknown metric %d", s->metric);
-    HG_REQUIRE(s->pos == nullptr || (s->pos_dim >= 1 && s->pos_dim <= 3), HG_ERR_UNSUPPORTED, "hg_knn_staged: pos_dim must be 1..3");
-    HG_REQUIRE(s->num_lanes >= 0 && s->num_lanes <= 4, HG_ERR_BAD_ARG, "hg_knn_staged: 1..4 lanes");
+               HG_ERR_BAD_ARG, "hg_knn_part: unknown metric %d", s->metric);
+    HG_REQUIRE(s->pos == nullptr || (s->pos_dim >= 1 && s->pos_dim <= 3), HG_ERR_UNSUPPORTED, "hg_knn_part: pos_dim must be 1..3");
     HG_REQUIRE(s->metric != HG_METRIC_GAUSSIAN || s->lambda_h > 0.f || s->pos == nullptr, HG_ERR_UNSUPPORTED,
-               "hg_knn_staged: lambda_h must be > 0 when positions are given");
+               "hg_knn_part: lambda_h must be > 0 when positions are given");
     return HG_OK;
 }
 
-static bool staged_has_pos(const hg_knn_staged* s) {
+static bool part_has_pos(const hg_knn_part* s) {
     return s->pos != nullptr && s->metric == HG_METRIC_GAUSSIAN && s->lambda_g != 0.f;
 }
 
-static int staged_plan(const hg_knn_staged* s, StagedWs* w) {
-    w->n_pad = ops_rows(s->n);
-    w->d_pad = ops_cols(s->d);
-    w->n_rows = s->row_end - s->row_begin;
-    const TcPlan probe = tc_make_plan_panel(s->max_panel_cols, w->n_rows, s->k, w->d_pad, 1);
-    w->kl = probe.kl;
-    w->lanes = s->num_lanes < 1 ? 1 : s->num_lanes;
-    w->spp = tc_panel_splits(s->max_panel_cols, w->n_rows, s->k, w->d_pad, TC_MAX_SPLITS);
-    if (const char* e = getenv("HG_B200_STAGED_SPP")) {          // tuning override: list slots per sweep
-        const int v = atoi(e);
-        if (v >= 1 && v <= TC_MAX_SPLITS) w->spp = v;
-    }
-    // the re-rank merges at most 768 list candidates per row
-    while (w->spp > 1 && w->lanes * w->spp * w->kl > 768) --w->spp;
-    HG_REQUIRE(w->lanes * w->spp * w->kl <= 768, HG_ERR_UNSUPPORTED, "hg_knn_staged: too many lanes (%d)", w->lanes);
-    size_t off = 0;
-    auto take = [&](size_t b) { size_t o = off; off += (b + 1023) & ~size_t(1023); return o; };
-    w->off_ops = take(hg_operand_bytes(s->n, s->d));
-    w->off_norms = take(size_t(w->n_pad) * 4);
-    w->off_colp = take(size_t(w->n_pad) * 8);
-    w->off_pos4 = take(staged_has_pos(s) ? size_t(w->n_pad) * 16 : 0);
-    const size_t part = size_t(w->lanes) * w->spp * size_t(w->n_rows) * size_t(w->kl);
-    w->off_pval = take(part * 4);
-    w->off_pidx = take(part * 4);
-    w->off_flags = take(16);                     // (unused flag, largest squared norm, uncertified-row counter)
-    w->off_unc_rows = take(size_t(w->n_rows) * 8);
-    w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
-    w->bytes = off;
-    return HG_OK;
-}
-
-static int staged_ws(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, StagedWs* w) {
-    int rc = staged_check(s);
-    if (rc != HG_OK) return rc;
-    rc = staged_plan(s, w);
-    if (rc != HG_OK) return rc;
-    HG_REQUIRE(workspace && workspace_bytes >= w->bytes, HG_ERR_WORKSPACE, "hg_knn_staged: workspace too small (%zu < %zu)",
-               workspace_bytes, w->bytes);
-    HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG,
-               "hg_knn_staged: workspace must be 1024-byte aligned");
-    return HG_OK;
-}
-
 }  // namespace hg
-
-extern "C" int hg_knn_staged_workspace_bytes(const hg_knn_staged* s, size_t* bytes) {
-    HG_REQUIRE(bytes, HG_ERR_BAD_ARG, "hg_knn_staged_workspace_bytes: null");
-    int rc = staged_check(s);
-    if (rc != HG_OK) return rc;
-    StagedWs w{};
-    rc = staged_plan(s, &w);
-    if (rc != HG_OK) return rc;
-    *bytes = w.bytes;
-    return HG_OK;
-}
-
-extern "C" int hg_knn_staged_begin(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, void* stream) {
-    StagedWs w{};
-    int rc = staged_ws(s, workspace, workspace_bytes, &w);
-    if (rc != HG_OK) return rc;
-    char* ws = static_cast<char*>(workspace);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 16, st));
-    // every list slot starts empty (index -1); the panel launches carry them forward
-    const size_t part = size_t(w.lanes) * w.spp * size_t(w.n_rows) * size_t(w.kl);
-    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_pidx, 0xff, part * 4, st));
-    return HG_OK;
-}
-
-static int staged_cols_ok(const hg_knn_staged* s, int64_t col_begin, int64_t col_end) {
-    HG_REQUIRE(col_begin >= 0 && col_begin < col_end && col_end <= s->n && col_end - col_begin <= s->max_panel_cols,
-               HG_ERR_BAD_ARG, "hg_knn_staged: bad column range [%lld, %lld)", (long long)col_begin, (long long)col_end);
-    HG_REQUIRE(col_begin % TC_BN == 0 && (col_end % TC_BN == 0 || col_end == s->n), HG_ERR_BAD_ARG,
-               "hg_knn_staged: panels start and end on multiples of %d columns (the last one ends at n)", TC_BN);
-    return HG_OK;
-}
-
-extern "C" int hg_knn_staged_load(const hg_knn_staged* s, const float* panel_feats, int64_t col_begin, int64_t col_end,
-                                  void* workspace, size_t workspace_bytes, void* stream) {
-    StagedWs w{};
-    int rc = staged_ws(s, workspace, workspace_bytes, &w);
-    if (rc != HG_OK) return rc;
-    HG_REQUIRE(panel_feats, HG_ERR_BAD_ARG, "hg_knn_staged_load: null panel");
-    rc = staged_cols_ok(s, col_begin, col_end);
-    if (rc != HG_OK) return rc;
-    char* ws = static_cast<char*>(workspace);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool has_pos = staged_has_pos(s);
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
-    float* norms = reinterpret_cast<float*>(ws + w.off_norms);
-    float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
-    float4* pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
-    float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
-    const int64_t cols = col_end - col_begin;
-    rc = launch_split(panel_feats, cols, s->d, ops + col_begin * ops_row_elems(w.d_pad), norms + col_begin, st);
-    if (rc != HG_OK) return rc;
-    return launch_colparams(norms + col_begin, has_pos ? s->pos + col_begin * s->pos_dim : nullptr, s->pos_dim, cols,
-                            ops_rows(cols), s->metric, colp + col_begin, has_pos ? pos4 + col_begin : nullptr, st, nullptr,
-                            nullptr, norm_max);
-}
-
-extern "C" int hg_knn_staged_sweep(const hg_knn_staged* s, int64_t col_begin, int64_t col_end, int lane,
-                                   void* workspace, size_t workspace_bytes, void* stream) {
-    StagedWs w{};
-    int rc = staged_ws(s, workspace, workspace_bytes, &w);
-    if (rc != HG_OK) return rc;
-    rc = staged_cols_ok(s, col_begin, col_end);
-    if (rc != HG_OK) return rc;
-    HG_REQUIRE(lane >= 0 && lane < w.lanes, HG_ERR_BAD_ARG, "hg_knn_staged_sweep: lane %d of %d", lane, w.lanes);
-    char* ws = static_cast<char*>(workspace);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool has_pos = staged_has_pos(s);
-    TcParams tp{};
-    tp.n = s->n; tp.row_begin = s->row_begin; tp.row_end = s->row_end; tp.d_pad = int(w.d_pad);
-    tp.plan = tc_make_plan_panel(col_end - col_begin, w.n_rows, s->k, w.d_pad, w.spp);
-    tp.ct_base = int(col_begin / TC_BN);
-    tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
-    tp.pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
-    tp.gscale = (has_pos && s->lambda_h > 0.f) ? s->lambda_g / s->lambda_h : 0.f;
-    tp.exclude_self = s->exclude_self;
-    tp.carry = 1;
-    const size_t slot = size_t(lane) * w.spp * size_t(w.n_rows) * size_t(w.kl);
-    tp.part_val = reinterpret_cast<float*>(ws + w.off_pval) + slot;
-    tp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx) + slot;
-    prof_begin(st);
-    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, tp, st);
-    prof_end(st);
-    return rc;
-}
-
-extern "C" int hg_knn_staged_finish(const hg_knn_staged* s, const float* feats_all, int32_t* out_idx, float* out_val,
-                                    float* out_cos, void* workspace, size_t workspace_bytes, void* stream) {
-    StagedWs w{};
-    int rc = staged_ws(s, workspace, workspace_bytes, &w);
-    if (rc != HG_OK) return rc;
-    HG_REQUIRE(feats_all && out_idx && out_val, HG_ERR_BAD_ARG, "hg_knn_staged_finish: null buffer");
-    char* ws = static_cast<char*>(workspace);
-    const bool has_pos = staged_has_pos(s);
-    RerankParams rp{};
-    rp.feats = feats_all; rp.n = s->n; rp.d = s->d; rp.pos = has_pos ? s->pos : nullptr; rp.pos_dim = s->pos_dim;
-    rp.sq_norms = reinterpret_cast<float*>(ws + w.off_norms);
-    rp.norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
-    rp.metric = s->metric; rp.lambda_h = s->lambda_h; rp.lambda_g = has_pos ? s->lambda_g : 0.f;
-    rp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
-    rp.part_idx = reinterpret_cast<int32_t*>(ws + w.off_pidx);
-    rp.splits = w.lanes * w.spp; rp.kl = w.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
-    rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
-    rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
-    rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
-    rp.more_cnt = rp.unc_cnt + 1; rp.more_rows = rp.unc_rows + w.n_rows;
-    rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
-    rp.exclude_self = s->exclude_self;
-    return rerank_launch(rp, static_cast<cudaStream_t>(stream));
-}
 
 // ---- grouped feature kNN: many small slides, a handful of launches ------------------------------------------
 // A slide of 2-8k patches is 16-64 row blocks: launched on its own it leaves SMs idle (128 units on 148 SMs at
@@ -725,8 +551,8 @@ struct SymPartWs {
     int64_t n_pad, d_pad, n_rows;
 };
 
-static int sympart_plan(const hg_knn_staged* s, SymPartWs* w) {
-    int rc = staged_check(s);
+static int sympart_plan(const hg_knn_part* s, SymPartWs* w) {
+    int rc = part_check(s);
     if (rc != HG_OK) return rc;
     HG_REQUIRE(s->row_begin % 256 == 0, HG_ERR_BAD_ARG, "hg_knn_sympart: row_begin must be a multiple of 256");
     w->n_pad = ops_rows(s->n);
@@ -743,7 +569,7 @@ static int sympart_plan(const hg_knn_staged* s, SymPartWs* w) {
     w->off_ops = take(hg_operand_bytes(s->n, s->d));
     w->off_norms = take(size_t(w->n_pad) * 4);
     w->off_colp = take(size_t(w->n_pad) * 8);
-    w->off_pos4 = take(staged_has_pos(s) ? size_t(w->n_pad) * 16 : 0);
+    w->off_pos4 = take(part_has_pos(s) ? size_t(w->n_pad) * 16 : 0);
     const size_t part = size_t(max_splits) * size_t(w->n_rows) * size_t(w->plan.kl);
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
@@ -754,7 +580,7 @@ static int sympart_plan(const hg_knn_staged* s, SymPartWs* w) {
     return HG_OK;
 }
 
-static int sympart_ws(const hg_knn_staged* s, void* workspace, size_t workspace_bytes, SymPartWs* w) {
+static int sympart_ws(const hg_knn_part* s, void* workspace, size_t workspace_bytes, SymPartWs* w) {
     int rc = sympart_plan(s, w);
     if (rc != HG_OK) return rc;
     HG_REQUIRE(workspace && workspace_bytes >= w->bytes, HG_ERR_WORKSPACE, "hg_knn_sympart: workspace too small (%zu < %zu)",
@@ -763,8 +589,8 @@ static int sympart_ws(const hg_knn_staged* s, void* workspace, size_t workspace_
     return HG_OK;
 }
 
-static TcParams sympart_params(const hg_knn_staged* s, const SymPartWs& w, char* ws) {
-    const bool has_pos = staged_has_pos(s);
+static TcParams sympart_params(const hg_knn_part* s, const SymPartWs& w, char* ws) {
+    const bool has_pos = part_has_pos(s);
     TcParams tp{};
     tp.n = s->n; tp.row_begin = s->row_begin; tp.row_end = s->row_end; tp.d_pad = int(w.d_pad);
     tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
@@ -777,7 +603,7 @@ static TcParams sympart_params(const hg_knn_staged* s, const SymPartWs& w, char*
 }
 }  // namespace hg
 
-extern "C" int hg_knn_sympart_workspace_bytes(const hg_knn_staged* s, size_t* bytes) {
+extern "C" int hg_knn_sympart_workspace_bytes(const hg_knn_part* s, size_t* bytes) {
     HG_REQUIRE(bytes, HG_ERR_BAD_ARG, "hg_knn_sympart_workspace_bytes: null");
     SymPartWs w{};
     int rc = sympart_plan(s, &w);
@@ -786,7 +612,7 @@ extern "C" int hg_knn_sympart_workspace_bytes(const hg_knn_staged* s, size_t* by
     return HG_OK;
 }
 
-extern "C" int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
+extern "C" int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_all, float* thr_all, int32_t* own_bkt_cnt,
                                       int* own_flags, void* workspace, size_t workspace_bytes, void* stream) {
     SymPartWs w{};
     int rc = sympart_ws(s, workspace, workspace_bytes, &w);
@@ -794,7 +620,7 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats
     HG_REQUIRE(feats_all && thr_all && own_bkt_cnt && own_flags, HG_ERR_BAD_ARG, "hg_knn_sympart_prepass: null buffer");
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool has_pos = staged_has_pos(s);
+    const bool has_pos = part_has_pos(s);
     __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
     float* norms = reinterpret_cast<float*>(ws + w.off_norms);
     float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
@@ -817,7 +643,7 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_staged* s, const float* feats
     return rc;
 }
 
-extern "C" int hg_knn_sympart_sweep(const hg_knn_staged* s, const float* thr_all, int64_t chunk, int num_peers,
+extern "C" int hg_knn_sympart_sweep(const hg_knn_part* s, const float* thr_all, int64_t chunk, int num_peers,
                                     void* const* peer_bkt_cnt, void* const* peer_bkt, int* own_flags,
                                     void* workspace, size_t workspace_bytes, void* stream) {
     SymPartWs w{};
@@ -844,7 +670,7 @@ extern "C" int hg_knn_sympart_sweep(const hg_knn_staged* s, const float* thr_all
     return rc;
 }
 
-extern "C" int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_all, const int* any_overflow,
+extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_all, const int* any_overflow,
                                      const int32_t* own_bkt_cnt, const void* own_bkt,
                                      int32_t* out_idx, float* out_val, float* out_cos,
                                      void* workspace, size_t workspace_bytes, void* stream) {
@@ -855,7 +681,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_staged* s, const float* feats_
                "hg_knn_sympart_finish: null buffer");
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool has_pos = staged_has_pos(s);
+    const bool has_pos = part_has_pos(s);
     // the classic pass over the own rows, which exits at once unless a bucket overflowed somewhere
     TcParams tp = sympart_params(s, w, ws);
     tp.plan = w.plan;

@@ -128,8 +128,8 @@ __device__ __forceinline__ UnitInfo unit_info(const TcParams& p, int u, uint32_t
     ui.rb = rb;
     ui.row0 = p.row_begin + int64_t(rb) * (TC_BM * CL) + int64_t(crank) * TC_BM;
     ui.row_end = p.row_end;
-    ui.ct0 = p.ct_base + split * p.plan.ct_per_split;                            // ct_base: column-panel launches
-    ui.ct1 = min(ui.ct0 + p.plan.ct_per_split, p.ct_base + p.plan.num_ct);
+    ui.ct0 = split * p.plan.ct_per_split;
+    ui.ct1 = min(ui.ct0 + p.plan.ct_per_split, p.plan.num_ct);
     ui.col_off = 0;
     ui.list_off = int64_t(split) * p.plan.n_rows * kl; ui.list_row0 = p.row_begin;
     return ui;
@@ -345,15 +345,6 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             int li[KLA];
 #pragma unroll
             for (int q = 0; q < KLA; ++q) { lv[q] = INFINITY; li[q] = -1; }
-            if (KL > 0 && p.carry && row < ui.row_end) {
-                // column-panel launches: go on from the list the previous panels left in this slot
-                const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
-#pragma unroll
-                for (int q = 0; q < KLA; ++q) {
-                    li[q] = p.part_idx[o + q];
-                    lv[q] = li[q] >= 0 ? p.part_val[o + q] : INFINITY;
-                }
-            }
             // this row's own score parameters; padded rows: (+inf, 0)
             const float2 me = (row < p.n_pad) ? __ldg(p.colp + row) : make_float2(INFINITY, 0.f);
             const float row_norm = me.x, ta = me.x, tb = me.y;
@@ -588,49 +579,6 @@ TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists)
     return pl;
 }
 
-// Column-panel plans (staged kNN): the split count is fixed by the caller (every panel owns the same
-// number of list slots); cc = the widest power of two dividing it that keeps the A blocks in the L2.
-static int panel_cc(int splits, int cl, int64_t d_pad) {
-    const int workers = kNumSMs / cl, cc_max = 4 / cl;
-    const int64_t a_block = int64_t(TC_BM * cl) * d_pad * 4;
-    const int64_t rc_cap = (int64_t(40) << 20) / a_block;
-    int cc = 1;
-    while (cc < cc_max && workers / cc > rc_cap && splits % (cc * 2) == 0) cc *= 2;
-    return cc;
-}
-
-TcPlan tc_make_plan_panel(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int splits) {
-    TcPlan pl{};
-    pl.cg = tc_cta_group();
-    pl.mc = tc_multicast();
-    pl.cl = (pl.cg == 2 || pl.mc) ? 2 : 1;
-    pl.n_rows = n_rows;
-    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cl));
-    pl.num_u = pl.num_rb;
-    pl.num_ct = int(ceil_div(panel_cols, TC_BN));
-    pl.kl = list_len(k);
-    const int workers = kNumSMs / pl.cl;
-    pl.splits = splits;
-    pl.cc = panel_cc(splits, pl.cl, d_pad);
-    pl.rc = workers / pl.cc;
-    pl.grid = int(min64(workers, int64_t(pl.num_rb) * pl.splits)) * pl.cl;
-    pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
-    return pl;
-}
-
-// List slots per sweep in [1, max_splits].  A slide swept in P launches pays the ragged end of a launch
-// P times (the CTAs run out of units at different moments, about half a unit of idle SMs per launch),
-// so panels want SHORT units: the largest power of two that still leaves >= 8 column tiles per unit
-// (measured at 8 panels of 31k columns, D = 1536: 8 slots +2 % over the one-shot call, 4 slots +8 %,
-// 2 slots +9 %; profiles/r01_staged_panels_slots.log).
-int tc_panel_splits(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int max_splits) {
-    const int tiles = int(ceil_div(panel_cols, TC_BN));
-    int s = 1;
-    while (s * 2 <= max_splits && s * 2 <= TC_MAX_SPLITS && tiles / (s * 2) >= 8) s *= 2;
-    (void)n_rows; (void)k; (void)d_pad;
-    return s;
-}
-
 // Threshold pre-pass: all rows against every stride-th column.  One unit per row block when the A
 // blocks of all 148 CTAs plus the column sample fit the L2 (the bound then comes straight out of the
 // kernel); otherwise 2 or 4 column splits run side by side on fewer row blocks and
@@ -813,8 +761,6 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
         if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
     }
     if (p.col_stride < 1) p.col_stride = 1;
-    HG_REQUIRE((p.ct_base == 0 && !p.carry) || (!p.plan.sym && p.col_stride == 1 && p.plan.kl > 0 && !p.thr_out), HG_ERR_BAD_ARG,
-               "tc_launch: column panels are for the classic list mode");
     HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.thr &&
                                ((p.peer_chunk == 0 && p.row_begin == 0 && p.row_end == p.n && p.bkt_cnt && p.bkt && p.ovf) ||
                                 (p.peer_chunk > 0 && p.ovf && p.row_begin % 256 == 0 && p.sblk_base == p.row_begin / 256))),
@@ -849,7 +795,7 @@ int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaSt
 // the rows of the whole group.
 int tc_launch_units(const __nv_bfloat16* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
                     const TcParams& p_in, cudaStream_t st) {
-    HG_REQUIRE(unit_tab != nullptr && num_units > 0 && !p_in.thr_out && !p_in.carry && p_in.col_stride <= 1, HG_ERR_BAD_ARG,
+    HG_REQUIRE(unit_tab != nullptr && num_units > 0 && !p_in.thr_out && p_in.col_stride <= 1, HG_ERR_BAD_ARG,
                "tc_launch_units: bad argument");
     TcParams p = p_in;
     p.plan = TcPlan{};
@@ -866,7 +812,7 @@ int tc_list_len(int k) { return list_len(k); }
 int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
                    const TcParams& p, cudaStream_t st) {
     HG_REQUIRE(ops_a != ops_b && !p.plan.sym && p.plan.cl == 1 && p.plan.kl > 0 && !p.exclude_self && !p.pos4 &&
-               !p.thr_out && !p.carry && p.ct_base == 0 && p.col_stride <= 1 && p.row_end <= n_pad_a,
+               !p.thr_out && p.col_stride <= 1 && p.row_end <= n_pad_a,
                HG_ERR_BAD_ARG, "tc_launch_rect: classic list mode without positions only");
     return tc_launch_impl(ops_a, n_pad_a, ops_b, n_pad_b, p, st);
 }

@@ -84,19 +84,10 @@ struct TcParams {
     const int* guard;           // non-null: the whole grid exits at once unless *guard != 0
     uint64_t hint_a, hint_b;    // L2 cache hints of the A / B tile loads (filled by tc_launch)
     int pair_stages;            // producer refills two 48 KB stages at a time (see tc_launch)
-    // column-panel launch (staged kNN, knn_api.cu): the plan describes the panel's own num_ct column
-    // tiles and splits; they sit ct_base tiles into the operand buffer.  carry: every unit starts from
-    // the list already stored in its (row, split) slot (index -1 = empty entry) instead of an empty one
-    int ct_base;
-    int carry;
     // grouped launch: non-null unit table (classic list mode, single CTAs); the plan then only carries kl
     const TcUnit* unit_tab;
     int num_tab_units;
 };
-
-// plan of one column panel of `panel_cols` columns swept by n_rows rows with `splits` lists per row
-TcPlan tc_make_plan_panel(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int splits);
-int tc_panel_splits(int64_t panel_cols, int64_t n_rows, int k, int64_t d_pad, int max_splits);
 
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists = true);   // lists = false: dense-output mode
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad);

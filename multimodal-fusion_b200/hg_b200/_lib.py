@@ -23,15 +23,15 @@ _i64, _i32, _f32, _vp, _sz = C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_size
 _psz = C.POINTER(C.c_size_t)
 _pi64 = C.POINTER(C.c_int64)
 
-class KnnStaged(C.Structure):
-    """struct hg_knn_staged of include/hg_b200.h"""
-    _fields_ = [("n", _i64), ("d", _i64), ("row_begin", _i64), ("row_end", _i64), ("max_panel_cols", _i64),
+class KnnPart(C.Structure):
+    """struct hg_knn_part of include/hg_b200.h"""
+    _fields_ = [("n", _i64), ("d", _i64), ("row_begin", _i64), ("row_end", _i64), ("reserved0", _i64),
                 ("pos", _vp), ("pos_dim", C.c_int32), ("metric", C.c_int32), ("k", C.c_int32),
-                ("exclude_self", C.c_int32), ("num_lanes", C.c_int32), ("reserved", C.c_int32),
+                ("exclude_self", C.c_int32), ("reserved1", C.c_int32), ("reserved2", C.c_int32),
                 ("lambda_h", _f32), ("lambda_g", _f32)]
 
 
-_pst = C.POINTER(KnnStaged)
+_pst = C.POINTER(KnnPart)
 
 # name -> (restype, argtypes); kept in one table so tests can check that every
 # symbol of include/hg_b200.h is exported
@@ -88,11 +88,6 @@ SIGNATURES = {
     "hg_build_batch_grouped_enqueue": (_i32, [_vp, _i32, _i64, _i32, _i32, _f32, _f32, _i32, _i32, _i64,
                                               _vp, _sz, _vp, _vp, _sz, _vp, _i32]),
     "hg_hypergraph_propagate": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
-    "hg_knn_staged_workspace_bytes": (_i32, [_pst, _psz]),
-    "hg_knn_staged_begin": (_i32, [_pst, _vp, _sz, _vp]),
-    "hg_knn_staged_load": (_i32, [_pst, _vp, _i64, _i64, _vp, _sz, _vp]),
-    "hg_knn_staged_sweep": (_i32, [_pst, _i64, _i64, _i32, _vp, _sz, _vp]),
-    "hg_knn_staged_finish": (_i32, [_pst, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hg_enable_peer_access": (_i32, [_i32]),
     "hg_ipc_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
     "hg_ipc_close": (_i32, [_vp]),

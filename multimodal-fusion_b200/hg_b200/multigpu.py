@@ -6,10 +6,12 @@
 * row-partitioned single slide: rank r owns rows [r*N/G, (r+1)*N/G); ONE all-gather of the
   feature row blocks (NCCL over NVLink), each rank runs the fused kernel on its row range
   against all N columns, ONE small all-gather of the [N/G, k] lists, assembly replicated.
-  With 256-aligned row blocks (`row_range_aligned`) the exchange is overlapped with the kernel:
-  every rank maps its peers' blocks (CUDA IPC), pulls them with the copy engines over NVLink on
-  a side stream, and the fused kernel sweeps each block as a column panel as soon as it is here
-  (`ops.StagedKnn`); the result is bit-identical to the gather-then-compute form.
+  With 256-aligned row blocks (`row_range_aligned`) the ranks run the SYMMETRIC pass instead
+  (hg_knn_sympart_*): they share the checkerboard of tile pairs and push the transposed survivors
+  into the owning rank's buckets over NVLink; the result is bit-identical to the single-GPU build.
+  (Round 1's "overlapped exchange" -- peers' blocks pulled by the copy engines while the fused
+  kernel swept the blocks already here, hg_knn_staged_* -- was never faster than gather-then-compute
+  on B200 (57.1 vs 56.2 ms at C5: the kernel is power-bound) and was removed in round 2.)
 
 One process per GPU (`torchrun`); `torch.distributed` is plumbing only.  The host-side logic
 is backend-agnostic so world_size-2 gloo tests cover it on CPU with the kNN stage injected.
@@ -43,12 +45,12 @@ def row_range(n: int, rank: int, world_size: int) -> Tuple[int, int]:
     return r0, r0 + base + (1 if rank < extra else 0)
 
 
-PANEL_ALIGN = 256     # column tile of the fused kernel: staged panels start on multiples of it
+PANEL_ALIGN = 256     # column tile of the fused kernel: aligned row blocks start on multiples of it
 
 
 def row_range_aligned(n: int, rank: int, world_size: int) -> Tuple[int, int]:
     """Row blocks whose boundaries are multiples of 256 (the last block takes what is left, trailing
-    ranks may own nothing): the partition the overlapped exchange needs."""
+    ranks may own nothing): the partition the symmetric pass needs."""
     chunk = -(-(-(-n // world_size)) // PANEL_ALIGN) * PANEL_ALIGN
     r0 = min(n, rank * chunk)
     return r0, min(n, r0 + chunk)
@@ -70,103 +72,6 @@ def all_gather_rows(local: torch.Tensor, n: int, group=None, ranges=row_range) -
     gathered = torch.empty((world * m,) + shape, dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(gathered, padded, group=group)
     return torch.cat([gathered[r * m: r * m + sizes[r]] for r in range(world)], 0)
-
-
-def _map_peer_blocks(local: torch.Tensor, group) -> Optional[list]:
-    """Every rank's block as a tensor usable from this process: the own block as is, the peers' blocks
-    mapped through CUDA IPC (torch's tensor sharing; the memory stays on the owning GPU).  None if any
-    rank could not export or map (all ranks agree on the outcome)."""
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
-    handle, ok = None, 1
-    try:
-        from torch.multiprocessing.reductions import reduce_tensor
-        handle = reduce_tensor(local)
-    except Exception:                      # noqa: BLE001 - allocator without IPC support, ...
-        ok = 0
-    handles = [None] * world
-    dist.all_gather_object(handles, handle, group=group)
-    blocks = []
-    if ok and all(h is not None for h in handles):
-        try:
-            for r, h in enumerate(handles):
-                blocks.append(local if r == rank else h[0](*h[1]))
-        except Exception:                  # noqa: BLE001
-            ok = 0
-    else:
-        ok = 0
-    flag = torch.tensor([ok], dtype=torch.int32, device=local.device)
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-    return blocks if int(flag.item()) == 1 else None
-
-
-class PeerExchange:
-    """A staging buffer [max_rows, d] float32 per rank, exported once over CUDA IPC and mapped by every
-    peer (collective constructor).  Per slide a rank writes its row block into its own buffer and the
-    peers pull it with their copy engines; nothing is pickled or synchronised with the host after
-    construction.  `blocks` is None when the mapping is not possible on this system."""
-
-    def __init__(self, max_rows: int, d: int, device, group=None):
-        self.buf = torch.empty((max_rows, d), dtype=torch.float32, device=device)
-        self.blocks = _map_peer_blocks(self.buf, group)
-        self.token = torch.zeros(1, dtype=torch.float32, device=device)
-        self.copy_stream = torch.cuda.Stream(device)
-
-
-_EXCHANGES = {}
-
-
-def peer_exchange(max_rows: int, d: int, device, group=None) -> PeerExchange:
-    """The cached exchange for this (group, shape): every rank reaches this with the same arguments, so
-    all of them create it (a collective) in the same call."""
-    key = (id(group) if group is not None else None, int(max_rows), int(d), torch.device(device).index)
-    if key not in _EXCHANGES:
-        _EXCHANGES[key] = PeerExchange(max_rows, d, device, group)
-    return _EXCHANGES[key]
-
-
-def _knn_overlapped(local_features: torch.Tensor, n: int, k: int, kernel: str, lambda_h: float, lambda_g: float,
-                    pos: Optional[torch.Tensor], group):
-    """Staged kNN over peer blocks pulled by the copy engines while earlier panels are swept.
-    Returns ((idx, val, cos), feats_all) or None when the peers' memory cannot be mapped.
-    The caller's next collective (the all-gather of the lists) is what tells a rank that all peers
-    are done reading its staging buffer before it is overwritten for the next slide."""
-    from . import ops
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
-    dev = local_features.device
-    ranges = [row_range_aligned(n, r, world) for r in range(world)]
-    widest = max(b - a for a, b in ranges)
-    r0, r1 = ranges[rank]
-    d = local_features.shape[1]
-    ex = peer_exchange(widest, d, dev, group)
-    if ex.blocks is None:
-        return None
-    main = torch.cuda.current_stream(dev)
-    if local_features.data_ptr() != ex.buf.data_ptr():
-        ex.buf[: r1 - r0].copy_(local_features, non_blocking=True)
-    dist.all_reduce(ex.token, group=group)                        # stream-ordered: every rank's block is in place
-    feats_all = torch.empty((n, d), dtype=torch.float32, device=dev)
-    order = [(rank + s) % world for s in range(world)]            # own block first, then ring order:
-    arrived = {}                                                  # at every step each GPU serves one reader
-    ex.copy_stream.wait_stream(main)
-    with torch.cuda.stream(ex.copy_stream):
-        for src in order:
-            a, b = ranges[src]
-            if b > a:
-                feats_all[a:b].copy_(ex.blocks[src][: b - a], non_blocking=True)   # peer -> local over NVLink (DMA)
-            ev = torch.cuda.Event()
-            ev.record(ex.copy_stream)
-            arrived[src] = ev
-    staged = ops.StagedKnn(n, d, k, kernel, (r0, r1), widest, positions=pos if lambda_g else None,
-                           lambda_h=lambda_h, lambda_g=lambda_g, device=dev)
-    for src in order:
-        a, b = ranges[src]
-        if b > a:
-            staged.add_panel(feats_all[a:b], a, b, ready=arrived[src])
-    local = staged.finish(feats_all, return_cos=True)
-    feats_all.record_stream(ex.copy_stream)
-    for st in staged.streams[1:]:
-        feats_all.record_stream(st)
-    return local, feats_all
 
 
 class _SymPartState:
@@ -255,9 +160,9 @@ def _knn_sympart(feats: torch.Tensor, n: int, k: int, kernel: str, lambda_h: flo
     d = feats.shape[1]
     use_pos = pos is not None and kernel == "gaussian" and lambda_g != 0.0
     p = L.f32c(pos, dev) if use_pos else None
-    desc = L.KnnStaged(n=n, d=d, row_begin=r0, row_end=r1, max_panel_cols=n, pos=L.ptr(p),
+    desc = L.KnnPart(n=n, d=d, row_begin=r0, row_end=r1, reserved0=0, pos=L.ptr(p),
                        pos_dim=0 if p is None else p.shape[1], metric=L.METRIC[kernel], k=k, exclude_self=1,
-                       num_lanes=1, reserved=0, lambda_h=float(lambda_h), lambda_g=float(lambda_g if use_pos else 0.0))
+                       reserved1=0, reserved2=0, lambda_h=float(lambda_h), lambda_g=float(lambda_g if use_pos else 0.0))
     n_pad = -(-n // 256) * 256
     with torch.cuda.device(dev):
         nbytes = C.c_size_t(0)
@@ -288,14 +193,14 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                                    lambda_h: float = 1.0, lambda_g: float = 0.0,
                                    positions: Optional[torch.Tensor] = None, spatial_k: int = 0,
                                    return_csr: bool = False, group=None, aligned: bool = False,
-                                   overlap: Optional[bool] = None, symmetric: Optional[bool] = None,
+                                   symmetric: Optional[bool] = None,
                                    knn_fn: Optional[Callable] = None, assemble_fn: Optional[Callable] = None,
                                    spatial_fn: Optional[Callable] = None) -> dict:
     """Config C5: `local_features` is this rank's row block [r1-r0, D] (`row_range`, or
     `row_range_aligned` with aligned=True); `positions` (replicated, [n, 2|3]) is small.  Returns
-    the same dict as `knn_hyperedges` on every rank.  overlap=True (aligned blocks on CUDA only):
-    the peers' feature blocks are pulled over NVLink while the fused kernel sweeps the blocks that are
-    already here (staged kNN, same result bit for bit); "overlapped" in the dict says whether it ran."""
+    the same dict as `knn_hyperedges` on every rank.  With aligned=True the feature kNN runs in symmetric mode
+    over the row blocks (see `_knn_sympart`; symmetric=False or HG_B200_SYMPART=0: classic pass); "mode" in the dict
+    says which pass ran."""
     from . import ops
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     ranges = row_range_aligned if aligned else row_range
@@ -303,23 +208,10 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
     assert local_features.shape[0] == r1 - r0, "local block does not match the row partition"
     pos = positions if (positions is not None) else None
     local = feats = None
-    overlapped = False
     all_have_rows = all(ranges(n, r, world)[1] > ranges(n, r, world)[0] for r in range(world))
-    if overlap is None:
-        # measured on 8 B200 at C5 the overlapped exchange is not faster (57.1 vs 56.2 ms: the fused kernel
-        # is power-bound, sweeping 8 panels costs 2-3 % more than one launch and the exchange it hides is
-        # ~1 ms), so gather-then-compute stays the default; HG_B200_OVERLAP=1 or overlap=True turns it on
-        overlap = os.environ.get("HG_B200_OVERLAP", "0") == "1"
-    if overlap:                            # decided from facts every rank sees alike (collectives inside)
-        overlap = aligned and knn_fn is None and local_features.is_cuda and all_have_rows and k <= 32
-    if overlap:
-        res = _knn_overlapped(local_features.contiguous(), n, k, kernel, lambda_h, lambda_g, pos, group)
-        if res is not None:
-            local, feats = res
-            overlapped = True
     # symmetric mode over aligned row blocks (default on CUDA; HG_B200_SYMPART=0 or symmetric=False: classic pass):
     # the ranks share the checkerboard of tile pairs instead of each computing every tile of its rows
-    mode = "overlapped staged panels" if overlapped else "classic row blocks"
+    mode = "classic row blocks"
     if symmetric is None:
         symmetric = os.environ.get("HG_B200_SYMPART", "1") != "0"
     stride = 16 if n >= 32768 else 8
@@ -346,7 +238,7 @@ def knn_hyperedges_row_partitioned(local_features: torch.Tensor, n: int, *, k: i
                 local += (torch.empty((0, k), dtype=torch.float32, device=feats.device),)
     idx_local, val_local = local[0], local[1]
     out = {"knn_idx": all_gather_rows(idx_local, n, group, ranges),
-           "knn_val": all_gather_rows(val_local, n, group, ranges), "overlapped": overlapped, "mode": mode}
+           "knn_val": all_gather_rows(val_local, n, group, ranges), "mode": mode}
     # cos(f_i, f_j) of every list entry travels with the lists: the edge weights are then looked up
     # instead of gathering two feature rows per edge
     knn_cos = all_gather_rows(local[2], n, group, ranges) if len(local) > 2 else None

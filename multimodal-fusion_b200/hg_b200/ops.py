@@ -51,76 +51,6 @@ def knn_feature(features: torch.Tensor, k: int, metric: str = "euclidean",
     return (out_idx, out_val, out_cos) if return_cos else (out_idx, out_val)
 
 
-class StagedKnn:
-    """Feature kNN of the rows [rows[0], rows[1]) of an n-row slide whose candidate columns are
-    handed over panel by panel (hg_knn_staged_*): the row-partitioned multi-GPU path feeds it the
-    peers' row blocks as they arrive.  Panel boundaries are multiples of 256 (the last ends at n);
-    the panel holding the query rows goes first.  Panels alternate between `lanes` list-slot sets,
-    each on its own stream (measured: no gain over one lane, which is the default; short work units
-    are what keeps the ragged end of every sweep small).  finish() returns what knn_feature(rows=...) does, on the stream that was current at
-    construction."""
-
-    def __init__(self, n: int, d: int, k: int, metric: str, rows: Tuple[int, int],
-                 max_panel_cols: int, positions: Optional[torch.Tensor] = None, lambda_h: float = 1.0,
-                 lambda_g: float = 0.0, exclude_self: bool = True, lanes: int = 1, device=None):
-        self.lib = L.load_library()
-        self.dev = L.require_cuda(device)
-        self.pos = L.f32c(positions, self.dev) if positions is not None else None
-        self.rows, self.k = rows, k
-        self.desc = L.KnnStaged(n=n, d=d, row_begin=rows[0], row_end=rows[1], max_panel_cols=max_panel_cols,
-                                pos=L.ptr(self.pos), pos_dim=0 if self.pos is None else self.pos.shape[1],
-                                metric=L.METRIC[metric], k=k, exclude_self=int(exclude_self), num_lanes=lanes,
-                                reserved=0, lambda_h=float(lambda_h), lambda_g=float(lambda_g))
-        self.main = torch.cuda.current_stream(self.dev)
-        with torch.cuda.device(self.dev):
-            self.nbytes = _size(self.lib.hg_knn_staged_workspace_bytes, C.byref(self.desc))
-            self.ws = L.Workspace.get(self.dev, self.nbytes, "staged")
-            L.check(self.lib.hg_knn_staged_begin(C.byref(self.desc), L.ptr(self.ws), self.nbytes, self.main.cuda_stream))
-            self.streams = [self.main] + [torch.cuda.Stream(self.dev) for _ in range(lanes - 1)]
-        for st in self.streams[1:]:
-            st.wait_stream(self.main)                  # the reset of the list slots, whatever produced the inputs
-        self.query_loaded = None
-        self.count = 0
-
-    def add_panel(self, panel_feats: torch.Tensor, col_begin: int, col_end: int,
-                  ready: Optional[torch.cuda.Event] = None) -> None:
-        """Load + sweep the columns [col_begin, col_end); `ready` = event after which the rows are there."""
-        first = self.count == 0
-        if first and not (col_begin <= self.rows[0] and self.rows[1] <= col_end):
-            raise ValueError("the first panel must contain the query rows")
-        x = panel_feats
-        if x.dtype != torch.float32 or not x.is_contiguous() or x.device != self.dev or x.shape[0] != col_end - col_begin:
-            raise ValueError("panel_feats must be a contiguous float32 [col_end - col_begin, d] tensor on the build device")
-        lane = self.count % len(self.streams)
-        st = self.streams[lane]
-        if ready is not None:
-            st.wait_event(ready)
-        with torch.cuda.device(self.dev):
-            L.check(self.lib.hg_knn_staged_load(C.byref(self.desc), L.ptr(x), col_begin, col_end,
-                                                L.ptr(self.ws), self.nbytes, st.cuda_stream))
-            if first:
-                self.query_loaded = torch.cuda.Event()
-                self.query_loaded.record(st)
-            elif st is not self.streams[0]:
-                st.wait_event(self.query_loaded)       # the sweep reads the query rows' operands
-            L.check(self.lib.hg_knn_staged_sweep(C.byref(self.desc), col_begin, col_end, lane,
-                                                 L.ptr(self.ws), self.nbytes, st.cuda_stream))
-        self.count += 1
-
-    def finish(self, feats_all: torch.Tensor, return_cos: bool = False):
-        r = max(self.rows[1] - self.rows[0], 0)
-        with torch.cuda.stream(self.main):
-            out_idx = torch.empty((r, self.k), dtype=torch.int32, device=self.dev)
-            out_val = torch.empty((r, self.k), dtype=torch.float32, device=self.dev)
-            out_cos = torch.empty_like(out_val) if return_cos else None
-        for st in self.streams[1:]:
-            self.main.wait_stream(st)
-        with torch.cuda.device(self.dev):
-            L.check(self.lib.hg_knn_staged_finish(C.byref(self.desc), L.ptr(feats_all), L.ptr(out_idx), L.ptr(out_val),
-                                                  L.ptr(out_cos), L.ptr(self.ws), self.nbytes, self.main.cuda_stream))
-        return (out_idx, out_val, out_cos) if return_cos else (out_idx, out_val)
-
-
 def knn_spatial(positions: torch.Tensor, k: int, rows: Optional[Tuple[int, int]] = None,
                 device=None) -> Tuple[torch.Tensor, torch.Tensor]:
     """A3: k smallest squared spatial distances, ties by (d2, index).  (idx int32, d2 float32)."""

@@ -126,7 +126,7 @@ def knn_hyperedges(features: torch.Tensor, positions: Optional[torch.Tensor] = N
     n = x.shape[0]
     pos = L.f32c(positions, dev) if positions is not None else None
     full = rows is None or (rows[0] == 0 and rows[1] == n)
-    if full and k <= 32 and not os.environ.get("HG_B200_STAGED"):
+    if full and k <= 32:
         # whole slide: one C call, one stream synchronisation
         return ops.build_knn_hypergraph(x, k, kernel, positions=pos, lambda_h=lambda_h,
                                         lambda_g=lambda_g if kernel == "gaussian" else 0.0, spatial_k=spatial_k,

@@ -36,24 +36,22 @@ def main():
     for key in ("knn_idx", "knn_val", "spatial_idx", "spatial_d2", "edge_index", "edge_weights", "csr_rowptr",
                 "csr_col", "csr_eid"):
         assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs"
-    # 256-aligned row blocks: peers' blocks pulled over NVLink while the fused kernel sweeps the ones that
-    # are here (staged kNN); same result bit for bit, with and without the overlap
+    # 256-aligned row blocks: classic pass, then the symmetric pass (tile pairs shared by the ranks, buckets over
+    # NVLink) twice in a row on the same exchange buffers; same result bit for bit
     a0, a1 = multigpu.row_range_aligned(n, rank, world)
     modes = []
-    for overlap, symmetric in ((True, False), (False, False), (False, True), (False, True)):
+    for symmetric in (False, True, True):
         out = multigpu.knn_hyperedges_row_partitioned(x[a0:a1].contiguous(), n, k=k, kernel="gaussian", lambda_h=1.0,
                                                       lambda_g=lam_g, positions=p, spatial_k=8, return_csr=True,
-                                                      aligned=True, overlap=overlap, symmetric=symmetric)
+                                                      aligned=True, symmetric=symmetric)
         for key in ("knn_idx", "knn_val", "spatial_idx", "spatial_d2", "edge_index", "edge_weights", "csr_rowptr",
                     "csr_col", "csr_eid"):
-            assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, overlap={overlap}, symmetric={symmetric})"
+            assert torch.equal(out[key], ref[key]), f"rank {rank}: {key} differs (aligned, symmetric={symmetric})"
         modes.append(out["mode"])
         torch.cuda.synchronize()
         if rank == 0 and os.environ.get("HG_NCCL_CHECK_VERBOSE"):
-            print(f"phase ok: overlap={overlap} symmetric={symmetric} mode={out['mode']}", flush=True)
-        if overlap:
-            overlapped = out["overlapped"]
-    assert modes[2].startswith("symmetric") and modes[3].startswith("symmetric"), (modes, _lib_err())     # twice: buffers reused
+            print(f"phase ok: symmetric={symmetric} mode={out['mode']}", flush=True)
+    assert modes[0].startswith("classic") and modes[1].startswith("symmetric") and modes[2].startswith("symmetric"), (modes, _lib_err())
     E_small = int(ref["edge_index"].shape[1])
     dist.barrier()
     # the same at C5's width and beyond C3's row count: n = 100,003 x 1536 (ragged blocks), every rank generates
@@ -77,7 +75,7 @@ def main():
         big = (nb, db, int(refb["edge_index"].shape[1]))
         dist.barrier()
     if rank == 0:
-        print(f"NCCL_ROWPART_OK world={world} n={n} E={E_small} overlapped={overlapped} big={big}")
+        print(f"NCCL_ROWPART_OK world={world} n={n} E={E_small} modes={modes} big={big}")
     dist.destroy_process_group()
 
 

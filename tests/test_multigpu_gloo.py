@@ -67,7 +67,7 @@ def _worker(rank, world, port, n, d, k, q, aligned=False):
 
         out = multigpu.knn_hyperedges_row_partitioned(torch.from_numpy(feats[r0:r1]), n, k=k, knn_fn=knn_fn,
                                                       assemble_fn=assemble_fn, aligned=aligned)
-        assert out["overlapped"] is False                      # no CUDA here: gather-then-compute
+        assert out["mode"] == "classic row blocks"             # no CUDA here: gather-then-compute
         q.put((rank, out["knn_idx"].numpy(), out["edge_index"].numpy()))
     finally:
         dist.destroy_process_group()

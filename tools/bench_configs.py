@@ -146,7 +146,7 @@ def main():
             modes = {}
             for mode, ranges, kwm in (("classic_row_blocks", multigpu.row_range, dict(aligned=False, symmetric=False)),
                                       ("symmetric_tile_pairs", multigpu.row_range_aligned, dict(aligned=True, symmetric=True)),
-                                      ("overlapped_staged", multigpu.row_range_aligned, dict(aligned=True, overlap=True, symmetric=False))):
+                                      ("classic_aligned_blocks", multigpu.row_range_aligned, dict(aligned=True, symmetric=False))):
                 r0, r1 = ranges(n, rank, world)
                 modes[mode] = dict(rows=r1 - r0, kw=kwm, ms=[], kms=[], out=None,
                                    feats=torch.from_numpy(synth.make_features(r1 - r0, d, 1239 + rank, "gaussian")).to(dev))
