@@ -201,7 +201,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         if (rc != HG_OK) return rc;
         if (w.pre_plan.splits > 1) {
             rc = thr_merge_launch(pre.part_val, w.pre_plan.splits, n, w.pre_plan.kl, k, colp, norm_max, cosine,
-                                  pre.hi_only ? TC_SLACK_HI : TC_SLACK_3X, thr, st);
+                                  pre.hi_only ? TC_SLACK_HI : tc_slack_3x(w.d_pad), thr, st);
             if (rc != HG_OK) return rc;
         }
         TcParams sp = tp;

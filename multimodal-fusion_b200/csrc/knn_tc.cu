@@ -494,7 +494,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     // most 2^-8 (n_i + n_j) above their coarse ones (|x - hi| <= 2^-9 |x| per element), so the
                     // bound stays valid with that much more slack.
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
-                    p.thr_out[row] = t + (p.hi_only ? TC_SLACK_HI : TC_SLACK_3X) * scale;
+                    p.thr_out[row] = t + (p.hi_only ? TC_SLACK_HI : tc_slack_3x(p.d_pad)) * scale + TC_SLACK_REL * fabsf(t);
                 } else {
                     const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
 #pragma unroll

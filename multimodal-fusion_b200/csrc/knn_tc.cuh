@@ -148,8 +148,25 @@ inline size_t rerank_unc_part_bytes(int64_t n_rows, int k) { return size_t(n_row
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
                      const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st);
-constexpr float TC_SLACK_3X = 4.8828125e-4f;      // 2^-11: both 3xBF16 scores of a comparison, see knn_tc.cu
+constexpr float TC_SLACK_3X = 4.8828125e-4f;      // 2^-11: the D-independent bound of round 1 (still used by kmeans.cu)
 constexpr float TC_SLACK_HI = 4.39453125e-3f;     // 2^-8 + 2^-11: a hi-only pre-pass score against a 3xBF16 one
+
+// Guaranteed slack of a COMPARISON of two 3xBF16 scores of one row, as a multiple of (|x_i|^2 + max_j |x_j|^2)
+// (Euclidean / Gaussian scores n_j - 2 dot) or of |x_i| (cosine scores -dot / |x_j|).  Error of one dot product,
+// relative to |x_i||x_j|:
+//   * representation: x = hi + lo + r with |lo| <= 2^-9 |x|, |r| <= 2^-18 |x| per element; the products left out are
+//     lo.lo + r.y + x.r, each <= 2^-18 by Cauchy-Schwarz                                         ->  3 * 2^-18 = 1.15e-5
+//   * accumulation: 3 D_pad / 16 tensor-core steps into one FP32 accumulator whose add truncates; at most 2^-22 of the
+//     running magnitude (<= |x_i||x_j|) per step.  (Measured in the dense mode, one accumulator, D = 1024: worst entry
+//     of 2.7e8 off by 7e-6, an eighth of this bound.)                                          ->  (3 D_pad / 16) * 2^-22
+// A score is n_j - 2 dot, so its error is 2 eps |x_i||x_j| <= eps (n_i + n_j), and two scores differ from their exact
+// difference by at most 2 eps (n_i + n_max): 1.1e-4 at D = 1024, 1.6e-4 at D = 1536 (round 1 used 4.9e-4 for every D,
+// which this bound exceeds from D ~ 5,000 up).  The FP32 rounding of the score arithmetic itself (fma, spatial term)
+// is relative to the score: TC_SLACK_REL * |score| on top.
+__host__ __device__ inline float tc_slack_3x(int64_t d_pad) {
+    return 2.f * (1.15e-5f + float(3 * (d_pad / 16)) * 2.3842e-7f);
+}
+constexpr float TC_SLACK_REL = 4.8e-7f;           // 2^-21
 
 // also resets the symmetric-mode state when given: thr = NaN, bucket counts = 0, and folds the
 // largest squared norm into *norm_max (zeroed by the caller)

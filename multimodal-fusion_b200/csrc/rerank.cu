@@ -216,7 +216,8 @@ rerank_kernel(const RerankParams p) {
     // guaranteed 3xBF16 error slack (both scores off by <= eps in opposite directions): such a
     // candidate cannot enter the exact top-k, and neither can any later one.
     const float ni = c.sq_norms[row];
-    const float slack = 4.8828125e-4f * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
+    const float slack_abs = tc_slack_3x(round_up(p.d, kColPad)) * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
+    float slack = slack_abs;                             // + TC_SLACK_REL |k-th best| once that is known
     // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
     // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still
     // belong to the exact top-k (many near-duplicates): the row goes to the exact fallback
@@ -271,7 +272,7 @@ rerank_kernel(const RerankParams p) {
                 if (pair_less(ov, oi, bv, bi)) { bv = ov; bi = oi; }
             }
             if (bi == 0x7fffffff) { last = true; break; }                  // no candidates left
-            if (taken + t == p.k - 1) kth = bv;
+            if (taken + t == p.k - 1) { kth = bv; slack = slack_abs + TC_SLACK_REL * fabsf(bv); }
             if (taken + t >= p.k && bv > kth + slack) { last = true; break; }
 #pragma unroll
             for (int q = 0; q < RR_MAX_CAND / 32; ++q) {
@@ -575,7 +576,7 @@ __global__ void thr_merge_kernel(const float* __restrict__ part_val, int splits,
     }
     const float2 me = colp[row];
     const float scale = cosine ? 1.f / fmaxf(fabsf(me.y), 1e-30f) : me.x + *norm_max;
-    thr[row] = t + slack * scale;
+    thr[row] = t + slack * scale + TC_SLACK_REL * fabsf(t);
 }
 
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
