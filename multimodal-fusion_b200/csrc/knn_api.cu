@@ -57,7 +57,7 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
     w.off_ovf = take(16);                       // overflow flag, largest squared norm, uncertified-row counter
-    w.off_unc_rows = take(size_t(w.plan.n_rows) * 8);        // uncertified rows | rows of the multi-round re-rank
+    w.off_unc_rows = take(size_t(w.plan.n_rows) * 12);       // uncertified rows | rows of the multi-round re-rank | split masks
     w.off_unc_part = take(rerank_unc_part_bytes(w.plan.n_rows, k));
     if (w.sym_stride > 0) {
         w.off_thr = take(size_t(w.n_pad) * 4);
@@ -220,6 +220,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
+    rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rp.unc_cnt = ovf + 2;
@@ -357,7 +358,7 @@ static GroupLayout group_layout(const KnnGroupSlide* slides, int num, int64_t d,
     g.o_pval = take(size_t(part) * 4);
     g.o_pidx = take(size_t(part) * 4);
     g.o_flags = take(16);
-    g.o_unc_rows = take(size_t(g.n_pad) * 8);
+    g.o_unc_rows = take(size_t(g.n_pad) * 12);
     g.o_unc_part = take(rerank_unc_part_bytes(g.n_pad, k));
     g.o_units = take(size_t(units) * sizeof(TcUnit));
     g.o_slides = take(size_t(num) * sizeof(RrSlide));
@@ -437,7 +438,8 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     for (int i = 0; i < num; ++i) {
         const KnnGroupSlide& s = slides[i];
         vec = vec && (reinterpret_cast<uintptr_t>(s.feats) & 15) == 0;
-        rs[i] = RrSlide{s.feats, has_pos ? s.pos : nullptr, g.off[i], s.n, g.part_off[i], g.splits[i], 0, s.out_idx, s.out_val, s.out_cos};
+        rs[i] = RrSlide{s.feats, has_pos ? s.pos : nullptr, g.off[i], s.n, g.part_off[i], g.splits[i], 0, s.out_idx, s.out_val, s.out_cos,
+                        int64_t(ceil_div(ceil_div(s.n, TC_BN), g.splits[i])) * TC_BN};
         for (int64_t b = g.off[i] / kRowPad; b < (g.off[i] + ops_rows(s.n)) / kRowPad; ++b) map[size_t(b)] = i;
         const int tiles = int(ceil_div(s.n, TC_BN)), cps = int(ceil_div(tiles, g.splits[i]));
         const int ct_base = int(g.off[i] / TC_BN);
@@ -574,7 +576,7 @@ static int sympart_plan(const hg_knn_part* s, SymPartWs* w) {
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
     w->off_flags = take(16);
-    w->off_unc_rows = take(size_t(w->n_rows) * 8);
+    w->off_unc_rows = take(size_t(w->n_rows) * 12);
     w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
     w->bytes = off;
     return HG_OK;
@@ -697,6 +699,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     rp.metric = s->metric; rp.lambda_h = s->lambda_h; rp.lambda_g = has_pos ? s->lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
+    rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     rp.sym_plan = w.sym_plan; rp.bkt_cnt = own_bkt_cnt; rp.bkt = static_cast<const uint2*>(own_bkt); rp.bkt_cap = bucket_cap();
     rp.ovf = any_overflow; rp.bkt_row0 = s->row_begin;

@@ -114,6 +114,7 @@ struct RrSlide {                 // one slide of a grouped launch, as the re-ran
     int64_t part_off;            // element offset of the slide's [splits][n][kl] candidate lists
     int32_t splits, reserved;
     int32_t* out_idx; float* out_val; float* out_cos;
+    int64_t cols_per_split;      // columns swept by one split of the slide's lists
 };
 
 struct RerankParams {
@@ -124,6 +125,8 @@ struct RerankParams {
     int metric; float lambda_h, lambda_g;
     const float* part_val; const int32_t* part_idx;
     int splits, kl; int64_t n_rows, row_begin;
+    int64_t cols_per_split;      // columns swept by one split of the (classic-plan) lists; 0 = unknown: the fallback
+                                 // rescans every column instead of the flagged splits' ranges
     // symmetric mode: candidates = per-(row, split) lists of the sym plan + the row's bucket;
     // if *ovf != 0 the classic kernel re-ran and (splits, kl) above describe its lists
     TcPlan sym_plan; const int32_t* bkt_cnt; const uint2* bkt; int bkt_cap; const int* ovf;
@@ -132,8 +135,10 @@ struct RerankParams {
     int32_t* out_idx; float* out_val;
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
     // certification fallback (rerank.cu): rows whose lists cannot vouch for the exact top-k are appended to
-    // unc_rows (counter *unc_cnt, zeroed by the caller) and recomputed exactly against all n columns;
-    // unc_part = [n_rows][RR_UNC_SLICES][k] scratch.  All three null: no certification.
+    // unc_rows (counter *unc_cnt, zeroed by the caller) and recomputed exactly against the columns of the splits whose
+    // list was full inside the slack; unc_rows holds 3 * n_rows ints (uncertified rows | rows of the multi-round
+    // kernel | split masks of the uncertified rows), unc_part = [n_rows][RR_UNC_SLICES][k] scratch.  All null: no
+    // certification.
     int32_t* unc_rows; int32_t* unc_cnt; uint2* unc_part;
     // rows with more than 32 candidates inside the slack: worklist of the multi-round re-rank kernel (counter zeroed
     // by the caller, list of n_rows entries)

@@ -89,6 +89,7 @@ struct RowCtx {
     const float* part_val; const int32_t* part_idx;
     int64_t n, n_rows;            // rows of the slide; row stride between two splits' lists
     int splits;
+    int64_t cols_per_split;       // columns swept by one split of the lists (0: unknown), classic plan
     int32_t* out_idx; float* out_val; float* out_cos;
     int64_t r, row;               // r: row of the lists / outputs, row: row of the features
 };
@@ -98,14 +99,14 @@ struct RowCtx {
 __device__ __noinline__ bool row_ctx(const RerankParams& p, int64_t rg, RowCtx& c) {
     if (p.g_slides == nullptr) {
         c.feats = p.feats; c.pos = p.pos; c.sq_norms = p.sq_norms; c.part_val = p.part_val; c.part_idx = p.part_idx;
-        c.n = p.n; c.n_rows = p.n_rows; c.splits = p.splits;
+        c.n = p.n; c.n_rows = p.n_rows; c.splits = p.splits; c.cols_per_split = p.cols_per_split;
         c.out_idx = p.out_idx; c.out_val = p.out_val; c.out_cos = p.out_cos;
         c.r = rg; c.row = p.row_begin + rg;
         return true;
     }
     const RrSlide* sl = p.g_slides + p.g_blk2slide[rg >> 8];
     const int64_t off = sl->off;
-    c.n = sl->n; c.n_rows = c.n; c.splits = sl->splits;
+    c.n = sl->n; c.n_rows = c.n; c.splits = sl->splits; c.cols_per_split = sl->cols_per_split;
     c.r = rg - off; c.row = c.r;
     if (c.r >= c.n) return false;
     c.feats = sl->feats; c.pos = sl->pos; c.sq_norms = p.sq_norms + off;
@@ -376,12 +377,17 @@ rerank_kernel(const RerankParams p) {
         if (c.out_cos != nullptr) c.out_cos[r * p.k + t] = NAN;
     }
     if (p.unc_cnt != nullptr) {
-        bool full_inside = false;
-        for (int s2 = lane; s2 < splits; s2 += 32) {
-            const int64_t o = (int64_t(s2) * c.n_rows + r) * p.kl + (p.kl - 1);
-            full_inside |= c.part_idx[o] >= 0 && c.part_val[o] <= kth + slack;
+        bool full_inside = false;                        // lane s2 looks at split s2 (at most 32 splits)
+        if (lane < splits) {
+            const int64_t o = (int64_t(lane) * c.n_rows + r) * p.kl + (p.kl - 1);
+            full_inside = c.part_idx[o] >= 0 && c.part_val[o] <= kth + slack;
         }
-        if (__any_sync(0xffffffffu, full_inside) && lane == 0) p.unc_rows[atomicAdd(p.unc_cnt, 1)] = int32_t(rg);
+        const unsigned mask = __ballot_sync(0xffffffffu, full_inside);
+        if (mask != 0u && lane == 0) {
+            const int e = atomicAdd(p.unc_cnt, 1);
+            p.unc_rows[e] = int32_t(rg);
+            p.unc_rows[2 * p.n_rows + e] = int32_t(mask);            // which splits' column ranges have to be rescanned
+        }
     }
     }  // rows of this warp
 }
@@ -418,12 +424,18 @@ exact_slices_kernel(const RerankParams p) {
         row_ctx(p, p.unc_rows[e], c);
         const int64_t row = c.row;
         const bool vec = rows_vectorisable(c.feats, p.d);
-        const int64_t per_slice = ceil_div(c.n, RR_UNC_SLICES);
+        const int64_t per_slice = round_up(ceil_div(c.n, RR_UNC_SLICES), CB);
         const float* xi = c.feats + row * p.d;
         const float ni = c.sq_norms[row];
         const int64_t c0 = slice * per_slice, c1 = min64(c.n, c0 + per_slice);
+        // only the column ranges of the splits whose list could have dropped a member of the exact top-k: every other
+        // column inside the slack is in a list, was evaluated by the re-rank and competes through its output (merge)
+        const bool sym = p.ovf != nullptr && *p.ovf == 0;
+        const int64_t cps = sym ? int64_t(p.sym_plan.ct_per_split) * TC_BN : c.cols_per_split;
+        const unsigned mask = cps > 0 ? unsigned(p.unc_rows[2 * p.n_rows + e]) : 0xffffffffu;
         float mv = INFINITY; int mi = 0x7fffffff;                      // this warp's list, lane t = t-th best
         for (int64_t j0 = c0 + warp * CB; j0 < c1; j0 += RR_UNC_WARPS * CB) {
+            if (cps > 0 && ((mask >> int(j0 / cps)) & 1u) == 0u) continue;     // a batch of CB columns lies in one split
             const float* xj[CB];
 #pragma unroll
             for (int q = 0; q < CB; ++q) xj[q] = c.feats + min64(j0 + q, c.n - 1) * p.d;
@@ -495,10 +507,25 @@ exact_merge_kernel(const RerankParams p) {
                 cv[q] = __uint_as_float(u.x); ci[q] = int(u.y);
             }
         }
+        // ... plus what the re-rank already wrote for this row: the exact top-k of every candidate the lists held (the
+        // rescan above skipped the column ranges of the splits that were not flagged); keys recomputed, lane t = entry t
+        const float* xi = c.feats + row * p.d;
+        const float ni = c.sq_norms[row];
+        float pv = INFINITY; int pi = 0x7fffffff;
+        for (int t = 0; t < p.k; ++t) {
+            const int j = c.out_idx[r * p.k + t];
+            if (j < 0) break;                                        // warp-uniform: the list is padded at its end
+            const float* xj[1] = {c.feats + int64_t(j) * p.d};
+            float d2[1], dt[1];
+            warp_pair_sums<WANT_D2, WANT_DOT, 1>(xi, xj, p.d, lane, vec, d2, dt);
+            float key, out, cs;
+            exact_key<MODE>(p, c, j, d2[0], dt[0], ni, key, out, cs);
+            if (lane == t) { pv = key; pi = j; }
+        }
         int sel = 0x7fffffff;
         int nsel = 0;
         for (int t = 0; t < p.k; ++t) {
-            float bv = INFINITY; int bi = 0x7fffffff;
+            float bv = pv; int bi = pi;
 #pragma unroll
             for (int q = 0; q < RR_UNC_SLICES; ++q)
                 if (pair_less(cv[q], ci[q], bv, bi)) { bv = cv[q]; bi = ci[q]; }
@@ -512,12 +539,11 @@ exact_merge_kernel(const RerankParams p) {
 #pragma unroll
             for (int q = 0; q < RR_UNC_SLICES; ++q)
                 if (ci[q] == bi) { cv[q] = INFINITY; ci[q] = 0x7fffffff; }
+            if (pi == bi) { pv = INFINITY; pi = 0x7fffffff; }           // a column may be in a slice list AND in the output
             if (lane == t) sel = bi;
             nsel = t + 1;
         }
         // the selection order IS the (exact key, index) order; recompute value and cosine of every winner
-        const float* xi = c.feats + row * p.d;
-        const float ni = c.sq_norms[row];
         for (int t = 0; t < nsel; ++t) {
             const int j = __shfl_sync(0xffffffffu, sel, t);
             const float* xj[1] = {c.feats + int64_t(j) * p.d};

@@ -232,6 +232,39 @@ def test_knn_near_duplicates_stay_exact(k, metric, groups, monkeypatch, capfd):
     assert near <= 3 or metric != "euclidean"
 
 
+@pytest.mark.parametrize("sym", ["0", "8"])
+def test_knn_fallback_rescans_only_the_flagged_splits(sym, monkeypatch, capfd):
+    """40 groups of 500 near-duplicates, each group CONTIGUOUS in the row order: every row's in-slack candidates fall
+    into one column split, whose list overflows with copies; the row is flagged with that split's bit only and the
+    exact fallback rescans that split's column range, merging with what the re-rank already evaluated from the other
+    splits (rerank.cu, exact_slices_kernel / exact_merge_kernel).  Classic pass (HG_B200_TC_SYM=0) and symmetric pass;
+    result = the float64 direct-difference ranking up to near-ties relative to the distance itself."""
+    n, d, k, groups = 20_000, 128, 16, 40
+    rng = np.random.default_rng(72)
+    base = synth.make_features(groups, d, 72, "gaussian")
+    feats = (np.repeat(base, n // groups, axis=0) + 1e-4 * rng.standard_normal((n, d))).astype(np.float32)
+    monkeypatch.setenv("HG_B200_TC_SYM", sym)
+    monkeypatch.setenv("HG_B200_TC_DEBUG", "1")
+    idx, val = ops.knn_feature(_cuda(feats), k, "euclidean")
+    torch.cuda.synchronize()
+    err = capfd.readouterr().err
+    flagged = int(err.split("hg_b200 rerank:")[1].split()[0])
+    assert flagged > n // 2, f"expected most rows to be uncertified, got {flagged}"
+    idx, val = idx.cpu().numpy().astype(np.int64), val.cpu().numpy()
+    x = feats.astype(np.float64)
+    for r in range(0, n, 97):
+        g0 = (r // 500) * 500
+        d2 = ((x[g0:g0 + 500] - x[r]) ** 2).sum(1)            # every neighbour lies in the row's own group
+        d2[r - g0] = np.inf
+        ref = g0 + np.argsort(d2, kind="stable")[:k]
+        assert ((idx[r] >= g0) & (idx[r] < g0 + 500)).all()
+        if set(ref.tolist()) != set(idx[r].tolist()):
+            only_g, only_o = np.setdiff1d(idx[r], ref), np.setdiff1d(ref, idx[r])
+            gap = abs(d2[only_g - g0].max() - d2[only_o - g0].min()) / d2[only_o - g0].min()
+            assert gap <= 1e-5, f"row {r}: picked {only_g} over {only_o}, relative gap {gap:.2e}"
+        np.testing.assert_allclose(val[r], d2[idx[r] - g0], rtol=1e-4, atol=0)
+
+
 def test_knn_gaussian_with_positions():
     n, d, k = 3000, 128, 16
     feats, pos = synth.make_slide(n, d, 41, "gaussian")
