@@ -15,9 +15,10 @@ one full per-slide build.  With N > 1 GPUs every rank builds its own slide of th
              features and positions and D2H of every output inside the timed region, every step.
 `roofline` : the fused similarity + top-k stage (knn_tc_kernel: threshold pre-pass + symmetric half
              pass), algorithmic 2*N^2*D FLOP per slide (full N x N, symmetry NOT credited, SURVEY.md
-             8(d)) over its CUDA-event duration, against measured BF16 peak / 3 (3 BF16 MMAs per
-             FP32-accurate product).  The symmetric pass issues ~0.57 of the tiles, so `frac` can
-             exceed 1; `executed_frac` = BF16 MMA work actually issued / the raw BF16 peak.
+             8(d)) over its CUDA-event duration, against the measured 16-bit tensor peak / MMAs per
+             logical product (2 in the symmetric passes, 3 elsewhere: split-FP16 operands).  The
+             symmetric pass issues ~0.57 of the tiles, so `frac` can exceed 1; `executed_frac` = MMA
+             work actually issued / the raw tensor peak.
 `secondary`: C2 (N=50k x 1024, Gaussian kNN k=16 + CSR), last round's headline, for continuity.
 `c4`       : 512 slides (N in [2048, 8192], D=1024) sharded slide-per-GPU by LPT: slides/s resident
              (one grouped build per rank) and end to end from pinned host memory.
@@ -428,6 +429,9 @@ def run_ours(args):
         bf16 = peaks["bf16_sustained"] if sustained else peaks["bf16"]
         sym_stride, mma_flop = ctypes.c_int(0), ctypes.c_double(0.0)
         _lib.check(lib.hg_knn_feature_plan(n, d, k, 0, n, ctypes.byref(sym_stride), ctypes.byref(mma_flop)))
+        prods, pre_prods = ctypes.c_int(0), ctypes.c_int(0)
+        _lib.check(lib.hg_knn_feature_products(n, d, k, 0, n, ctypes.byref(prods), ctypes.byref(pre_prods)))
+        per = float(prods.value)                                  # MMAs per logical product of the main pass
         executed = mma_flop.value / (kern_ms * 1e-3) / 1e12 if kern_ms > 0 else None
         mode = (f"symmetric half pass + 1/{sym_stride.value} threshold pre-pass" if sym_stride.value > 0 else "full pass")
         traffic = None
@@ -435,18 +439,19 @@ def run_ours(args):
         if os.path.exists(prof):
             t = json.load(open(prof))
             traffic = t.get(f"dram_bytes_per_launch_n{n}_d{d}", t.get("dram_bytes_per_launch") if n == 50_000 else None)
-        return {"bound": "tensor", "kernel": f"knn_tc_kernel (fused 3xBF16 similarity + top-k, {mode})",
-                "achieved": achieved, "peak": bf16 / 3.0, "unit": "TFLOP/s",
-                "frac": (achieved / (bf16 / 3.0)) if achieved else None, "traffic": traffic,
-                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step,
-                "peak_source": (f"{peaks['source']} bf16_tflops{'_sustained' if sustained else ''} / 3 MMAs per product "
-                                f"(burst {peaks['bf16']:.0f}, sustained {peaks['bf16_sustained']:.0f} TFLOP/s BF16); "
-                                f"{'sustained: the timed region is many 40 ms launches back to back' if sustained else 'burst: 5 ms launches'}"),
+        return {"bound": "tensor", "kernel": f"knn_tc_kernel (fused split-FP16 similarity + top-k, {prods.value} MMAs per product, {mode})",
+                "achieved": achieved, "peak": bf16 / per, "unit": "TFLOP/s",
+                "frac": (achieved / (bf16 / per)) if achieved else None, "traffic": traffic,
+                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step, "mma_per_product": prods.value,
+                "peak_source": (f"{peaks['source']} bf16_tflops{'_sustained' if sustained else ''} (kind::f16 MMAs: FP16 operands "
+                                f"run at the BF16 rate) / {prods.value} MMAs per product "
+                                f"(burst {peaks['bf16']:.0f}, sustained {peaks['bf16_sustained']:.0f} TFLOP/s); "
+                                f"{'sustained: the timed region is many long launches back to back' if sustained else 'burst: 5 ms launches'}"),
                 "frac_note": "frac = algorithmic 2*N^2*D FLOP (full N x N, symmetry not credited) / time / peak: above 1 is "
-                             "possible because the symmetric pass issues ~0.57 of the tiles; executed_frac = issued BF16 MMA "
-                             "FLOP / time / raw BF16 peak is the hardware-utilisation figure",
-                "algorithmic_flop": flop, "executed_bf16_mma_flop": mma_flop.value,
-                "executed_bf16_tflops": executed, "executed_frac": (executed / bf16) if executed else None,
+                             "possible because the symmetric pass issues ~0.57 of the tiles; executed_frac = issued 16-bit MMA "
+                             "FLOP / time / raw 16-bit tensor peak is the hardware-utilisation figure",
+                "algorithmic_flop": flop, "executed_mma_flop": mma_flop.value,
+                "executed_tflops": executed, "executed_frac": (executed / bf16) if executed else None,
                 "executed_frac_of_burst": (executed / peaks["bf16"]) if executed else None}
 
     def parity_check(w, r, rows_n=256):
@@ -507,7 +512,7 @@ def run_ours(args):
                  "e2e": {"value": world * C2["n"] / (r2["e2e_ms"] * 1e-3), "ms_per_step": r2["e2e_ms"],
                          "h2d_bytes_per_step": r2["h2d"], "d2h_bytes_per_step": r2["d2h"]},
                  "gpu_launches": r2["launches"],
-                 "roofline": {key: roof2[key] for key in ("achieved", "peak", "frac", "kernel_ms", "executed_bf16_tflops",
+                 "roofline": {key: roof2[key] for key in ("achieved", "peak", "frac", "kernel_ms", "executed_tflops",
                                                           "executed_frac", "peak_source")}}
     r2 = None
     _lib.Workspace.clear()
@@ -598,12 +603,12 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": "patches/s", "n_gpus": world, "steps": steps,
             "warmup": warmup, "ms_per_step": r3["ms_step"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16x3+f32", "data": "synthetic",
+            "vs_baseline": None, "dtype": "f16-split+f32", "data": "synthetic",
             "config": {"workload": C3["name"], "n": n, "d": C3["d"], "k": C3["k"], "spatial_k": C3["spatial_k"],
                        "kernel": C3["kernel"], "lambda_h": C3["lambda_h"], "lambda_g": C3["lambda_g"],
                        "edges": r3["num_edges"], "slides_per_s": world / (r3["ms_step"] * 1e-3),
                        "parallelism": f"slide-per-gpu x{world}",
-                       "l2": "inputs larger than L2 (614 MB FP32 features + 614 MB BF16 hi/lo operands per step)"},
+                       "l2": "inputs larger than L2 (614 MB FP32 features + 614 MB FP16 hi/lo operands per step)"},
             "e2e": {"value": e2e_value, "unit": "patches/s", "ms_per_step": r3["e2e_ms"],
                     "api": f"hg_b200.pipeline.build_many (H2D stream / {r3['lanes']} stream-ordered build lanes / D2H stream, "
                            "wall clock, best of 3 K-step regions)",

@@ -54,7 +54,7 @@ int hg_profile_enable(int on);
 int hg_profile_collect(float* ms_total, int* launches);
 
 /* ---- operand preparation -------------------------------------------------
- * Splits FP32 rows into BF16 hi/lo halves (x ~= hi + lo, 16 significant bits)
+ * Splits FP32 rows, scaled by a per-row power of two, into FP16 hi/lo halves (s x ~= hi + lo, 22 significant bits)
  * laid out [n_pad][d_pad / 32][2][32] for TMA (every 128 bytes = 32 hi | 32 lo values
  * of one 32-wide k-block), zero padded to n_pad = ceil256(n), d_pad = ceil64(d), and
  * writes per-row squared norms (FP32, from the original data).  Replaces `torch.sum(features**2)` (similarity_kernel.py:43) and is the
@@ -74,7 +74,7 @@ int hg_split_operands(const float* feats, int64_t n, int64_t d,
  *   COSINE   : sklearn metric='cosine' (preprocess_hypergraph.py:311) /
  *              F.cosine_similarity (:419).
  * out_idx [rows, k] int32 (-1 when fewer than k candidates exist),
- * out_val [rows, k] float32.  `precision`: 0 = 3xBF16 tensor-core candidates +
+ * out_val [rows, k] float32.  `precision`: 0 = split-FP16 tensor-core candidates +
  * exact FP32 re-rank (default), 1 = plain FP32 SIMT kernel (any shape).
  * Over the full row range of a large slide (n >= 9216) the tensor-core pass exploits the symmetry
  * of K: about half of the tiles are computed and each serves both (i, j) and (j, i); results are
@@ -83,10 +83,17 @@ int hg_knn_feature_workspace_bytes(int64_t n, int64_t d, int k,
                                    int64_t row_begin, int64_t row_end, size_t* bytes);
 /* What hg_knn_feature will run for this shape: symmetric_stride > 0 means the symmetric
  * (half-of-the-tiles) pass with a threshold pre-pass over every stride-th column; mma_flop is the
- * BF16 tensor-core work actually issued (3 MMAs per product, padded tiles), which is about
- * 0.56 x 3 x 2 N^2 D in symmetric mode. */
+ * FP16 tensor-core work actually issued (hg_knn_feature_products MMAs per product, padded tiles),
+ * which is about 0.56 x 2 x 2 N^2 D in symmetric mode. */
 int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
                         int* symmetric_stride, double* mma_flop);
+/* Tensor-core MMAs issued per logical product x_i . x_j by the main pass and by the threshold
+ * pre-pass (0 when there is none) of hg_knn_feature for this shape: 3 = hi*hi + hi*lo + lo*hi
+ * of the split-FP16 operands (classic full pass, grouped and dense launches), 2 = hi*hi + hi*lo
+ * (symmetric passes; HG_B200_TC_SYM_PRODS=3 in the environment keeps three).  The roofline of the
+ * fused kernel is the 16-bit tensor-core peak divided by this number. */
+int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
+                            int* main_pass, int* pre_pass);
 int hg_knn_feature(const float* feats, int64_t n, int64_t d,
                    const float* pos, int pos_dim,
                    int metric, float lambda_h, float lambda_g,
@@ -124,10 +131,10 @@ int hg_similarity_stats(const float* values, int64_t count, int64_t exclude_diag
                         double* stats_out, void* workspace, size_t workspace_bytes, void* stream);
 
 /* A9 when N x N does not fit: the same five statistics of K = K_h * K_g over all N^2 entries,
- * streamed chunk by chunk through the tensor-core kernel (K from 3xBF16 dot products, relative
+ * streamed chunk by chunk through the tensor-core kernel (K from split-FP16 dot products, relative
  * error ~1e-6) -- the matrix is never stored in full.  preprocess_hypergraph.py:137,190-196. */
 /* A1 / A2 for large square inputs: K of one matrix against itself through the tensor-core kernel's
- * dense-output mode (3xBF16 Gram product, FP32 accumulation; same expansion form, un-clamped).  13-20x faster
+ * dense-output mode (split-FP16 Gram product, 3 MMAs per k-step, FP32 accumulation; same expansion form, un-clamped).  13-20x faster
  * than hg_similarity_dense, entries within ~1.5e-5 relative of float64 (measured) instead of 1e-5: opt-in.
  * ld_out >= n, lambda_h > 0, workspace 1024-byte aligned. */
 int hg_similarity_dense_tc_workspace_bytes(int64_t n, int64_t d, size_t* bytes);

@@ -59,11 +59,11 @@ struct Carver {
 
 // ---- geometry of the tensor-core operand buffer ------------------------------
 constexpr int kRowPad = 256;   // operand rows padded to a multiple of the widest TMA box
-constexpr int kColPad = 64;    // feature dim padded to one 128-byte swizzle atom of BF16
+constexpr int kColPad = 64;    // feature dim padded to one 128-byte swizzle atom of 16-bit values
 
 inline int64_t ops_rows(int64_t n) { return round_up(n, kRowPad); }
 inline int64_t ops_cols(int64_t d) { return round_up(d, kColPad); }
-// BF16 elements from one operand row to the next: 2 * d_pad (32 hi | 32 lo per k-block) plus a pad
+// 16-bit elements from one operand row to the next: 2 * d_pad (32 hi | 32 lo per k-block) plus a pad
 // that keeps the row pitch off multiples of 2 KB (split.cu)
 int64_t ops_row_elems(int64_t d_pad);
 
@@ -72,6 +72,6 @@ int64_t ops_row_elems(int64_t d_pad);
 struct ColParam { float a, b; };
 
 int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
-                 cudaStream_t st);
+                 cudaStream_t st, bool dense = false);
 
 }  // namespace hg

@@ -240,7 +240,7 @@ __global__ void km_tol_kernel(const double* __restrict__ part, int nrb, int64_t 
     if (threadIdx.x == 0) { st->tol_abs = tol * tot / double(d); st->best_inertia = 0.0; }
 }
 
-// xc = x - column means: distances do not change, but the FP32 expansion |x|^2 + |c|^2 - 2 x.c and the BF16
+// xc = x - column means: distances do not change, but the FP32 expansion |x|^2 + |c|^2 - 2 x.c and the FP16
 // split stop cancelling on data that sits far from the origin (scikit-learn's fit centres X for the same reason;
 // without it nearly constant data, e.g. a similarity matrix with entries around 0.98, never stops moving labels)
 __global__ void __launch_bounds__(256)
@@ -527,7 +527,7 @@ __global__ void km_take_kernel(const KmState* __restrict__ st, const int32_t* __
 }
 
 // Tensor-core assignment, second half: the fused kernel (knn_tc.cu, rectangular launch) left every row the
-// KL centres with the smallest 3xBF16 scores |c|^2 - 2 x.c.  Every candidate whose score lies within the
+// KL centres with the smallest split-FP16 (3-product) scores |c|^2 - 2 x.c.  Every candidate whose score lies within the
 // guaranteed error slack of the best one is recomputed as sum (x - c)^2 in FP32 (almost always one), and the
 // smallest exact distance wins, ties to the lower centre.  One warp per row.
 __global__ void __launch_bounds__(256, 4)
@@ -547,7 +547,7 @@ km_pick_kernel(const float* __restrict__ x, const float* __restrict__ centers, i
     float best = sc;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) best = fminf(best, __shfl_xor_sync(0xffffffffu, best, o));
-    const float slack = TC_SLACK_3X * (norms_x[r] + __ldg(norm_max));
+    const float slack = tc_slack(round_up(d, kColPad), 3, 3) * (norms_x[r] + __ldg(norm_max));
     unsigned todo = __ballot_sync(0xffffffffu, idx >= 0 && sc <= best + slack);
     const float* xi = x + r * d;
     const bool vec = rows_vectorisable(x, d) && rows_vectorisable(centers, d);
@@ -666,6 +666,7 @@ static int km_assign(const KmAssign& a, cudaStream_t st) {
     TcParams tp{};
     tp.n = c; tp.row_begin = 0; tp.row_end = n; tp.d_pad = int(a.d_pad);
     tp.plan = a.plan; tp.colp = a.colp; tp.part_val = a.part_val; tp.part_idx = a.part_idx;
+    tp.norms_a = a.norms_x; tp.norms_b = a.norms_c; tp.prods = 3;
     rc = tc_launch_rect(a.ops_x, a.n_pad_x, a.ops_c, a.c_pad, tp, st);
     if (rc != HG_OK) return rc;
     km_pick_kernel<<<(unsigned)ceil_div(n * 32, 256), 256, 0, st>>>(a.sim.a, a.sim.b, n, d, a.part_val, a.part_idx, a.plan.kl,

@@ -28,10 +28,18 @@ static int bucket_cap() {
     return TC_BKT_CAP;
 }
 
-// the threshold pre-pass ranks with one BF16 product (hi * hi) instead of three; HG_B200_TC_PRE_HI=0/1
-static bool prepass_hi_only() {
-    if (const char* e = getenv("HG_B200_TC_PRE_HI")) return atoi(e) != 0;
-    return false;
+// Tensor-core products per k-step (knn_tc.cuh tc_eps) of the symmetric passes: 2 by default -- the query rows
+// rounded to FP16, the columns whole -- which issues two thirds of the MMAs for a wider slack that the many short lists
+// and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3 keeps all three.  Classic, grouped and dense
+// launches always use three.  The threshold pre-pass uses the main pass's count, or one product with
+// HG_B200_TC_PRE_HI=1.
+static int sym_prods() {
+    if (const char* e = getenv("HG_B200_TC_SYM_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
+    return 2;
+}
+static int prepass_prods() {
+    if (const char* e = getenv("HG_B200_TC_PRE_HI")) if (atoi(e) != 0) return 1;
+    return sym_prods();
 }
 
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
@@ -105,11 +113,21 @@ extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begi
             }
         return t;
     };
-    const double per_tile = 3.0 * 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);     // 3 BF16 MMAs per product
-    double tiles = w.sym_stride > 0 ? tiles_of(w.sym_plan) + tiles_of(w.pre_plan) / (prepass_hi_only() ? 3.0 : 1.0)
-                                    : tiles_of(w.plan) * w.plan.cl;
+    const double per_tile = 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);           // one MMA sweep of a tile
+    const double flop = w.sym_stride > 0 ? (tiles_of(w.sym_plan) * sym_prods() + tiles_of(w.pre_plan) * prepass_prods()) * per_tile
+                                         : tiles_of(w.plan) * w.plan.cl * 3.0 * per_tile;
     if (symmetric_stride) *symmetric_stride = w.sym_stride;
-    if (mma_flop) *mma_flop = tiles * per_tile;
+    if (mma_flop) *mma_flop = flop;
+    return HG_OK;
+}
+
+extern "C" int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
+                                       int* main_pass, int* pre_pass) {
+    int rc = check_knn_args(n, d, k, row_begin, row_end);
+    if (rc != HG_OK) return rc;
+    const bool sym = tc_sym_stride(n, row_end - row_begin, k) > 0;
+    if (main_pass) *main_pass = sym ? sym_prods() : 3;
+    if (pre_pass) *pre_pass = sym ? prepass_prods() : 0;
     return HG_OK;
 }
 
@@ -182,6 +200,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     TcParams tp{};
     tp.n = n; tp.row_begin = row_begin; tp.row_end = row_end; tp.d_pad = int(w.d_pad);
     tp.plan = w.plan; tp.colp = colp; tp.pos4 = pos4;
+    tp.norms_a = norms; tp.prods = 3;
     tp.gscale = (pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
@@ -195,16 +214,17 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         pre.plan = w.pre_plan; pre.col_stride = w.sym_stride; pre.exclude_self = 0;
         const int cosine = (metric == HG_METRIC_COSINE) ? 1 : 0;
         pre.thr_rank = k; pre.thr_margin_cos = cosine; pre.norm_max = norm_max;
-        pre.hi_only = prepass_hi_only() ? 1 : 0;
+        pre.prods = prepass_prods(); pre.pre_main_prods = sym_prods();
         pre.thr_out = (w.pre_plan.splits == 1) ? thr : nullptr;     // several splits: lists, merged below
         rc = tc_launch(ops, w.n_pad, pre, st);
         if (rc != HG_OK) return rc;
         if (w.pre_plan.splits > 1) {
             rc = thr_merge_launch(pre.part_val, w.pre_plan.splits, n, w.pre_plan.kl, k, colp, norm_max, cosine,
-                                  pre.hi_only ? TC_SLACK_HI : tc_slack_3x(w.d_pad), thr, st);
+                                  tc_slack(w.d_pad, pre.prods, pre.pre_main_prods), thr, st);
             if (rc != HG_OK) return rc;
         }
         TcParams sp = tp;
+        sp.prods = sym_prods();
         sp.plan = w.sym_plan; sp.thr = thr; sp.bkt_cnt = bkt_cnt; sp.bkt = bkt; sp.bkt_cap = bucket_cap(); sp.ovf = ovf;
         rc = tc_launch(ops, w.n_pad, sp, st);
         if (rc != HG_OK) return rc;
@@ -222,7 +242,8 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
     rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
-    if (sym) { rp.sym_plan = w.sym_plan; rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
+    rp.prods = 3;
+    if (sym) { rp.sym_plan = w.sym_plan; rp.sym_prods = sym_prods(); rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rp.unc_cnt = ovf + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
     rp.more_cnt = ovf + 3; rp.more_rows = rp.unc_rows + w.plan.n_rows;
@@ -484,6 +505,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     TcParams tp{};
     tp.d_pad = int(g.d_pad);
     tp.colp = colp; tp.pos4 = pos4;
+    tp.norms_a = norms; tp.prods = 3;
     tp.gscale = (has_pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + g.o_pval);
@@ -504,7 +526,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = has_pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = max_splits; rp.kl = g.kl; rp.n_rows = g.n_pad; rp.row_begin = 0;
-    rp.k = k;
+    rp.k = k; rp.prods = 3;
     const float* any_cos = nullptr;
     for (int i = 0; i < num; ++i) if (slides[i].out_cos != nullptr) any_cos = slides[i].out_cos;
     rp.out_cos = const_cast<float*>(any_cos);                       // only selects the kernel variant; per slide in the kernel
@@ -597,6 +619,7 @@ static TcParams sympart_params(const hg_knn_part* s, const SymPartWs& w, char* w
     tp.n = s->n; tp.row_begin = s->row_begin; tp.row_end = s->row_end; tp.d_pad = int(w.d_pad);
     tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
     tp.pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
+    tp.norms_a = reinterpret_cast<float*>(ws + w.off_norms); tp.prods = 3;
     tp.gscale = (has_pos && s->lambda_h > 0.f) ? s->lambda_g / s->lambda_h : 0.f;
     tp.exclude_self = s->exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
@@ -639,6 +662,7 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_a
     pre.plan = w.pre_plan; pre.col_stride = w.stride; pre.exclude_self = 0;
     pre.thr_rank = s->k; pre.thr_margin_cos = (s->metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
     pre.thr_out = thr_all;                                    // indexed by the global row
+    pre.prods = prepass_prods(); pre.pre_main_prods = sym_prods();
     prof_begin(st);
     rc = tc_launch(ops, w.n_pad, pre, st);
     prof_end(st);
@@ -656,7 +680,7 @@ extern "C" int hg_knn_sympart_sweep(const hg_knn_part* s, const float* thr_all, 
                "hg_knn_sympart_sweep: bad partition (1..8 peers, 256-aligned chunks covering n)");
     char* ws = static_cast<char*>(workspace);
     TcParams sp = sympart_params(s, w, ws);
-    sp.plan = w.sym_plan;
+    sp.plan = w.sym_plan; sp.prods = sym_prods();
     sp.thr = thr_all; sp.bkt_cap = bucket_cap(); sp.ovf = own_flags;
     sp.sblk_base = int(s->row_begin / 256);
     sp.peer_chunk = chunk;
@@ -701,6 +725,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
     rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
+    rp.prods = 3; rp.sym_prods = sym_prods();
     rp.sym_plan = w.sym_plan; rp.bkt_cnt = own_bkt_cnt; rp.bkt = static_cast<const uint2*>(own_bkt); rp.bkt_cap = bucket_cap();
     rp.ovf = any_overflow; rp.bkt_row0 = s->row_begin;
     rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;

@@ -6,10 +6,12 @@
 //             similarity_kernel.py:79-84,122  the spatial factor K_g
 //             preprocess_hypergraph.py:379-382  sklearn brute-force kNN
 //
-// Arithmetic: FP32 rows are pre-split into BF16 hi/lo halves (split.cu), interleaved per 32-wide
-// k-block so that one 128-byte operand row carries 32 hi | 32 lo values.  The dot
-// product is accumulated in FP32 in TMEM from three tcgen05 MMAs per k-step:
-//   hi*lo^T + lo*hi^T + hi*hi^T   ("3xBF16", ~2^-17 relative per product).
+// Arithmetic: FP32 rows are scaled by a power of two and pre-split into FP16 hi/lo halves (split.cu, knn_tc.cuh),
+// interleaved per 32-wide k-block so that one 128-byte operand row carries 32 hi | 32 lo values.  The dot
+// product is accumulated in FP32 in TMEM from tcgen05 MMAs (kind::f16, FP16 operands) per k-step:
+//   3 products  hi*lo^T + lo*hi^T + hi*hi^T   (~2^-21 relative: classic, grouped and dense launches)
+//   2 products  hi*lo^T + hi*hi^T             (the A rows rounded to 11 bits, 2^-11 relative: symmetric passes,
+//                                              whose many short lists + buckets absorb the wider slack)
 // The epilogue turns the accumulator into a ranking score  a_j + b_j * dot
 // (+ g * |pos_i - pos_j|^2)  and keeps a per-row sorted list of the KL best
 // (score, column) pairs in registers.  The candidates are re-ranked exactly in
@@ -46,6 +48,7 @@
 #include "topk_list.cuh"
 #include <cudaTypedefs.h>
 #include <stdlib.h>
+#include <algorithm>
 
 namespace hg {
 
@@ -65,7 +68,7 @@ struct TcCfg {
     static constexpr int B_TILE = B_ROWS * 128;                     // 32 / 16 KB
     static constexpr int STAGE_BYTES = A_TILE + B_TILE;             // 48 / 32 KB
 };
-constexpr int TC_MAX_STAGES = 6;
+constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_THREADS = 192;
 constexpr int TC_EPI_THREADS = 128;
 // dense-output mode: eight epilogue warps (two per TMEM lane quarter, 128 of the 256 tile columns each).  Its
@@ -81,6 +84,7 @@ struct TcSmem {                       // lives after the (1024-byte aligned) sta
     float2 colp[2][TC_BN];
     float4 cpos[2][TC_BN];
     float thr[2][TC_BN];              // SYM: admission threshold of each column of the tile
+    float cinv[2][TC_BN];             // SYM: 1 / operand scale of each column (the transposed score needs it apart)
     uint2 wq[4][TC_WQ_CAP];           // SYM: (score bits, column-in-tile << 8 | row-in-block)
     int wq_cnt[4];
     uint64_t full[TC_MAX_STAGES], empty[TC_MAX_STAGES], tmem_full[2], tmem_empty[2];
@@ -181,7 +185,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     using Cfg = TcCfg<CG>;
     constexpr int TC_STAGES = Cfg::STAGES;
     constexpr int TC_A_TILE = Cfg::A_TILE, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
-    static_assert(!SYM || (CG == 1 && KL > 0), "symmetric mode: single-CTA tiles with candidate lists");
+    static_assert(!SYM || KL > 0, "symmetric mode keeps candidate lists");
     static_assert(!MC || CG == 1, "multicast pairs issue single-CTA MMAs");
     constexpr int CL = (CG == 2 || MC) ? 2 : 1;        // CTAs per cluster = 128-row blocks per work unit
     constexpr bool DENSE = KL == 0;                    // dense-output mode: K written out, no candidate lists
@@ -198,7 +202,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
     const int wid = blockIdx.x / CL, nworkers = gridDim.x / CL;          // a worker = one CTA or one pair
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_STAGES; ++s) {
+        for (int s = 0; s < TC_MAX_STAGES; ++s) {
             ptx::mbar_init(ptx::smem_u32(&sm->full[s]), 1);
             ptx::mbar_init(ptx::smem_u32(&sm->empty[s]), MC ? 2 : 1);      // MC: both CTAs' MMAs release a stage
         }
@@ -226,52 +230,64 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 
     if (warp == 0) {
         // ============================ TMA producer ============================
-        if (lane == 0) {
-            uint32_t it = 0;
+        // elect.sync instead of lane == 0: the compiler then knows that ONE thread runs the block and emits the TMA /
+        // MMA / commit instructions bare; behind a plain lane test it wraps each of them in an ELECT + BRA.U.ANY loop
+        // over the active threads -- ~150 instructions per pipeline stage in the MMA issuer, which made the issuing
+        // thread, not the tensor pipe, the limit once a stage held two products instead of three (ncu source view)
+        if (ptx::elect_one()) {
+            // B tile: 128-byte rows (32 hi | 32 lo) or, when no product reads the lo halves of B, their first 64 bytes;
+            // the smaller stages then come six or eight to the buffer instead of four or six
+            const uint32_t b_bytes = p.b_hi_only ? Cfg::B_TILE / 2 : Cfg::B_TILE;
+            const uint32_t stage_bytes = TC_A_TILE + b_bytes, stage_tx = stage_bytes;
+            const uint32_t nstages = uint32_t(p.stages);
+            uint32_t stage = 0, ph = 0;
             for (int u = wid; u < units; u += nworkers) {
                 const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
                 const int row0 = int(ui.row0), rb = ui.rb;
                 for (int ct = ui.ct0; ct < ui.ct1; ++ct) {
                     if (!owns_tile<SYM>(p.sblk_base + (CL == 2 ? rb : rb >> 1), ct)) continue;
-                    for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                        const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
+                    for (int kb = 0; kb < num_kb; ++kb) {
                         if (!p.pair_stages) {
                             ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
-                        } else if ((it & 1u) == 0) {       // stages are refilled in pairs (STAGES and num_kb are even)
+                        } else if ((stage & 1u) == 0) {    // stages are refilled in pairs (the stage count and num_kb are even)
                             ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage]), ph ^ 1u);
                             ptx::mbar_wait(ptx::smem_u32(&sm->empty[stage + 1]), ph ^ 1u);
                         }
                         const uint32_t full = ptx::smem_u32(&sm->full[stage]);
-                        const uint32_t dst = smem_base + stage * TC_STAGE_BYTES;
+                        const uint32_t dst = smem_base + stage * stage_bytes;
                         if (MC) {
                             // own A rows + the own half of the B tile, which also lands in the peer; the peer's
                             // half arrives here the same way (its bytes may precede this expect_tx: same phase)
-                            constexpr int HALF = Cfg::B_TILE / 2;
-                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            const int HALF = int(b_bytes / 2);
+                            ptx::mbar_expect_tx(full, stage_tx);
                             ptx::tma_load_3d(dst, &tmap_a, full, kb * (2 * TC_BK), row0, 0, p.hint_a);
                             ptx::tma_load_3d_mc(dst + TC_A_TILE + int(crank) * HALF, &tmap_b, full, kb * (2 * TC_BK),
                                                 ct * TC_BN + int(crank) * (TC_BN / 2), 0, uint16_t(3), p.hint_b);
                         } else if (CG == 1) {
-                            ptx::mbar_expect_tx(full, TC_STAGE_BYTES);
+                            ptx::mbar_expect_tx(full, stage_tx);
                             ptx::tma_load_3d(dst, &tmap_a, full, kb * (2 * TC_BK), row0, 0, p.hint_a);
                             ptx::tma_load_3d(dst + TC_A_TILE, &tmap_b, full, kb * (2 * TC_BK), ct * TC_BN, 0, p.hint_b);
                         } else {
                             // both CTAs' bytes are counted on the LEADER's barrier (peer bit cleared)
                             const uint32_t lead_full = full & 0xFEFFFFFFu;
-                            if (crank == 0) ptx::mbar_expect_tx(full, 2 * TC_STAGE_BYTES);
+                            if (crank == 0) ptx::mbar_expect_tx(full, 2 * stage_tx);
                             ptx::tma_load_3d_2sm(dst, &tmap_a, lead_full, kb * (2 * TC_BK), row0, 0, p.hint_a);
                             ptx::tma_load_3d_2sm(dst + TC_A_TILE, &tmap_b, lead_full, kb * (2 * TC_BK),
                                                  ct * TC_BN + int(crank) * Cfg::B_ROWS, 0, p.hint_b);
                         }
+                        if (++stage == nstages) { stage = 0; ph ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ==============================
-        if (lane == 0 && (crank == 0 || MC)) {
-            constexpr uint32_t idesc = ptx::make_idesc_bf16(TC_BM * CG, TC_BN);
-            uint32_t it = 0, tile = 0;
+        if ((crank == 0 || MC) && ptx::elect_one()) {
+            constexpr uint32_t idesc = ptx::make_idesc_f16(TC_BM * CG, TC_BN);
+            const int prods = p.prods;
+            const uint32_t stage_bytes = TC_A_TILE + (p.b_hi_only ? Cfg::B_TILE / 2 : Cfg::B_TILE);
+            const uint32_t nstages = uint32_t(p.stages);
+            uint32_t stage = 0, ph = 0, tile = 0;
             for (int u = wid; u < units; u += nworkers) {
                 const UnitInfo ui = unit_info<CL>(p, u, crank, KL);
                 const int rb = ui.rb;
@@ -284,39 +300,44 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     const uint32_t d_tmem = tmem_base + buf * TC_BN;
                     // The tensor core adds every MMA into the FP32 accumulator with a truncating add, so a long chain
                     // drifts by ~1 ulp of the running sum per step (1.4e-5 relative on exp(-d2) after 192 steps at
-                    // D = 1024).  List mode does not care (exact FP32 re-rank).  Dense mode sums the two cross terms
+                    // D = 1024).  List mode does not care (exact FP32 re-rank).  Dense mode sums the small products
                     // (2^-8 of the magnitude) in an accumulator of their own and adds the two in FP32 in the epilogue:
-                    // the large accumulator sees D / 16 steps instead of 3 D / 16.
+                    // the large accumulator sees D / 16 steps instead of 4 D / 16.
                     const uint32_t d_cross = DENSE ? d_tmem + TC_BN : d_tmem;
-                    for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                        const uint32_t stage = it % TC_STAGES, ph = (it / TC_STAGES) & 1u;
+                    for (int kb = 0; kb < num_kb; ++kb) {
                         ptx::mbar_wait(ptx::smem_u32(&sm->full[stage]), ph);
                         ptx::tc_fence_after();
-                        const uint32_t a_addr = smem_base + stage * TC_STAGE_BYTES;
+                        const uint32_t a_addr = smem_base + stage * stage_bytes;
                         const uint32_t b_addr = a_addr + TC_A_TILE;
                         // inside a 128-byte swizzled row: hi values at bytes [0, 64), lo at [64, 128)
                         const uint64_t a_hi = ptx::make_smem_desc_sw128(a_addr);
                         const uint64_t a_lo = a_hi + 4;                     // + 64 bytes, in 16-byte units
-                        const uint64_t b_hi = ptx::make_smem_desc_sw128(b_addr);
-                        const uint64_t b_lo = b_hi + 4;
+                        const uint64_t b_hi = p.b_hi_only ? ptx::make_smem_desc_sw64(b_addr) : ptx::make_smem_desc_sw128(b_addr);
+                        const uint64_t b_lo = b_hi + 4;                     // (128-byte rows only)
 #pragma unroll
                         for (int ks = 0; ks < TC_BK / 16; ++ks) {
                             const uint64_t off = uint64_t(ks * 2);        // 32 bytes per k-step, >> 4
-                            if (!p.hi_only) {
-                                // dense mode also adds lo*lo: on the diagonal and for near-duplicate rows the dropped
-                                // term is a sum of squares (no cancellation), 5e-6 of exp(-d2) on its own
-                                if (DENSE) ptx::mma_bf16<CG>(d_cross, a_lo + off, b_lo + off, idesc, (kb | ks) != 0);
-                                ptx::mma_bf16<CG>(d_cross, a_hi + off, b_lo + off, idesc, DENSE ? 1u : uint32_t((kb | ks) != 0));
-                                ptx::mma_bf16<CG>(d_cross, a_lo + off, b_hi + off, idesc, 1u);
-                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, DENSE ? uint32_t((kb | ks) != 0) : 1u);
-                            } else {                          // coarse pre-pass: one BF16 product
-                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kb | ks) != 0);
+                            const uint32_t acc0 = uint32_t((kb | ks) != 0);
+                            if (prods >= 2) {
+                                // lo*hi first: the small terms enter the (empty) accumulator before the large one;
+                                // lo*lo (2^-22 of the magnitude) is left out.  Dense mode: operands with 8-bit hi
+                                // halves (split.cu), so lo*lo is 2^-16 and counts -- on the diagonal and for
+                                // near-duplicate rows it is a sum of squares, no cancellation -- and the small
+                                // products get an accumulator of their own.
+                                // Two products: lo*hi + hi*hi -- the B tiles then carry no lo halves at all.
+                                if (DENSE) ptx::mma_f16<CG>(d_cross, a_lo + off, b_lo + off, idesc, acc0);
+                                ptx::mma_f16<CG>(d_cross, a_lo + off, b_hi + off, idesc, DENSE ? 1u : acc0);
+                                if (prods >= 3) ptx::mma_f16<CG>(d_cross, a_hi + off, b_lo + off, idesc, 1u);
+                                ptx::mma_f16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, DENSE ? acc0 : 1u);
+                            } else {                          // coarse pre-pass: one product
+                                ptx::mma_f16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, acc0);
                             }
                         }
                         // frees the stage (in both CTAs of a pair) when the MMAs retire
                         if (MC) ptx::mma_commit_mc(ptx::smem_u32(&sm->empty[stage]), 3);
                         else if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->empty[stage]));
                         else ptx::mma_commit_2sm(ptx::smem_u32(&sm->empty[stage]), 3);
+                        if (++stage == nstages) { stage = 0; ph ^= 1u; }
                     }
                     if (CG == 1) ptx::mma_commit(ptx::smem_u32(&sm->tmem_full[buf]));
                     else ptx::mma_commit_2sm(ptx::smem_u32(&sm->tmem_full[buf]), 3);     // (buf = 0 in dense mode)
@@ -348,6 +369,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
             // this row's own score parameters; padded rows: (+inf, 0)
             const float2 me = (row < p.n_pad) ? __ldg(p.colp + row) : make_float2(INFINITY, 0.f);
             const float row_norm = me.x, ta = me.x, tb = me.y;
+            // the accumulator holds (s_i x_i) . (s_j x_j): 1 / s_i here, 1 / s_j folded into the column multiplier
+            const float rinv = (row < ui.row_end) ? op_inv_scale(__ldg(p.norms_a + row)) : 1.f;   // padding rows: dot = 0
             float4 mypos = make_float4(0.f, 0.f, 0.f, 0.f);
             if (HAS_POS && row < ui.row_end) mypos = __ldg(p.pos4 + row);
             // SYM: the pre-pass bound of this row also gates its own list (nothing above it can be in
@@ -362,7 +385,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 for (int c = et; c < TC_BN; c += EPI) {
                     const int64_t src = int64_t(col0 + c) * cstride;      // operand row behind column c
                     const bool ok = src < p.n_pad;
-                    sm->colp[buf][c] = ok ? __ldg(p.colp + src) : make_float2(INFINITY, 0.f);
+                    float2 cpj = ok ? __ldg(p.colp + src) : make_float2(INFINITY, 0.f);
+                    const float cinv = ok ? op_inv_scale(__ldg(p.norms_b + src)) : 1.f;
+                    cpj.y *= cinv;                                        // exact: a power of two
+                    sm->colp[buf][c] = cpj;
+                    if (SYM) sm->cinv[buf][c] = cinv;
                     if (HAS_POS) sm->cpos[buf][c] = ok ? __ldg(p.pos4 + src) : make_float4(0.f, 0.f, 0.f, 0.f);
                     if (SYM) sm->thr[buf][c] = __ldg(p.thr + col0 + c);    // NaN beyond n: never admitted
                 }
@@ -373,10 +400,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                 const int self_col = diag ? int(row - col0) : -1;     // column inside this tile, if any
                 const bool transposed = SYM && ct != sblk;             // the diagonal tile serves rows only
                 // ranking score of (this row, column c) and, SYM, of (column c, this row)
-                auto scores = [&](int c, float dot, float& s_row, float& s_tr) {
+                auto scores = [&](int c, float acc, float& s_row, float& s_tr) {
                     const float2 cp = sm->colp[buf][c];
+                    const float dot = acc * rinv;                         // exact (power of two): x_i . x_j * s_j
                     s_row = fmaf(cp.y, dot, cp.x);
-                    if (SYM) s_tr = fmaf(tb, dot, ta);
+                    if (SYM) s_tr = fmaf(tb * sm->cinv[buf][c], dot, ta);
                     if (HAS_POS) {
                         const float4 q = sm->cpos[buf][c];
                         const float dx = mypos.x - q.x, dy = mypos.y - q.y, dz = mypos.z - q.z;
@@ -487,14 +515,11 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     float t = INFINITY;                   // the list ascends: min over q >= rank is lv[rank]
 #pragma unroll
                     for (int q = 0; q < KLA; ++q) t = fminf(t, (q >= p.thr_rank) ? lv[q] : INFINITY);
-                    // guaranteed slack for the 3xBF16 error of a score (dropped lo*lo term <= 2^-16 |x_i||x_j|,
-                    // FP32 accumulation, both tile orientations): Euclidean / Gaussian scores n_j - 2 dot,
-                    // cosine scores -dot / |x_j|
-                    // A hi-only pre-pass ranks with x ~ bf16(x): its k best sample columns have 3xBF16 scores at
-                    // most 2^-8 (n_i + n_j) above their coarse ones (|x - hi| <= 2^-9 |x| per element), so the
-                    // bound stays valid with that much more slack.
+                    // guaranteed slack (knn_tc.cuh tc_eps): the error of this pass's score plus that of the main
+                    // pass's score the bound will be compared with; Euclidean / Gaussian scores n_j - 2 dot scale
+                    // with n_i + n_max, cosine scores -dot / |x_j| with |x_i|
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
-                    p.thr_out[row] = t + (p.hi_only ? TC_SLACK_HI : tc_slack_3x(p.d_pad)) * scale + TC_SLACK_REL * fabsf(t);
+                    p.thr_out[row] = t + tc_slack(p.d_pad, p.prods, p.pre_main_prods) * scale + TC_SLACK_REL * fabsf(t);
                 } else {
                     const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
 #pragma unroll
@@ -516,6 +541,16 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
 int tc_cta_group() {                       // 1 (default) or 2 = CTA pairs, HG_B200_TC_CG=2
     const char* e = getenv("HG_B200_TC_CG");
     return (e && atoi(e) == 2) ? 2 : 1;
+}
+// CTA pairs in the symmetric pass (cta_group::2: each CTA stages its own 128 A rows and half of the B tile, so a
+// B tile leaves the L2 once per pair).  The pass runs against the board's power limit, and of all the variants
+// measured back to back for seconds (profiles/r02_power_probe_variants.jsonl) the pairs hold the highest clock per
+// unit of work from D = 1024 up: C3 30.8 ms against 36.3 (single CTAs, same tiles) and 32.5 (whole B rows, 4 stages).
+// Narrow rows are bound by the epilogue, where single CTAs are 1-3 % ahead.  HG_B200_TC_SYM_CG=1/2 overrides.
+static int tc_sym_cta_group(int64_t d_pad) {
+    if (const char* e = getenv("HG_B200_TC_SYM_CG")) { const int v = atoi(e); if (v == 1 || v == 2) return v; }
+    if (tc_cta_group() == 2) return 2;
+    return d_pad >= 1024 ? 2 : 1;
 }
 static int tc_multicast() {                // multicast pairs (cg 1 only): HG_B200_TC_MC=0/1
     if (tc_cta_group() != 1) return 0;
@@ -610,9 +645,9 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
 // only the tiles it owns (about every other one).
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
     TcPlan pl{};
-    pl.cg = 1;
-    pl.mc = tc_multicast();
-    pl.cl = pl.mc ? 2 : 1;
+    pl.cg = tc_sym_cta_group(d_pad);
+    pl.mc = pl.cg == 1 ? tc_multicast() : 0;
+    pl.cl = (pl.cg == 2 || pl.mc) ? 2 : 1;
     pl.sym = 1;
     pl.n_rows = n;
     pl.num_rb = int(ceil_div(n, TC_BM * pl.cl));
@@ -658,7 +693,7 @@ TcPlan tc_make_plan_prepass_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad
 // wins from n ~ 9k up (measured at D = 1024: 2 % at n = 8192, 21 % at n = 10240; break-even at 9k x 512).  HG_B200_TC_SYM=0 disables it,
 // HG_B200_TC_SYM=<stride> forces it (any n with enough sample columns) with that pre-pass stride.
 int tc_sym_stride(int64_t n, int64_t n_rows, int k) {
-    if (n_rows != n || tc_cta_group() != 1) return 0;
+    if (n_rows != n) return 0;
     int stride = (n >= 32768) ? 16 : 8;
     bool forced = false;
     if (const char* e = getenv("HG_B200_TC_SYM")) {
@@ -684,18 +719,20 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 }
 
 // row_stride > 1: a view of every row_stride-th operand row (the pre-pass column sample)
+// hi_only: the box is the first 64 bytes (32 hi values) of every 128-byte k-block, 64-byte swizzle
 static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows,
-                     int row_stride = 1) {
+                     int row_stride = 1, bool hi_only = false) {
     auto enc = get_encode_fn();
     HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
-    // operand row = d_pad / 32 blocks of (32 hi | 32 lo) BF16 = 4 * d_pad bytes; one box row = one such block
+    // operand row = d_pad / 32 blocks of (32 hi | 32 lo) FP16 = 4 * d_pad bytes; one box row = one such block
     const cuuint64_t row_bytes = cuuint64_t(ops_row_elems(d_pad)) * 2;
     cuuint64_t dims[3] = {cuuint64_t(d_pad) * 2, cuuint64_t(ceil_div(n_pad, row_stride)), 1};
     cuuint64_t strides[2] = {row_bytes * cuuint64_t(row_stride), row_bytes * cuuint64_t(n_pad)};
-    cuuint32_t box[3] = {cuuint32_t(2 * TC_BK), cuuint32_t(box_rows), 1};
+    cuuint32_t box[3] = {cuuint32_t(hi_only ? TC_BK : 2 * TC_BK), cuuint32_t(box_rows), 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, hi_only ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     HG_REQUIRE(r == CUDA_SUCCESS, HG_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", int(r));
     return HG_OK;
@@ -728,6 +765,8 @@ static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
     if constexpr (KL > 0) {
         if (p.plan.sym && p.plan.mc)
             return p.pos4 ? launch_one<KL, true, 1, true, true>(ta, tb, p, st) : launch_one<KL, false, 1, true, true>(ta, tb, p, st);
+        if (p.plan.sym && p.plan.cg == 2)
+            return p.pos4 ? launch_one<KL, true, 2, true>(ta, tb, p, st) : launch_one<KL, false, 2, true>(ta, tb, p, st);
         if (p.plan.sym)
             return p.pos4 ? launch_one<KL, true, 1, true>(ta, tb, p, st) : launch_one<KL, false, 1, true>(ta, tb, p, st);
         if (p.plan.mc)
@@ -761,18 +800,37 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
         if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
     }
     if (p.col_stride < 1) p.col_stride = 1;
-    HG_REQUIRE(!p.plan.sym || (p.plan.cg == 1 && p.plan.kl > 0 && p.col_stride == 1 && p.thr &&
+    HG_REQUIRE(!p.plan.sym || (p.plan.kl > 0 && p.col_stride == 1 && p.thr && (p.plan.cg == 1 || p.peer_chunk == 0) &&
                                ((p.peer_chunk == 0 && p.row_begin == 0 && p.row_end == p.n && p.bkt_cnt && p.bkt && p.ovf) ||
                                 (p.peer_chunk > 0 && p.ovf && p.row_begin % 256 == 0 && p.sblk_base == p.row_begin / 256))),
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");
     HG_REQUIRE(p.col_stride == 1 || (p.plan.cl == 1 && p.plan.kl > 0), HG_ERR_BAD_ARG, "tc_launch: strided columns need single CTAs");
     HG_REQUIRE(!p.plan.mc || p.plan.kl > 0, HG_ERR_BAD_ARG, "tc_launch: multicast pairs keep lists (no dense mode)");
     CUtensorMap ta, tb;
-    HG_REQUIRE(!p.hi_only || (p.plan.cg == 1 && p.col_stride > 1), HG_ERR_BAD_ARG,
-               "tc_launch: the hi-only product is for the threshold pre-pass");
+    if (p.prods == 0) p.prods = 3;
+    if (p.pre_main_prods == 0) p.pre_main_prods = p.prods;
+    HG_REQUIRE(p.prods >= 1 && p.prods <= 3 && (p.prods > 1 || (p.plan.cg == 1 && p.col_stride > 1)), HG_ERR_BAD_ARG,
+               "tc_launch: 1 to 3 products per k-step, the single product is for the threshold pre-pass");
+    HG_REQUIRE(p.prods == 3 || p.plan.kl > 0, HG_ERR_BAD_ARG, "tc_launch: dense output needs all three products");
+    HG_REQUIRE(p.norms_a != nullptr, HG_ERR_BAD_ARG, "tc_launch: the row norms behind the operand scales are missing");
+    if (p.norms_b == nullptr) p.norms_b = p.norms_a;
+#ifdef HG_TC_FORCE_PRODS          // timing experiments only (results are wrong): tools/README in DESIGN.md 9
+    if (p.plan.kl > 0) p.prods = HG_TC_FORCE_PRODS;
+#endif
+    // No product reads the lo halves of B when there are two or one: the B tiles are then 64-byte rows, a stage is
+    // 32 KB (24 KB for CTA pairs) instead of 48 (32) and more of them fit.  What binds the kernel is the 64 B / clock
+    // an SM takes in from the L2: with whole B rows a tile needs 1280 D bytes for 16 D cycles of MMAs (2 products).
+    p.b_hi_only = p.prods <= 2 ? 1 : 0;
+    if (const char* e = getenv("HG_B200_TC_B_HI")) { if (atoi(e) == 0) p.b_hi_only = 0; }    // A/B switch
+    {
+        const int b_rows = TC_BN / (p.plan.cg == 2 ? 2 : 1);
+        const int stage_bytes = TC_BM * 128 + b_rows * (p.b_hi_only ? 64 : 128);
+        const int budget = (p.plan.cg == 2 ? 6 * 32 : 4 * 48) * 1024;
+        p.stages = std::min(TC_MAX_STAGES, budget / stage_bytes) & ~1;               // even: stages are refilled in pairs
+    }
     int rc = make_tmap(&ta, ops_a, n_pad_a, p.d_pad, TC_BM, 1);
     if (rc != HG_OK) return rc;
-    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cl, p.col_stride);   // a CTA of a pair stages half of the B tile
+    rc = make_tmap(&tb, ops, n_pad, p.d_pad, TC_BN / p.plan.cl, p.col_stride, p.b_hi_only != 0);   // a CTA of a pair stages half of the B tile
     if (rc != HG_OK) return rc;
     switch (p.plan.kl) {
         case 0:  return launch_kl<0>(ta, tb, p, st);

@@ -6,7 +6,7 @@ namespace hg {
 
 constexpr int TC_BM = 128;      // query rows per CTA tile  (UMMA M)
 constexpr int TC_BN = 256;      // candidate columns per tile (UMMA N)
-constexpr int TC_BK = 32;       // K per pipeline stage: one 128-byte operand row = 32 hi | 32 lo BF16
+constexpr int TC_BK = 32;       // K per pipeline stage: one 128-byte operand row = 32 hi | 32 lo FP16
 constexpr int TC_MAX_SPLITS = 8;
 
 struct TcPlan {
@@ -63,7 +63,16 @@ struct TcParams {
     int col_stride;
     float* thr_out;
     int thr_rank;
-    int hi_only;                // pre-pass only: one BF16 product hi*hi, wider slack
+    // tensor-core products per k-step (see tc_eps below): 3 = hi*hi + hi*lo + lo*hi, 2 = hi*hi + lo*hi (the B rows
+    // rounded to FP16, the A rows whole; symmetric passes), 1 = hi*hi (threshold pre-pass only).  0 means 3.
+    int prods;
+    int b_hi_only;              // prods <= 2: the B tiles carry the hi halves only (64-byte rows); set by tc_launch
+    int stages;                 // pipeline stages that fit the shared-memory buffer with such tiles; set by tc_launch
+    int pre_main_prods;         // pre-pass only: products of the main pass its bound will gate (slack of thr_out)
+    // squared norms of the operand rows behind the query rows / the columns: every operand row was scaled by the
+    // power of two op_scale(norm) before its FP16 split, the epilogue undoes both scales.  norms_b null = norms_a.
+    const float* norms_a;
+    const float* norms_b;
     int thr_margin_cos;         // error slack added to thr_out scales with |x_i| (cosine) or n_i + norm_max
     const float* norm_max;      // largest squared row norm
     // symmetric mode: transposed candidates (column j gets row i) with score < thr[j] are
@@ -132,6 +141,7 @@ struct RerankParams {
     TcPlan sym_plan; const int32_t* bkt_cnt; const uint2* bkt; int bkt_cap; const int* ovf;
     int64_t bkt_row0;            // bkt_cnt / bkt are indexed by (row - bkt_row0): 0, or row_begin for a partitioned slide
     int k;
+    int prods, sym_prods;        // tensor-core products per k-step behind the classic lists / the symmetric lists + buckets
     int32_t* out_idx; float* out_val;
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
     // certification fallback (rerank.cu): rows whose lists cannot vouch for the exact top-k are appended to
@@ -153,23 +163,54 @@ inline size_t rerank_unc_part_bytes(int64_t n_rows, int k) { return size_t(n_row
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
                      const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st);
-constexpr float TC_SLACK_3X = 4.8828125e-4f;      // 2^-11: the D-independent bound of round 1 (still used by kmeans.cu)
-constexpr float TC_SLACK_HI = 4.39453125e-3f;     // 2^-8 + 2^-11: a hi-only pre-pass score against a 3xBF16 one
+// ---- operand format and the guaranteed error of a tensor-core score ---------------------------------------------
+// An operand row x is scaled by s = op_scale(|x|^2), a power of two that puts |s x| into [2^5, 2^6), and split into
+// two FP16 values per element: hi = fp16(s x), lo = fp16(s x - hi).  Every element is below 2^6 (no overflow);
+// elements below 2^-14 land on FP16's subnormal grid, spacing 2^-24, an ABSOLUTE error of 2^-25 at most.
+__host__ __device__ inline int op_scale_log2(float sq_norm) {
+#ifdef __CUDA_ARCH__
+    const int e = (__float_as_int(sq_norm) >> 23) & 0xff;
+#else
+    union { float f; int i; } u; u.f = sq_norm;
+    const int e = (u.i >> 23) & 0xff;
+#endif
+    // |x|^2 in [2^(e-127), 2^(e-126))  ->  |x| < 2^h, h = ceil((e - 126) / 2);  s = 2^(6 - h)
+    const int h = (e - 125) >> 1;
+    return 6 - h;
+}
+__host__ __device__ inline float pow2f(int e) {          // 2^e, -126 <= e <= 127
+#ifdef __CUDA_ARCH__
+    return __int_as_float((e + 127) << 23);
+#else
+    union { float f; int i; } u; u.i = (e + 127) << 23; return u.f;
+#endif
+}
+__host__ __device__ inline float op_scale(float sq_norm) { return pow2f(op_scale_log2(sq_norm)); }
+__host__ __device__ inline float op_inv_scale(float sq_norm) { return pow2f(-op_scale_log2(sq_norm)); }
 
-// Guaranteed slack of a COMPARISON of two 3xBF16 scores of one row, as a multiple of (|x_i|^2 + max_j |x_j|^2)
-// (Euclidean / Gaussian scores n_j - 2 dot) or of |x_i| (cosine scores -dot / |x_j|).  Error of one dot product,
-// relative to |x_i||x_j|:
-//   * representation: x = hi + lo + r with |lo| <= 2^-9 |x|, |r| <= 2^-18 |x| per element; the products left out are
-//     lo.lo + r.y + x.r, each <= 2^-18 by Cauchy-Schwarz                                         ->  3 * 2^-18 = 1.15e-5
-//   * accumulation: 3 D_pad / 16 tensor-core steps into one FP32 accumulator whose add truncates; at most 2^-22 of the
-//     running magnitude (<= |x_i||x_j|) per step.  (Measured in the dense mode, one accumulator, D = 1024: worst entry
-//     of 2.7e8 off by 7e-6, an eighth of this bound.)                                          ->  (3 D_pad / 16) * 2^-22
-// A score is n_j - 2 dot, so its error is 2 eps |x_i||x_j| <= eps (n_i + n_j), and two scores differ from their exact
-// difference by at most 2 eps (n_i + n_max): 1.1e-4 at D = 1024, 1.6e-4 at D = 1536 (round 1 used 4.9e-4 for every D,
-// which this bound exceeds from D ~ 5,000 up).  The FP32 rounding of the score arithmetic itself (fma, spatial term)
-// is relative to the score: TC_SLACK_REL * |score| on top.
-__host__ __device__ inline float tc_slack_3x(int64_t d_pad) {
-    return 2.f * (1.15e-5f + float(3 * (d_pad / 16)) * 2.3842e-7f);
+// Guaranteed error of ONE dot product x_i . x_j out of the tensor cores, relative to |x_i||x_j|, by the number of
+// products per k-step.  With u = 2^-11 (FP16 round to nearest, 11 significant bits) and, per element,
+// |x - hi| <= u |x| + 2^-25 and |x - hi - lo| <= u^2 |x| + 2^-25 (scaled units, |x_row| >= 2^5):
+//   * representation, by Cauchy-Schwarz over the row (the absolute parts sum to 2^-25 sqrt(D) |y| <= 2^-30 sqrt(D)
+//     |x||y| each):
+//       3 products: lo.lo + r.y + x.r left out                       ->  3 u^2 + 2 * 2^-30 sqrt(D)
+//       2 products: x_i . (x_j - hi_j) left out as well             ->  u + u^2 + 2 * 2^-30 sqrt(D)
+//       1 product : both rows rounded                                ->  2 u + u^2 + 2 * 2^-30 sqrt(D)
+//   * accumulation: prods * D_pad / 16 tensor-core steps into one FP32 accumulator whose add truncates, at most 2^-22
+//     of the running magnitude (<= |x_i||x_j|) per step.  (Measured in the dense mode, one accumulator of 192 steps,
+//     D = 1024: worst entry of 2.7e8 off by 7e-6 relative, an eighth of this bound.)
+// A Euclidean / Gaussian score is n_j - 2 dot, so its error is 2 eps |x_i||x_j| <= eps (n_i + n_j); a cosine score
+// -dot / |x_j| is off by eps |x_i|.  Two scores of one row therefore compare correctly once they differ by more than
+// (eps_a + eps_b) * (n_i + n_max) resp. (eps_a + eps_b) * |x_i| -- tc_slack() -- plus the FP32 rounding of the score
+// arithmetic itself (fma, spatial term), which is relative to the score: TC_SLACK_REL * |score| on top.
+__host__ __device__ inline float tc_eps(int64_t d_pad, int prods) {
+    const float u = 4.8828125e-4f, u2 = 2.3841858e-7f;                 // 2^-11, 2^-22
+    if (prods <= 0) prods = 3;
+    const float repr = (prods >= 3 ? 3.f * u2 : prods == 2 ? u + u2 : 2.f * u + u2) + 1.8627e-9f * sqrtf(float(d_pad));
+    return repr + float(prods * (d_pad / 16)) * u2;
+}
+__host__ __device__ inline float tc_slack(int64_t d_pad, int prods_a, int prods_b) {
+    return tc_eps(d_pad, prods_a) + tc_eps(d_pad, prods_b);
 }
 constexpr float TC_SLACK_REL = 4.8e-7f;           // 2^-21
 

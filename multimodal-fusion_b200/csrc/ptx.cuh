@@ -134,9 +134,9 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// D[tmem] (+)= A[smem] * B[smem], BF16 inputs, FP32 accumulate
+// D[tmem] (+)= A[smem] * B[smem], 16-bit inputs (format in the instruction descriptor), FP32 accumulate
 template <int CG>
-__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                          uint32_t accumulate) {
     if (CG == 1)
         asm volatile(
@@ -180,7 +180,7 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ---------------------------------------------------------------------------
-// K-major operand tile, rows of 64 BF16 (128 B) packed at a 128-B pitch, 128-byte swizzle:
+// K-major operand tile, rows of 64 16-bit values (128 B) packed at a 128-B pitch, 128-byte swizzle:
 // 8-row groups are 1024 B apart (SBO), LBO unused (1), descriptor version 1 (sm_100).
 __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
     uint64_t d = 0;
@@ -191,9 +191,20 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
     d |= uint64_t(2) << 61;                 // SWIZZLE_128B
     return d;
 }
-// kind::f16 instruction descriptor: BF16 x BF16 -> FP32, A and B K-major
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(n >> 3) << 17) | (uint32_t(m >> 4) << 24);
+// the same with rows of 32 16-bit values (64 B) at a 64-B pitch, 64-byte swizzle: 8-row groups are 512 B apart
+__device__ __forceinline__ uint64_t make_smem_desc_sw64(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= uint64_t((smem_addr & 0x3FFFFu) >> 4);
+    d |= uint64_t(1) << 16;
+    d |= uint64_t(512 >> 4) << 32;
+    d |= uint64_t(1) << 46;
+    d |= uint64_t(4) << 61;                 // SWIZZLE_64B
+    return d;
+}
+// kind::f16 instruction descriptor: FP16 x FP16 -> FP32, A and B K-major.  Bits [4, 6) accumulator format (1 = F32),
+// [7, 10) A format and [10, 13) B format (0 = F16, 1 = BF16), [17, 23) N / 8, [24, 29) M / 16.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
+    return (1u << 4) | (0u << 7) | (0u << 10) | (uint32_t(n >> 3) << 17) | (uint32_t(m >> 4) << 24);
 }
 
 // ---- cluster ---------------------------------------------------------------------------------

@@ -1,7 +1,7 @@
 // Merge of the per-split candidate lists + exact FP32 re-rank, and the per-column
 // epilogue parameters of the fused kernel.
 //
-// The tensor-core pass (knn_tc.cu) ranks with 3xBF16 dot products; this pass
+// The tensor-core pass (knn_tc.cu) ranks with split-FP16 dot products (2 or 3 products per k-step); this pass
 // recomputes the distance of every surviving candidate in direct-difference
 // FP32 -- sum (x_i - x_j)^2, the more accurate of the two forms the reference
 // uses (preprocess_hypergraph.py:254-255 vs similarity_kernel.py:49) -- and
@@ -214,10 +214,11 @@ rerank_kernel(const RerankParams p) {
 
     const int ncand = total + nbkt;
     // Selection stops once a candidate's approximate score exceeds the k-th best by more than the
-    // guaranteed 3xBF16 error slack (both scores off by <= eps in opposite directions): such a
+    // guaranteed tensor-core error slack (both scores off by <= eps in opposite directions): such a
     // candidate cannot enter the exact top-k, and neither can any later one.
     const float ni = c.sq_norms[row];
-    const float slack_abs = tc_slack_3x(round_up(p.d, kColPad)) * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
+    const int prods = sym ? p.sym_prods : p.prods;       // tensor-core products behind the candidates' scores
+    const float slack_abs = tc_slack(round_up(p.d, kColPad), prods, prods) * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
     float slack = slack_abs;                             // + TC_SLACK_REL |k-th best| once that is known
     // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
     // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still

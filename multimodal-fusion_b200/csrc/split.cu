@@ -1,6 +1,7 @@
 // Operand preparation for the tensor-core Gram product.
 //
-// FP32 row x  ->  hi = bf16(x), lo = bf16(x - hi)  (x = hi + lo up to 2^-17 |x|)
+// FP32 row x  ->  s = op_scale(|x|^2), a power of two with |s x| in [2^5, 2^6) (knn_tc.cuh);
+//                 hi = fp16(s x), lo = fp16(s x - hi)  (s x = hi + lo up to 2^-22 |s x| + 2^-25 per element)
 // plus the FP32 squared row norm taken from the ORIGINAL data.  Replaces
 // `torch.sum(features ** 2, dim=1)` (reference similarity_kernel.py:43) and
 // prepares the inputs of the MMA that replaces `torch.mm` (:46).
@@ -12,9 +13,11 @@
 // contribute dot = 0.
 //
 // HBM-bound: reads 4 B and writes 4 B per element; one warp per row (4 rows per CTA),
-// 128-bit loads, 64-bit stores.
+// 128-bit loads, 64-bit stores.  Two passes over the row: the norm (which fixes the scale), then the split --
+// the second pass finds the row in L1.
 #include "knn_tc.cuh"
 #include "rowdot.cuh"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 namespace hg {
@@ -33,11 +36,20 @@ int64_t ops_row_elems(int64_t d_pad) {
     return 2 * d_pad + pad_bytes / 2;
 }
 
+// hi half of a scaled element: FP16 round to nearest, or (hi8, dense-output launches) rounded to 8 significant bits
+// first.  The tensor core aligns the 16 products of a k-step to the largest and truncates what falls below its
+// adder: products of two 11-bit values are 22 bits wide and lose their tails there (measured: 1.2e-5 on exp(-d2) at
+// D = 1536 against 6e-6), products of two 8-bit values go through whole -- and lo = fp16(x - hi) still holds the next
+// 11 bits, so hi + lo carries 19 bits; the dense mode adds lo*lo as well.
+__device__ __forceinline__ __half hi_half(float x, int hi8) {
+    return hi8 ? __float2half_rn(__bfloat162float(__float2bfloat16_rn(x))) : __float2half_rn(x);
+}
+
 template <bool VEC4>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
                   int64_t row_elems, __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms,
-                  const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide) {
+                  const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide, int hi8) {
     const int lane = threadIdx.x & 31;
     int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
     if (row >= n_pad) return;
@@ -65,44 +77,53 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
             if (v < nvec) x = __ldg(reinterpret_cast<const float4*>(src) + v);
             lo = fmaf(x.x, x.x, lo); hi = fmaf(x.y, x.y, hi);
             lo = fmaf(x.z, x.z, lo); hi = fmaf(x.w, x.w, hi);
-            __nv_bfloat16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y);
-            __nv_bfloat16 h2 = __float2bfloat16_rn(x.z), h3 = __float2bfloat16_rn(x.w);
-            __nv_bfloat16 l0 = __float2bfloat16_rn(x.x - __bfloat162float(h0));
-            __nv_bfloat16 l1 = __float2bfloat16_rn(x.y - __bfloat162float(h1));
-            __nv_bfloat16 l2 = __float2bfloat16_rn(x.z - __bfloat162float(h2));
-            __nv_bfloat16 l3 = __float2bfloat16_rn(x.w - __bfloat162float(h3));
-            __nv_bfloat162 hp0(h0, h1), hp1(h2, h3), lp0(l0, l1), lp1(l2, l3);
+        }
+        norm = warp_butterfly(lo + hi);
+        const float s = op_scale(norm);
+        for (int64_t v = lane; v < (d_pad >> 2); v += 32) {
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v < nvec) x = __ldg(reinterpret_cast<const float4*>(src) + v);
+            x.x *= s; x.y *= s; x.z *= s; x.w *= s;
+            const __half h0 = hi_half(x.x, hi8), h1 = hi_half(x.y, hi8);
+            const __half h2 = hi_half(x.z, hi8), h3 = hi_half(x.w, hi8);
+            const __half l0 = __float2half_rn(x.x - __half2float(h0)), l1 = __float2half_rn(x.y - __half2float(h1));
+            const __half l2 = __float2half_rn(x.z - __half2float(h2)), l3 = __float2half_rn(x.w - __half2float(h3));
             uint2 hv, lv;
-            hv.x = *reinterpret_cast<uint32_t*>(&hp0); hv.y = *reinterpret_cast<uint32_t*>(&hp1);
-            lv.x = *reinterpret_cast<uint32_t*>(&lp0); lv.y = *reinterpret_cast<uint32_t*>(&lp1);
+            hv.x = uint32_t(__half_as_ushort(h0)) | (uint32_t(__half_as_ushort(h1)) << 16);
+            hv.y = uint32_t(__half_as_ushort(h2)) | (uint32_t(__half_as_ushort(h3)) << 16);
+            lv.x = uint32_t(__half_as_ushort(l0)) | (uint32_t(__half_as_ushort(l1)) << 16);
+            lv.y = uint32_t(__half_as_ushort(l2)) | (uint32_t(__half_as_ushort(l3)) << 16);
             __nv_bfloat16* dst = hi_at(v << 2);
             *reinterpret_cast<uint2*>(dst) = hv;
             *reinterpret_cast<uint2*>(dst + 32) = lv;
         }
-        norm = lo + hi;
     } else {
         norm = 0.f;
         for (int64_t c = lane; c < d_pad; c += 32) {
             const float x = (c < d) ? __ldg(src + c) : 0.f;
             norm = fmaf(x, x, norm);
-            __nv_bfloat16 h = __float2bfloat16_rn(x);
-            __nv_bfloat16* dst = hi_at(c);
-            dst[0] = h;
-            dst[32] = __float2bfloat16_rn(x - __bfloat162float(h));
+        }
+        norm = warp_butterfly(norm);
+        const float s = op_scale(norm);
+        for (int64_t c = lane; c < d_pad; c += 32) {
+            const float x = ((c < d) ? __ldg(src + c) : 0.f) * s;
+            const __half h = hi_half(x, hi8);
+            unsigned short* dst = reinterpret_cast<unsigned short*>(hi_at(c));
+            dst[0] = __half_as_ushort(h);
+            dst[32] = __half_as_ushort(__float2half_rn(x - __half2float(h)));
         }
     }
-    norm = warp_butterfly(norm);
     if (lane == 0 && norm_out != nullptr) *norm_out = norm;
 }
 
 int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
-                 cudaStream_t st) {
+                 cudaStream_t st, bool dense) {
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (vec)
-        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr);
+        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0);
     else
-        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr);
+        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -114,9 +135,9 @@ int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int6
     const int64_t d_pad = ops_cols(d);
     const unsigned blocks = (unsigned)ceil_div(n_pad, SPLIT_WARPS);
     if (vec)
-        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide);
+        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0);
     else
-        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide);
+        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -133,5 +154,5 @@ extern "C" int hg_split_operands(const float* feats, int64_t n, int64_t d, void*
                                  void* stream) {
     HG_REQUIRE(feats && ops && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_split_operands: bad argument");
     return hg::launch_split(feats, n, d, static_cast<__nv_bfloat16*>(ops), sq_norms,
-                            static_cast<cudaStream_t>(stream));
+                            static_cast<cudaStream_t>(stream), false);
 }

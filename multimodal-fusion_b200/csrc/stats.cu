@@ -207,7 +207,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
     float* chunk = reinterpret_cast<float*>(ws + w.off_chunk);
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
 
-    int rc = launch_split(feats, n, d, ops, norms, st);
+    int rc = launch_split(feats, n, d, ops, norms, st, true);      // dense-output operands: 8-bit hi halves
     if (rc != HG_OK) return rc;
     rc = launch_colparams(norms, pos, pos_dim, n, n_pad, HG_METRIC_GAUSSIAN, colp, pos4, st);
     if (rc != HG_OK) return rc;
@@ -221,7 +221,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
             tp.n = n; tp.row_begin = r0; tp.row_end = r1; tp.d_pad = int(d_pad);
             tp.plan = tc_make_plan(n, r1 - r0, 1, d_pad, false);
             tp.plan.kl = 0;                                        // dense-output mode
-            tp.colp = colp; tp.pos4 = pos4;
+            tp.colp = colp; tp.pos4 = pos4; tp.norms_a = norms; tp.prods = 3;
             tp.gscale = pos ? lambda_g / lambda_h : 0.f;
             tp.exclude_self = 0;
             tp.dense_out = chunk; tp.dense_ld = n; tp.lambda_h = lambda_h; tp.dense_self = 1;
@@ -245,7 +245,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
 
 // ---- A1 / A2 dense output for large square inputs: the tensor-core kernel in dense-output mode ----------------
 // K[i, j] = exp(-lambda_h (|x_i|^2 + |x_j|^2 - 2 x_i.x_j) - lambda_g |p_i - p_j|^2) for one matrix against itself
-// (similarity_kernel.py:43-52, :122), the Gram product as 3xBF16 MMAs with FP32 accumulation.  13-20x the
+// (similarity_kernel.py:43-52, :122), the Gram product as three split-FP16 MMAs per k-step with FP32 accumulation.  13-20x the
 // throughput of hg_similarity_dense from a few thousand rows up, but its entries are within ~1.5e-5 relative of
 // float64, not 1e-5 (tests/test_gpu_parity.py::test_dense_tc_opt_in_accuracy): opt-in on the Python side.
 extern "C" int hg_similarity_dense_tc_workspace_bytes(int64_t n, int64_t d, size_t* bytes) {
@@ -278,7 +278,7 @@ extern "C" int hg_similarity_dense_tc(const float* feats, int64_t n, int64_t d, 
     float2* colp = reinterpret_cast<float2*>(ws);
     ws += al(size_t(n_pad) * 8);
     float4* pos4 = pos ? reinterpret_cast<float4*>(ws) : nullptr;
-    int rc = launch_split(feats, n, d, ops, norms, st);
+    int rc = launch_split(feats, n, d, ops, norms, st, true);      // dense-output operands: 8-bit hi halves
     if (rc != HG_OK) return rc;
     rc = launch_colparams(norms, pos, pos_dim, n, n_pad, HG_METRIC_GAUSSIAN, colp, pos4, st);
     if (rc != HG_OK) return rc;
@@ -286,7 +286,7 @@ extern "C" int hg_similarity_dense_tc(const float* feats, int64_t n, int64_t d, 
     tp.n = n; tp.row_begin = 0; tp.row_end = n; tp.d_pad = int(d_pad);
     tp.plan = tc_make_plan(n, n, 1, d_pad, false);
     tp.plan.kl = 0;                                            // dense-output mode
-    tp.colp = colp; tp.pos4 = pos4;
+    tp.colp = colp; tp.pos4 = pos4; tp.norms_a = norms; tp.prods = 3;
     tp.gscale = pos ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = 0;
     tp.dense_out = out; tp.dense_ld = ld_out; tp.lambda_h = lambda_h; tp.dense_self = 1;

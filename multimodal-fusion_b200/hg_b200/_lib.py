@@ -45,6 +45,7 @@ SIGNATURES = {
     "hg_split_operands": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "hg_knn_feature_workspace_bytes": (_i32, [_i64, _i64, _i32, _i64, _i64, _psz]),
     "hg_knn_feature_plan": (_i32, [_i64, _i64, _i32, _i64, _i64, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
+    "hg_knn_feature_products": (_i32, [_i64, _i64, _i32, _i64, _i64, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "hg_knn_feature": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i64, _i64, _i32, _i32,
                               _vp, _vp, _vp, _sz, _vp]),
     "hg_knn_feature_cos": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _f32, _f32, _i32, _i64, _i64, _i32, _i32,

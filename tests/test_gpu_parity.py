@@ -66,13 +66,22 @@ def test_split_operands():
     nbytes = lib.hg_operand_bytes(n, d)
     n_pad, d_pad = 512, 128
     assert nbytes == 2 * n_pad * d_pad * 2
-    ops_buf = torch.empty(nbytes // 2, dtype=torch.bfloat16, device="cuda")
+    ops_buf = torch.empty(nbytes // 2, dtype=torch.float16, device="cuda")
     norms = torch.empty(n, dtype=torch.float32, device="cuda")
     _lib.check(lib.hg_split_operands(xc.data_ptr(), n, d, ops_buf.data_ptr(), norms.data_ptr(), 0))
     torch.cuda.synchronize()
     blocks = ops_buf.view(n_pad, d_pad // 32, 2, 32).float().cpu().numpy()      # [row][k-block][hi | lo][32]
     rec = (blocks[:, :, 0, :] + blocks[:, :, 1, :]).reshape(n_pad, d_pad)
-    assert np.abs(rec[:n, :d] - x).max() <= 2.0 ** -16 * np.abs(x).max()
+    # every row was scaled by the power of two that puts its norm into [2^5, 2^6) (knn_tc.cuh op_scale)
+    nrm = norms.cpu().numpy()
+    e = (nrm.view(np.int32) >> 23) & 0xff
+    scale = np.ldexp(np.float32(1.0), 6 - ((e - 125) >> 1)).astype(np.float32)
+    scaled_norm = np.sqrt((rec[:n].astype(np.float64) ** 2).sum(1))
+    assert (scaled_norm >= 2.0 ** 5 * (1 - 1e-6)).all() and (scaled_norm < 2.0 ** 6).all()
+    # hi + lo carries 22 significant bits (2^-25 absolute on the subnormal grid)
+    err = np.abs(rec[:n, :d].astype(np.float64) - x.astype(np.float64) * scale[:, None])
+    assert (err <= 2.0 ** -22 * np.abs(x * scale[:, None]) + 2.0 ** -25).all()
+    assert (np.abs(blocks[:n, :, 1, :]) <= 2.0 ** -11 * np.abs(blocks[:n, :, 0, :]) + 2.0 ** -25).all()   # lo is the rounding residue of hi
     assert (rec[n:] == 0).all() and (rec[:, d:] == 0).all()
     np.testing.assert_allclose(norms.cpu().numpy(), (x.astype(np.float64) ** 2).sum(1), rtol=1e-6)
 

@@ -89,7 +89,16 @@ def test_row_ranges_and_small_slides_use_the_full_pass():
     with _env(HG_B200_TC_SYM=0):
         assert _plan(50000, 1024, 16)[0] == 0
     stride, flop = _plan(50000, 1024, 16)
-    assert stride == 16 and 0.5 < flop / (3 * 2.0 * 50000.0 ** 2 * 1024) < 0.6
+    lib = _lib.load_library()
+    main, pre = ctypes.c_int(0), ctypes.c_int(0)
+    _lib.check(lib.hg_knn_feature_products(50000, 1024, 16, 0, 50000, ctypes.byref(main), ctypes.byref(pre)))
+    assert (main.value, pre.value) == (2, 2)                           # symmetric passes: hi*hi + hi*lo
+    assert stride == 16 and 0.5 < flop / (main.value * 2.0 * 50000.0 ** 2 * 1024) < 0.6            # ~0.5 + 1/16
+    _lib.check(lib.hg_knn_feature_products(4096, 1024, 8, 0, 4096, ctypes.byref(main), ctypes.byref(pre)))
+    assert (main.value, pre.value) == (3, 0)                           # classic full pass: all three products
+    with _env(HG_B200_TC_SYM_PRODS=3):
+        _lib.check(lib.hg_knn_feature_products(50000, 1024, 16, 0, 50000, ctypes.byref(main), ctypes.byref(pre)))
+        assert (main.value, pre.value) == (3, 3)
 
 
 def test_bucket_overflow_falls_back_to_the_full_pass():
