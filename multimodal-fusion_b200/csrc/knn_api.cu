@@ -28,9 +28,9 @@ static int bucket_cap() {
     return TC_BKT_CAP;
 }
 
-// Tensor-core products per k-step (knn_tc.cuh tc_eps) of the symmetric passes: 2 by default -- the query rows
-// rounded to FP16, the columns whole -- which issues two thirds of the MMAs for a wider slack that the many short lists
-// and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3 keeps all three.  Classic, grouped and dense
+// Tensor-core products per k-step (knn_tc.cuh tc_eps) of the symmetric passes: 2 by default -- the columns
+// rounded to FP16, the query rows whole -- which issues two thirds of the MMAs and loads no lo half of a B tile, for a
+// wider slack that the many short lists and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3 keeps all three.  Classic, grouped and dense
 // launches always use three.  The threshold pre-pass uses the main pass's count, or one product with
 // HG_B200_TC_PRE_HI=1.
 static int sym_prods() {

@@ -10,8 +10,9 @@
 // interleaved per 32-wide k-block so that one 128-byte operand row carries 32 hi | 32 lo values.  The dot
 // product is accumulated in FP32 in TMEM from tcgen05 MMAs (kind::f16, FP16 operands) per k-step:
 //   3 products  hi*lo^T + lo*hi^T + hi*hi^T   (~2^-21 relative: classic, grouped and dense launches)
-//   2 products  hi*lo^T + hi*hi^T             (the A rows rounded to 11 bits, 2^-11 relative: symmetric passes,
-//                                              whose many short lists + buckets absorb the wider slack)
+//   2 products  lo*hi^T + hi*hi^T             (the B rows rounded to 11 bits, 2^-11 relative: symmetric passes,
+//                                              whose many short lists + buckets absorb the wider slack; their B
+//                                              tiles are loaded without the lo halves)
 // The epilogue turns the accumulator into a ranking score  a_j + b_j * dot
 // (+ g * |pos_i - pos_j|^2)  and keeps a per-row sorted list of the KL best
 // (score, column) pairs in registers.  The candidates are re-ranked exactly in
@@ -661,10 +662,10 @@ TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
 
 TcPlan tc_make_plan_sym_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     TcPlan pl{};
-    pl.cg = 1; pl.mc = 0; pl.cl = 1;
+    pl.cg = tc_sym_cta_group(d_pad); pl.mc = 0; pl.cl = pl.cg;
     pl.sym = 1;
     pl.n_rows = n_rows;
-    pl.num_rb = int(ceil_div(n_rows, TC_BM));
+    pl.num_rb = int(ceil_div(n_rows, TC_BM * pl.cl));
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(n, TC_BN));
     pl.kl = list_len(k);
@@ -800,7 +801,7 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
         if (e[0] && e[1]) { p.hint_a = pick(e[0], p.hint_a); p.hint_b = pick(e[1], p.hint_b); }
     }
     if (p.col_stride < 1) p.col_stride = 1;
-    HG_REQUIRE(!p.plan.sym || (p.plan.kl > 0 && p.col_stride == 1 && p.thr && (p.plan.cg == 1 || p.peer_chunk == 0) &&
+    HG_REQUIRE(!p.plan.sym || (p.plan.kl > 0 && p.col_stride == 1 && p.thr &&
                                ((p.peer_chunk == 0 && p.row_begin == 0 && p.row_end == p.n && p.bkt_cnt && p.bkt && p.ovf) ||
                                 (p.peer_chunk > 0 && p.ovf && p.row_begin % 256 == 0 && p.sblk_base == p.row_begin / 256))),
                HG_ERR_BAD_ARG, "tc_launch: incomplete symmetric-mode parameters");

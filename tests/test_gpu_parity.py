@@ -274,6 +274,46 @@ def test_knn_fallback_rescans_only_the_flagged_splits(sym, monkeypatch, capfd):
         np.testing.assert_allclose(val[r], d2[idx[r] - g0], rtol=1e-4, atol=0)
 
 
+@pytest.mark.parametrize("sym", ["0", "8"])
+def test_knn_cosine_is_blind_to_row_scales(sym, monkeypatch):
+    """The operands are FP16 halves of rows scaled by a per-row power of two (knn_tc.cuh op_scale): rows whose norms
+    span 2^-40 .. 2^40 must give the cosine lists of the unscaled rows -- classic pass (three products) and
+    symmetric pass (two products, forced at this size)."""
+    n, d, k = 6000, 200, 12
+    feats = synth.make_features(n, d, 81, "cosine")
+    rng = np.random.default_rng(81)
+    scaled = (feats * np.exp2(rng.integers(-40, 41, size=(n, 1))).astype(np.float32)).astype(np.float32)
+    monkeypatch.setenv("HG_B200_TC_SYM", sym)
+    idx0, val0 = ops.knn_feature(_cuda(feats), k, "cosine")
+    idx1, val1 = ops.knn_feature(_cuda(scaled), k, "cosine")
+    check_knn(idx1.cpu().numpy(), feats, k, "cosine")
+    same = (idx0 == idx1).all(1).float().mean().item()
+    assert same > 0.995, same                                      # the rest: near-ties that FP32 norms of scaled rows resolve differently
+    np.testing.assert_allclose(val1.cpu().numpy(), val0.cpu().numpy(), rtol=0, atol=2e-6)
+
+
+@pytest.mark.parametrize("sym", ["0", "8"])
+def test_knn_wide_dynamic_range_inside_rows_and_tiny_rows(sym, monkeypatch):
+    """Elements spanning twelve orders of magnitude inside a row (most of them land on FP16's subnormal grid after the
+    row scale, or vanish), rows with tiny norms next to large ones, and an all-zero row: the exact re-rank decides, so
+    the lists equal the float64 oracle's."""
+    n, d, k = 5000, 96, 8
+    rng = np.random.default_rng(82)
+    feats = synth.make_features(n, d, 82, "gaussian")
+    feats *= np.exp(rng.uniform(-14, 14, size=(1, d))).astype(np.float32)          # per-column scales e^-14 .. e^14
+    feats[::7] *= 1e-6                                                             # tiny rows
+    feats[11] = 0.0                                                                # a zero row
+    feats = feats.astype(np.float32)
+    monkeypatch.setenv("HG_B200_TC_SYM", sym)
+    idx, val = ops.knn_feature(_cuda(feats), k, "euclidean")
+    idx, val = idx.cpu().numpy(), val.cpu().numpy()
+    check_knn(idx, feats, k, "euclidean", max_near_ties=25)
+    x = feats.astype(np.float64)
+    for r in (0, 7, 11, 12, 4999):
+        d2 = ((x[idx[r].astype(np.int64)] - x[r]) ** 2).sum(1)
+        np.testing.assert_allclose(val[r], d2, rtol=RTOL, atol=1e-30)
+
+
 def test_knn_gaussian_with_positions():
     n, d, k = 3000, 128, 16
     feats, pos = synth.make_slide(n, d, 41, "gaussian")
