@@ -277,12 +277,13 @@ def test_knn_fallback_rescans_only_the_flagged_splits(sym, monkeypatch, capfd):
 @pytest.mark.parametrize("sym", ["0", "8"])
 def test_knn_cosine_is_blind_to_row_scales(sym, monkeypatch):
     """The operands are FP16 halves of rows scaled by a per-row power of two (knn_tc.cuh op_scale): rows whose norms
-    span 2^-40 .. 2^40 must give the cosine lists of the unscaled rows -- classic pass (three products) and
-    symmetric pass (two products, forced at this size)."""
+    span 2^-20 .. 2^40 must give the cosine lists of the unscaled rows -- classic pass (three products) and
+    symmetric pass (two products, forced at this size).  (Norms stay above the 1e-8 clamp of F.cosine_similarity,
+    preprocess_hypergraph.py:419, below which the reference's cosine stops being scale-free.)"""
     n, d, k = 6000, 200, 12
     feats = synth.make_features(n, d, 81, "cosine")
     rng = np.random.default_rng(81)
-    scaled = (feats * np.exp2(rng.integers(-40, 41, size=(n, 1))).astype(np.float32)).astype(np.float32)
+    scaled = (feats * np.exp2(rng.integers(-20, 41, size=(n, 1))).astype(np.float32)).astype(np.float32)
     monkeypatch.setenv("HG_B200_TC_SYM", sym)
     idx0, val0 = ops.knn_feature(_cuda(feats), k, "cosine")
     idx1, val1 = ops.knn_feature(_cuda(scaled), k, "cosine")
