@@ -603,6 +603,9 @@ static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
 TcPlan tc_make_plan(int64_t n, int64_t n_rows, int k, int64_t d_pad, bool lists) {
     TcPlan pl{};
     pl.cg = tc_cta_group();
+    // long classic launches over wide rows (the row block of a giant slide: 12.5k x 100k x 1536 runs 7.9 ms on CTA
+    // pairs against 9.1) are up against the same power / L2-feed limits as the symmetric pass; short ones are not
+    if (lists && !getenv("HG_B200_TC_CG") && d_pad >= 1024 && double(n) * double(n_rows) >= double(1 << 30)) pl.cg = 2;
     pl.mc = lists ? tc_multicast() : 0;
     pl.cl = (pl.cg == 2 || pl.mc) ? 2 : 1;
     pl.n_rows = n_rows;

@@ -9,7 +9,7 @@ from hg_b200 import _lib, ops, synth
 lib = _lib.load_library()
 ALL = {"c2": (50000, 1024, 16, False, None, 5), "c3": (100000, 1536, 16, True, None, 3), "n4096": (4096, 1024, 16, False, None, 30),
        "n16k": (16384, 1024, 16, False, None, 10), "c5rows": (100000, 1536, 16, False, (0, 12500), 3),
-       "c3d1024": (100000, 1024, 16, True, None, 3), "n10k": (10240, 1024, 16, False, None, 20), "n24k": (24576, 1024, 16, False, None, 10),
+       "c3d1024": (100000, 1024, 16, True, None, 3), "n10k": (10240, 1024, 16, False, None, 20), "n8192": (8192, 1024, 16, False, None, 20), "n24k": (24576, 1024, 16, False, None, 10),
        "n10kd256": (10240, 256, 16, False, None, 20), "c2d256": (50000, 256, 16, False, None, 8), "c2d512": (50000, 512, 16, False, None, 6)}
 args = sys.argv[1:]
 cases = ["c2", "c3"]
