@@ -455,7 +455,8 @@ km_segsum_kernel(const float* __restrict__ x, int64_t d, const uint32_t* __restr
     }
 }
 
-// centre cc <- mean of its members (empty clusters keep their centre); shift_part[cc] = |new - old|^2
+// centre cc <- mean of its members (empty clusters keep their centre here; km_relocate_kernel moves them);
+// shift_part[cc] = |new - old|^2
 __global__ void __launch_bounds__(128)
 km_finalize_det_kernel(const float* __restrict__ partial, const uint32_t* __restrict__ start, int split, int c,
                        int64_t d, float* __restrict__ centers, double* __restrict__ shift_part,
@@ -477,6 +478,88 @@ km_finalize_det_kernel(const float* __restrict__ partial, const uint32_t* __rest
     }
     const double tot = km_block_sum(local, sh);
     if (threadIdx.x == 0) shift_part[cc] = tot;
+}
+
+// scikit-learn's _relocate_empty_clusters_dense (cluster/_k_means_common.pyx): the e-th empty cluster takes the point
+// that lies e-th farthest from its own centre (distances of this iteration's assignment), and that point leaves
+// the mean of the cluster it was counted in.  One block; a no-op (one pass over `start`) unless a cluster is
+// empty, which is rare -- but without it a restart that loses a cluster keeps it lost, and the reference pipeline
+// (preprocess_hypergraph.py:164) raises "Cluster i is empty" on slides scikit-learn handles.
+constexpr int KM_RELOC_MAX_C = 4096;
+__global__ void __launch_bounds__(1024)
+km_relocate_kernel(const float* __restrict__ x, int64_t n, int64_t d, const int32_t* __restrict__ labels,
+                   float* __restrict__ d2, const uint32_t* __restrict__ start, int c, float* __restrict__ centers,
+                   double* __restrict__ shift_part, KmState* __restrict__ st) {
+    if (st->done) return;
+    __shared__ int s_any, s_far;
+    __shared__ float s_bv[32];
+    __shared__ int s_bi[32];
+    __shared__ double s_sum[32];
+    __shared__ unsigned short s_removed[KM_RELOC_MAX_C];
+    if (threadIdx.x == 0) s_any = 0;
+    for (int q = threadIdx.x; q < KM_RELOC_MAX_C; q += blockDim.x) s_removed[q] = 0;
+    __syncthreads();
+    for (int q = threadIdx.x; q < c; q += blockDim.x)
+        if (start[q + 1] == start[q]) s_any = 1;
+    __syncthreads();
+    if (!s_any) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int e = 0; e < c; ++e) {
+        if (start[e + 1] != start[e]) continue;                      // block-uniform
+        float bv = -1.f; int bi = 0x7fffffff;                       // largest distance, lowest index among equals
+        for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+            const float v = d2[i];
+            if (v > bv) { bv = v; bi = int(i); }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { s_bv[warp] = bv; s_bi[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            bv = s_bv[lane]; bi = s_bi[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) s_far = (bv >= 0.f) ? bi : -1;
+        }
+        __syncthreads();
+        const int far = s_far;
+        if (far < 0) break;                                           // every point already taken
+        const int old = labels[far];
+        int cnt_old = int(start[old + 1] - start[old]);
+        if (old < KM_RELOC_MAX_C) cnt_old -= int(s_removed[old]);
+        double local = 0.0;
+        for (int64_t j = threadIdx.x; j < d; j += blockDim.x) {
+            const float nv = x[int64_t(far) * d + j];
+            const float ov = centers[int64_t(e) * d + j];
+            local += double(nv - ov) * double(nv - ov);
+            centers[int64_t(e) * d + j] = nv;
+            if (cnt_old > 1) {
+                const double m = double(centers[int64_t(old) * d + j]);
+                centers[int64_t(old) * d + j] = float((m * double(cnt_old) - double(nv)) / double(cnt_old - 1));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+        if (lane == 0) s_sum[warp] = local;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 32; ++w) t += s_sum[w];
+            shift_part[e] = t;
+            d2[far] = -1.f;                                           // taken
+            if (old < KM_RELOC_MAX_C) s_removed[old] += 1;
+            st->moved = 1ull;                                         // the labels will change: not converged
+        }
+        __syncthreads();
+    }
 }
 
 // scikit-learn's two stopping tests: no label moved (strict convergence) or centre shift <= tol
@@ -850,6 +933,9 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
     a.a = x; a.b = centers; a.m = n; a.n = c; a.d = d; a.metric = HG_METRIC_EUCLIDEAN; a.k = 1;
     a.row_begin = 0; a.row_end = n; a.exclude_self = 0; a.out_idx = cur; a.out_val = d2;
 
+    // HG_B200_KMEANS_RELOCATE=0: empty clusters keep their centre (tests compare both behaviours)
+    const char* reloc_env = getenv("HG_B200_KMEANS_RELOCATE");
+    const bool relocate = !(reloc_env && atoi(reloc_env) == 0);
     for (int run = 0; run < n_init; ++run) {
         // ---- greedy k-means++ ----
         km_seed_first_kernel<<<1, 1, 0, st>>>(state, cand, center_idx, seed, run, n);
@@ -883,8 +969,9 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
                 if (vec) km_segsum_kernel<true><<<dim3(c, pl.split), 256, 0, st>>>(x, d, order, start, c, part, state);
                 else     km_segsum_kernel<false><<<dim3(c, pl.split), 256, 0, st>>>(x, d, order, start, c, part, state);
                 km_finalize_det_kernel<<<c, 128, 0, st>>>(part, start, pl.split, c, d, centers, shift_part, state);
+                if (relocate) km_relocate_kernel<<<1, 1024, 0, st>>>(x, n, d, cur, d2, start, c, centers, shift_part, state);
                 km_check_kernel<<<1, 1, 0, st>>>(shift_part, c, state);
-                count_launches(4);
+                count_launches(relocate ? 5 : 4);
             }
             HG_CHECK_LAUNCH();
             it += chunk;

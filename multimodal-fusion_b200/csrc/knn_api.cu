@@ -33,13 +33,21 @@ static int bucket_cap() {
 // wider slack that the many short lists and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3 keeps all three.  Classic, grouped and dense
 // launches always use three.  The threshold pre-pass uses the main pass's count, or one product with
 // HG_B200_TC_PRE_HI=1.
-static int sym_prods() {
+static int sym_prods(int64_t n) {
     if (const char* e = getenv("HG_B200_TC_SYM_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
-    return 2;
+    return n <= 160000 ? 2 : 3;          // giant slides: see sympart_prods below
 }
-static int prepass_prods() {
+static int prepass_prods(int64_t n) {
     if (const char* e = getenv("HG_B200_TC_PRE_HI")) if (atoi(e) != 0) return 1;
-    return sym_prods();
+    return sym_prods(n);
+}
+// The symmetric pass over the row block of a PARTITIONED slide keeps three products unless HG_B200_TC_SYMPART_PRODS=2:
+// such slides are the giant ones (C5: 250k rows), and the denser the slide the more columns fall inside the wider slack
+// of two products -- on C5's data 6-28 % of the rows had more than 32 of them (multi-round re-rank) and a few hundred
+// filled a list (exact fallback): 20 ms of fused kernel per rank instead of 28, but 64 ms per slide instead of 35.
+static int sympart_prods() {
+    if (const char* e = getenv("HG_B200_TC_SYMPART_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
+    return 3;
 }
 
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
@@ -114,7 +122,7 @@ extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begi
         return t;
     };
     const double per_tile = 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);           // one MMA sweep of a tile
-    const double flop = w.sym_stride > 0 ? (tiles_of(w.sym_plan) * sym_prods() + tiles_of(w.pre_plan) * prepass_prods()) * per_tile
+    const double flop = w.sym_stride > 0 ? (tiles_of(w.sym_plan) * sym_prods(n) + tiles_of(w.pre_plan) * prepass_prods(n)) * per_tile
                                          : tiles_of(w.plan) * w.plan.cl * 3.0 * per_tile;
     if (symmetric_stride) *symmetric_stride = w.sym_stride;
     if (mma_flop) *mma_flop = flop;
@@ -126,8 +134,8 @@ extern "C" int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_
     int rc = check_knn_args(n, d, k, row_begin, row_end);
     if (rc != HG_OK) return rc;
     const bool sym = tc_sym_stride(n, row_end - row_begin, k) > 0;
-    if (main_pass) *main_pass = sym ? sym_prods() : 3;
-    if (pre_pass) *pre_pass = sym ? prepass_prods() : 0;
+    if (main_pass) *main_pass = sym ? sym_prods(n) : 3;
+    if (pre_pass) *pre_pass = sym ? prepass_prods(n) : 0;
     return HG_OK;
 }
 
@@ -214,7 +222,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         pre.plan = w.pre_plan; pre.col_stride = w.sym_stride; pre.exclude_self = 0;
         const int cosine = (metric == HG_METRIC_COSINE) ? 1 : 0;
         pre.thr_rank = k; pre.thr_margin_cos = cosine; pre.norm_max = norm_max;
-        pre.prods = prepass_prods(); pre.pre_main_prods = sym_prods();
+        pre.prods = prepass_prods(n); pre.pre_main_prods = sym_prods(n);
         pre.thr_out = (w.pre_plan.splits == 1) ? thr : nullptr;     // several splits: lists, merged below
         rc = tc_launch(ops, w.n_pad, pre, st);
         if (rc != HG_OK) return rc;
@@ -224,7 +232,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
             if (rc != HG_OK) return rc;
         }
         TcParams sp = tp;
-        sp.prods = sym_prods();
+        sp.prods = sym_prods(n);
         sp.plan = w.sym_plan; sp.thr = thr; sp.bkt_cnt = bkt_cnt; sp.bkt = bkt; sp.bkt_cap = bucket_cap(); sp.ovf = ovf;
         rc = tc_launch(ops, w.n_pad, sp, st);
         if (rc != HG_OK) return rc;
@@ -243,7 +251,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
     rp.prods = 3;
-    if (sym) { rp.sym_plan = w.sym_plan; rp.sym_prods = sym_prods(); rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
+    if (sym) { rp.sym_plan = w.sym_plan; rp.sym_prods = sym_prods(n); rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rp.unc_cnt = ovf + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
     rp.more_cnt = ovf + 3; rp.more_rows = rp.unc_rows + w.plan.n_rows;
@@ -662,7 +670,7 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_a
     pre.plan = w.pre_plan; pre.col_stride = w.stride; pre.exclude_self = 0;
     pre.thr_rank = s->k; pre.thr_margin_cos = (s->metric == HG_METRIC_COSINE) ? 1 : 0; pre.norm_max = norm_max;
     pre.thr_out = thr_all;                                    // indexed by the global row
-    pre.prods = prepass_prods(); pre.pre_main_prods = sym_prods();
+    pre.prods = sympart_prods(); pre.pre_main_prods = sympart_prods();
     prof_begin(st);
     rc = tc_launch(ops, w.n_pad, pre, st);
     prof_end(st);
@@ -680,7 +688,7 @@ extern "C" int hg_knn_sympart_sweep(const hg_knn_part* s, const float* thr_all, 
                "hg_knn_sympart_sweep: bad partition (1..8 peers, 256-aligned chunks covering n)");
     char* ws = static_cast<char*>(workspace);
     TcParams sp = sympart_params(s, w, ws);
-    sp.plan = w.sym_plan; sp.prods = sym_prods();
+    sp.plan = w.sym_plan; sp.prods = sympart_prods();
     sp.thr = thr_all; sp.bkt_cap = bucket_cap(); sp.ovf = own_flags;
     sp.sblk_base = int(s->row_begin / 256);
     sp.peer_chunk = chunk;
@@ -725,7 +733,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;
     rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = s->k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
-    rp.prods = 3; rp.sym_prods = sym_prods();
+    rp.prods = 3; rp.sym_prods = sympart_prods();
     rp.sym_plan = w.sym_plan; rp.bkt_cnt = own_bkt_cnt; rp.bkt = static_cast<const uint2*>(own_bkt); rp.bkt_cap = bucket_cap();
     rp.ovf = any_overflow; rp.bkt_row0 = s->row_begin;
     rp.unc_cnt = reinterpret_cast<int32_t*>(ws + w.off_flags) + 2;
@@ -733,5 +741,13 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     rp.more_cnt = rp.unc_cnt + 1; rp.more_rows = rp.unc_rows + w.n_rows;
     rp.unc_part = reinterpret_cast<uint2*>(ws + w.off_unc_part);
     rp.exclude_self = s->exclude_self;
-    return rerank_launch(rp, st);
+    rc = rerank_launch(rp, st);
+    if (rc == HG_OK && getenv("HG_B200_TC_DEBUG")) {             // tuning aid: rows sent to the exact fallback (synchronises)
+        int h[2] = {0, 0};
+        HG_CHECK_CUDA(cudaStreamSynchronize(st));
+        HG_CHECK_CUDA(cudaMemcpy(h, rp.unc_cnt, 8, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "hg_b200 sympart rows [%lld, %lld): splits=%d, %d rows uncertified -> exact fallback, %d rows multi-round\n",
+                (long long)s->row_begin, (long long)s->row_end, w.sym_plan.splits, h[0], h[1]);
+    }
+    return rc;
 }

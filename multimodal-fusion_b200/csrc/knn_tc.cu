@@ -568,7 +568,7 @@ static int list_len(int k) {            // k plus slack for the exact re-rank, i
 // (hi + lo)); keep them under ~40 MB of the 126 MB L2.  Then the fewest column splits (a
 // multiple of cc) whose last round wastes the least.  `major` = row blocks or row-block pairs,
 // `tiles` = column tiles a major unit sweeps.
-static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
+static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad, int min_splits = 1) {
     const int workers = kNumSMs / pl.cl;               // CTAs or CTA pairs
     const int64_t a_block = int64_t(TC_BM * pl.cl) * d_pad * 4;
     int64_t a_mb = 40;
@@ -582,6 +582,7 @@ static void shape_plan(TcPlan& pl, int major, int tiles, int64_t d_pad) {
         if (rc > rc_cap && cc < cc_max) continue;
         for (int s = cc; s <= TC_MAX_SPLITS; s += cc) {
             if (s > tiles && s > cc) break;
+            if (s < min_splits && s + cc <= TC_MAX_SPLITS && s + cc <= tiles) continue;
             const int64_t units = int64_t(major) * s;
             // a unit is ceil(tiles / s) tiles long: count the padding of the last split as waste too
             const double fill = double(tiles) / double(ceil_div(tiles, s) * s);
@@ -645,6 +646,13 @@ TcPlan tc_make_plan_prepass(int64_t n, int k, int64_t d_pad, int stride) {
     return pl;
 }
 
+// Lists per row in a symmetric pass over a giant slide.  The wider slack of the two-product pass puts ~24 candidates
+// per row inside it at 100k rows and more the denser the slide; a list that fills up inside the slack sends its row to
+// the exact fallback, which at this scale costs milliseconds per thousand rows.  A row block of an 8-way partitioned
+// 250k slide would get 3 lists per row from the load balance alone (C5: 20 ms of fused kernel, 37 ms of fallback);
+// six spread the candidates thin enough.
+static int sym_min_splits(int64_t n) { return n >= 65536 ? 6 : 1; }
+
 // Symmetric plan over the full row range: the classic unit grid, of which each unit computes
 // only the tiles it owns (about every other one).
 TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
@@ -658,7 +666,7 @@ TcPlan tc_make_plan_sym(int64_t n, int k, int64_t d_pad) {
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(n, TC_BN));
     pl.kl = list_len(k);
-    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad);
+    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad, sym_min_splits(n));
     pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
     return pl;
 }
@@ -672,7 +680,7 @@ TcPlan tc_make_plan_sym_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad) {
     pl.num_u = pl.num_rb;
     pl.num_ct = int(ceil_div(n, TC_BN));
     pl.kl = list_len(k);
-    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad);
+    shape_plan(pl, pl.num_rb, pl.num_ct, d_pad, sym_min_splits(n));
     pl.ct_per_split = int(ceil_div(pl.num_ct, pl.splits));
     return pl;
 }

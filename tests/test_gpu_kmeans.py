@@ -177,3 +177,27 @@ def test_native_fit_matches_the_oracle_restatement(n, d, c, n_init, assign, monk
     assert abs(inertia - ref_inertia) <= 1e-4 * ref_inertia
     if (labels == ref_labels).all():
         np.testing.assert_allclose(centers.cpu().numpy(), ref_centers, rtol=1e-4, atol=1e-5)
+
+
+def test_empty_clusters_are_relocated_like_sklearn(monkeypatch):
+    """scikit-learn moves an empty cluster onto the point farthest from its centre (_relocate_empty_clusters_dense);
+    the device fit does the same, so a restart never ends with a lost cluster while there are at least c distinct
+    points -- which is what keeps aggregate_wsi_super_patches (preprocess_hypergraph.py:164 'Cluster i is empty') from
+    failing on slides the reference handles.  Many more centres than natural blobs: without the relocation
+    (HG_B200_KMEANS_RELOCATE=0) some of these fits do lose clusters."""
+    c, lost_without = 24, 0
+    problems = []
+    for seed in range(40):
+        rng = np.random.default_rng(500 + seed)
+        blobs = rng.standard_normal((6, 2)) * 4.0
+        x = (blobs[rng.integers(0, 6, 96)] + 0.05 * rng.standard_normal((96, 2))).astype(np.float32)
+        problems.append(x)
+    for x in problems:
+        labels, centers, inertia = kmeans(torch.from_numpy(x).cuda(), c, n_init=1, max_iter=100, seed=3)
+        assert len(np.unique(labels)) == c, "a cluster stayed empty"
+        assert np.isfinite(inertia) and np.isfinite(centers.cpu().numpy()).all()
+    monkeypatch.setenv("HG_B200_KMEANS_RELOCATE", "0")
+    for x in problems:
+        labels, _, _ = kmeans(torch.from_numpy(x).cuda(), c, n_init=1, max_iter=100, seed=3)
+        lost_without += int(len(np.unique(labels)) < c)
+    assert lost_without > 0, "the problems never lose a cluster: the test does not exercise the relocation"

@@ -1,6 +1,6 @@
 """A/B of environment switches of the fused kernel in one process, interleaved rounds, lists checked equal.
-    python tools/ab_env.py [--cases c2,c3] "" "HG_B200_TC_MC=1" "HG_B200_TC_SYM_PRODS=3" "HG_B200_TC_MC=1,HG_B200_TC_PAIR=0"
-Every argument is one setting (comma-separated NAME=VALUE pairs, "" = defaults); fused-kernel ms from the in-stream
+    python tools/ab_env.py [--cases c2,c3] "" "HG_B200_TC_MC=1" "HG_B200_TC_SYM_PRODS=3" "HG_B200_TC_MC=1;HG_B200_TC_PAIR=0"
+Every argument is one setting (NAME=VALUE pairs separated by ";", "" = defaults); fused-kernel ms from the in-stream
 profile events (hg_profile_*)."""
 import ctypes, json, os, statistics, sys, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -18,7 +18,7 @@ if args and args[0] == "--cases":
 settings = args or [""]
 names = set()
 for s in settings:
-    for kv in filter(None, s.split(",")): names.add(kv.split("=")[0])
+    for kv in filter(None, s.split(";")): names.add(kv.split("=")[0])
 for name in cases:
     n, d, k, pos, rows, reps = ALL[name]
     feats, p = synth.make_slide(n, d, 1, "gaussian")
@@ -30,7 +30,7 @@ for name in cases:
     for r in range(3):
         for s in settings:
             for nm in names: os.environ.pop(nm, None)
-            for kv in filter(None, s.split(",")):
+            for kv in filter(None, s.split(";")):
                 a, b = kv.split("="); os.environ[a] = b
             idx, _ = ops.knn_feature(x, k, "gaussian", **kw)
             if ref is None: ref = idx.clone()
