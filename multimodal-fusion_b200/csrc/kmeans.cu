@@ -562,6 +562,10 @@ km_relocate_kernel(const float* __restrict__ x, int64_t n, int64_t d, const int3
     }
 }
 
+__global__ void km_test_far_centre_kernel(float* __restrict__ centre, int64_t d) {
+    for (int64_t j = threadIdx.x; j < d; j += blockDim.x) centre[j] = 1.0e6f;
+}
+
 // scikit-learn's two stopping tests: no label moved (strict convergence) or centre shift <= tol
 __global__ void km_check_kernel(const double* __restrict__ shift_part, int c, KmState* __restrict__ st) {
     if (st->done) return;
@@ -936,6 +940,7 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
     // HG_B200_KMEANS_RELOCATE=0: empty clusters keep their centre (tests compare both behaviours)
     const char* reloc_env = getenv("HG_B200_KMEANS_RELOCATE");
     const bool relocate = !(reloc_env && atoi(reloc_env) == 0);
+    const bool test_far_seed = getenv("HG_B200_KMEANS_TEST_FAR_SEED") != nullptr;           // tests/test_gpu_kmeans.py only
     for (int run = 0; run < n_init; ++run) {
         // ---- greedy k-means++ ----
         km_seed_first_kernel<<<1, 1, 0, st>>>(state, cand, center_idx, seed, run, n);
@@ -951,6 +956,8 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
             count_launches(5);
         }
         km_gather_centers_kernel<<<c, 128, 0, st>>>(x, d, center_idx, centers);
+        if (test_far_seed && c > 1)        // test hook: the last centre starts far from every point, its cluster is empty
+            km_test_far_centre_kernel<<<1, 128, 0, st>>>(centers + int64_t(c - 1) * d, d);
         HG_CHECK_CUDA(cudaMemsetAsync(prev, 0xff, size_t(n) * 4, st));
         HG_CHECK_LAUNCH();
         count_launches(1);

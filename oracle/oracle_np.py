@@ -403,8 +403,8 @@ def kmeans_fit(features, n_clusters, n_init=10, max_iter=300, tol=1e-4, seed=42)
     shift is <= tolerance (`_kmeans_single_lloyd`), labels of the final centres, best restart by inertia.
     scikit-learn draws from numpy's MT19937; the CUDA path cannot share that stream, so the random numbers
     here are the counter-based ones of hg_kmeans_fit (kmeans.cu) -- which makes this restatement comparable
-    label for label with the device result.  Empty clusters keep their centre (scikit-learn relocates them;
-    neither happens on the test data).  Returns (labels int64 [n], centres float64 [k, d], inertia)."""
+    label for label with the device result.  Empty clusters keep their centre here (scikit-learn relocates them, and so
+    does hg_kmeans_fit -- km_relocate_kernel; it does not happen on the data this restatement is compared on).  Returns (labels int64 [n], centres float64 [k, d], inertia)."""
     x32 = np.ascontiguousarray(features, dtype=np.float32)
     n, d = x32.shape
     if n < n_clusters:

@@ -181,23 +181,27 @@ def test_native_fit_matches_the_oracle_restatement(n, d, c, n_init, assign, monk
 
 def test_empty_clusters_are_relocated_like_sklearn(monkeypatch):
     """scikit-learn moves an empty cluster onto the point farthest from its centre (_relocate_empty_clusters_dense);
-    the device fit does the same, so a restart never ends with a lost cluster while there are at least c distinct
-    points -- which is what keeps aggregate_wsi_super_patches (preprocess_hypergraph.py:164 'Cluster i is empty') from
-    failing on slides the reference handles.  Many more centres than natural blobs: without the relocation
-    (HG_B200_KMEANS_RELOCATE=0) some of these fits do lose clusters."""
-    c, lost_without = 24, 0
-    problems = []
-    for seed in range(40):
-        rng = np.random.default_rng(500 + seed)
-        blobs = rng.standard_normal((6, 2)) * 4.0
-        x = (blobs[rng.integers(0, 6, 96)] + 0.05 * rng.standard_normal((96, 2))).astype(np.float32)
-        problems.append(x)
-    for x in problems:
-        labels, centers, inertia = kmeans(torch.from_numpy(x).cuda(), c, n_init=1, max_iter=100, seed=3)
+    the device fit does the same, so a restart does not end with a lost cluster -- which is what keeps
+    aggregate_wsi_super_patches (preprocess_hypergraph.py:164 'Cluster i is empty') from failing on slides the
+    reference handles.  Lloyd started from k-means++ loses clusters too rarely to build a test on, so a test hook
+    starts the last centre far away from every point: its cluster is empty after the first assignment and stays empty
+    without the relocation (HG_B200_KMEANS_RELOCATE=0)."""
+    c = 12
+    monkeypatch.setenv("HG_B200_KMEANS_TEST_FAR_SEED", "1")
+    for seed in range(6):
+        x = synth.make_features(700, 24, 600 + seed, "gaussian")
+        xd = torch.from_numpy(x).cuda()
+        monkeypatch.setenv("HG_B200_KMEANS_RELOCATE", "0")
+        lost, _, inertia_lost = kmeans(xd, c, n_init=1, max_iter=100, seed=3)
+        assert len(np.unique(lost)) == c - 1                       # the hook bites: one cluster never gets a point
+        monkeypatch.delenv("HG_B200_KMEANS_RELOCATE")
+        labels, centers, inertia = kmeans(xd, c, n_init=1, max_iter=100, seed=3)
         assert len(np.unique(labels)) == c, "a cluster stayed empty"
-        assert np.isfinite(inertia) and np.isfinite(centers.cpu().numpy()).all()
-    monkeypatch.setenv("HG_B200_KMEANS_RELOCATE", "0")
-    for x in problems:
-        labels, _, _ = kmeans(torch.from_numpy(x).cuda(), c, n_init=1, max_iter=100, seed=3)
-        lost_without += int(len(np.unique(labels)) < c)
-    assert lost_without > 0, "the problems never lose a cluster: the test does not exercise the relocation"
+        cen = centers.cpu().numpy().astype(np.float64)
+        assert np.isfinite(cen).all() and np.isfinite(inertia)
+        assert inertia < inertia_lost                              # twelve centres fit better than eleven
+        # a fixed point of Lloyd: every centre is the mean of its members, every point sits with its nearest centre
+        x64 = x.astype(np.float64)
+        d2 = ((x64[:, None, :] - cen[None]) ** 2).sum(-1)
+        assert (d2[np.arange(len(x)), labels] <= d2.min(1) * (1 + 1e-5) + 1e-9).all()
+        assert abs(d2[np.arange(len(x)), labels].sum() - inertia) <= 1e-4 * inertia
