@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -10,6 +11,10 @@
 #include "../../include/hg_b200.h"
 
 namespace hg {
+
+// one half of a split operand: the bit pattern of an FP16 value (split.cu, knn_tc.cuh); buffers of them are only ever
+// written by the split kernel and read by TMA
+typedef unsigned short op16_t;
 
 // ---- error plumbing: no exceptions cross the C ABI -------------------------
 void set_error(const char* fmt, ...);
@@ -71,7 +76,7 @@ int64_t ops_row_elems(int64_t d_pad);
 // per-column epilogue parameters of the fused kernel: score = a_j + b_j * dot
 struct ColParam { float a, b; };
 
-int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
+int launch_split(const float* feats, int64_t n, int64_t d, op16_t* ops, float* sq_norms,
                  cudaStream_t st, bool dense = false);
 
 }  // namespace hg

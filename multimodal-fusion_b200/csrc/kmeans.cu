@@ -731,7 +731,7 @@ struct KmCarver {
 struct KmAssign {                 // everything one assignment pass needs
     SimArgs sim;                  // FP32 SIMT path (and the shapes / outputs of both paths)
     bool tc;
-    __nv_bfloat16 *ops_x, *ops_c;
+    op16_t *ops_x, *ops_c;
     float *norms_x, *norms_c, *norm_max;
     float2* colp;
     float* part_val; int32_t* part_idx;
@@ -905,8 +905,8 @@ extern "C" int hg_kmeans_fit(const float* x, int64_t n, int64_t d, int c, int n_
     KmAssign ka{};
     ka.tc = pl.tc;
     if (pl.tc) {
-        ka.ops_x = reinterpret_cast<__nv_bfloat16*>(cv.take<char>(hg_operand_bytes(n, d)));
-        ka.ops_c = reinterpret_cast<__nv_bfloat16*>(cv.take<char>(hg_operand_bytes(c, d)));
+        ka.ops_x = reinterpret_cast<op16_t*>(cv.take<char>(hg_operand_bytes(n, d)));
+        ka.ops_c = reinterpret_cast<op16_t*>(cv.take<char>(hg_operand_bytes(c, d)));
         ka.norms_x = cv.take<float>(pl.n_pad_x);
         ka.norms_c = cv.take<float>(pl.c_pad);
         ka.colp = cv.take<float2>(pl.c_pad);

@@ -187,7 +187,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG,
                "hg_knn_feature: workspace must be 1024-byte aligned");
     char* ws = static_cast<char*>(workspace);
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    op16_t* ops = reinterpret_cast<op16_t*>(ws + w.off_ops);
     float* norms = reinterpret_cast<float*>(ws + w.off_norms);
     float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
     float4* pos4 = pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
@@ -442,7 +442,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
                workspace_bytes, g.bytes);
     HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "knn_group: workspace must be 1024-byte aligned");
     char* ws = static_cast<char*>(workspace);
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + g.o_ops);
+    op16_t* ops = reinterpret_cast<op16_t*>(ws + g.o_ops);
     float* norms = reinterpret_cast<float*>(ws + g.o_norms);
     float2* colp = reinterpret_cast<float2*>(ws + g.o_colp);
     float4* pos4 = has_pos ? reinterpret_cast<float4*>(ws + g.o_pos4) : nullptr;
@@ -654,7 +654,7 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_a
     char* ws = static_cast<char*>(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool has_pos = part_has_pos(s);
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    op16_t* ops = reinterpret_cast<op16_t*>(ws + w.off_ops);
     float* norms = reinterpret_cast<float*>(ws + w.off_norms);
     float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
     HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 16, st));
@@ -699,7 +699,7 @@ extern "C" int hg_knn_sympart_sweep(const hg_knn_part* s, const float* thr_all, 
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     prof_begin(st);
-    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, sp, st);
+    rc = tc_launch(reinterpret_cast<op16_t*>(ws + w.off_ops), w.n_pad, sp, st);
     prof_end(st);
     return rc;
 }
@@ -721,7 +721,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     tp.plan = w.plan;
     tp.guard = any_overflow;
     prof_begin(st);
-    rc = tc_launch(reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops), w.n_pad, tp, st);
+    rc = tc_launch(reinterpret_cast<op16_t*>(ws + w.off_ops), w.n_pad, tp, st);
     prof_end(st);
     if (rc != HG_OK) return rc;
     RerankParams rp{};

@@ -732,7 +732,7 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 
 // row_stride > 1: a view of every row_stride-th operand row (the pre-pass column sample)
 // hi_only: the box is the first 64 bytes (32 hi values) of every 128-byte k-block, 64-byte swizzle
-static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, int64_t d_pad, int box_rows,
+static int make_tmap(CUtensorMap* tm, const op16_t* ops, int64_t n_pad, int64_t d_pad, int box_rows,
                      int row_stride = 1, bool hi_only = false) {
     auto enc = get_encode_fn();
     HG_REQUIRE(enc != nullptr, HG_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
@@ -742,7 +742,7 @@ static int make_tmap(CUtensorMap* tm, const __nv_bfloat16* ops, int64_t n_pad, i
     cuuint64_t strides[2] = {row_bytes * cuuint64_t(row_stride), row_bytes * cuuint64_t(n_pad)};
     cuuint32_t box[3] = {cuuint32_t(hi_only ? TC_BK : 2 * TC_BK), cuuint32_t(box_rows), 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__nv_bfloat16*>(ops), dims, strides, box, estr,
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<op16_t*>(ops), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, hi_only ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -791,7 +791,7 @@ static int launch_kl(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
 
 // ops_a / ops_b: operand buffers behind the query rows and the candidate columns -- the same buffer for a
 // slide's self-kNN, two buffers for a rectangular product (rows of one matrix against another's)
-static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops, int64_t n_pad,
+static int tc_launch_impl(const op16_t* ops_a, int64_t n_pad_a, const op16_t* ops, int64_t n_pad,
                           const TcParams& p_in, cudaStream_t st) {
     TcParams p = p_in;
     p.n_pad = n_pad;
@@ -856,14 +856,14 @@ static int tc_launch_impl(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __n
     return HG_ERR_UNSUPPORTED;
 }
 
-int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
+int tc_launch(const op16_t* ops, int64_t n_pad, const TcParams& p, cudaStream_t st) {
     return tc_launch_impl(ops, n_pad, ops, n_pad, p, st);
 }
 
 // Grouped launch: the units of several slides that share one operand buffer (TcUnit, knn_tc.cuh).  Classic list
 // mode on single CTAs; p carries colp / pos4 / gscale / exclude_self / part_val / part_idx / d_pad, and n = n_pad =
 // the rows of the whole group.
-int tc_launch_units(const __nv_bfloat16* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
+int tc_launch_units(const op16_t* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
                     const TcParams& p_in, cudaStream_t st) {
     HG_REQUIRE(unit_tab != nullptr && num_units > 0 && !p_in.thr_out && p_in.col_stride <= 1, HG_ERR_BAD_ARG,
                "tc_launch_units: bad argument");
@@ -879,7 +879,7 @@ int tc_list_len(int k) { return list_len(k); }
 
 // Rows of matrix A (p.row_begin .. p.row_end) against the p.n rows of matrix B: classic list mode only.
 // p.colp / p.n describe B; nothing is excluded by index.
-int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
+int tc_launch_rect(const op16_t* ops_a, int64_t n_pad_a, const op16_t* ops_b, int64_t n_pad_b,
                    const TcParams& p, cudaStream_t st) {
     HG_REQUIRE(ops_a != ops_b && !p.plan.sym && p.plan.cl == 1 && p.plan.kl > 0 && !p.exclude_self && !p.pos4 &&
                !p.thr_out && p.col_stride <= 1 && p.row_end <= n_pad_a,

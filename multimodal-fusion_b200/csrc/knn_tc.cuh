@@ -106,13 +106,13 @@ TcPlan tc_make_plan_sym_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad);
 TcPlan tc_make_plan_prepass_rows(int64_t n, int64_t n_rows, int k, int64_t d_pad, int stride);
 int tc_sym_stride(int64_t n, int64_t n_rows, int k);     // 0 = classic, else the pre-pass column stride
 constexpr int TC_BKT_CAP = 512;
-int tc_launch(const __nv_bfloat16* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
-int tc_launch_units(const __nv_bfloat16* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
+int tc_launch(const op16_t* ops, int64_t n_pad, const TcParams& p, cudaStream_t st);
+int tc_launch_units(const op16_t* ops, int64_t n_pad, int k, const TcUnit* unit_tab, int num_units,
                     const TcParams& p, cudaStream_t st);
 int tc_list_len(int k);
 // rectangular product (kmeans.cu): rows of A against the rows of another matrix B, classic list mode
 TcPlan tc_make_plan_rect(int64_t cols, int64_t n_rows, int k, int64_t d_pad);
-int tc_launch_rect(const __nv_bfloat16* ops_a, int64_t n_pad_a, const __nv_bfloat16* ops_b, int64_t n_pad_b,
+int tc_launch_rect(const op16_t* ops_a, int64_t n_pad_a, const op16_t* ops_b, int64_t n_pad_b,
                    const TcParams& p, cudaStream_t st);
 
 struct RrSlide {                 // one slide of a grouped launch, as the re-rank sees it
@@ -221,7 +221,7 @@ int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64
                      float* thr = nullptr, int32_t* bkt_cnt = nullptr, float* norm_max = nullptr);
 
 int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
-                       __nv_bfloat16* ops, float* sq_norms, cudaStream_t st);
+                       op16_t* ops, float* sq_norms, cudaStream_t st);
 int launch_colparams_group(const float* sq_norms, int pos_dim, int64_t n_pad, int metric, float2* colp, float4* pos4,
                            float* norm_max, const RrSlide* g_slides, const int32_t* g_blk2slide, cudaStream_t st);
 

@@ -48,12 +48,12 @@ __device__ __forceinline__ __half hi_half(float x, int hi8) {
 template <bool VEC4>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
-                  int64_t row_elems, __nv_bfloat16* __restrict__ ops, float* __restrict__ sq_norms,
+                  int64_t row_elems, op16_t* __restrict__ ops, float* __restrict__ sq_norms,
                   const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide, int hi8) {
     const int lane = threadIdx.x & 31;
     int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
     if (row >= n_pad) return;
-    __nv_bfloat16* out_row = ops + row * row_elems;
+    op16_t* out_row = ops + row * row_elems;
     float* norm_out = sq_norms != nullptr ? sq_norms + row : nullptr;
     if (g_slides != nullptr) {                   // grouped launch: operand row `row` is row (row - off) of its slide
         const RrSlide sl = g_slides[g_blk2slide[row >> 8]];
@@ -93,7 +93,7 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
             hv.y = uint32_t(__half_as_ushort(h2)) | (uint32_t(__half_as_ushort(h3)) << 16);
             lv.x = uint32_t(__half_as_ushort(l0)) | (uint32_t(__half_as_ushort(l1)) << 16);
             lv.y = uint32_t(__half_as_ushort(l2)) | (uint32_t(__half_as_ushort(l3)) << 16);
-            __nv_bfloat16* dst = hi_at(v << 2);
+            op16_t* dst = hi_at(v << 2);
             *reinterpret_cast<uint2*>(dst) = hv;
             *reinterpret_cast<uint2*>(dst + 32) = lv;
         }
@@ -116,7 +116,7 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
     if (lane == 0 && norm_out != nullptr) *norm_out = norm;
 }
 
-int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, float* sq_norms,
+int launch_split(const float* feats, int64_t n, int64_t d, op16_t* ops, float* sq_norms,
                  cudaStream_t st, bool dense) {
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
@@ -131,7 +131,7 @@ int launch_split(const float* feats, int64_t n, int64_t d, __nv_bfloat16* ops, f
 
 // the rows of a whole group of slides (device tables, knn_tc.cuh) in one launch; n_pad = the group's operand rows
 int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
-                       __nv_bfloat16* ops, float* sq_norms, cudaStream_t st) {
+                       op16_t* ops, float* sq_norms, cudaStream_t st) {
     const int64_t d_pad = ops_cols(d);
     const unsigned blocks = (unsigned)ceil_div(n_pad, SPLIT_WARPS);
     if (vec)
@@ -147,12 +147,12 @@ int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int6
 
 extern "C" size_t hg_operand_bytes(int64_t n, int64_t d) {
     if (n <= 0 || d <= 0) return 0;
-    return size_t(hg::ops_rows(n)) * size_t(hg::ops_row_elems(hg::ops_cols(d))) * sizeof(__nv_bfloat16);
+    return size_t(hg::ops_rows(n)) * size_t(hg::ops_row_elems(hg::ops_cols(d))) * sizeof(hg::op16_t);
 }
 
 extern "C" int hg_split_operands(const float* feats, int64_t n, int64_t d, void* ops, float* sq_norms,
                                  void* stream) {
     HG_REQUIRE(feats && ops && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_split_operands: bad argument");
-    return hg::launch_split(feats, n, d, static_cast<__nv_bfloat16*>(ops), sq_norms,
+    return hg::launch_split(feats, n, d, static_cast<hg::op16_t*>(ops), sq_norms,
                             static_cast<cudaStream_t>(stream), false);
 }

@@ -199,7 +199,7 @@ extern "C" int hg_similarity_stats_streaming(const float* feats, int64_t n, int6
     HG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, HG_ERR_BAD_ARG, "workspace must be 1024-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     char* ws = static_cast<char*>(workspace);
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws + w.off_ops);
+    op16_t* ops = reinterpret_cast<op16_t*>(ws + w.off_ops);
     float* norms = reinterpret_cast<float*>(ws + w.off_norms);
     float2* colp = reinterpret_cast<float2*>(ws + w.off_colp);
     float4* pos4 = pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
@@ -271,7 +271,7 @@ extern "C" int hg_similarity_dense_tc(const float* feats, int64_t n, int64_t d, 
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     char* ws = static_cast<char*>(workspace);
     auto al = [](size_t b) { return (b + 1023) & ~size_t(1023); };
-    __nv_bfloat16* ops = reinterpret_cast<__nv_bfloat16*>(ws);
+    op16_t* ops = reinterpret_cast<op16_t*>(ws);
     ws += al(hg_operand_bytes(n, d));
     float* norms = reinterpret_cast<float*>(ws);
     ws += al(size_t(n_pad) * 4);

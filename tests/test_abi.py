@@ -67,6 +67,24 @@ def test_python_surface_mirrors_reference():
     assert all(p.kind is inspect.Parameter.KEYWORD_ONLY for p in params[8:])      # extras never shift the reference's arguments
 
 
+def test_products_per_pass_by_shape(monkeypatch):
+    """host-side plan logic (no GPU): two MMAs per product in the symmetric passes of one GPU up to 160k rows, three
+    in classic launches and on giant slides; the issued-MMA count follows"""
+    lib = _lib.load_library()
+    main, pre = ctypes.c_int(-1), ctypes.c_int(-1)
+    for n, d, k, r1, want in ((50_000, 1024, 16, 50_000, (2, 2)), (100_000, 1536, 16, 100_000, (2, 2)),
+                              (250_000, 1536, 16, 250_000, (3, 3)), (4096, 1024, 8, 4096, (3, 0)),
+                              (100_000, 1536, 16, 12_500, (3, 0))):
+        assert lib.hg_knn_feature_products(n, d, k, 0, r1, ctypes.byref(main), ctypes.byref(pre)) == 0
+        assert (main.value, pre.value) == want, (n, d, k, r1)
+    stride, flop2, flop3 = ctypes.c_int(0), ctypes.c_double(0), ctypes.c_double(0)
+    assert lib.hg_knn_feature_plan(50_000, 1024, 16, 0, 50_000, ctypes.byref(stride), ctypes.byref(flop2)) == 0
+    monkeypatch.setenv("HG_B200_TC_SYM_PRODS", "3")
+    assert lib.hg_knn_feature_plan(50_000, 1024, 16, 0, 50_000, ctypes.byref(stride), ctypes.byref(flop3)) == 0
+    assert stride.value == 16 and abs(flop3.value / flop2.value - 1.5) < 1e-9
+    assert lib.hg_knn_feature_products(1, 16, 4, 0, 1, ctypes.byref(main), ctypes.byref(pre)) == _lib.HG_ERR_BAD_ARG
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
 def test_no_cpu_fallback():
     with pytest.raises(RuntimeError, match="no CPU fallback"):

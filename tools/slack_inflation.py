@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""would a 1xBF16 (hi*hi only) MAIN pass pay?  Its scores are off by up to TC_SLACK_HI * scale
-(2^-8 + 2^-11, knn_tc.cuh) instead of TC_SLACK_3X * scale (2^-11), scale = |x_i|^2 + max |x|^2, so every column whose
+"""VERDICT r01 item 8(a), asked when the operands were split BF16: would a 1xBF16 (hi*hi only) MAIN pass pay?  Its
+scores are off by up to SLACK_HI * scale (2^-8 + 2^-11, the constant of that time) instead of SLACK_3X * scale (2^-11),
+scale = |x_i|^2 + max |x|^2, so every column whose
 exact score lies within that slack of the row's k-th best has to be kept as a candidate and re-ranked exactly.
 This counts those columns per row with float64 scores (torch on the GPU, sampled rows), for both slacks:
     python tools/slack_inflation.py [c2|c3]"""
