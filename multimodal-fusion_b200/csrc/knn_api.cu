@@ -45,6 +45,13 @@ static int prepass_prods(int64_t n) {
 // such slides are the giant ones (C5: 250k rows), and the denser the slide the more columns fall inside the wider slack
 // of two products -- on C5's data 6-28 % of the rows had more than 32 of them (multi-round re-rank) and a few hundred
 // filled a list (exact fallback): 20 ms of fused kernel per rank instead of 28, but 64 ms per slide instead of 35.
+// Classic launches over SMALL slides (one or two lists per row): two products pay when the slide is sparse enough for
+// the wider slack to stay inside the lists -- see classic_prods() at its call sites.  HG_B200_TC_CLASSIC_PRODS=2/3.
+static int classic_prods(int64_t n) {
+    if (const char* e = getenv("HG_B200_TC_CLASSIC_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
+    (void)n;
+    return 3;
+}
 static int sympart_prods() {
     if (const char* e = getenv("HG_B200_TC_SYMPART_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
     return 3;
@@ -208,7 +215,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     TcParams tp{};
     tp.n = n; tp.row_begin = row_begin; tp.row_end = row_end; tp.d_pad = int(w.d_pad);
     tp.plan = w.plan; tp.colp = colp; tp.pos4 = pos4;
-    tp.norms_a = norms; tp.prods = 3;
+    tp.norms_a = norms; tp.prods = sym ? 3 : classic_prods(n);      // (sym: the guarded fallback pass)
     tp.gscale = (pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
@@ -250,7 +257,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
     rp.cols_per_split = int64_t(w.plan.ct_per_split) * TC_BN;
     rp.k = k; rp.out_idx = out_idx; rp.out_val = out_val; rp.out_cos = out_cos;
-    rp.prods = 3;
+    rp.prods = tp.prods;
     if (sym) { rp.sym_plan = w.sym_plan; rp.sym_prods = sym_prods(n); rp.bkt_cnt = bkt_cnt; rp.bkt = bkt; rp.bkt_cap = bucket_cap(); rp.ovf = ovf; }
     rp.unc_cnt = ovf + 2;
     rp.unc_rows = reinterpret_cast<int32_t*>(ws + w.off_unc_rows);
@@ -513,7 +520,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     TcParams tp{};
     tp.d_pad = int(g.d_pad);
     tp.colp = colp; tp.pos4 = pos4;
-    tp.norms_a = norms; tp.prods = 3;
+    tp.norms_a = norms; tp.prods = classic_prods(g.n_pad);
     tp.gscale = (has_pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + g.o_pval);
@@ -534,7 +541,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = has_pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = max_splits; rp.kl = g.kl; rp.n_rows = g.n_pad; rp.row_begin = 0;
-    rp.k = k; rp.prods = 3;
+    rp.k = k; rp.prods = tp.prods;
     const float* any_cos = nullptr;
     for (int i = 0; i < num; ++i) if (slides[i].out_cos != nullptr) any_cos = slides[i].out_cos;
     rp.out_cos = const_cast<float*>(any_cos);                       // only selects the kernel variant; per slide in the kernel
@@ -551,9 +558,18 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
         HG_CHECK_CUDA(cudaEventRecord(swept, st));
         HG_CHECK_CUDA(cudaStreamWaitEvent(st_rerank, swept, 0));
         HG_CHECK_CUDA(cudaEventDestroy(swept));                    // released once the wait has been satisfied
-        return rerank_launch(rp, st_rerank);
+        rc = rerank_launch(rp, st_rerank);
+    } else {
+        rc = rerank_launch(rp, st);
     }
-    return rerank_launch(rp, st);
+    if (rc == HG_OK && getenv("HG_B200_TC_DEBUG")) {             // tuning aid: rows sent to the exact fallback (synchronises)
+        int h[4] = {0, 0, 0, 0};
+        HG_CHECK_CUDA(cudaDeviceSynchronize());
+        HG_CHECK_CUDA(cudaMemcpy(h, flags, 16, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "hg_b200 group of %d slides, %lld operand rows: %d rows uncertified -> exact fallback, %d rows multi-round\n",
+                num, (long long)g.n_pad, h[2], h[3]);
+    }
+    return rc;
 }
 
 }  // namespace hg
