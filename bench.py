@@ -443,6 +443,8 @@ def run_ours(args):
                 "achieved": achieved, "peak": bf16 / per, "unit": "TFLOP/s",
                 "frac": (achieved / (bf16 / per)) if achieved else None, "traffic": traffic,
                 "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step, "mma_per_product": prods.value,
+                # continuity with the lines of rounds 1-2 before the two-product pass (peak / 3, SURVEY 8(d)'s 3xBF16 figure)
+                "frac_vs_3_product_roofline": (achieved / (bf16 / 3.0)) if achieved else None,
                 "peak_source": (f"{peaks['source']} bf16_tflops{'_sustained' if sustained else ''} (kind::f16 MMAs: FP16 operands "
                                 f"run at the BF16 rate) / {prods.value} MMAs per product "
                                 f"(burst {peaks['bf16']:.0f}, sustained {peaks['bf16_sustained']:.0f} TFLOP/s); "
