@@ -70,6 +70,25 @@ def test_symmetric_equals_full_pass(n, d, k, metric, with_pos):
               lambda_h=1.0, lambda_g=1.0 / 128 if with_pos else 0.0)
 
 
+@pytest.mark.parametrize("n,d,k,metric,with_pos", [(12_000, 1024, 16, "gaussian", True), (9_500, 1100, 8, "cosine", False)])
+def test_symmetric_variants_give_the_same_lists(n, d, k, metric, with_pos):
+    """The symmetric pass comes as single CTAs or CTA pairs (cta_group::2, the default from D = 1024 up), with two or
+    three tensor-core products per k-step, and B tiles with or without lo halves: the exact re-rank decides, so every
+    variant returns the lists of the classic full pass bit for bit."""
+    feats, pos = synth.make_slide(n, d, 17, "cosine" if metric == "cosine" else "gaussian")
+    kw = dict(positions=_cuda(pos), lambda_h=1.0, lambda_g=1.0 / 128) if with_pos else {}
+    x = _cuda(feats)
+    with _env(HG_B200_TC_SYM=0):
+        ref_i, ref_v = ops.knn_feature(x, k, metric, **kw)
+    for env in (dict(), dict(HG_B200_TC_SYM_CG=1), dict(HG_B200_TC_SYM_CG=2), dict(HG_B200_TC_SYM_PRODS=3),
+                dict(HG_B200_TC_SYM_CG=1, HG_B200_TC_SYM_PRODS=3), dict(HG_B200_TC_B_HI=0), dict(HG_B200_TC_MC=1, HG_B200_TC_SYM_CG=1),
+                dict(HG_B200_TC_PRE_HI=1)):
+        with _env(**env):
+            assert _plan(n, d, k)[0] == 8                          # symmetric by default at this size
+            idx, val = ops.knn_feature(x, k, metric, **kw)
+        assert torch.equal(idx, ref_i) and torch.equal(val, ref_v), env
+
+
 @pytest.mark.parametrize("cc", [2, 4])
 def test_prepass_with_column_splits(cc):
     """Large D: the threshold pre-pass runs 2 or 4 column splits side by side and thr_merge_kernel
