@@ -77,6 +77,6 @@ int64_t ops_row_elems(int64_t d_pad);
 struct ColParam { float a, b; };
 
 int launch_split(const float* feats, int64_t n, int64_t d, op16_t* ops, float* sq_norms,
-                 cudaStream_t st, bool dense = false);
+                 cudaStream_t st, bool dense = false, float* rho_max = nullptr);
 
 }  // namespace hg

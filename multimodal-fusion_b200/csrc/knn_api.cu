@@ -79,7 +79,7 @@ static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool h
     const size_t part = size_t(max_splits) * size_t(w.plan.n_rows) * size_t(w.plan.kl);
     w.off_pval = take(part * 4);
     w.off_pidx = take(part * 4);
-    w.off_ovf = take(16);                       // overflow flag, largest squared norm, uncertified-row counter
+    w.off_ovf = take(32);                       // overflow flag, largest squared norm, uncertified-row counters, measured rho
     w.off_unc_rows = take(size_t(w.plan.n_rows) * 12);       // uncertified rows | rows of the multi-round re-rank | split masks
     w.off_unc_part = take(rerank_unc_part_bytes(w.plan.n_rows, k));
     if (w.sym_stride > 0) {
@@ -205,10 +205,11 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     int* ovf = reinterpret_cast<int*>(ws + w.off_ovf);
     uint2* bkt = sym ? reinterpret_cast<uint2*>(ws + w.off_bkt) : nullptr;
 
-    rc = launch_split(feats, n, d, ops, norms, st);
-    if (rc != HG_OK) return rc;
     float* norm_max = reinterpret_cast<float*>(ws + w.off_ovf) + 1;
-    HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 16, st));
+    float* rho_max = reinterpret_cast<float*>(ws + w.off_ovf) + 4;      // largest rounding residual of an operand row (tc_eps)
+    HG_CHECK_CUDA(cudaMemsetAsync(ovf, 0, 32, st));
+    rc = launch_split(feats, n, d, ops, norms, st, false, rho_max);
+    if (rc != HG_OK) return rc;
     rc = launch_colparams(norms, pos, pos_dim, n, w.n_pad, metric, colp, pos4, st, thr, bkt_cnt, norm_max);
     if (rc != HG_OK) return rc;
 
@@ -216,6 +217,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
     tp.n = n; tp.row_begin = row_begin; tp.row_end = row_end; tp.d_pad = int(w.d_pad);
     tp.plan = w.plan; tp.colp = colp; tp.pos4 = pos4;
     tp.norms_a = norms; tp.prods = sym ? 3 : classic_prods(n);      // (sym: the guarded fallback pass)
+    tp.rho_max = rho_max;
     tp.gscale = (pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
@@ -235,7 +237,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
         if (rc != HG_OK) return rc;
         if (w.pre_plan.splits > 1) {
             rc = thr_merge_launch(pre.part_val, w.pre_plan.splits, n, w.pre_plan.kl, k, colp, norm_max, cosine,
-                                  tc_slack(w.d_pad, pre.prods, pre.pre_main_prods), thr, st);
+                                  w.d_pad, pre.prods, pre.pre_main_prods, rho_max, thr, st);
             if (rc != HG_OK) return rc;
         }
         TcParams sp = tp;
@@ -251,7 +253,7 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
 
     RerankParams rp{};
     rp.feats = feats; rp.n = n; rp.d = d; rp.pos = pos; rp.pos_dim = pos_dim;
-    rp.sq_norms = norms; rp.norm_max = norm_max;
+    rp.sq_norms = norms; rp.norm_max = norm_max; rp.rho_max = rho_max;
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.plan.n_rows; rp.row_begin = row_begin;
@@ -278,10 +280,13 @@ extern "C" int hg_knn_feature_cos(const float* feats, int64_t n, int64_t d,
                 double(sum) / double(n), mx, h_ovf);
     }
     if (rc == HG_OK && getenv("HG_B200_TC_DEBUG")) {             // tuning aid: rows sent to the exact fallback (synchronises)
-        int h_unc = 0;
+        int h_unc[2] = {0, 0};
+        float h_rho = 0.f;
         HG_CHECK_CUDA(cudaStreamSynchronize(st));
-        HG_CHECK_CUDA(cudaMemcpy(&h_unc, ovf + 2, 4, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "hg_b200 rerank: %d of %lld rows uncertified -> exact fallback\n", h_unc, (long long)(row_end - row_begin));
+        HG_CHECK_CUDA(cudaMemcpy(h_unc, ovf + 2, 8, cudaMemcpyDeviceToHost));
+        HG_CHECK_CUDA(cudaMemcpy(&h_rho, rho_max, 4, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "hg_b200 rerank: %d of %lld rows uncertified -> exact fallback, %d rows multi-round, rho = %.3g (2^-11 = 4.88e-4)\n",
+                h_unc[0], (long long)(row_end - row_begin), h_unc[1], double(h_rho));
     }
     return rc;
 }
@@ -621,7 +626,7 @@ static int sympart_plan(const hg_knn_part* s, SymPartWs* w) {
     const size_t part = size_t(max_splits) * size_t(w->n_rows) * size_t(w->plan.kl);
     w->off_pval = take(part * 4);
     w->off_pidx = take(part * 4);
-    w->off_flags = take(16);
+    w->off_flags = take(32);                    // [guard, largest squared norm, uncertified rows, multi-round rows, measured rho]
     w->off_unc_rows = take(size_t(w->n_rows) * 12);
     w->off_unc_part = take(rerank_unc_part_bytes(w->n_rows, s->k));
     w->bytes = off;
@@ -644,6 +649,7 @@ static TcParams sympart_params(const hg_knn_part* s, const SymPartWs& w, char* w
     tp.colp = reinterpret_cast<float2*>(ws + w.off_colp);
     tp.pos4 = has_pos ? reinterpret_cast<float4*>(ws + w.off_pos4) : nullptr;
     tp.norms_a = reinterpret_cast<float*>(ws + w.off_norms); tp.prods = 3;
+    tp.rho_max = reinterpret_cast<float*>(ws + w.off_flags) + 4;
     tp.gscale = (has_pos && s->lambda_h > 0.f) ? s->lambda_g / s->lambda_h : 0.f;
     tp.exclude_self = s->exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + w.off_pval);
@@ -673,10 +679,11 @@ extern "C" int hg_knn_sympart_prepass(const hg_knn_part* s, const float* feats_a
     op16_t* ops = reinterpret_cast<op16_t*>(ws + w.off_ops);
     float* norms = reinterpret_cast<float*>(ws + w.off_norms);
     float* norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
-    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 16, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(ws + w.off_flags, 0, 32, st));
     HG_CHECK_CUDA(cudaMemsetAsync(own_flags, 0, 8, st));
     HG_CHECK_CUDA(cudaMemsetAsync(own_bkt_cnt, 0, size_t(w.n_rows) * 4, st));
-    rc = launch_split(feats_all, s->n, s->d, ops, norms, st);
+    // every rank splits ALL rows itself, so the measured rounding residual (rho) is the same number on every rank
+    rc = launch_split(feats_all, s->n, s->d, ops, norms, st, false, reinterpret_cast<float*>(ws + w.off_flags) + 4);
     if (rc != HG_OK) return rc;
     TcParams tp = sympart_params(s, w, ws);
     rc = launch_colparams(norms, has_pos ? s->pos : nullptr, s->pos_dim, s->n, w.n_pad, s->metric,
@@ -744,6 +751,7 @@ extern "C" int hg_knn_sympart_finish(const hg_knn_part* s, const float* feats_al
     rp.feats = feats_all; rp.n = s->n; rp.d = s->d; rp.pos = has_pos ? s->pos : nullptr; rp.pos_dim = s->pos_dim;
     rp.sq_norms = reinterpret_cast<float*>(ws + w.off_norms);
     rp.norm_max = reinterpret_cast<float*>(ws + w.off_flags) + 1;
+    rp.rho_max = reinterpret_cast<float*>(ws + w.off_flags) + 4;
     rp.metric = s->metric; rp.lambda_h = s->lambda_h; rp.lambda_g = has_pos ? s->lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = w.plan.splits; rp.kl = w.plan.kl; rp.n_rows = w.n_rows; rp.row_begin = s->row_begin;

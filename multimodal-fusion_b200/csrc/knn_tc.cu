@@ -520,7 +520,8 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant_
                     // pass's score the bound will be compared with; Euclidean / Gaussian scores n_j - 2 dot scale
                     // with n_i + n_max, cosine scores -dot / |x_j| with |x_i|
                     const float scale = (p.thr_margin_cos != 0) ? 1.f / fmaxf(fabsf(tb), 1e-30f) : ta + __ldg(p.norm_max);
-                    p.thr_out[row] = t + tc_slack(p.d_pad, p.prods, p.pre_main_prods) * scale + TC_SLACK_REL * fabsf(t);
+                    const float rho = p.rho_max != nullptr ? __ldg(p.rho_max) : TC_RHO_WORST;
+                    p.thr_out[row] = t + tc_slack(p.d_pad, p.prods, p.pre_main_prods, rho) * scale + TC_SLACK_REL * fabsf(t);
                 } else {
                     const int64_t o = ui.list_off + (row - ui.list_row0) * KL;
 #pragma unroll

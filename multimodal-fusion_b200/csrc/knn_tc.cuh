@@ -73,6 +73,7 @@ struct TcParams {
     // power of two op_scale(norm) before its FP16 split, the epilogue undoes both scales.  norms_b null = norms_a.
     const float* norms_a;
     const float* norms_b;
+    const float* rho_max;       // measured rounding residual of the operand rows (tc_eps), or null = worst case
     int thr_margin_cos;         // error slack added to thr_out scales with |x_i| (cosine) or n_i + norm_max
     const float* norm_max;      // largest squared row norm
     // symmetric mode: transposed candidates (column j gets row i) with score < thr[j] are
@@ -142,6 +143,7 @@ struct RerankParams {
     int64_t bkt_row0;            // bkt_cnt / bkt are indexed by (row - bkt_row0): 0, or row_begin for a partitioned slide
     int k;
     int prods, sym_prods;        // tensor-core products per k-step behind the classic lists / the symmetric lists + buckets
+    const float* rho_max;        // measured rounding residual of the operand rows (tc_eps), or null = worst case
     int32_t* out_idx; float* out_val;
     float* out_cos;              // optional [n_rows, k]: cos(x_row, x_idx) of every list entry (edge weights)
     // certification fallback (rerank.cu): rows whose lists cannot vouch for the exact top-k are appended to
@@ -162,7 +164,8 @@ constexpr int RR_UNC_SLICES = 8;
 inline size_t rerank_unc_part_bytes(int64_t n_rows, int k) { return size_t(n_rows) * RR_UNC_SLICES * size_t(k) * 8; }
 int rerank_launch(const RerankParams& p, cudaStream_t st);
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
-                     const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st);
+                     const float* norm_max, int cosine, int64_t d_pad, int prods_pre, int prods_main, const float* rho_max,
+                     float* thr, cudaStream_t st);
 // ---- operand format and the guaranteed error of a tensor-core score ---------------------------------------------
 // An operand row x is scaled by s = op_scale(|x|^2), a power of two that puts |s x| into [2^5, 2^6), and split into
 // two FP16 values per element: hi = fp16(s x), lo = fp16(s x - hi).  Every element is below 2^6 (no overflow);
@@ -203,14 +206,20 @@ __host__ __device__ inline float op_inv_scale(float sq_norm) { return pow2f(-op_
 // -dot / |x_j| is off by eps |x_i|.  Two scores of one row therefore compare correctly once they differ by more than
 // (eps_a + eps_b) * (n_i + n_max) resp. (eps_a + eps_b) * |x_i| -- tc_slack() -- plus the FP32 rounding of the score
 // arithmetic itself (fma, spatial term), which is relative to the score: TC_SLACK_REL * |score| on top.
-__host__ __device__ inline float tc_eps(int64_t d_pad, int prods) {
-    const float u = 4.8828125e-4f, u2 = 2.3841858e-7f;                 // 2^-11, 2^-22
+// `rho` = the largest ||s x - hi|| / ||s x|| over the operand rows, MEASURED by the split kernel (split.cu; at most u, and
+// ~0.3 u on real rows because rounding errors do not line up): Cauchy-Schwarz with the actual residual norm instead of
+// its worst case, still a guarantee.  It replaces u in the terms that come from rounding a whole operand to its hi half
+// (two products: one operand; one product: both).  Pass TC_RHO_WORST when no measurement is at hand.
+constexpr float TC_RHO_WORST = 4.8828125e-4f;       // u = 2^-11
+__host__ __device__ inline float tc_eps(int64_t d_pad, int prods, float rho) {
+    const float u2 = 2.3841858e-7f;                                    // 2^-22
     if (prods <= 0) prods = 3;
-    const float repr = (prods >= 3 ? 3.f * u2 : prods == 2 ? u + u2 : 2.f * u + u2) + 1.8627e-9f * sqrtf(float(d_pad));
+    rho = fminf(fmaxf(rho, 0.f), TC_RHO_WORST) * 1.01f + 1e-7f;        // FP32 rounding of the measurement itself
+    const float repr = (prods >= 3 ? 3.f * u2 : prods == 2 ? rho + u2 : 2.f * rho + u2) + 1.8627e-9f * sqrtf(float(d_pad));
     return repr + float(prods * (d_pad / 16)) * u2;
 }
-__host__ __device__ inline float tc_slack(int64_t d_pad, int prods_a, int prods_b) {
-    return tc_eps(d_pad, prods_a) + tc_eps(d_pad, prods_b);
+__host__ __device__ inline float tc_slack(int64_t d_pad, int prods_a, int prods_b, float rho = TC_RHO_WORST) {
+    return tc_eps(d_pad, prods_a, rho) + tc_eps(d_pad, prods_b, rho);
 }
 constexpr float TC_SLACK_REL = 4.8e-7f;           // 2^-21
 

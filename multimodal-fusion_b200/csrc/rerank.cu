@@ -218,7 +218,8 @@ rerank_kernel(const RerankParams p) {
     // candidate cannot enter the exact top-k, and neither can any later one.
     const float ni = c.sq_norms[row];
     const int prods = sym ? p.sym_prods : p.prods;       // tensor-core products behind the candidates' scores
-    const float slack_abs = tc_slack(round_up(p.d, kColPad), prods, prods) * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
+    const float rho = p.rho_max != nullptr ? __ldg(p.rho_max) : TC_RHO_WORST;
+    const float slack_abs = tc_slack(round_up(p.d, kColPad), prods, prods, rho) * ((p.metric == HG_METRIC_COSINE) ? sqrtf(ni) : ni + __ldg(p.norm_max));
     float slack = slack_abs;                             // + TC_SLACK_REL |k-th best| once that is known
     // Certification.  A list keeps the kl best of its column range; what it dropped scores at least its
     // last entry.  If a FULL list ends inside the slack of the k-th best, a dropped column could still
@@ -580,9 +581,11 @@ static int launch_exact_fallback(const RerankParams& p, cudaStream_t st) {
 // kernel adds in its single-split path.  One thread per row, S-way merge by list heads.
 __global__ void thr_merge_kernel(const float* __restrict__ part_val, int splits, int64_t n, int kl, int rank,
                                  const float2* __restrict__ colp, const float* __restrict__ norm_max, int cosine,
-                                 float slack, float* __restrict__ thr) {
+                                 int64_t d_pad, int prods_pre, int prods_main, const float* __restrict__ rho_max,
+                                 float* __restrict__ thr) {
     const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (row >= n) return;
+    const float slack = tc_slack(d_pad, prods_pre, prods_main, rho_max != nullptr ? __ldg(rho_max) : TC_RHO_WORST);
     int head[TC_MAX_SPLITS];
 #pragma unroll
     for (int s = 0; s < TC_MAX_SPLITS; ++s) head[s] = 0;
@@ -607,9 +610,10 @@ __global__ void thr_merge_kernel(const float* __restrict__ part_val, int splits,
 }
 
 int thr_merge_launch(const float* part_val, int splits, int64_t n, int kl, int rank, const float2* colp,
-                     const float* norm_max, int cosine, float slack, float* thr, cudaStream_t st) {
+                     const float* norm_max, int cosine, int64_t d_pad, int prods_pre, int prods_main, const float* rho_max,
+                     float* thr, cudaStream_t st) {
     thr_merge_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(part_val, splits, n, kl, rank, colp, norm_max, cosine,
-                                                                 slack, thr);
+                                                                 d_pad, prods_pre, prods_main, rho_max, thr);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;

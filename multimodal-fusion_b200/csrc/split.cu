@@ -49,7 +49,8 @@ template <bool VEC4>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t n_pad, int64_t d_pad,
                   int64_t row_elems, op16_t* __restrict__ ops, float* __restrict__ sq_norms,
-                  const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide, int hi8) {
+                  const RrSlide* __restrict__ g_slides, const int32_t* __restrict__ g_blk2slide, int hi8,
+                  float* __restrict__ rho_max) {
     const int lane = threadIdx.x & 31;
     int64_t row = int64_t(blockIdx.x) * SPLIT_WARPS + (threadIdx.x >> 5);
     if (row >= n_pad) return;
@@ -68,7 +69,7 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
     const float* src = feats + row * d;
     // one warp per row, lane l owns the float4 groups l, l + 32, ...: the squared norm comes out in
     // the canonical order of rowdot.cuh in the same pass
-    float norm;
+    float norm, res2 = 0.f;                      // res2: |s x - hi|^2, what a product that skips this row's lo half leaves out
     if (VEC4) {
         const int64_t nvec = d >> 2;
         float lo = 0.f, hi = 0.f;               // the two halves of the packed accumulator
@@ -86,8 +87,11 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
             x.x *= s; x.y *= s; x.z *= s; x.w *= s;
             const __half h0 = hi_half(x.x, hi8), h1 = hi_half(x.y, hi8);
             const __half h2 = hi_half(x.z, hi8), h3 = hi_half(x.w, hi8);
-            const __half l0 = __float2half_rn(x.x - __half2float(h0)), l1 = __float2half_rn(x.y - __half2float(h1));
-            const __half l2 = __float2half_rn(x.z - __half2float(h2)), l3 = __float2half_rn(x.w - __half2float(h3));
+            const float r0 = x.x - __half2float(h0), r1 = x.y - __half2float(h1);     // exact: the residue of a rounding
+            const float r2 = x.z - __half2float(h2), r3 = x.w - __half2float(h3);
+            res2 = fmaf(r0, r0, fmaf(r1, r1, fmaf(r2, r2, fmaf(r3, r3, res2))));
+            const __half l0 = __float2half_rn(r0), l1 = __float2half_rn(r1);
+            const __half l2 = __float2half_rn(r2), l3 = __float2half_rn(r3);
             uint2 hv, lv;
             hv.x = uint32_t(__half_as_ushort(h0)) | (uint32_t(__half_as_ushort(h1)) << 16);
             hv.y = uint32_t(__half_as_ushort(h2)) | (uint32_t(__half_as_ushort(h3)) << 16);
@@ -108,22 +112,31 @@ split_rows_kernel(const float* __restrict__ feats, int64_t n, int64_t d, int64_t
         for (int64_t c = lane; c < d_pad; c += 32) {
             const float x = ((c < d) ? __ldg(src + c) : 0.f) * s;
             const __half h = hi_half(x, hi8);
+            const float r = x - __half2float(h);
+            res2 = fmaf(r, r, res2);
             unsigned short* dst = reinterpret_cast<unsigned short*>(hi_at(c));
             dst[0] = __half_as_ushort(h);
-            dst[32] = __half_as_ushort(__float2half_rn(x - __half2float(h)));
+            dst[32] = __half_as_ushort(__float2half_rn(r));
         }
     }
     if (lane == 0 && norm_out != nullptr) *norm_out = norm;
+    if (rho_max != nullptr) {
+        // rho = |s x - hi| / |s x| (<= 2^-11 up to the subnormal grid); the largest over the rows bounds the error of a
+        // product that reads only hi halves of one operand (tc_eps, knn_tc.cuh).  Non-negative floats order like ints.
+        res2 = warp_butterfly(res2);
+        const float sn = op_scale(norm) * sqrtf(norm);
+        if (lane == 0 && sn > 0.f) atomicMax(reinterpret_cast<int*>(rho_max), __float_as_int(sqrtf(res2) / sn));
+    }
 }
 
 int launch_split(const float* feats, int64_t n, int64_t d, op16_t* ops, float* sq_norms,
-                 cudaStream_t st, bool dense) {
+                 cudaStream_t st, bool dense, float* rho_max) {
     const int64_t n_pad = ops_rows(n), d_pad = ops_cols(d);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (vec)
-        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0);
+        split_rows_kernel<true><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0, rho_max);
     else
-        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0);
+        split_rows_kernel<false><<<(unsigned)ceil_div(n_pad, SPLIT_WARPS), SPLIT_WARPS * 32, 0, st>>>(feats, n, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, nullptr, nullptr, dense ? 1 : 0, rho_max);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -135,9 +148,9 @@ int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int6
     const int64_t d_pad = ops_cols(d);
     const unsigned blocks = (unsigned)ceil_div(n_pad, SPLIT_WARPS);
     if (vec)
-        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0);
+        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, nullptr);
     else
-        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0);
+        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, nullptr);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
@@ -154,5 +167,5 @@ extern "C" int hg_split_operands(const float* feats, int64_t n, int64_t d, void*
                                  void* stream) {
     HG_REQUIRE(feats && ops && n > 0 && d > 0, HG_ERR_BAD_ARG, "hg_split_operands: bad argument");
     return hg::launch_split(feats, n, d, static_cast<hg::op16_t*>(ops), sq_norms,
-                            static_cast<cudaStream_t>(stream), false);
+                            static_cast<cudaStream_t>(stream), false, nullptr);
 }
