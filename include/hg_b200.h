@@ -90,7 +90,7 @@ int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begin, int64_t 
 /* Tensor-core MMAs issued per logical product x_i . x_j by the main pass and by the threshold
  * pre-pass (0 when there is none) of hg_knn_feature for this shape: 3 = hi*hi + hi*lo + lo*hi
  * of the split-FP16 operands (classic full pass, grouped and dense launches), 2 = hi*hi + hi*lo
- * (symmetric passes of slides up to 160,000 rows; HG_B200_TC_SYM_PRODS=3 in the environment keeps three).  The roofline of the
+ * (symmetric passes; HG_B200_TC_SYM_PRODS=3 in the environment keeps three).  The roofline of the
  * fused kernel is the 16-bit tensor-core peak divided by this number. */
 int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
                             int* main_pass, int* pre_pass);

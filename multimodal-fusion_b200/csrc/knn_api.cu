@@ -30,30 +30,34 @@ static int bucket_cap() {
 
 // Tensor-core products per k-step (knn_tc.cuh tc_eps) of the symmetric passes: 2 by default -- the columns
 // rounded to FP16, the query rows whole -- which issues two thirds of the MMAs and loads no lo half of a B tile, for a
-// wider slack that the many short lists and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3 keeps all three.  Classic, grouped and dense
-// launches always use three.  The threshold pre-pass uses the main pass's count, or one product with
+// wider slack that the many short lists and the buckets of the symmetric mode hold easily; HG_B200_TC_SYM_PRODS=3
+// keeps all three.  Classic, grouped and dense launches always use three.  The threshold pre-pass uses the main pass's count, or one product with
 // HG_B200_TC_PRE_HI=1.
 static int sym_prods(int64_t n) {
     if (const char* e = getenv("HG_B200_TC_SYM_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
-    return n <= 160000 ? 2 : 3;          // giant slides: see sympart_prods below
+    (void)n;
+    return 2;
 }
 static int prepass_prods(int64_t n) {
     if (const char* e = getenv("HG_B200_TC_PRE_HI")) if (atoi(e) != 0) return 1;
     return sym_prods(n);
 }
-// The symmetric pass over the row block of a PARTITIONED slide keeps three products unless HG_B200_TC_SYMPART_PRODS=2:
-// such slides are the giant ones (C5: 250k rows), and the denser the slide the more columns fall inside the wider slack
-// of two products -- on C5's data 6-28 % of the rows had more than 32 of them (multi-round re-rank) and a few hundred
-// filled a list (exact fallback): 20 ms of fused kernel per rank instead of 28, but 64 ms per slide instead of 35.
-// Classic launches over SMALL slides (one or two lists per row): two products pay when the slide is sparse enough for
-// the wider slack to stay inside the lists -- see classic_prods() at its call sites.  HG_B200_TC_CLASSIC_PRODS=2/3.
+// The symmetric pass over the row block of a PARTITIONED slide (the giant ones, C5: 250k rows): two products as well,
+// HG_B200_TC_SYMPART_PRODS=3 keeps three.  With the WORST-CASE slack (2^-11 per rounded operand) this did not pay: the
+// denser the slide, the more columns fall inside the band -- on C5's data 6-28 % of the rows had more than 32 of them
+// (multi-round re-rank) and a few hundred filled a list (exact fallback): 20 ms of fused kernel per rank instead of 28,
+// but 64 ms per slide instead of 36.  With the MEASURED rounding residual of the rows (tc_eps, 0.47 of the worst case)
+// the band is half as wide: no row uncertified, at most 73 multi-round rows per rank, 29 ms per slide.
+static int sympart_prods() {
+    if (const char* e = getenv("HG_B200_TC_SYMPART_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
+    return 2;
+}
+// Classic launches (one or two lists of 24 entries per row) keep three products: with two, 1.5-4.5 % of the rows of a
+// group of small slides have a list that fills up inside the slack and take the exact fallback (C4: 111 -> 171 ms,
+// DESIGN section 9).  HG_B200_TC_CLASSIC_PRODS=2 is the experiment switch behind that number.
 static int classic_prods(int64_t n) {
     if (const char* e = getenv("HG_B200_TC_CLASSIC_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
     (void)n;
-    return 3;
-}
-static int sympart_prods() {
-    if (const char* e = getenv("HG_B200_TC_SYMPART_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
     return 3;
 }
 
@@ -398,7 +402,7 @@ static GroupLayout group_layout(const KnnGroupSlide* slides, int num, int64_t d,
     g.o_pos4 = take(has_pos ? size_t(g.n_pad) * 16 : 0);
     g.o_pval = take(size_t(part) * 4);
     g.o_pidx = take(size_t(part) * 4);
-    g.o_flags = take(16);
+    g.o_flags = take(32);
     g.o_unc_rows = take(size_t(g.n_pad) * 12);
     g.o_unc_part = take(rerank_unc_part_bytes(g.n_pad, k));
     g.o_units = take(size_t(units) * sizeof(TcUnit));
@@ -503,7 +507,8 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     HG_CHECK_CUDA(cudaMemcpyAsync(d_units, hs, tab_bytes, cudaMemcpyHostToDevice, st));
     rc = stage_release(stage, st);
     if (rc != HG_OK) return rc;
-    HG_CHECK_CUDA(cudaMemsetAsync(flags, 0, 16, st));
+    HG_CHECK_CUDA(cudaMemsetAsync(flags, 0, 32, st));
+    float* rho_max = reinterpret_cast<float*>(flags) + 4;           // measured rounding residual of the group's rows (tc_eps)
 
     const bool dbg = getenv("HG_B200_GROUP_DEBUG") != nullptr;      // synchronise after every phase and say which one failed
     auto phase = [&](const char* what) {
@@ -514,7 +519,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     };
     rc = phase("table upload");
     if (rc != HG_OK) return rc;
-    rc = launch_split_group(d_slides, d_map, g.n_pad, d, vec, ops, norms, st);
+    rc = launch_split_group(d_slides, d_map, g.n_pad, d, vec, ops, norms, st, rho_max);
     if (rc != HG_OK) return rc;
     if ((rc = phase("operand split")) != HG_OK) return rc;
     float* norm_max = reinterpret_cast<float*>(flags) + 1;
@@ -525,7 +530,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     TcParams tp{};
     tp.d_pad = int(g.d_pad);
     tp.colp = colp; tp.pos4 = pos4;
-    tp.norms_a = norms; tp.prods = classic_prods(g.n_pad);
+    tp.norms_a = norms; tp.prods = classic_prods(g.n_pad); tp.rho_max = rho_max;
     tp.gscale = (has_pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + g.o_pval);
@@ -542,7 +547,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
 
     RerankParams rp{};
     rp.d = d; rp.n = g.n_pad; rp.pos_dim = pos_dim;
-    rp.sq_norms = norms; rp.norm_max = norm_max;
+    rp.sq_norms = norms; rp.norm_max = norm_max; rp.rho_max = rho_max;
     rp.metric = metric; rp.lambda_h = lambda_h; rp.lambda_g = has_pos ? lambda_g : 0.f;
     rp.part_val = tp.part_val; rp.part_idx = tp.part_idx;
     rp.splits = max_splits; rp.kl = g.kl; rp.n_rows = g.n_pad; rp.row_begin = 0;

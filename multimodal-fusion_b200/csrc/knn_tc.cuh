@@ -230,7 +230,7 @@ int launch_colparams(const float* sq_norms, const float* pos, int pos_dim, int64
                      float* thr = nullptr, int32_t* bkt_cnt = nullptr, float* norm_max = nullptr);
 
 int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
-                       op16_t* ops, float* sq_norms, cudaStream_t st);
+                       op16_t* ops, float* sq_norms, cudaStream_t st, float* rho_max = nullptr);
 int launch_colparams_group(const float* sq_norms, int pos_dim, int64_t n_pad, int metric, float2* colp, float4* pos4,
                            float* norm_max, const RrSlide* g_slides, const int32_t* g_blk2slide, cudaStream_t st);
 

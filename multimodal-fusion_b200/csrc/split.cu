@@ -144,13 +144,13 @@ int launch_split(const float* feats, int64_t n, int64_t d, op16_t* ops, float* s
 
 // the rows of a whole group of slides (device tables, knn_tc.cuh) in one launch; n_pad = the group's operand rows
 int launch_split_group(const RrSlide* g_slides, const int32_t* g_blk2slide, int64_t n_pad, int64_t d, bool vec,
-                       op16_t* ops, float* sq_norms, cudaStream_t st) {
+                       op16_t* ops, float* sq_norms, cudaStream_t st, float* rho_max) {
     const int64_t d_pad = ops_cols(d);
     const unsigned blocks = (unsigned)ceil_div(n_pad, SPLIT_WARPS);
     if (vec)
-        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, nullptr);
+        split_rows_kernel<true><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, rho_max);
     else
-        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, nullptr);
+        split_rows_kernel<false><<<blocks, SPLIT_WARPS * 32, 0, st>>>(nullptr, 0, d, n_pad, d_pad, ops_row_elems(d_pad), ops, sq_norms, g_slides, g_blk2slide, 0, rho_max);
     HG_CHECK_LAUNCH();
     count_launches(1);
     return HG_OK;
