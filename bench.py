@@ -547,12 +547,17 @@ def run_ours(args):
         c4_from_host()
         wall = max_over_ranks((time.perf_counter() - t0) * 1e3)
         e2e4 = wall if e2e4 is None else min(e2e4, wall)
+    _p4, _q4 = ctypes.c_int(0), ctypes.c_int(0)
+    _lib.check(lib.hg_knn_feature_products(4096, 1024, 16, 0, 4096, ctypes.byref(_p4), ctypes.byref(_q4)))
+    c4_prods = float(_p4.value)                     # MMAs per product of the grouped launches (small slides)
     tot4 = int(sizes.sum())
     flop4 = float(sum(2.0 * float(sizes[i]) ** 2 * 1024 for i in mine))
     c4 = {"workload": "C4: 512 slides, N ~ U{2048..8192} x D=1024, Gaussian kNN k=16 + CSR, LPT slide-per-GPU",
           "slides": 512, "patches": tot4, "gpus": world, "lanes": lanes4, "ms_total": ms4,
           "slides_per_s": 512 / (ms4 * 1e-3), "patches_per_s": tot4 / (ms4 * 1e-3),
           "tc_kernel_ms_rank0": kms4, "tc_tflops_algorithmic_rank0": flop4 / (kms4 * 1e-3) / 1e12 if kms4 > 0 else None,
+          "tc_mma_per_product": c4_prods,
+          "tc_frac_of_burst_roofline": (flop4 / (kms4 * 1e-3) / 1e12) / (peaks["bf16"] / c4_prods) if kms4 > 0 else None,
           "tc_frac_of_burst_peak_over_3": (flop4 / (kms4 * 1e-3) / 1e12) / (peaks["bf16"] / 3.0) if kms4 > 0 else None,
           "whole_batch_tflops_algorithmic_rank0": flop4 / (ms4 * 1e-3) / 1e12,
           "gpu_launches": launches4,

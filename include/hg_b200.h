@@ -89,8 +89,9 @@ int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begin, int64_t 
                         int* symmetric_stride, double* mma_flop);
 /* Tensor-core MMAs issued per logical product x_i . x_j by the main pass and by the threshold
  * pre-pass (0 when there is none) of hg_knn_feature for this shape: 3 = hi*hi + hi*lo + lo*hi
- * of the split-FP16 operands (classic full pass, grouped and dense launches), 2 = hi*hi + hi*lo
- * (symmetric passes; HG_B200_TC_SYM_PRODS=3 in the environment keeps three).  The roofline of the
+ * of the split-FP16 operands (classic pass over more than 16,384 columns, dense launches),
+ * 2 = hi*hi + lo*hi (symmetric passes, classic and grouped launches over small slides;
+ * HG_B200_TC_SYM_PRODS=3 / HG_B200_TC_CLASSIC_PRODS=3 in the environment keep three).  The roofline of the
  * fused kernel is the 16-bit tensor-core peak divided by this number. */
 int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_begin, int64_t row_end,
                             int* main_pass, int* pre_pass);

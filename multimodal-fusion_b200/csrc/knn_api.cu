@@ -52,13 +52,15 @@ static int sympart_prods() {
     if (const char* e = getenv("HG_B200_TC_SYMPART_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
     return 2;
 }
-// Classic launches (one or two lists of 24 entries per row) keep three products: with two, 1.5-4.5 % of the rows of a
-// group of small slides have a list that fills up inside the slack and take the exact fallback (C4: 111 -> 171 ms,
-// DESIGN section 9).  HG_B200_TC_CLASSIC_PRODS=2 is the experiment switch behind that number.
-static int classic_prods(int64_t n) {
+// Classic launches keep ONE or two lists of 24 entries per row, so the width of the slack decides how many rows have a
+// list that fills up inside it and take the exact fallback.  With the worst-case two-product slack that was 1.5-4.5 %
+// of the rows of a group of small slides (C4: 111 -> 171 ms); with the measured one (tc_eps: rho) it is 60-100 rows
+// of 128,000 and the batch runs in 99.5 ms (fused kernel 49 ms instead of 65).  Small slides (up to 16,384 columns:
+// every grouped launch, single small slides) therefore use two products; a classic launch over more columns -- the
+// row block of a large slide -- is denser per list and keeps three.  HG_B200_TC_CLASSIC_PRODS=2/3 overrides.
+static int classic_prods(int64_t n_cols) {
     if (const char* e = getenv("HG_B200_TC_CLASSIC_PRODS")) { const int v = atoi(e); if (v == 2 || v == 3) return v; }
-    (void)n;
-    return 3;
+    return n_cols <= 16384 ? 2 : 3;
 }
 
 static KnnWs plan_ws(int64_t n, int64_t d, int k, int64_t r0, int64_t r1, bool has_pos) {
@@ -134,7 +136,7 @@ extern "C" int hg_knn_feature_plan(int64_t n, int64_t d, int k, int64_t row_begi
     };
     const double per_tile = 2.0 * double(TC_BM) * double(TC_BN) * double(w.d_pad);           // one MMA sweep of a tile
     const double flop = w.sym_stride > 0 ? (tiles_of(w.sym_plan) * sym_prods(n) + tiles_of(w.pre_plan) * prepass_prods(n)) * per_tile
-                                         : tiles_of(w.plan) * w.plan.cl * 3.0 * per_tile;
+                                         : tiles_of(w.plan) * w.plan.cl * double(classic_prods(n)) * per_tile;
     if (symmetric_stride) *symmetric_stride = w.sym_stride;
     if (mma_flop) *mma_flop = flop;
     return HG_OK;
@@ -145,7 +147,7 @@ extern "C" int hg_knn_feature_products(int64_t n, int64_t d, int k, int64_t row_
     int rc = check_knn_args(n, d, k, row_begin, row_end);
     if (rc != HG_OK) return rc;
     const bool sym = tc_sym_stride(n, row_end - row_begin, k) > 0;
-    if (main_pass) *main_pass = sym ? sym_prods(n) : 3;
+    if (main_pass) *main_pass = sym ? sym_prods(n) : classic_prods(n);
     if (pre_pass) *pre_pass = sym ? prepass_prods(n) : 0;
     return HG_OK;
 }
@@ -530,7 +532,7 @@ int knn_group_enqueue(const KnnGroupSlide* slides, int num, int64_t d, int pos_d
     TcParams tp{};
     tp.d_pad = int(g.d_pad);
     tp.colp = colp; tp.pos4 = pos4;
-    tp.norms_a = norms; tp.prods = classic_prods(g.n_pad); tp.rho_max = rho_max;
+    tp.norms_a = norms; tp.prods = classic_prods(GB_MAX_N); tp.rho_max = rho_max;      // every slide of a group is at most GB_MAX_N rows
     tp.gscale = (has_pos && lambda_h > 0.f) ? lambda_g / lambda_h : 0.f;
     tp.exclude_self = exclude_self;
     tp.part_val = reinterpret_cast<float*>(ws + g.o_pval);

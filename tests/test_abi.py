@@ -68,12 +68,12 @@ def test_python_surface_mirrors_reference():
 
 
 def test_products_per_pass_by_shape(monkeypatch):
-    """host-side plan logic (no GPU): two MMAs per product in the symmetric passes, three in classic launches
-    (DESIGN 3.0); the issued-MMA count follows"""
+    """host-side plan logic (no GPU): two MMAs per product in the symmetric passes and in classic launches over small
+    slides, three in classic launches over more than 16,384 columns; the issued-MMA count follows"""
     lib = _lib.load_library()
     main, pre = ctypes.c_int(-1), ctypes.c_int(-1)
     for n, d, k, r1, want in ((50_000, 1024, 16, 50_000, (2, 2)), (100_000, 1536, 16, 100_000, (2, 2)),
-                              (250_000, 1536, 16, 250_000, (2, 2)), (4096, 1024, 8, 4096, (3, 0)),
+                              (250_000, 1536, 16, 250_000, (2, 2)), (4096, 1024, 8, 4096, (2, 0)),
                               (100_000, 1536, 16, 12_500, (3, 0))):
         assert lib.hg_knn_feature_products(n, d, k, 0, r1, ctypes.byref(main), ctypes.byref(pre)) == 0
         assert (main.value, pre.value) == want, (n, d, k, r1)

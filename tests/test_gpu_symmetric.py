@@ -114,7 +114,9 @@ def test_row_ranges_and_small_slides_use_the_full_pass():
     assert (main.value, pre.value) == (2, 2)                           # symmetric passes: hi*hi + hi*lo
     assert stride == 16 and 0.5 < flop / (main.value * 2.0 * 50000.0 ** 2 * 1024) < 0.6            # ~0.5 + 1/16
     _lib.check(lib.hg_knn_feature_products(4096, 1024, 8, 0, 4096, ctypes.byref(main), ctypes.byref(pre)))
-    assert (main.value, pre.value) == (3, 0)                           # classic full pass: all three products
+    assert (main.value, pre.value) == (2, 0)                           # classic pass over a small slide: two as well
+    _lib.check(lib.hg_knn_feature_products(50000, 1024, 16, 0, 25000, ctypes.byref(main), ctypes.byref(pre)))
+    assert (main.value, pre.value) == (3, 0)                           # row block of a large slide: all three products
     with _env(HG_B200_TC_SYM_PRODS=3):
         _lib.check(lib.hg_knn_feature_products(50000, 1024, 16, 0, 50000, ctypes.byref(main), ctypes.byref(pre)))
         assert (main.value, pre.value) == (3, 3)
