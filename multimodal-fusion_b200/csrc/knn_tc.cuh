@@ -214,7 +214,7 @@ constexpr float TC_RHO_WORST = 4.8828125e-4f;       // u = 2^-11
 __host__ __device__ inline float tc_eps(int64_t d_pad, int prods, float rho) {
     const float u2 = 2.3841858e-7f;                                    // 2^-22
     if (prods <= 0) prods = 3;
-    rho = fminf(fmaxf(rho, 0.f), TC_RHO_WORST) * 1.01f + 1e-7f;        // FP32 rounding of the measurement itself
+    rho = fmaxf(rho, 0.f) * 1.01f + 1e-7f;                             // FP32 rounding of the measurement itself
     const float repr = (prods >= 3 ? 3.f * u2 : prods == 2 ? rho + u2 : 2.f * rho + u2) + 1.8627e-9f * sqrtf(float(d_pad));
     return repr + float(prods * (d_pad / 16)) * u2;
 }
