@@ -827,7 +827,8 @@ static int tc_launch_impl(const op16_t* ops_a, int64_t n_pad_a, const op16_t* op
     HG_REQUIRE(p.prods == 3 || p.plan.kl > 0, HG_ERR_BAD_ARG, "tc_launch: dense output needs all three products");
     HG_REQUIRE(p.norms_a != nullptr, HG_ERR_BAD_ARG, "tc_launch: the row norms behind the operand scales are missing");
     if (p.norms_b == nullptr) p.norms_b = p.norms_a;
-#ifdef HG_TC_FORCE_PRODS          // timing experiments only (results are wrong): tools/README in DESIGN.md 9
+#ifdef HG_TC_FORCE_PRODS          // timing experiments only, never defined by the Makefile (results are wrong): the
+                                  // one-product run behind "64 B / clock / SM" in DESIGN.md 3.0 was built with -DHG_TC_FORCE_PRODS=1
     if (p.plan.kl > 0) p.prods = HG_TC_FORCE_PRODS;
 #endif
     // No product reads the lo halves of B when there are two or one: the B tiles are then 64-byte rows, a stage is
